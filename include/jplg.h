@@ -1,0 +1,252 @@
+/*
+ * jplg.h — C ABI of the B200-native many-source spatial renderer.
+ *
+ * Drop-in boundary for ONE hot path of JPL Spatial (reference paths are relative to
+ * Spatialization/include/JPLSpatial/ = "inc/", Spatialization/src/Spatialization/ = "src/"):
+ *
+ *   batched VBAP/MDAP panner gains  ->  fractional-delay/Doppler ring reads  ->
+ *   LR4 four-band propagation filter with ramped band gains  ->  gain-ramped mix of N sources into
+ *   an L-channel speaker bus.
+ *
+ * The reference has no C ABI (it is a C++ header-template library); its boundary is the component API
+ * in namespace JPL. Every entry point below names the reference interface it replaces. The calls are
+ * BATCHED (a GPU call per source is meaningless), otherwise argument meaning, channel order
+ * (ascending EChannel bit order, LFE included with gain 0), coordinate system (right handed, +Y up,
+ * -Z forward) and error behaviour (no exceptions; a status code + last-error string + optional trace
+ * callback instead of `false`/JPL_ERROR_TAG) follow the reference.
+ *
+ * All data buffers are caller-owned. A `mem` argument says whether the data pointers of that call are
+ * host memory (JPLG_MEM_HOST: the call copies in/out on the context stream and synchronises before
+ * returning) or device memory of the context's GPU (JPLG_MEM_DEVICE: the call only enqueues work on
+ * the context stream and returns; no synchronisation).
+ *
+ * Thread model: same as the reference (inc/Auralization/DirectSound.h:52-65): one "audio" caller per
+ * renderer (process_block), one "non-audio" caller (update); panner queries are const and may be
+ * called concurrently after creation *from one thread per context stream*.
+ */
+#ifndef JPLG_H
+#define JPLG_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(_WIN32)
+#define JPLG_API __declspec(dllexport)
+#else
+#define JPLG_API __attribute__((visibility("default")))
+#endif
+
+/* ---------------------------------------------------------------------------------------------- */
+/* status / errors  (replaces: bool returns + JPL_ERROR_TAG, inc/ErrorReporting.h:96-129)          */
+
+typedef int32_t jplg_status;
+enum {
+    JPLG_OK = 0,
+    JPLG_ERR_INVALID_ARGUMENT = 1,
+    JPLG_ERR_INVALID_CHANNEL_MAP = 2, /* Initialize() returned false in the reference */
+    JPLG_ERR_NOT_INITIALIZED = 3,
+    JPLG_ERR_CUDA = 4,                /* sticky: the context is unusable afterwards */
+    JPLG_ERR_NO_DEVICE = 5,           /* no CUDA device: the library has NO CPU fallback */
+    JPLG_ERR_OUT_OF_MEMORY = 6,
+    JPLG_ERR_UNSUPPORTED = 7,
+    JPLG_ERR_TRIANGULATION = 8
+};
+
+enum { JPLG_MEM_HOST = 0, JPLG_MEM_DEVICE = 1 };
+
+/* Arithmetic mode of the render kernels.
+ *  JPLG_MODE_PARITY     every reference FMA(a,b,c) is a separately rounded mul + add, exactly like the
+ *                       reference's SSE2 baseline build (inc/Math/SIMD.h:1843-1850 without JPL_USE_FMADD):
+ *                       per-source rendered audio is BIT-EXACT against that build.
+ *  JPLG_MODE_THROUGHPUT fused multiply-adds at the reference's FMA call sites (the semantic of its
+ *                       JPL_ENABLE_AVX2_FMA build); meets 1e-5 relative against the SSE2 build. */
+enum { JPLG_MODE_PARITY = 0, JPLG_MODE_THROUGHPUT = 1 };
+
+typedef struct jplg_context_t*       jplg_context;
+typedef struct jplg_panner_t*        jplg_panner;
+typedef struct jplg_source_layout_t* jplg_source_layout;
+typedef struct jplg_renderer_t*      jplg_renderer;
+typedef struct jplg_crossover_bank_t* jplg_crossover_bank;
+typedef struct jplg_delay_bank_t*    jplg_delay_bank;
+
+/* replaces: JPL::SpatialTrace (inc/ErrorReporting.h:44-47) */
+typedef void (*jplg_trace_fn)(const char* message);
+JPLG_API void jplg_set_trace_callback(jplg_trace_fn fn);
+
+JPLG_API const char* jplg_version(void);
+/* 0 if no usable CUDA device is visible. The library never computes on the CPU. */
+JPLG_API int32_t jplg_device_count(void);
+
+/* ---------------------------------------------------------------------------------------------- */
+/* context: device, stream, constant tables                                                        */
+
+JPLG_API jplg_status jplg_context_create(int32_t device, jplg_context* out);
+JPLG_API void        jplg_context_destroy(jplg_context ctx);
+JPLG_API const char* jplg_last_error(jplg_context ctx);
+/* cudaStream_t of the context, as void*; all work of this context is enqueued on it. */
+JPLG_API void*       jplg_context_stream(jplg_context ctx);
+JPLG_API jplg_status jplg_context_synchronize(jplg_context ctx);
+/* 1 when the host's RSQRTPS matched the "2048-entry table + exact exponent scaling" model the device
+ * uses to reproduce _mm_rsqrt_ps (inc/Math/SIMD.h:1709) on every probed input, else 0. */
+JPLG_API int32_t     jplg_context_rsqrt_model_verified(jplg_context ctx);
+/* number of kernels this context has launched so far (bench.py's gpu_launches) */
+JPLG_API uint64_t    jplg_context_launch_count(jplg_context ctx);
+
+/* ---------------------------------------------------------------------------------------------- */
+/* ChannelMap helpers  (replaces: inc/ChannelMap.h:153-249; masks are EChannel bit masks :38-79)    */
+
+JPLG_API uint32_t jplg_channel_map_num_channels(uint32_t mask);            /* GetNumChannels :165 */
+JPLG_API int32_t  jplg_channel_map_has_lfe(uint32_t mask);                 /* HasLFE :161 */
+JPLG_API int32_t  jplg_channel_map_has_top_channels(uint32_t mask);        /* HasTopChannels :162 */
+JPLG_API uint32_t jplg_channel_map_channel_index(uint32_t mask, uint32_t channel_bit); /* GetChannelIndex :167-183; 0xFFFFFFFF if absent */
+JPLG_API uint32_t jplg_channel_map_from_num_channels(uint32_t n);          /* FromNumChannels :203-219 */
+
+/* ---------------------------------------------------------------------------------------------- */
+/* Panners: VBAPanner2D / VBAPanner3D  (replaces: inc/Panning/PannerBase.h:315-389)                 */
+
+/* Initialize(ChannelMap) (:315,455-482). 2D panner for masks without top channels
+ * (inc/Panning/VBAPanning2D.h:124-137), 3D panner (KB_983 LUT) otherwise (VBAPanning3D.h:157-166).
+ * Builds the LUT on the host exactly as LUTBuilder2D / LUTBuilder do and uploads it. */
+JPLG_API jplg_status jplg_panner_create(jplg_context ctx, uint32_t target_mask, jplg_panner* out);
+JPLG_API void        jplg_panner_destroy(jplg_panner p);
+JPLG_API int32_t     jplg_panner_is_3d(jplg_panner p);
+JPLG_API uint32_t    jplg_panner_num_channels(jplg_panner p);              /* GetNumChannels :346 */
+JPLG_API uint32_t    jplg_panner_channel_mask(jplg_panner p);              /* GetChannelMap :349 */
+JPLG_API float       jplg_panner_shortest_aperture(jplg_panner p);         /* GetShortestSpeakerAperture :353 */
+/* 1 when the 3D speaker triangulation came from the built-in table of the reference's standard layouts,
+ * 0 when the generic convex-hull triangulator was used (LUT parity then reported, not promised). */
+JPLG_API int32_t     jplg_panner_triangulation_is_tabulated(jplg_panner p);
+/* number of speaker triangles / copies them (vertex numbering = non-LFE channel order, then dummies) */
+JPLG_API uint32_t    jplg_panner_triangles(jplg_panner p, uint8_t* out_tris /* [n][3] or NULL */);
+
+/* GetLUT (:320). 2D: `gains` receives 1024*L floats, `speakers` ignored (VBAPLUT2D.h:91-99).
+ * 3D: `gains` receives 65536*3 floats and `speakers` 65536*3 bytes (VBAPLUT3D.h:163-171). Host pointers. */
+JPLG_API jplg_status jplg_panner_get_lut(jplg_panner p, float* gains, uint8_t* speakers);
+/* Replace the LUT contents (host pointers, same shapes as get_lut). Lets a caller run the kernels on a
+ * LUT built elsewhere (used by the parity tests to decouple kernel parity from LUT-construction parity). */
+JPLG_API jplg_status jplg_panner_set_lut(jplg_panner p, const float* gains, const uint8_t* speakers);
+
+/* GetSpeakerGains(direction, outGains) batched (:329,441-445). dirs [n][3] normalised, non-zero;
+ * out [n][L]. Unlike the reference's 3D query (which writes only 3 entries, VBAPLUT3D.h:1001-1009)
+ * every row is fully written (zeros elsewhere). */
+JPLG_API jplg_status jplg_panner_point_gains(jplg_panner p, const float* dirs, uint32_t n, float* out, int32_t mem);
+
+/* InitializeSourceLayout(ChannelMap, SourceLayout&) (:324; VBAPanning2D.h:150-193; VBAPanning3D.h:242-310) */
+JPLG_API jplg_status jplg_source_layout_create(jplg_panner p, uint32_t source_mask, jplg_source_layout* out);
+JPLG_API void        jplg_source_layout_destroy(jplg_source_layout l);
+JPLG_API uint32_t    jplg_source_layout_num_channels(jplg_source_layout l);        /* ChannelGroups.size() (LFE skipped) */
+JPLG_API uint32_t    jplg_source_layout_num_virtual_sources(jplg_source_layout l); /* GetNumVirtualSources */
+/* info[0]=channels, [1]=VS per channel, [2]=rings, [3]=samples per ring (3D; 0 for 2D) */
+JPLG_API void        jplg_source_layout_info(jplg_source_layout l, uint32_t info[4], float* phi_term, float* offset_term, float* vs_weight);
+/* channel-group quaternions [channels][4] = {x,y,z,w} (PannerBase.h:255-262) */
+JPLG_API void        jplg_source_layout_groups(jplg_source_layout l, float* out_quats, uint32_t* out_channel_ids);
+
+/* ProcessVBAPData(sourceLayout, PanUpdateData, outChannelMixMap) batched (:369,486-500).
+ * params [n][5] = { dir.x, dir.y, dir.z, focus, spread } ; out [n][channels*L]. */
+JPLG_API jplg_status jplg_panner_mdap(jplg_panner p, jplg_source_layout l, const float* params, uint32_t n, float* out, int32_t mem);
+
+/* ProcessVirtualSources(span<VirtualSource>, outGains) (:385,731-742): ONE gain vector from n weighted
+ * directions. vs [n][4] = { dir.x, dir.y, dir.z, weight }; out [L] is ACCUMULATED INTO and then L2-normalised,
+ * like the reference (caller zeroes it). `batches` independent sets of n (vs [batches][n][4], out [batches][L]). */
+JPLG_API jplg_status jplg_panner_process_virtual_sources(jplg_panner p, const float* vs, uint32_t n, uint32_t batches, float* out, int32_t mem);
+/* NormalizeWeights (:389,879-892), host helper, in place on [n][4] records */
+JPLG_API void        jplg_normalize_weights(float* vs, uint32_t n);
+/* GetSpreadFromSourceSize (:69-74) */
+JPLG_API float       jplg_spread_from_source_size(float source_size, float distance);
+
+/* ---------------------------------------------------------------------------------------------- */
+/* Renderer: N x DirectSoundEffect  (replaces: inc/Auralization/DirectSound.h:41-125,               */
+/*                                              src/Auralization/DirectSound.cpp:34-239)            */
+
+typedef struct jplg_renderer_config {
+    float    sample_rate;        /* DirectSoundEffect ctor `sampleRate` */
+    uint32_t num_sources;        /* number of effects in the batch */
+    uint32_t source_channels;    /* `numSourceChannels` (same for every source of one renderer) */
+    uint32_t output_channels;    /* `numOutputChannels` = L */
+    uint32_t ring_size;          /* 0 = reference value bit_ceil(2*fs) (DirectSound.cpp:79); else a power of two */
+    uint32_t max_block_frames;   /* largest numFrames of process_block; 0 = 512 */
+    int32_t  mode;               /* JPLG_MODE_PARITY / JPLG_MODE_THROUGHPUT */
+    float    split_f1, split_f2, split_f3; /* 0 = reference defaults 176/775/3408 Hz (inc/FrequencyBands.h:46) */
+} jplg_renderer_config;
+
+/* Allocates rings/state for cfg.num_sources effects. Initial parameters like the ctor:
+ * band_gains [N][4] (b1..b4), delay_seconds [N], mix_maps [N][C*L]; host pointers, any may be NULL
+ * (gains 1, delay 0, mix 0). */
+JPLG_API jplg_status jplg_renderer_create(jplg_context ctx, const jplg_renderer_config* cfg,
+                                          const float* band_gains, const float* delay_seconds, const float* mix_maps,
+                                          jplg_renderer* out);
+JPLG_API void        jplg_renderer_destroy(jplg_renderer r);
+
+/* UpdateParameters(filterGains, delayTimeSeconds, channelMixMap) for all N sources (DirectSound.cpp:231-239).
+ * The new targets become visible at the next process_block (the reference picks them up at its next
+ * 480-frame chunk, DirectSound.cpp:136-142). Any pointer may be NULL = leave unchanged. */
+JPLG_API jplg_status jplg_renderer_update(jplg_renderer r, const float* band_gains, const float* delay_seconds,
+                                          const float* mix_maps, int32_t mem);
+
+/* ProcessInterleaved for all N sources (DirectSound.cpp:95-229).
+ * in : [N][frames][C] (each source's block is interleaved exactly as the reference's `input` span)
+ * bus: [frames][L] interleaved, ACCUMULATED INTO like the reference's `output` span; all N sources add
+ *      into the same bus (the host loop "for each effect: ProcessInterleaved(in_i, bus)"). */
+JPLG_API jplg_status jplg_renderer_process_block(jplg_renderer r, const float* in, float* bus, uint32_t frames, int32_t mem);
+/* Same, but also writes every source's own contribution: per_source [N][frames][L] (overwritten). */
+JPLG_API jplg_status jplg_renderer_process_block_debug(jplg_renderer r, const float* in, float* bus, float* per_source,
+                                                       uint32_t frames, int32_t mem);
+/* Device pointer of the renderer's partial bus for the LAST block ([frames][L], not accumulated into
+ * anything): the buffer a multi-GPU caller reduces across ranks. */
+JPLG_API float*      jplg_renderer_device_bus(jplg_renderer r);
+
+/* Checkpoint / parity seeding: per-source-channel state, host pointers.
+ * state [N*C][JPLG_STATE_FLOATS]: [0] smoothed delay (samples), [1] Thiran y[n-1], [2..25] crossover state
+ * (X2.S1{s1,s2} X2.S2{s1,s2} X13.S1 lanes0,1{s1,s2} X13.S2 lanes0..3{s1,s2} allpass lanes0..3{s1,s2}),
+ * [26..29] current band gains b1..b4, [30..31] reserved, [32..63] current mix gains (first L used).
+ * rings [N*C][ring_size]: raw ring, the sample pushed at time t lives at index t & (ring_size-1);
+ * `*ring_pos` = number of samples pushed so far. */
+#define JPLG_STATE_FLOATS 64
+JPLG_API uint32_t    jplg_renderer_ring_size(jplg_renderer r);
+JPLG_API jplg_status jplg_renderer_state_export(jplg_renderer r, float* state, float* rings /* may be NULL */, uint64_t* ring_pos);
+JPLG_API jplg_status jplg_renderer_state_import(jplg_renderer r, const float* state, const float* rings /* may be NULL */, uint64_t ring_pos);
+
+/* ---------------------------------------------------------------------------------------------- */
+/* Components (batched value types)                                                                 */
+
+/* FourBandCrossover x n (replaces inc/Auralization/CrossoverFilter.h:416-535) */
+JPLG_API jplg_status jplg_crossover_bank_create(jplg_context ctx, uint32_t n, float sample_rate,
+                                                float f1, float f2, float f3, int32_t mode, jplg_crossover_bank* out); /* Prepare :425 */
+JPLG_API void        jplg_crossover_bank_destroy(jplg_crossover_bank b);
+JPLG_API jplg_status jplg_crossover_bank_reset(jplg_crossover_bank b);                                                /* Reset :433 */
+/* coefficients as 27 floats: X2{g,d,-(R+g)}, X13{g[4],d[4],-(R+g)[4]}, allpass{g[4],d[4],-(R+g)[4]} */
+JPLG_API void        jplg_crossover_bank_coeffs(jplg_crossover_bank b, float out[27]);
+/* ProcessBlock(in, startGains, endGains, out) (:505-535): in/out [n][frames]; gains [n][4]. In place allowed. */
+JPLG_API jplg_status jplg_crossover_bank_process_ramp(jplg_crossover_bank b, const float* in, const float* start_gains,
+                                                      const float* end_gains, float* out, uint32_t frames, int32_t mem);
+/* ProcessBlock(in, outBands) (:462-470): out_bands [n][frames][4] in band order b1..b4 */
+JPLG_API jplg_status jplg_crossover_bank_split(jplg_crossover_bank b, const float* in, float* out_bands, uint32_t frames, int32_t mem);
+
+/* DelayLine + DelayTap x n (replaces inc/Auralization/DelayLine.h:43-68,129-230; FractionalDelay.h:65-136) */
+enum { JPLG_INTERP_NEAREST = 0, JPLG_INTERP_LINEAR = 1, JPLG_INTERP_THIRAN1 = 2 };
+JPLG_API jplg_status jplg_delay_bank_create(jplg_context ctx, uint32_t n, uint32_t min_size, jplg_delay_bank* out);   /* DelayLine(minSize) :142 */
+JPLG_API void        jplg_delay_bank_destroy(jplg_delay_bank b);
+JPLG_API uint32_t    jplg_delay_bank_size(jplg_delay_bank b);                                                         /* GetSize :171 */
+JPLG_API jplg_status jplg_delay_bank_clear(jplg_delay_bank b);                                                        /* Clear :175 */
+/* Push (:183-197) `frames` samples per line: in [n][frames] */
+JPLG_API jplg_status jplg_delay_bank_push(jplg_delay_bank b, const float* in, uint32_t frames, int32_t mem);
+/* For each line: for k in [0,taps): tap.SetDelay(delays[line][k]); out[line][k] = tap.Process(line) (:53-67),
+ * the tap's interpolator state carried across k (and across calls for Thiran). */
+JPLG_API jplg_status jplg_delay_bank_read(jplg_delay_bank b, const float* delays, uint32_t taps, int32_t interp, float* out, int32_t mem);
+
+/* ChannelMixing free functions (replaces inc/Auralization/ChannelMixing.h:32-136), batched over `n`
+ * independent (dest, source) pairs laid out back to back. */
+JPLG_API jplg_status jplg_mix_add_and_apply_gain_ramp(jplg_context ctx, float* dest, const float* source, uint32_t n,
+                                                      uint32_t dest_channel, uint32_t source_channel,
+                                                      uint32_t dest_num_channels, uint32_t source_num_channels,
+                                                      uint32_t frames, const float* gain_start, const float* gain_end, int32_t mem); /* :89-107 */
+JPLG_API jplg_status jplg_mix_apply_gain(jplg_context ctx, float* dest, uint32_t n, uint32_t frames, const float* gains, int32_t mem); /* :50-63 */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* JPLG_H */

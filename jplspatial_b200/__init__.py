@@ -1,0 +1,21 @@
+"""jplspatial_b200 — B200-native many-source spatial renderer (JPL Spatial hot path).
+
+Python is only plumbing here (tests, bench, torch.distributed launch): the product is the C-ABI shared
+library `libjplg.so` (include/jplg.h) built from hand-written CUDA for sm_100a. This module mirrors the
+reference's component interface (same names / argument meaning, batched) on top of that ABI through ctypes:
+
+    ChannelMask / ChannelMap          inc/ChannelMap.h
+    VBAPanner (2D/3D), SourceLayout   inc/Panning/PannerBase.h:315-389
+    DirectSoundBatch                  inc/Auralization/DirectSound.h:41-125 (N effects at once)
+    CrossoverBank, DelayBank          inc/Auralization/CrossoverFilter.h, DelayLine.h
+
+There is NO CPU fallback: without the built library the import fails, without a GPU every data-path call raises.
+"""
+from ._capi import (  # noqa: F401
+    JplgError, lib, lib_path, device_count, version,
+    MEM_HOST, MEM_DEVICE, MODE_PARITY, MODE_THROUGHPUT,
+    EChannel, ChannelMask, ChannelMap,
+    Context, VBAPanner, SourceLayout, DirectSoundBatch, CrossoverBank, DelayBank,
+    add_and_apply_gain_ramp, apply_gain, normalize_weights, get_spread_from_source_size,
+    STATE_FLOATS,
+)

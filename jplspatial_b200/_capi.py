@@ -1,0 +1,572 @@
+"""ctypes binding of include/jplg.h plus a thin object layer mirroring the reference's component API."""
+import ctypes as C
+import os
+import numpy as np
+
+_here = os.path.dirname(os.path.abspath(__file__))
+lib_path = os.path.join(_here, "libjplg.so")
+if not os.path.exists(lib_path):
+    raise ImportError(
+        f"{lib_path} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+        "(there is no CPU/PyTorch fallback for this package)")
+lib = C.CDLL(lib_path)
+
+MEM_HOST, MEM_DEVICE = 0, 1
+MODE_PARITY, MODE_THROUGHPUT = 0, 1
+STATE_FLOATS = 64
+_vp, _u32, _i32, _f32, _u64 = C.c_void_p, C.c_uint32, C.c_int32, C.c_float, C.c_uint64
+_fp = C.c_void_p  # float* as raw address (numpy .ctypes.data or a device pointer)
+
+
+class RendererConfig(C.Structure):
+    _fields_ = [("sample_rate", _f32), ("num_sources", _u32), ("source_channels", _u32), ("output_channels", _u32),
+                ("ring_size", _u32), ("max_block_frames", _u32), ("mode", _i32),
+                ("split_f1", _f32), ("split_f2", _f32), ("split_f3", _f32)]
+
+
+def _sig(name, res, args):
+    f = getattr(lib, name)
+    f.restype = res
+    f.argtypes = args
+
+
+_TRACE = C.CFUNCTYPE(None, C.c_char_p)
+_sig("jplg_set_trace_callback", None, [_TRACE])
+_sig("jplg_version", C.c_char_p, [])
+_sig("jplg_device_count", _i32, [])
+_sig("jplg_context_create", _i32, [_i32, C.POINTER(_vp)])
+_sig("jplg_context_destroy", None, [_vp])
+_sig("jplg_last_error", C.c_char_p, [_vp])
+_sig("jplg_context_stream", _vp, [_vp])
+_sig("jplg_context_synchronize", _i32, [_vp])
+_sig("jplg_context_rsqrt_model_verified", _i32, [_vp])
+_sig("jplg_context_launch_count", _u64, [_vp])
+_sig("jplg_channel_map_num_channels", _u32, [_u32])
+_sig("jplg_channel_map_has_lfe", _i32, [_u32])
+_sig("jplg_channel_map_has_top_channels", _i32, [_u32])
+_sig("jplg_channel_map_channel_index", _u32, [_u32, _u32])
+_sig("jplg_channel_map_from_num_channels", _u32, [_u32])
+_sig("jplg_panner_create", _i32, [_vp, _u32, C.POINTER(_vp)])
+_sig("jplg_panner_destroy", None, [_vp])
+_sig("jplg_panner_is_3d", _i32, [_vp])
+_sig("jplg_panner_num_channels", _u32, [_vp])
+_sig("jplg_panner_channel_mask", _u32, [_vp])
+_sig("jplg_panner_shortest_aperture", _f32, [_vp])
+_sig("jplg_panner_triangulation_is_tabulated", _i32, [_vp])
+_sig("jplg_panner_triangles", _u32, [_vp, _vp])
+_sig("jplg_panner_get_lut", _i32, [_vp, _fp, _vp])
+_sig("jplg_panner_set_lut", _i32, [_vp, _fp, _vp])
+_sig("jplg_panner_point_gains", _i32, [_vp, _fp, _u32, _fp, _i32])
+_sig("jplg_source_layout_create", _i32, [_vp, _u32, C.POINTER(_vp)])
+_sig("jplg_source_layout_destroy", None, [_vp])
+_sig("jplg_source_layout_num_channels", _u32, [_vp])
+_sig("jplg_source_layout_num_virtual_sources", _u32, [_vp])
+_sig("jplg_source_layout_info", None, [_vp, C.POINTER(_u32), C.POINTER(_f32), C.POINTER(_f32), C.POINTER(_f32)])
+_sig("jplg_source_layout_groups", None, [_vp, _fp, _vp])
+_sig("jplg_panner_mdap", _i32, [_vp, _vp, _fp, _u32, _fp, _i32])
+_sig("jplg_panner_process_virtual_sources", _i32, [_vp, _fp, _u32, _u32, _fp, _i32])
+_sig("jplg_normalize_weights", None, [_fp, _u32])
+_sig("jplg_spread_from_source_size", _f32, [_f32, _f32])
+_sig("jplg_renderer_create", _i32, [_vp, C.POINTER(RendererConfig), _fp, _fp, _fp, C.POINTER(_vp)])
+_sig("jplg_renderer_destroy", None, [_vp])
+_sig("jplg_renderer_update", _i32, [_vp, _fp, _fp, _fp, _i32])
+_sig("jplg_renderer_process_block", _i32, [_vp, _fp, _fp, _u32, _i32])
+_sig("jplg_renderer_process_block_debug", _i32, [_vp, _fp, _fp, _fp, _u32, _i32])
+_sig("jplg_renderer_device_bus", _vp, [_vp])
+_sig("jplg_renderer_ring_size", _u32, [_vp])
+_sig("jplg_renderer_state_export", _i32, [_vp, _fp, _fp, C.POINTER(_u64)])
+_sig("jplg_renderer_state_import", _i32, [_vp, _fp, _fp, _u64])
+_sig("jplg_crossover_bank_create", _i32, [_vp, _u32, _f32, _f32, _f32, _f32, _i32, C.POINTER(_vp)])
+_sig("jplg_crossover_bank_destroy", None, [_vp])
+_sig("jplg_crossover_bank_reset", _i32, [_vp])
+_sig("jplg_crossover_bank_coeffs", None, [_vp, _fp])
+_sig("jplg_crossover_bank_process_ramp", _i32, [_vp, _fp, _fp, _fp, _fp, _u32, _i32])
+_sig("jplg_crossover_bank_split", _i32, [_vp, _fp, _fp, _u32, _i32])
+_sig("jplg_delay_bank_create", _i32, [_vp, _u32, _u32, C.POINTER(_vp)])
+_sig("jplg_delay_bank_destroy", None, [_vp])
+_sig("jplg_delay_bank_size", _u32, [_vp])
+_sig("jplg_delay_bank_clear", _i32, [_vp])
+_sig("jplg_delay_bank_push", _i32, [_vp, _fp, _u32, _i32])
+_sig("jplg_delay_bank_read", _i32, [_vp, _fp, _u32, _i32, _fp, _i32])
+_sig("jplg_mix_add_and_apply_gain_ramp", _i32, [_vp, _fp, _fp, _u32, _u32, _u32, _u32, _u32, _u32, _fp, _fp, _i32])
+_sig("jplg_mix_apply_gain", _i32, [_vp, _fp, _u32, _u32, _fp, _i32])
+
+DECLARED_SYMBOLS = [n for n in dir(lib) if n.startswith("jplg_")]
+
+
+class JplgError(RuntimeError):
+    def __init__(self, status, message):
+        super().__init__(f"jplg status {status}: {message}")
+        self.status = status
+
+
+def version():
+    return lib.jplg_version().decode()
+
+
+def device_count():
+    return int(lib.jplg_device_count())
+
+
+# ------------------------------------------------------------------------------------------------
+class EChannel:
+    """inc/ChannelMap.h:38-79"""
+    FrontLeft, FrontRight, FrontCenter, LFE = 1 << 0, 1 << 1, 1 << 2, 1 << 3
+    SideLeft, SideRight, FrontLeftCenter, FrontRightCenter = 1 << 4, 1 << 5, 1 << 6, 1 << 7
+    BackLeft, BackRight, BackCenter, WideLeft, WideRight = 1 << 8, 1 << 9, 1 << 10, 1 << 11, 1 << 12
+    TopCenter, TopFrontLeft, TopFrontCenter, TopFrontRight = 1 << 13, 1 << 14, 1 << 15, 1 << 16
+    TopSideLeft, TopSideRight, TopBackLeft, TopBackCenter, TopBackRight = 1 << 17, 1 << 18, 1 << 19, 1 << 20, 1 << 21
+
+
+class ChannelMask:
+    """inc/ChannelMap.h:87-147"""
+    E = EChannel
+    Invalid = 0
+    Mono = E.FrontCenter
+    Stereo = E.FrontLeft | E.FrontRight
+    LCR = Stereo | E.FrontCenter
+    LRS = Stereo | E.BackCenter
+    LCRS = LCR | E.BackCenter
+    Quad = Stereo | E.BackLeft | E.BackRight
+    Octagonal = LCR | E.BackLeft | E.BackRight | E.BackCenter | E.WideLeft | E.WideRight
+    Surround_4_1 = Quad | E.LFE
+    Surround_5_0 = LCR | E.BackLeft | E.BackRight
+    Surround_5_1 = Surround_5_0 | E.LFE
+    Surround_6_0 = Surround_5_0 | E.BackCenter
+    Surround_6_1 = Surround_6_0 | E.LFE
+    Surround_7_0 = Surround_5_0 | E.SideLeft | E.SideRight
+    Surround_7_1 = Surround_7_0 | E.LFE
+    Surround_5_0_2 = Surround_5_0 | E.TopSideLeft | E.TopSideRight
+    Surround_5_1_2 = Surround_5_0_2 | E.LFE
+    Surround_5_0_4 = Surround_5_0 | E.TopFrontLeft | E.TopFrontRight | E.TopBackLeft | E.TopBackRight
+    Surround_5_1_4 = Surround_5_0_4 | E.LFE
+    Surround_7_0_2 = Surround_7_0 | E.TopSideLeft | E.TopSideRight
+    Surround_7_1_2 = Surround_7_0_2 | E.LFE
+    Surround_7_0_4 = Surround_7_0 | E.TopFrontLeft | E.TopFrontRight | E.TopBackLeft | E.TopBackRight
+    Surround_7_1_4 = Surround_7_0_4 | E.LFE
+    Surround_7_0_6 = Surround_7_0_4 | E.TopSideLeft | E.TopSideRight
+    Surround_7_1_6 = Surround_7_0_6 | E.LFE
+    Surround_9_0_4 = Surround_7_0_4 | E.WideLeft | E.WideRight
+    Surround_9_1_4 = Surround_9_0_4 | E.LFE
+    Surround_9_0_6 = Surround_9_0_4 | E.TopSideLeft | E.TopSideRight
+    Surround_9_1_6 = Surround_9_0_6 | E.LFE
+
+
+class ChannelMap:
+    """inc/ChannelMap.h:153-249"""
+
+    def __init__(self, mask=0):
+        self.mask = int(mask)
+
+    @staticmethod
+    def FromChannelMask(mask):
+        return ChannelMap(mask)
+
+    @staticmethod
+    def FromNumChannels(n):
+        return ChannelMap(lib.jplg_channel_map_from_num_channels(n))
+
+    def IsValid(self):
+        return self.mask != 0
+
+    def Has(self, ch):
+        return (self.mask & ch) == ch
+
+    def HasLFE(self):
+        return bool(lib.jplg_channel_map_has_lfe(self.mask))
+
+    def HasTopChannels(self):
+        return bool(lib.jplg_channel_map_has_top_channels(self.mask))
+
+    def GetNumChannels(self):
+        return int(lib.jplg_channel_map_num_channels(self.mask))
+
+    def GetChannelIndex(self, ch):
+        return int(lib.jplg_channel_map_channel_index(self.mask, ch))
+
+    def GetChannelMask(self):
+        return self.mask
+
+    def __eq__(self, o):
+        return isinstance(o, ChannelMap) and o.mask == self.mask
+
+
+def _mask(m):
+    return m.mask if isinstance(m, ChannelMap) else int(m)
+
+
+# ------------------------------------------------------------------------------------------------
+def _is_torch(x):
+    return type(x).__module__.startswith("torch")
+
+
+def _arg(x, dtype=np.float32):
+    """-> (address, mem, keepalive). numpy arrays are host memory, CUDA torch tensors device memory."""
+    if x is None:
+        return None, None, None
+    if _is_torch(x):
+        assert x.is_contiguous()
+        return x.data_ptr(), (MEM_DEVICE if x.is_cuda else MEM_HOST), x
+    a = np.ascontiguousarray(x, dtype=dtype)
+    return a.ctypes.data, MEM_HOST, a
+
+
+class Context:
+    """Device + stream + constant tables. device=-1 gives a host-only context: the builders (LUTs, layouts,
+    filter coefficients) work, every data-path call raises JplgError(JPLG_ERR_NO_DEVICE)."""
+
+    def __init__(self, device=0):
+        h = _vp()
+        st = lib.jplg_context_create(int(device), C.byref(h))
+        if st != 0:
+            raise JplgError(st, "jplg_context_create failed (no CUDA device? this library has no CPU fallback)")
+        self.h = h
+        self.device = device
+
+    def check(self, st):
+        if st != 0:
+            raise JplgError(st, lib.jplg_last_error(self.h).decode())
+
+    def synchronize(self):
+        self.check(lib.jplg_context_synchronize(self.h))
+
+    @property
+    def stream(self):
+        return lib.jplg_context_stream(self.h)
+
+    def torch_stream(self):
+        import torch
+        return torch.cuda.ExternalStream(self.stream, device=torch.device("cuda", self.device))
+
+    @property
+    def rsqrt_model_verified(self):
+        return bool(lib.jplg_context_rsqrt_model_verified(self.h))
+
+    @property
+    def launch_count(self):
+        return int(lib.jplg_context_launch_count(self.h))
+
+    def close(self):
+        if self.h:
+            lib.jplg_context_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class SourceLayout:
+    """VBAPLayoutBase / SourceLayout (inc/Panning/PannerBase.h:268-289)"""
+
+    def __init__(self, panner, source_map):
+        h = _vp()
+        panner.ctx.check(lib.jplg_source_layout_create(panner.h, _mask(source_map), C.byref(h)))
+        self.h = h
+        self.panner = panner
+        info = (_u32 * 4)()
+        a, b, c = _f32(), _f32(), _f32()
+        lib.jplg_source_layout_info(h, info, C.byref(a), C.byref(b), C.byref(c))
+        self.num_channels, self.num_virtual_sources, self.num_rings, self.samples_per_ring = [int(v) for v in info]
+        self.phi_term, self.offset_term, self.vs_weight = a.value, b.value, c.value
+
+    def groups(self):
+        q = np.zeros((self.num_channels, 4), np.float32)
+        ids = np.zeros(self.num_channels, np.uint32)
+        lib.jplg_source_layout_groups(self.h, q.ctypes.data, ids.ctypes.data)
+        return q, ids
+
+    def GetNumVirtualSources(self):
+        return self.num_virtual_sources
+
+    def __del__(self):
+        try:
+            if self.h:
+                lib.jplg_source_layout_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+
+class VBAPanner:
+    """VBAPanner2D / VBAPanner3D (inc/Panning/PannerBase.h:315-389), batched."""
+
+    def __init__(self, ctx):
+        self.ctx = ctx
+        self.h = None
+
+    def Initialize(self, channel_map):
+        h = _vp()
+        st = lib.jplg_panner_create(self.ctx.h, _mask(channel_map), C.byref(h))
+        if st != 0:
+            self.last_error = lib.jplg_last_error(self.ctx.h).decode()
+            return False  # like the reference: false + trace
+        self.h = h
+        return True
+
+    def IsInitialized(self):
+        return self.h is not None
+
+    def GetNumChannels(self):
+        return int(lib.jplg_panner_num_channels(self.h))
+
+    def GetChannelMap(self):
+        return ChannelMap(lib.jplg_panner_channel_mask(self.h))
+
+    def GetShortestSpeakerAperture(self):
+        return float(lib.jplg_panner_shortest_aperture(self.h))
+
+    def is_3d(self):
+        return bool(lib.jplg_panner_is_3d(self.h))
+
+    def triangulation_is_tabulated(self):
+        return bool(lib.jplg_panner_triangulation_is_tabulated(self.h))
+
+    def triangles(self):
+        n = lib.jplg_panner_triangles(self.h, None)
+        t = np.zeros((n, 3), np.uint8)
+        if n:
+            lib.jplg_panner_triangles(self.h, t.ctypes.data)
+        return t
+
+    def GetLUT(self):
+        L = self.GetNumChannels()
+        if self.is_3d():
+            g = np.zeros((65536, 3), np.float32)
+            s = np.zeros((65536, 3), np.uint8)
+            self.ctx.check(lib.jplg_panner_get_lut(self.h, g.ctypes.data, s.ctypes.data))
+            return g, s
+        g = np.zeros((1024, L), np.float32)
+        self.ctx.check(lib.jplg_panner_get_lut(self.h, g.ctypes.data, None))
+        return g, None
+
+    def SetLUT(self, gains, speakers=None):
+        g = np.ascontiguousarray(gains, np.float32)
+        s = None if speakers is None else np.ascontiguousarray(speakers, np.uint8)
+        self.ctx.check(lib.jplg_panner_set_lut(self.h, g.ctypes.data, None if s is None else s.ctypes.data))
+
+    def InitializeSourceLayout(self, source_map):
+        return SourceLayout(self, source_map)
+
+    def GetSpeakerGains(self, directions, out=None):
+        """directions [n,3] -> gains [n,L]"""
+        d, mem, keep = _arg(directions)
+        n = int(np.prod(keep.shape[:-1])) if keep is not None else 0
+        L = self.GetNumChannels()
+        if out is None:
+            if mem == MEM_DEVICE:
+                import torch
+                out = torch.empty((n, L), dtype=torch.float32, device=keep.device)
+            else:
+                out = np.empty((n, L), np.float32)
+        o, omem, okeep = _arg(out)
+        assert omem == mem
+        self.ctx.check(lib.jplg_panner_point_gains(self.h, d, n, o, mem))
+        return out
+
+    def ProcessVBAPData(self, layout, params, out=None):
+        """params [n,5] = {dir.xyz, focus, spread} -> mix maps [n, channels, L]"""
+        p, mem, keep = _arg(params)
+        n = keep.shape[0]
+        L = self.GetNumChannels()
+        if out is None:
+            if mem == MEM_DEVICE:
+                import torch
+                out = torch.empty((n, layout.num_channels, L), dtype=torch.float32, device=keep.device)
+            else:
+                out = np.empty((n, layout.num_channels, L), np.float32)
+        o, omem, okeep = _arg(out)
+        assert omem == mem
+        self.ctx.check(lib.jplg_panner_mdap(self.h, layout.h, p, n, o, mem))
+        return out
+
+    def ProcessVirtualSources(self, virtual_sources, out=None):
+        """virtual_sources [batches, n, 4] = {dir.xyz, weight} -> gains [batches, L] (accumulated into `out`, then L2-normalised)"""
+        v = np.ascontiguousarray(virtual_sources, np.float32)
+        if v.ndim == 2:
+            v = v[None]
+        b, n = v.shape[0], v.shape[1]
+        if out is None:
+            out = np.zeros((b, self.GetNumChannels()), np.float32)
+        self.ctx.check(lib.jplg_panner_process_virtual_sources(self.h, v.ctypes.data, n, b, out.ctypes.data, MEM_HOST))
+        return out
+
+    def __del__(self):
+        try:
+            if self.h:
+                lib.jplg_panner_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+
+def normalize_weights(vs):
+    v = np.ascontiguousarray(vs, np.float32)
+    lib.jplg_normalize_weights(v.ctypes.data, v.shape[0])
+    return v
+
+
+def get_spread_from_source_size(size, distance):
+    return float(lib.jplg_spread_from_source_size(size, distance))
+
+
+# ------------------------------------------------------------------------------------------------
+class DirectSoundBatch:
+    """N x DirectSoundEffect (inc/Auralization/DirectSound.h:41-125): ctor, UpdateParameters, ProcessInterleaved."""
+
+    def __init__(self, ctx, sample_rate, num_sources, num_source_channels, num_output_channels,
+                 initial_filter_gains=None, initial_delay_seconds=None, initial_mix_maps=None,
+                 ring_size=0, max_block_frames=512, mode=MODE_PARITY, splits=(0.0, 0.0, 0.0)):
+        self.ctx = ctx
+        self.N, self.C, self.L = int(num_sources), int(num_source_channels), int(num_output_channels)
+        cfg = RendererConfig(float(sample_rate), self.N, self.C, self.L, int(ring_size), int(max_block_frames), int(mode),
+                             float(splits[0]), float(splits[1]), float(splits[2]))
+        b, _, kb = _arg(initial_filter_gains)
+        d, _, kd = _arg(initial_delay_seconds)
+        m, _, km = _arg(initial_mix_maps)
+        h = _vp()
+        ctx.check(lib.jplg_renderer_create(ctx.h, C.byref(cfg), b, d, m, C.byref(h)))
+        self.h = h
+        self.ring_size = int(lib.jplg_renderer_ring_size(h))
+
+    def UpdateParameters(self, filter_gains=None, delay_seconds=None, mix_maps=None):
+        b, m1, kb = _arg(filter_gains)
+        d, m2, kd = _arg(delay_seconds)
+        m, m3, km = _arg(mix_maps)
+        mems = {x for x in (m1, m2, m3) if x is not None}
+        assert len(mems) <= 1, "all update arrays must live in the same memory space"
+        self.ctx.check(lib.jplg_renderer_update(self.h, b, d, m, mems.pop() if mems else MEM_HOST))
+
+    def ProcessInterleaved(self, inp, bus, num_frames, per_source=None):
+        """inp [N, frames, C]; bus [frames, L] accumulated into; per_source optional [N, frames, L] (debug)."""
+        i, mem, ki = _arg(inp)
+        o, omem, ko = _arg(bus)
+        assert mem == omem
+        if per_source is None:
+            self.ctx.check(lib.jplg_renderer_process_block(self.h, i, o, int(num_frames), mem))
+        else:
+            p, pmem, kp = _arg(per_source)
+            assert pmem == mem
+            self.ctx.check(lib.jplg_renderer_process_block_debug(self.h, i, o, p, int(num_frames), mem))
+        return bus
+
+    def device_bus_ptr(self):
+        return lib.jplg_renderer_device_bus(self.h)
+
+    def state_export(self, with_rings=False):
+        st = np.zeros((self.N * self.C, STATE_FLOATS), np.float32)
+        rings = np.zeros((self.N * self.C, self.ring_size), np.float32) if with_rings else None
+        pos = _u64()
+        self.ctx.check(lib.jplg_renderer_state_export(self.h, st.ctypes.data, None if rings is None else rings.ctypes.data, C.byref(pos)))
+        return st, rings, int(pos.value)
+
+    def state_import(self, state, rings, pos):
+        st = np.ascontiguousarray(state, np.float32)
+        rg = None if rings is None else np.ascontiguousarray(rings, np.float32)
+        self.ctx.check(lib.jplg_renderer_state_import(self.h, st.ctypes.data, None if rg is None else rg.ctypes.data, int(pos)))
+
+    def close(self):
+        if self.h:
+            lib.jplg_renderer_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class CrossoverBank:
+    """n x FourBandCrossover (inc/Auralization/CrossoverFilter.h:416-535)"""
+
+    def __init__(self, ctx, n, sample_rate, splits=(0.0, 0.0, 0.0), mode=MODE_PARITY):
+        self.ctx, self.n = ctx, int(n)
+        h = _vp()
+        ctx.check(lib.jplg_crossover_bank_create(ctx.h, self.n, float(sample_rate), float(splits[0]), float(splits[1]), float(splits[2]), int(mode), C.byref(h)))
+        self.h = h
+
+    def coeffs(self):
+        c = np.zeros(27, np.float32)
+        lib.jplg_crossover_bank_coeffs(self.h, c.ctypes.data)
+        return c
+
+    def Reset(self):
+        self.ctx.check(lib.jplg_crossover_bank_reset(self.h))
+
+    def ProcessBlock(self, inp, start_gains, end_gains):
+        x = np.ascontiguousarray(inp, np.float32)
+        g0 = np.ascontiguousarray(start_gains, np.float32)
+        g1 = np.ascontiguousarray(end_gains, np.float32)
+        out = np.empty_like(x)
+        self.ctx.check(lib.jplg_crossover_bank_process_ramp(self.h, x.ctypes.data, g0.ctypes.data, g1.ctypes.data, out.ctypes.data, x.shape[1], MEM_HOST))
+        return out
+
+    def SplitBlock(self, inp):
+        x = np.ascontiguousarray(inp, np.float32)
+        out = np.empty(x.shape + (4,), np.float32)
+        self.ctx.check(lib.jplg_crossover_bank_split(self.h, x.ctypes.data, out.ctypes.data, x.shape[1], MEM_HOST))
+        return out
+
+    def __del__(self):
+        try:
+            if self.h:
+                lib.jplg_crossover_bank_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+
+class DelayBank:
+    """n x (DelayLine + DelayTap) (inc/Auralization/DelayLine.h:43-68,129-230)"""
+    NEAREST, LINEAR, THIRAN1 = 0, 1, 2
+
+    def __init__(self, ctx, n, min_size):
+        self.ctx, self.n = ctx, int(n)
+        h = _vp()
+        ctx.check(lib.jplg_delay_bank_create(ctx.h, self.n, int(min_size), C.byref(h)))
+        self.h = h
+
+    def GetSize(self):
+        return int(lib.jplg_delay_bank_size(self.h))
+
+    def Clear(self):
+        self.ctx.check(lib.jplg_delay_bank_clear(self.h))
+
+    def Push(self, samples):
+        x = np.ascontiguousarray(samples, np.float32).reshape(self.n, -1)
+        self.ctx.check(lib.jplg_delay_bank_push(self.h, x.ctypes.data, x.shape[1], MEM_HOST))
+
+    def Read(self, delays, interp=2):
+        d = np.ascontiguousarray(delays, np.float32).reshape(self.n, -1)
+        out = np.empty_like(d)
+        self.ctx.check(lib.jplg_delay_bank_read(self.h, d.ctypes.data, d.shape[1], int(interp), out.ctypes.data, MEM_HOST))
+        return out
+
+    def __del__(self):
+        try:
+            if self.h:
+                lib.jplg_delay_bank_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+
+def add_and_apply_gain_ramp(ctx, dest, source, dest_channel, source_channel, frames, gain_start, gain_end):
+    """AddAndApplyGainRamp (inc/Auralization/ChannelMixing.h:89-107) for n (dest, source) pairs: dest [n, frames, nDest], source [n, frames, nSrc]"""
+    d = np.ascontiguousarray(dest, np.float32)
+    s = np.ascontiguousarray(source, np.float32)
+    g0 = np.ascontiguousarray(gain_start, np.float32)
+    g1 = np.ascontiguousarray(gain_end, np.float32)
+    ctx.check(lib.jplg_mix_add_and_apply_gain_ramp(ctx.h, d.ctypes.data, s.ctypes.data, d.shape[0], dest_channel, source_channel,
+                                                   d.shape[2], s.shape[2], frames, g0.ctypes.data, g1.ctypes.data, MEM_HOST))
+    return d
+
+
+def apply_gain(ctx, dest, gains):
+    d = np.ascontiguousarray(dest, np.float32)
+    g = np.ascontiguousarray(gains, np.float32)
+    ctx.check(lib.jplg_mix_apply_gain(ctx.h, d.ctypes.data, d.shape[0], d.shape[1], g.ctypes.data, MEM_HOST))
+    return d

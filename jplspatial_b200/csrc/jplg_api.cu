@@ -1,0 +1,872 @@
+// C-ABI layer (include/jplg.h): handles, host<->device staging, launch sequencing. No compute happens on the host:
+// every data-path call fails with JPLG_ERR_NO_DEVICE when the context has no GPU.
+#include "../../include/jplg.h"
+#include "jplg_host.hpp"
+#include "jplg_kernels.hpp"
+
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+using namespace jplg;
+
+static jplg_trace_fn gTrace = nullptr;
+
+struct jplg_context_t
+{
+	int device = -1;              // -1: host-only context (builders work, data-path calls fail loudly)
+	cudaStream_t stream = nullptr;
+	int numSMs = 0;
+	uint32_t* dRsq = nullptr;
+	bool rsqVerified = false;
+	bool sticky = false;
+	uint64_t launches = 0;
+	std::string lastError;
+	// growable device scratch for JPLG_MEM_HOST calls
+	void* scratch[4] = { nullptr, nullptr, nullptr, nullptr };
+	size_t scratchBytes[4] = { 0, 0, 0, 0 };
+	std::mutex mtx;
+};
+
+static jplg_status Fail(jplg_context ctx, jplg_status st, const std::string& msg)
+{
+	if (ctx) ctx->lastError = msg;
+	if (gTrace) gTrace(msg.c_str());
+	return st;
+}
+
+#define JPLG_CUDA_TRY(ctx, expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { (ctx)->sticky = true; \
+	return Fail((ctx), JPLG_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e)); } } while (0)
+#define JPLG_NEED_DEVICE(ctx) do { if (!(ctx) || (ctx)->device < 0) return Fail((ctx), JPLG_ERR_NO_DEVICE, \
+	"no CUDA device in this context: the library has no CPU fallback"); if ((ctx)->sticky) return Fail((ctx), JPLG_ERR_CUDA, "context is in a sticky CUDA error state: " + (ctx)->lastError); } while (0)
+
+static jplg_status Scratch(jplg_context ctx, int slot, size_t bytes, void** out)
+{
+	if (bytes > ctx->scratchBytes[slot])
+	{
+		if (ctx->scratch[slot]) { JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream)); cudaFree(ctx->scratch[slot]); ctx->scratch[slot] = nullptr; ctx->scratchBytes[slot] = 0; }
+		const size_t want = bytes + bytes / 4 + 256;
+		if (cudaMalloc(&ctx->scratch[slot], want) != cudaSuccess) { cudaGetLastError(); return Fail(ctx, JPLG_ERR_OUT_OF_MEMORY, "device scratch allocation failed"); }
+		ctx->scratchBytes[slot] = want;
+	}
+	*out = ctx->scratch[slot];
+	return JPLG_OK;
+}
+
+extern "C" {
+
+void jplg_set_trace_callback(jplg_trace_fn fn) { gTrace = fn; }
+const char* jplg_version(void) { return "jplspatial_b200 0.1 (sm_100a)"; }
+int32_t jplg_device_count(void)
+{
+	int n = 0;
+	if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+	return n;
+}
+
+//==================================================================================================
+jplg_status jplg_context_create(int32_t device, jplg_context* out)
+{
+	if (!out) return JPLG_ERR_INVALID_ARGUMENT;
+	*out = nullptr;
+	auto* ctx = new jplg_context_t();
+	static uint32_t sTable[2048];
+	static bool sVerified = false, sBuilt = false;
+	static std::mutex sMtx;
+	{
+		std::lock_guard<std::mutex> lk(sMtx);
+		if (!sBuilt) { sVerified = BuildRsqrtTable(sTable); sBuilt = true; }
+	}
+	ctx->rsqVerified = sVerified;
+	if (device < 0) { ctx->device = -1; *out = ctx; return JPLG_OK; }
+	if (device >= jplg_device_count()) { delete ctx; if (gTrace) gTrace("jplg_context_create: no such CUDA device"); return JPLG_ERR_NO_DEVICE; }
+	ctx->device = device;
+	cudaError_t e = cudaSetDevice(device);
+	if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+	if (e == cudaSuccess) e = cudaDeviceGetAttribute(&ctx->numSMs, cudaDevAttrMultiProcessorCount, device);
+	if (e == cudaSuccess) e = cudaMalloc(&ctx->dRsq, sizeof(sTable));
+	if (e == cudaSuccess) e = cudaMemcpy(ctx->dRsq, sTable, sizeof(sTable), cudaMemcpyHostToDevice);
+	if (e != cudaSuccess) { if (gTrace) gTrace(cudaGetErrorString(e)); delete ctx; return JPLG_ERR_CUDA; }
+	*out = ctx;
+	return JPLG_OK;
+}
+
+void jplg_context_destroy(jplg_context ctx)
+{
+	if (!ctx) return;
+	if (ctx->device >= 0)
+	{
+		cudaSetDevice(ctx->device);
+		if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+		for (auto& s : ctx->scratch) if (s) cudaFree(s);
+		if (ctx->dRsq) cudaFree(ctx->dRsq);
+		if (ctx->stream) cudaStreamDestroy(ctx->stream);
+	}
+	delete ctx;
+}
+const char* jplg_last_error(jplg_context ctx) { return ctx ? ctx->lastError.c_str() : "null context"; }
+void* jplg_context_stream(jplg_context ctx) { return ctx ? static_cast<void*>(ctx->stream) : nullptr; }
+jplg_status jplg_context_synchronize(jplg_context ctx)
+{
+	JPLG_NEED_DEVICE(ctx);
+	JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	return JPLG_OK;
+}
+int32_t jplg_context_rsqrt_model_verified(jplg_context ctx) { return ctx && ctx->rsqVerified ? 1 : 0; }
+uint64_t jplg_context_launch_count(jplg_context ctx) { return ctx ? ctx->launches : 0; }
+
+//==================================================================================================
+uint32_t jplg_channel_map_num_channels(uint32_t mask) { return NumChannels(mask); }
+int32_t jplg_channel_map_has_lfe(uint32_t mask) { return HasLFE(mask) ? 1 : 0; }
+int32_t jplg_channel_map_has_top_channels(uint32_t mask) { return HasTopChannels(mask) ? 1 : 0; }
+uint32_t jplg_channel_map_channel_index(uint32_t mask, uint32_t bit) { return ChannelIndex(mask, bit); }
+uint32_t jplg_channel_map_from_num_channels(uint32_t n) { return MaskFromNumChannels(n); }
+
+} // extern "C"
+
+//==================================================================================================
+struct jplg_panner_t
+{
+	jplg_context ctx = nullptr;
+	PannerData host;
+	uint4* dLut3d = nullptr;
+	float* dLut2d = nullptr;
+	PannerDev dev;
+};
+
+struct jplg_source_layout_t
+{
+	jplg_panner panner = nullptr;
+	LayoutData host;
+	MdapLayoutParams lp;
+};
+
+static jplg_status UploadLUT(jplg_panner p)
+{
+	jplg_context ctx = p->ctx;
+	if (ctx->device < 0) return JPLG_OK;
+	cudaSetDevice(ctx->device);
+	if (p->host.is3D)
+	{
+		std::vector<uint4> cells(kLUT3DCells);
+		for (uint32_t i = 0; i < kLUT3DCells; ++i)
+		{
+			uint32_t g[3]; std::memcpy(g, &p->host.lut3dGains[size_t(i) * 3], 12);
+			const uint8_t* s = &p->host.lut3dSpeakers[size_t(i) * 3];
+			cells[i] = make_uint4(g[0], g[1], g[2], uint32_t(s[0]) | (uint32_t(s[1]) << 8) | (uint32_t(s[2]) << 16));
+		}
+		if (!p->dLut3d) JPLG_CUDA_TRY(ctx, cudaMalloc(&p->dLut3d, sizeof(uint4) * kLUT3DCells));
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(p->dLut3d, cells.data(), sizeof(uint4) * kLUT3DCells, cudaMemcpyHostToDevice, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	}
+	else
+	{
+		const size_t bytes = p->host.lut2d.size() * sizeof(float);
+		if (!p->dLut2d) JPLG_CUDA_TRY(ctx, cudaMalloc(&p->dLut2d, bytes));
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(p->dLut2d, p->host.lut2d.data(), bytes, cudaMemcpyHostToDevice, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	}
+	p->dev.is3D = p->host.is3D;
+	p->dev.numChannels = p->host.numChannels;
+	p->dev.lut3d = p->dLut3d;
+	p->dev.lut2d = p->dLut2d;
+	p->dev.rsqTable = ctx->dRsq;
+	return JPLG_OK;
+}
+
+extern "C" {
+
+jplg_status jplg_panner_create(jplg_context ctx, uint32_t target_mask, jplg_panner* out)
+{
+	if (!ctx || !out) return JPLG_ERR_INVALID_ARGUMENT;
+	*out = nullptr;
+	auto* p = new jplg_panner_t();
+	p->ctx = ctx;
+	std::string err;
+	if (!BuildPanner(target_mask, p->host, err))
+	{
+		delete p;
+		return Fail(ctx, err.find("triangulate") != std::string::npos ? JPLG_ERR_TRIANGULATION : JPLG_ERR_INVALID_CHANNEL_MAP, "VBAPannerBase: " + err);
+	}
+	const jplg_status st = UploadLUT(p);
+	if (st != JPLG_OK) { delete p; return st; }
+	*out = p;
+	return JPLG_OK;
+}
+void jplg_panner_destroy(jplg_panner p)
+{
+	if (!p) return;
+	if (p->ctx->device >= 0) { cudaSetDevice(p->ctx->device); cudaStreamSynchronize(p->ctx->stream); if (p->dLut3d) cudaFree(p->dLut3d); if (p->dLut2d) cudaFree(p->dLut2d); }
+	delete p;
+}
+int32_t jplg_panner_is_3d(jplg_panner p) { return p && p->host.is3D ? 1 : 0; }
+uint32_t jplg_panner_num_channels(jplg_panner p) { return p ? p->host.numChannels : 0; }
+uint32_t jplg_panner_channel_mask(jplg_panner p) { return p ? p->host.mask : 0; }
+float jplg_panner_shortest_aperture(jplg_panner p) { return p ? p->host.shortestAperture : 0.0f; }
+int32_t jplg_panner_triangulation_is_tabulated(jplg_panner p) { return p && p->host.trisTabulated ? 1 : 0; }
+uint32_t jplg_panner_triangles(jplg_panner p, uint8_t* out_tris)
+{
+	if (!p) return 0;
+	if (out_tris && !p->host.tris.empty()) std::memcpy(out_tris, p->host.tris.data(), p->host.tris.size());
+	return static_cast<uint32_t>(p->host.tris.size() / 3);
+}
+
+jplg_status jplg_panner_get_lut(jplg_panner p, float* gains, uint8_t* speakers)
+{
+	if (!p || !gains) return JPLG_ERR_INVALID_ARGUMENT;
+	if (p->host.is3D)
+	{
+		std::memcpy(gains, p->host.lut3dGains.data(), p->host.lut3dGains.size() * sizeof(float));
+		if (speakers) std::memcpy(speakers, p->host.lut3dSpeakers.data(), p->host.lut3dSpeakers.size());
+	}
+	else std::memcpy(gains, p->host.lut2d.data(), p->host.lut2d.size() * sizeof(float));
+	return JPLG_OK;
+}
+jplg_status jplg_panner_set_lut(jplg_panner p, const float* gains, const uint8_t* speakers)
+{
+	if (!p || !gains) return JPLG_ERR_INVALID_ARGUMENT;
+	if (p->host.is3D)
+	{
+		if (!speakers) return JPLG_ERR_INVALID_ARGUMENT;
+		std::memcpy(p->host.lut3dGains.data(), gains, p->host.lut3dGains.size() * sizeof(float));
+		std::memcpy(p->host.lut3dSpeakers.data(), speakers, p->host.lut3dSpeakers.size());
+	}
+	else std::memcpy(p->host.lut2d.data(), gains, p->host.lut2d.size() * sizeof(float));
+	return UploadLUT(p);
+}
+
+jplg_status jplg_panner_point_gains(jplg_panner p, const float* dirs, uint32_t n, float* out, int32_t mem)
+{
+	if (!p || (n && (!dirs || !out))) return JPLG_ERR_INVALID_ARGUMENT;
+	jplg_context ctx = p->ctx;
+	JPLG_NEED_DEVICE(ctx);
+	if (n == 0) return JPLG_OK;
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	const uint32_t L = p->host.numChannels;
+	const float* dDirs = dirs; float* dOut = out;
+	if (mem == JPLG_MEM_HOST)
+	{
+		void *a, *b;
+		jplg_status st = Scratch(ctx, 0, size_t(n) * 3 * 4, &a); if (st) return st;
+		st = Scratch(ctx, 1, size_t(n) * L * 4, &b); if (st) return st;
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(a, dirs, size_t(n) * 3 * 4, cudaMemcpyHostToDevice, ctx->stream));
+		dDirs = static_cast<float*>(a); dOut = static_cast<float*>(b);
+	}
+	JPLG_CUDA_TRY(ctx, LaunchPointGains(p->dev, dDirs, n, dOut, ctx->stream)); ctx->launches++;
+	if (mem == JPLG_MEM_HOST)
+	{
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(out, dOut, size_t(n) * L * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	}
+	return JPLG_OK;
+}
+
+jplg_status jplg_source_layout_create(jplg_panner p, uint32_t source_mask, jplg_source_layout* out)
+{
+	if (!p || !out) return JPLG_ERR_INVALID_ARGUMENT;
+	*out = nullptr;
+	auto* l = new jplg_source_layout_t();
+	l->panner = p;
+	std::string err;
+	if (!BuildSourceLayout(p->host, source_mask, l->host, err)) { delete l; return Fail(p->ctx, JPLG_ERR_INVALID_CHANNEL_MAP, "SourceLayout: " + err); }
+	MdapLayoutParams& lp = l->lp;
+	std::memset(&lp, 0, sizeof(lp));
+	lp.numChannels = l->host.numChannels; lp.numVS = l->host.numVS; lp.numRings = l->host.numRings; lp.samplesPerRing = l->host.samplesPerRing;
+	const uint32_t numSIMDOps = l->host.samplesPerRing >> 2;
+	lp.halfSamples = (numSIMDOps & ~1u) >> 1; lp.tail = numSIMDOps & 1u;
+	lp.phiTerm = l->host.phiTerm; lp.offsetTerm = l->host.offsetTerm; lp.vsWeight = l->host.vsWeight;
+	std::memcpy(lp.quats, l->host.quats, sizeof(lp.quats));
+	if (l->host.is3D)
+	{
+		if (l->host.azSin.size() > kMaxAzimuthFloats || l->host.numRings > 24)
+		{
+			delete l;
+			return Fail(p->ctx, JPLG_ERR_UNSUPPORTED, "SourceLayout: spread-cap dimensions exceed the kernel's tables (rings > 24 or samples per ring > 128)");
+		}
+		for (size_t i = 0; i < l->host.azSin.size(); ++i) { lp.azSin[i] = l->host.azSin[i]; lp.azCos[i] = l->host.azCos[i]; }
+	}
+	*out = l;
+	return JPLG_OK;
+}
+void jplg_source_layout_destroy(jplg_source_layout l) { delete l; }
+uint32_t jplg_source_layout_num_channels(jplg_source_layout l) { return l ? l->host.numChannels : 0; }
+uint32_t jplg_source_layout_num_virtual_sources(jplg_source_layout l) { return l ? l->host.numVS : 0; }
+void jplg_source_layout_info(jplg_source_layout l, uint32_t info[4], float* phi_term, float* offset_term, float* vs_weight)
+{
+	if (!l) return;
+	info[0] = l->host.numChannels; info[1] = l->host.numVS; info[2] = l->host.numRings; info[3] = l->host.samplesPerRing;
+	if (phi_term) *phi_term = l->host.phiTerm;
+	if (offset_term) *offset_term = l->host.offsetTerm;
+	if (vs_weight) *vs_weight = l->host.vsWeight;
+}
+void jplg_source_layout_groups(jplg_source_layout l, float* out_quats, uint32_t* out_channel_ids)
+{
+	if (!l) return;
+	for (uint32_t i = 0; i < l->host.numChannels; ++i)
+	{
+		if (out_quats) std::memcpy(out_quats + 4 * i, l->host.quats[i], 16);
+		if (out_channel_ids) out_channel_ids[i] = l->host.channelIds[i];
+	}
+}
+
+jplg_status jplg_panner_mdap(jplg_panner p, jplg_source_layout l, const float* params, uint32_t n, float* out, int32_t mem)
+{
+	if (!p || !l || l->panner != p || (n && (!params || !out))) return JPLG_ERR_INVALID_ARGUMENT;
+	jplg_context ctx = p->ctx;
+	JPLG_NEED_DEVICE(ctx);
+	if (n == 0) return JPLG_OK;
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	const size_t outFloats = size_t(n) * l->host.numChannels * p->host.numChannels;
+	const float* dParams = params; float* dOut = out;
+	if (mem == JPLG_MEM_HOST)
+	{
+		void *a, *b;
+		jplg_status st = Scratch(ctx, 0, size_t(n) * 5 * 4, &a); if (st) return st;
+		st = Scratch(ctx, 1, outFloats * 4, &b); if (st) return st;
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(a, params, size_t(n) * 5 * 4, cudaMemcpyHostToDevice, ctx->stream));
+		dParams = static_cast<float*>(a); dOut = static_cast<float*>(b);
+	}
+	JPLG_CUDA_TRY(ctx, LaunchMdap(p->dev, l->lp, dParams, n, dOut, ctx->numSMs, ctx->stream)); ctx->launches++;
+	if (mem == JPLG_MEM_HOST)
+	{
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(out, dOut, outFloats * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	}
+	return JPLG_OK;
+}
+
+jplg_status jplg_panner_process_virtual_sources(jplg_panner p, const float* vs, uint32_t n, uint32_t batches, float* out, int32_t mem)
+{
+	if (!p || (batches && (!out || (n && !vs)))) return JPLG_ERR_INVALID_ARGUMENT;
+	jplg_context ctx = p->ctx;
+	JPLG_NEED_DEVICE(ctx);
+	if (batches == 0) return JPLG_OK;
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	const uint32_t L = p->host.numChannels;
+	const float* dVs = vs; float* dOut = out;
+	if (mem == JPLG_MEM_HOST)
+	{
+		void *a, *b;
+		jplg_status st = Scratch(ctx, 0, size_t(batches) * n * 16 + 16, &a); if (st) return st;
+		st = Scratch(ctx, 1, size_t(batches) * L * 4, &b); if (st) return st;
+		if (n) JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(a, vs, size_t(batches) * n * 16, cudaMemcpyHostToDevice, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(b, out, size_t(batches) * L * 4, cudaMemcpyHostToDevice, ctx->stream)); // accumulated into
+		dVs = static_cast<float*>(a); dOut = static_cast<float*>(b);
+	}
+	JPLG_CUDA_TRY(ctx, LaunchProcessVS(p->dev, dVs, n, batches, dOut, ctx->stream)); ctx->launches++;
+	if (mem == JPLG_MEM_HOST)
+	{
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(out, dOut, size_t(batches) * L * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	}
+	return JPLG_OK;
+}
+
+void jplg_normalize_weights(float* vs, uint32_t n)
+{
+	// VBAPannerBase::NormalizeWeights (inc/Panning/PannerBase.h:879-892)
+	float sum = 0.0f;
+	for (uint32_t i = 0; i < n; ++i) { const float w = vs[4 * i + 3]; sum += (w < 0 ? -w : w); }
+	const float invSum = sum == 0.0f ? 0.0f : 1.0f / sum;
+	for (uint32_t i = 0; i < n; ++i) vs[4 * i + 3] *= invSum;
+}
+float jplg_spread_from_source_size(float source_size, float distance)
+{
+	// GetSpreadFromSourceSize (inc/Panning/PannerBase.h:69-74)
+	return distance <= 0.0f ? 1.0f : atanf((source_size * 0.5f) / distance) * (0.318309886183790671538f * 2.0f);
+}
+
+} // extern "C"
+
+//==================================================================================================
+// Renderer
+struct jplg_renderer_t
+{
+	jplg_context ctx = nullptr;
+	jplg_renderer_config cfg{};
+	uint32_t numSC = 0, ringSize = 0, maxFrames = 0, numCTAs = 0;
+	uint64_t pos = 0;
+	float alpha = 0.0f, coef[27] = {};
+	float *state = nullptr, *curMix = nullptr, *tgtDelay = nullptr, *tgtBand = nullptr, *tgtMix = nullptr, *rings = nullptr;
+	float *partial = nullptr, *deviceBus = nullptr, *stageIn = nullptr, *stageBus = nullptr, *stagePerSource = nullptr;
+	float *stageParams = nullptr; // update staging: band [N][4] | delay [N] | mix [N][C*L]
+	size_t stagePerSourceFloats = 0;
+};
+
+// targets in the reference's layouts -> SoA per source-channel (UpdateParameters, src/Auralization/DirectSound.cpp:231-239)
+__global__ void k_update_targets(const float* __restrict__ band, const float* __restrict__ delaySec, const float* __restrict__ mix,
+								 uint32_t numSC, uint32_t C, uint32_t L, float sampleRate,
+								 float* __restrict__ tgtBand, float* __restrict__ tgtDelay, float* __restrict__ tgtMix)
+{
+	const uint32_t sc = blockIdx.x * blockDim.x + threadIdx.x;
+	if (sc >= numSC) return;
+	const uint32_t src = sc / C, k = sc - src * C;
+	if (band) for (uint32_t b = 0; b < 4; ++b) tgtBand[size_t(b) * numSC + sc] = band[size_t(src) * 4 + b];
+	if (delaySec) tgtDelay[sc] = delaySec[src] * sampleRate;
+	if (mix) for (uint32_t c = 0; c < L; ++c) tgtMix[size_t(c) * numSC + sc] = mix[(size_t(src) * C + k) * L + c];
+}
+// constructor semantics: current = target (DirectSound.cpp:48-63)
+__global__ void k_init_current(uint32_t numSC, uint32_t L, const float* __restrict__ tgtBand, const float* __restrict__ tgtDelay, const float* __restrict__ tgtMix,
+							   float* __restrict__ state, float* __restrict__ curMix)
+{
+	const uint32_t sc = blockIdx.x * blockDim.x + threadIdx.x;
+	if (sc >= numSC) return;
+	state[size_t(ST_DELAY) * numSC + sc] = tgtDelay[sc];
+	for (uint32_t b = 0; b < 4; ++b) state[size_t(ST_BAND + b) * numSC + sc] = tgtBand[size_t(b) * numSC + sc];
+	for (uint32_t c = 0; c < L; ++c) curMix[size_t(c) * numSC + sc] = tgtMix[size_t(c) * numSC + sc];
+}
+__global__ void k_fill(float* p, size_t n, float v)
+{
+	const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+	if (i < n) p[i] = v;
+}
+// state blob [numSC][64] (AoS) <-> device SoA state[32][numSC] + curMix[L][numSC]
+__global__ void k_state_export(const float* __restrict__ state, const float* __restrict__ curMix, uint32_t numSC, uint32_t L, float* __restrict__ blob)
+{
+	const size_t idx = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+	if (idx >= size_t(numSC) * 64) return;
+	const uint32_t sc = static_cast<uint32_t>(idx / 64), k = static_cast<uint32_t>(idx % 64);
+	float v = 0.0f;
+	if (k < 32) v = state[size_t(k) * numSC + sc]; else if (k - 32 < L) v = curMix[size_t(k - 32) * numSC + sc];
+	blob[idx] = v;
+}
+__global__ void k_state_import(float* __restrict__ state, float* __restrict__ curMix, uint32_t numSC, uint32_t L, const float* __restrict__ blob)
+{
+	const size_t idx = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+	if (idx >= size_t(numSC) * 64) return;
+	const uint32_t sc = static_cast<uint32_t>(idx / 64), k = static_cast<uint32_t>(idx % 64);
+	if (k < 32) state[size_t(k) * numSC + sc] = blob[idx]; else if (k - 32 < L) curMix[size_t(k - 32) * numSC + sc] = blob[idx];
+}
+
+static void FreeRenderer(jplg_renderer r)
+{
+	float** ptrs[] = { &r->state, &r->curMix, &r->tgtDelay, &r->tgtBand, &r->tgtMix, &r->rings, &r->partial, &r->deviceBus, &r->stageIn, &r->stageBus, &r->stagePerSource, &r->stageParams };
+	for (float** p : ptrs) if (*p) { cudaFree(*p); *p = nullptr; }
+}
+
+static jplg_status RendererUpdateLocked(jplg_renderer r, const float* band, const float* delay, const float* mix, int32_t mem)
+{
+	jplg_context ctx = r->ctx;
+	const uint32_t N = r->cfg.num_sources, C = r->cfg.source_channels, L = r->cfg.output_channels;
+	const float *dBand = band, *dDelay = delay, *dMix = mix;
+	if (mem == JPLG_MEM_HOST)
+	{
+		float* base = r->stageParams;
+		if (band) { JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(base, band, size_t(N) * 4 * 4, cudaMemcpyHostToDevice, ctx->stream)); dBand = base; }
+		if (delay) { JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(base + size_t(N) * 4, delay, size_t(N) * 4, cudaMemcpyHostToDevice, ctx->stream)); dDelay = base + size_t(N) * 4; }
+		if (mix) { JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(base + size_t(N) * 5, mix, size_t(N) * C * L * 4, cudaMemcpyHostToDevice, ctx->stream)); dMix = base + size_t(N) * 5; }
+	}
+	k_update_targets<<<(r->numSC + 127) / 128, 128, 0, ctx->stream>>>(dBand, dDelay, dMix, r->numSC, C, L, r->cfg.sample_rate, r->tgtBand, r->tgtDelay, r->tgtMix);
+	JPLG_CUDA_TRY(ctx, cudaGetLastError()); ctx->launches++;
+	if (mem == JPLG_MEM_HOST) JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream)); // host buffers are caller-owned: safe to reuse on return
+	return JPLG_OK;
+}
+
+extern "C" {
+
+jplg_status jplg_renderer_create(jplg_context ctx, const jplg_renderer_config* cfgIn, const float* band_gains, const float* delay_seconds,
+								 const float* mix_maps, jplg_renderer* out)
+{
+	if (!ctx || !cfgIn || !out) return JPLG_ERR_INVALID_ARGUMENT;
+	*out = nullptr;
+	JPLG_NEED_DEVICE(ctx);
+	jplg_renderer_config cfg = *cfgIn;
+	if (cfg.num_sources == 0 || cfg.source_channels == 0 || cfg.source_channels > 128 || cfg.output_channels == 0 || cfg.output_channels > kMaxChannelsDev || !(cfg.sample_rate > 0.0f))
+		return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "jplg_renderer_create: bad configuration");
+	if (cfg.max_block_frames == 0) cfg.max_block_frames = 512;
+	uint32_t ring = cfg.ring_size;
+	if (ring == 0) { const uint32_t minSize = static_cast<uint32_t>(cfg.sample_rate * 2.0f); ring = 1; while (ring < minSize) ring <<= 1; } // std::bit_ceil (DirectSound.cpp:79)
+	if (ring & (ring - 1)) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "jplg_renderer_create: ring_size must be a power of two");
+	if (ring < 2 * cfg.max_block_frames + 4) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "jplg_renderer_create: ring_size too small for max_block_frames");
+	if (cfg.split_f1 == 0.0f) cfg.split_f1 = 176.0f;
+	if (cfg.split_f2 == 0.0f) cfg.split_f2 = 775.0f;
+	if (cfg.split_f3 == 0.0f) cfg.split_f3 = 3408.0f;
+	cfg.ring_size = ring;
+
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	auto* r = new jplg_renderer_t();
+	r->ctx = ctx; r->cfg = cfg; r->ringSize = ring; r->maxFrames = cfg.max_block_frames;
+	r->numSC = cfg.num_sources * cfg.source_channels;
+	r->numCTAs = RenderNumCTAs(r->numSC, cfg.source_channels);
+	r->alpha = ExpAlpha(kChunkFrames);                                    // CreateExpSmoothing(.., cScratchSize) (DirectSound.cpp:53)
+	CrossoverCoefficients(cfg.sample_rate, cfg.split_f1, cfg.split_f2, cfg.split_f3, r->coef); // Filter.Prepare(sampleRate, {}) (:83)
+	const uint32_t N = cfg.num_sources, C = cfg.source_channels, L = cfg.output_channels;
+	const size_t nsc = r->numSC;
+	auto alloc = [&](float** p, size_t floats) { return cudaMalloc(reinterpret_cast<void**>(p), floats * sizeof(float)) == cudaSuccess; };
+	bool ok = alloc(&r->state, nsc * kStateFloats) && alloc(&r->curMix, nsc * L) && alloc(&r->tgtDelay, nsc) && alloc(&r->tgtBand, nsc * 4) && alloc(&r->tgtMix, nsc * L)
+		&& alloc(&r->rings, nsc * ring) && alloc(&r->partial, size_t(r->numCTAs) * r->maxFrames * L) && alloc(&r->deviceBus, size_t(r->maxFrames) * L)
+		&& alloc(&r->stageIn, nsc * r->maxFrames) && alloc(&r->stageBus, size_t(r->maxFrames) * L) && alloc(&r->stageParams, size_t(N) * (5 + size_t(C) * L));
+	if (!ok) { cudaGetLastError(); FreeRenderer(r); delete r; return Fail(ctx, JPLG_ERR_OUT_OF_MEMORY, "jplg_renderer_create: device allocation failed (rings need num_sources*channels*ring_size*4 bytes)"); }
+	JPLG_CUDA_TRY(ctx, cudaMemsetAsync(r->state, 0, nsc * kStateFloats * 4, ctx->stream));
+	JPLG_CUDA_TRY(ctx, cudaMemsetAsync(r->rings, 0, nsc * ring * 4, ctx->stream));
+	JPLG_CUDA_TRY(ctx, cudaMemsetAsync(r->tgtDelay, 0, nsc * 4, ctx->stream));
+	JPLG_CUDA_TRY(ctx, cudaMemsetAsync(r->tgtMix, 0, nsc * L * 4, ctx->stream));
+	JPLG_CUDA_TRY(ctx, cudaMemsetAsync(r->deviceBus, 0, size_t(r->maxFrames) * L * 4, ctx->stream));
+	k_fill<<<static_cast<uint32_t>((nsc * 4 + 255) / 256), 256, 0, ctx->stream>>>(r->tgtBand, nsc * 4, 1.0f); ctx->launches++;
+	jplg_status st = RendererUpdateLocked(r, band_gains, delay_seconds, mix_maps, JPLG_MEM_HOST);
+	if (st != JPLG_OK) { FreeRenderer(r); delete r; return st; }
+	k_init_current<<<(r->numSC + 127) / 128, 128, 0, ctx->stream>>>(r->numSC, L, r->tgtBand, r->tgtDelay, r->tgtMix, r->state, r->curMix); ctx->launches++;
+	JPLG_CUDA_TRY(ctx, cudaGetLastError());
+	JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	*out = r;
+	return JPLG_OK;
+}
+
+void jplg_renderer_destroy(jplg_renderer r)
+{
+	if (!r) return;
+	cudaSetDevice(r->ctx->device);
+	cudaStreamSynchronize(r->ctx->stream);
+	FreeRenderer(r);
+	delete r;
+}
+
+jplg_status jplg_renderer_update(jplg_renderer r, const float* band_gains, const float* delay_seconds, const float* mix_maps, int32_t mem)
+{
+	if (!r) return JPLG_ERR_INVALID_ARGUMENT;
+	JPLG_NEED_DEVICE(r->ctx);
+	std::lock_guard<std::mutex> lk(r->ctx->mtx);
+	cudaSetDevice(r->ctx->device);
+	return RendererUpdateLocked(r, band_gains, delay_seconds, mix_maps, mem);
+}
+
+static jplg_status ProcessBlock(jplg_renderer r, const float* in, float* bus, float* perSource, uint32_t frames, int32_t mem)
+{
+	if (!r || (frames && (!in || !bus))) return JPLG_ERR_INVALID_ARGUMENT;
+	jplg_context ctx = r->ctx;
+	JPLG_NEED_DEVICE(ctx);
+	if (frames == 0) return JPLG_OK;
+	if (frames > r->maxFrames) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "process_block: frames exceeds max_block_frames");
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	const uint32_t N = r->cfg.num_sources, C = r->cfg.source_channels, L = r->cfg.output_channels;
+	const float* dIn = in; float* dBus = bus; float* dPer = perSource;
+	const size_t perFloats = size_t(N) * frames * L;
+	if (mem == JPLG_MEM_HOST)
+	{
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(r->stageIn, in, size_t(N) * frames * C * 4, cudaMemcpyHostToDevice, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(r->stageBus, bus, size_t(frames) * L * 4, cudaMemcpyHostToDevice, ctx->stream));
+		dIn = r->stageIn; dBus = r->stageBus;
+		if (perSource)
+		{
+			if (perFloats > r->stagePerSourceFloats)
+			{
+				JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+				if (r->stagePerSource) cudaFree(r->stagePerSource);
+				r->stagePerSource = nullptr; r->stagePerSourceFloats = 0;
+				if (cudaMalloc(reinterpret_cast<void**>(&r->stagePerSource), perFloats * 4) != cudaSuccess) { cudaGetLastError(); return Fail(ctx, JPLG_ERR_OUT_OF_MEMORY, "per-source debug buffer allocation failed"); }
+				r->stagePerSourceFloats = perFloats;
+			}
+			dPer = r->stagePerSource;
+		}
+	}
+	RenderParams rp{};
+	rp.numSC = r->numSC; rp.srcChannels = C; rp.L = L; rp.ringSize = r->ringSize; rp.ringMask = r->ringSize - 1; rp.pos = r->pos; rp.frames = frames;
+	rp.alpha = r->alpha; std::memcpy(rp.coef, r->coef, sizeof(rp.coef));
+	rp.state = r->state; rp.curMix = r->curMix; rp.tgtDelay = r->tgtDelay; rp.tgtBand = r->tgtBand; rp.tgtMix = r->tgtMix; rp.rings = r->rings;
+	rp.in = dIn; rp.partial = r->partial; rp.perSource = dPer; rp.numCTAs = r->numCTAs;
+	JPLG_CUDA_TRY(ctx, LaunchPush(rp, ctx->stream)); ctx->launches++;
+	JPLG_CUDA_TRY(ctx, LaunchRender(rp, r->cfg.mode, ctx->stream)); ctx->launches++;
+	JPLG_CUDA_TRY(ctx, LaunchBusReduce(rp, r->deviceBus, dBus, ctx->stream)); ctx->launches++;
+	r->pos += frames;
+	if (mem == JPLG_MEM_HOST)
+	{
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(bus, dBus, size_t(frames) * L * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		if (perSource) JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(perSource, dPer, perFloats * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	}
+	return JPLG_OK;
+}
+
+jplg_status jplg_renderer_process_block(jplg_renderer r, const float* in, float* bus, uint32_t frames, int32_t mem)
+{
+	return ProcessBlock(r, in, bus, nullptr, frames, mem);
+}
+jplg_status jplg_renderer_process_block_debug(jplg_renderer r, const float* in, float* bus, float* per_source, uint32_t frames, int32_t mem)
+{
+	if (!per_source) return JPLG_ERR_INVALID_ARGUMENT;
+	return ProcessBlock(r, in, bus, per_source, frames, mem);
+}
+float* jplg_renderer_device_bus(jplg_renderer r) { return r ? r->deviceBus : nullptr; }
+uint32_t jplg_renderer_ring_size(jplg_renderer r) { return r ? r->ringSize : 0; }
+
+jplg_status jplg_renderer_state_export(jplg_renderer r, float* state, float* rings, uint64_t* ring_pos)
+{
+	if (!r || !state) return JPLG_ERR_INVALID_ARGUMENT;
+	jplg_context ctx = r->ctx;
+	JPLG_NEED_DEVICE(ctx);
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	void* blob; jplg_status st = Scratch(ctx, 2, size_t(r->numSC) * 64 * 4, &blob); if (st) return st;
+	k_state_export<<<static_cast<uint32_t>((size_t(r->numSC) * 64 + 255) / 256), 256, 0, ctx->stream>>>(r->state, r->curMix, r->numSC, r->cfg.output_channels, static_cast<float*>(blob)); ctx->launches++;
+	JPLG_CUDA_TRY(ctx, cudaGetLastError());
+	JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(state, blob, size_t(r->numSC) * 64 * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	if (rings) JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(rings, r->rings, size_t(r->numSC) * r->ringSize * 4, cudaMemcpyDeviceToHost, ctx->stream));
+	JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	if (ring_pos) *ring_pos = r->pos;
+	return JPLG_OK;
+}
+jplg_status jplg_renderer_state_import(jplg_renderer r, const float* state, const float* rings, uint64_t ring_pos)
+{
+	if (!r || !state) return JPLG_ERR_INVALID_ARGUMENT;
+	jplg_context ctx = r->ctx;
+	JPLG_NEED_DEVICE(ctx);
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	void* blob; jplg_status st = Scratch(ctx, 2, size_t(r->numSC) * 64 * 4, &blob); if (st) return st;
+	JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(blob, state, size_t(r->numSC) * 64 * 4, cudaMemcpyHostToDevice, ctx->stream));
+	k_state_import<<<static_cast<uint32_t>((size_t(r->numSC) * 64 + 255) / 256), 256, 0, ctx->stream>>>(r->state, r->curMix, r->numSC, r->cfg.output_channels, static_cast<const float*>(blob)); ctx->launches++;
+	JPLG_CUDA_TRY(ctx, cudaGetLastError());
+	if (rings) JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(r->rings, rings, size_t(r->numSC) * r->ringSize * 4, cudaMemcpyHostToDevice, ctx->stream));
+	JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	r->pos = ring_pos;
+	return JPLG_OK;
+}
+
+} // extern "C"
+
+//==================================================================================================
+// Components
+struct jplg_crossover_bank_t { jplg_context ctx; uint32_t n; int mode; float coef[27]; float* state; };
+struct jplg_delay_bank_t { jplg_context ctx; uint32_t n, ringSize; uint64_t pos; float* rings; float* y1; };
+
+extern "C" {
+
+jplg_status jplg_crossover_bank_create(jplg_context ctx, uint32_t n, float sample_rate, float f1, float f2, float f3, int32_t mode, jplg_crossover_bank* out)
+{
+	if (!ctx || !out || n == 0 || !(sample_rate > 0.0f)) return JPLG_ERR_INVALID_ARGUMENT;
+	*out = nullptr;
+	auto* b = new jplg_crossover_bank_t{ ctx, n, mode, {}, nullptr };
+	if (f1 == 0.0f) f1 = 176.0f; if (f2 == 0.0f) f2 = 775.0f; if (f3 == 0.0f) f3 = 3408.0f;
+	CrossoverCoefficients(sample_rate, f1, f2, f3, b->coef);
+	if (ctx->device >= 0)
+	{
+		cudaSetDevice(ctx->device);
+		if (cudaMalloc(reinterpret_cast<void**>(&b->state), size_t(n) * 24 * 4) != cudaSuccess) { cudaGetLastError(); delete b; return Fail(ctx, JPLG_ERR_OUT_OF_MEMORY, "crossover bank allocation failed"); }
+		cudaMemsetAsync(b->state, 0, size_t(n) * 24 * 4, ctx->stream);
+	}
+	*out = b;
+	return JPLG_OK;
+}
+void jplg_crossover_bank_destroy(jplg_crossover_bank b)
+{
+	if (!b) return;
+	if (b->state) { cudaSetDevice(b->ctx->device); cudaStreamSynchronize(b->ctx->stream); cudaFree(b->state); }
+	delete b;
+}
+jplg_status jplg_crossover_bank_reset(jplg_crossover_bank b)
+{
+	if (!b) return JPLG_ERR_INVALID_ARGUMENT;
+	JPLG_NEED_DEVICE(b->ctx);
+	cudaSetDevice(b->ctx->device);
+	JPLG_CUDA_TRY(b->ctx, cudaMemsetAsync(b->state, 0, size_t(b->n) * 24 * 4, b->ctx->stream));
+	return JPLG_OK;
+}
+void jplg_crossover_bank_coeffs(jplg_crossover_bank b, float out[27]) { if (b && out) std::memcpy(out, b->coef, sizeof(b->coef)); }
+
+jplg_status jplg_crossover_bank_process_ramp(jplg_crossover_bank b, const float* in, const float* start_gains, const float* end_gains, float* out, uint32_t frames, int32_t mem)
+{
+	if (!b || !in || !start_gains || !end_gains || !out) return JPLG_ERR_INVALID_ARGUMENT;
+	jplg_context ctx = b->ctx;
+	JPLG_NEED_DEVICE(ctx);
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	const size_t nf = size_t(b->n) * frames;
+	const float *dIn = in, *dG0 = start_gains, *dG1 = end_gains; float* dOut = out;
+	if (mem == JPLG_MEM_HOST)
+	{
+		void *a, *g, *o;
+		jplg_status st = Scratch(ctx, 0, nf * 4, &a); if (st) return st;
+		st = Scratch(ctx, 1, size_t(b->n) * 8 * 4, &g); if (st) return st;
+		st = Scratch(ctx, 2, nf * 4, &o); if (st) return st;
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(a, in, nf * 4, cudaMemcpyHostToDevice, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(g, start_gains, size_t(b->n) * 16, cudaMemcpyHostToDevice, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(static_cast<float*>(g) + size_t(b->n) * 4, end_gains, size_t(b->n) * 16, cudaMemcpyHostToDevice, ctx->stream));
+		dIn = static_cast<float*>(a); dG0 = static_cast<float*>(g); dG1 = dG0 + size_t(b->n) * 4; dOut = static_cast<float*>(o);
+	}
+	XoverParams xp{}; xp.n = b->n; xp.frames = frames; std::memcpy(xp.coef, b->coef, sizeof(xp.coef)); xp.state = b->state;
+	JPLG_CUDA_TRY(ctx, LaunchXoverRamp(xp, dIn, dG0, dG1, dOut, b->mode, ctx->stream)); ctx->launches++;
+	if (mem == JPLG_MEM_HOST)
+	{
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(out, dOut, nf * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	}
+	return JPLG_OK;
+}
+
+jplg_status jplg_crossover_bank_split(jplg_crossover_bank b, const float* in, float* out_bands, uint32_t frames, int32_t mem)
+{
+	if (!b || !in || !out_bands) return JPLG_ERR_INVALID_ARGUMENT;
+	jplg_context ctx = b->ctx;
+	JPLG_NEED_DEVICE(ctx);
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	const size_t nf = size_t(b->n) * frames;
+	const float* dIn = in; float* dOut = out_bands;
+	if (mem == JPLG_MEM_HOST)
+	{
+		void *a, *o;
+		jplg_status st = Scratch(ctx, 0, nf * 4, &a); if (st) return st;
+		st = Scratch(ctx, 2, nf * 16, &o); if (st) return st;
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(a, in, nf * 4, cudaMemcpyHostToDevice, ctx->stream));
+		dIn = static_cast<float*>(a); dOut = static_cast<float*>(o);
+	}
+	XoverParams xp{}; xp.n = b->n; xp.frames = frames; std::memcpy(xp.coef, b->coef, sizeof(xp.coef)); xp.state = b->state;
+	JPLG_CUDA_TRY(ctx, LaunchXoverSplit(xp, dIn, dOut, b->mode, ctx->stream)); ctx->launches++;
+	if (mem == JPLG_MEM_HOST)
+	{
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(out_bands, dOut, nf * 16, cudaMemcpyDeviceToHost, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	}
+	return JPLG_OK;
+}
+
+jplg_status jplg_delay_bank_create(jplg_context ctx, uint32_t n, uint32_t min_size, jplg_delay_bank* out)
+{
+	if (!ctx || !out || n == 0) return JPLG_ERR_INVALID_ARGUMENT;
+	*out = nullptr;
+	JPLG_NEED_DEVICE(ctx);
+	uint32_t ring = 1; while (ring < min_size) ring <<= 1; // std::bit_ceil (inc/Utilities/AbstractIndex.h:235)
+	cudaSetDevice(ctx->device);
+	auto* b = new jplg_delay_bank_t{ ctx, n, ring, 0, nullptr, nullptr };
+	if (cudaMalloc(reinterpret_cast<void**>(&b->rings), size_t(n) * ring * 4) != cudaSuccess || cudaMalloc(reinterpret_cast<void**>(&b->y1), size_t(n) * 4) != cudaSuccess)
+	{
+		cudaGetLastError(); if (b->rings) cudaFree(b->rings); delete b;
+		return Fail(ctx, JPLG_ERR_OUT_OF_MEMORY, "delay bank allocation failed");
+	}
+	cudaMemsetAsync(b->rings, 0, size_t(n) * ring * 4, ctx->stream);
+	cudaMemsetAsync(b->y1, 0, size_t(n) * 4, ctx->stream);
+	*out = b;
+	return JPLG_OK;
+}
+void jplg_delay_bank_destroy(jplg_delay_bank b)
+{
+	if (!b) return;
+	cudaSetDevice(b->ctx->device); cudaStreamSynchronize(b->ctx->stream);
+	cudaFree(b->rings); cudaFree(b->y1);
+	delete b;
+}
+uint32_t jplg_delay_bank_size(jplg_delay_bank b) { return b ? b->ringSize : 0; }
+jplg_status jplg_delay_bank_clear(jplg_delay_bank b)
+{
+	if (!b) return JPLG_ERR_INVALID_ARGUMENT;
+	JPLG_NEED_DEVICE(b->ctx);
+	cudaSetDevice(b->ctx->device);
+	JPLG_CUDA_TRY(b->ctx, cudaMemsetAsync(b->rings, 0, size_t(b->n) * b->ringSize * 4, b->ctx->stream));
+	b->pos = 0; // mIndex.Reset()
+	return JPLG_OK;
+}
+jplg_status jplg_delay_bank_push(jplg_delay_bank b, const float* in, uint32_t frames, int32_t mem)
+{
+	if (!b || (frames && !in)) return JPLG_ERR_INVALID_ARGUMENT;
+	jplg_context ctx = b->ctx;
+	JPLG_NEED_DEVICE(ctx);
+	if (frames == 0) return JPLG_OK;
+	if (frames > b->ringSize) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "delay_bank_push: frames exceeds ring size");
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	const float* dIn = in;
+	if (mem == JPLG_MEM_HOST)
+	{
+		void* a; jplg_status st = Scratch(ctx, 0, size_t(b->n) * frames * 4, &a); if (st) return st;
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(a, in, size_t(b->n) * frames * 4, cudaMemcpyHostToDevice, ctx->stream));
+		dIn = static_cast<float*>(a);
+	}
+	JPLG_CUDA_TRY(ctx, LaunchDelayPush(b->rings, b->n, b->ringSize, b->pos, dIn, frames, ctx->stream)); ctx->launches++;
+	b->pos += frames;
+	if (mem == JPLG_MEM_HOST) JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	return JPLG_OK;
+}
+jplg_status jplg_delay_bank_read(jplg_delay_bank b, const float* delays, uint32_t taps, int32_t interp, float* out, int32_t mem)
+{
+	if (!b || (taps && (!delays || !out)) || interp < 0 || interp > 2) return JPLG_ERR_INVALID_ARGUMENT;
+	jplg_context ctx = b->ctx;
+	JPLG_NEED_DEVICE(ctx);
+	if (taps == 0) return JPLG_OK;
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	const size_t nt = size_t(b->n) * taps;
+	const float* dDelays = delays; float* dOut = out;
+	if (mem == JPLG_MEM_HOST)
+	{
+		void *a, *o;
+		jplg_status st = Scratch(ctx, 0, nt * 4, &a); if (st) return st;
+		st = Scratch(ctx, 1, nt * 4, &o); if (st) return st;
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(a, delays, nt * 4, cudaMemcpyHostToDevice, ctx->stream));
+		dDelays = static_cast<float*>(a); dOut = static_cast<float*>(o);
+	}
+	JPLG_CUDA_TRY(ctx, LaunchDelayRead(b->rings, b->n, b->ringSize, b->pos, dDelays, taps, interp, b->y1, dOut, ctx->stream)); ctx->launches++;
+	if (mem == JPLG_MEM_HOST)
+	{
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(out, dOut, nt * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	}
+	return JPLG_OK;
+}
+
+jplg_status jplg_mix_add_and_apply_gain_ramp(jplg_context ctx, float* dest, const float* source, uint32_t n, uint32_t dest_channel, uint32_t source_channel,
+											 uint32_t dest_num_channels, uint32_t source_num_channels, uint32_t frames, const float* gain_start, const float* gain_end, int32_t mem)
+{
+	if (!ctx || !dest || !source || !gain_start || !gain_end || dest_channel >= dest_num_channels || source_channel >= source_num_channels) return JPLG_ERR_INVALID_ARGUMENT;
+	JPLG_NEED_DEVICE(ctx);
+	if (n == 0 || frames == 0) return JPLG_OK;
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	const size_t nd = size_t(n) * frames * dest_num_channels, ns = size_t(n) * frames * source_num_channels;
+	float* dDest = dest; const float* dSrc = source; const float *dG0 = gain_start, *dG1 = gain_end;
+	if (mem == JPLG_MEM_HOST)
+	{
+		void *a, *s, *g;
+		jplg_status st = Scratch(ctx, 0, nd * 4, &a); if (st) return st;
+		st = Scratch(ctx, 1, ns * 4, &s); if (st) return st;
+		st = Scratch(ctx, 2, size_t(n) * 8, &g); if (st) return st;
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(a, dest, nd * 4, cudaMemcpyHostToDevice, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(s, source, ns * 4, cudaMemcpyHostToDevice, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(g, gain_start, size_t(n) * 4, cudaMemcpyHostToDevice, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(static_cast<float*>(g) + n, gain_end, size_t(n) * 4, cudaMemcpyHostToDevice, ctx->stream));
+		dDest = static_cast<float*>(a); dSrc = static_cast<float*>(s); dG0 = static_cast<float*>(g); dG1 = dG0 + n;
+	}
+	JPLG_CUDA_TRY(ctx, LaunchMixRamp(dDest, dSrc, n, dest_channel, source_channel, dest_num_channels, source_num_channels, frames, dG0, dG1, ctx->stream)); ctx->launches++;
+	if (mem == JPLG_MEM_HOST)
+	{
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(dest, dDest, nd * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	}
+	return JPLG_OK;
+}
+
+jplg_status jplg_mix_apply_gain(jplg_context ctx, float* dest, uint32_t n, uint32_t frames, const float* gains, int32_t mem)
+{
+	if (!ctx || !dest || !gains) return JPLG_ERR_INVALID_ARGUMENT;
+	JPLG_NEED_DEVICE(ctx);
+	if (n == 0 || frames == 0) return JPLG_OK;
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	const size_t nd = size_t(n) * frames;
+	float* dDest = dest; const float* dG = gains;
+	if (mem == JPLG_MEM_HOST)
+	{
+		void *a, *g;
+		jplg_status st = Scratch(ctx, 0, nd * 4, &a); if (st) return st;
+		st = Scratch(ctx, 1, size_t(n) * 4, &g); if (st) return st;
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(a, dest, nd * 4, cudaMemcpyHostToDevice, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(g, gains, size_t(n) * 4, cudaMemcpyHostToDevice, ctx->stream));
+		dDest = static_cast<float*>(a); dG = static_cast<float*>(g);
+	}
+	JPLG_CUDA_TRY(ctx, LaunchApplyGain(dDest, n, frames, dG, ctx->stream)); ctx->launches++;
+	if (mem == JPLG_MEM_HOST)
+	{
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(dest, dDest, nd * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	}
+	return JPLG_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,91 @@
+// Internal interface between the C-ABI layer (jplg_api.cu) and the kernels.
+#pragma once
+
+#include <cstdint>
+#include <cstddef>
+#include <cuda_runtime.h>
+
+#define JPLG_MDAP_WARPS 4
+
+namespace jplg
+{
+	constexpr uint32_t kMaxChannelsDev = 32;       // VBAPBaseTraits::MAX_CHANNELS
+	constexpr uint32_t kMaxSourceChannelsDev = 8;  // MAX_SOURCE_CHANNELS
+	constexpr uint32_t kMaxAzimuthFloats = 64;
+
+	struct PannerDev
+	{
+		bool is3D = false;
+		uint32_t numChannels = 0;
+		const uint4* lut3d = nullptr;    // 65536 cells {g0,g1,g2, spk0|spk1<<8|spk2<<16} (repacked KB_983 LUT, 1 MiB, L2 resident)
+		const float* lut2d = nullptr;    // [1024][L]
+		const uint32_t* rsqTable = nullptr; // 2048-entry RSQRTPS model
+	};
+
+	struct MdapLayoutParams
+	{
+		uint32_t numChannels, numVS, numRings, samplesPerRing, halfSamples, tail;
+		float phiTerm, offsetTerm, vsWeight;
+		float quats[kMaxSourceChannelsDev][4];
+		float azSin[kMaxAzimuthFloats], azCos[kMaxAzimuthFloats];
+	};
+
+	cudaError_t LaunchPointGains(const PannerDev& p, const float* dirs, uint32_t n, float* out, cudaStream_t st);
+	cudaError_t LaunchMdap(const PannerDev& p, const MdapLayoutParams& lp, const float* params, uint32_t n, float* out, int numSMs, cudaStream_t st);
+	cudaError_t LaunchProcessVS(const PannerDev& p, const float* vs, uint32_t n, uint32_t batches, float* out, cudaStream_t st);
+
+	//======================================================================
+	// Renderer
+	constexpr uint32_t kStateFloats = 32;   // device-side DSP state floats per source-channel (JPLG_STATE_FLOATS = 64 adds the 32 current mix gains)
+	constexpr uint32_t kChunkFrames = 480;  // DirectSoundEffect::cScratchSize (inc/Auralization/DirectSound.h:90)
+
+	// state float indices (SoA: state[k * numSC + sc])
+	enum : uint32_t
+	{
+		ST_DELAY = 0,      // SmoothedValue::Current (samples)
+		ST_THIRAN_Y1 = 1,  // Thiran1stInterpolator::mY1
+		ST_FILTER = 2,     // 24 floats: X2.S1{s1,s2} X2.S2{s1,s2} X13.S1 lane0{s1,s2} lane1{s1,s2} X13.S2 lanes0..3{s1,s2} AP lanes0..3{s1,s2}
+		ST_BAND = 26,      // current band gains b1..b4 (mFilterGains)
+		ST_SPARE = 30
+	};
+
+	struct RenderParams
+	{
+		uint32_t numSC;        // source-channels = sources * channels per source
+		uint32_t srcChannels;  // channels per source (C)
+		uint32_t L;            // output channels
+		uint32_t ringSize, ringMask;
+		uint64_t pos;          // samples pushed before this block
+		uint32_t frames;
+		float alpha;           // exp smoothing coefficient for cScratchSize ticks
+		float coef[27];        // crossover coefficients (see jplg_host.hpp)
+		float* state;          // [kStateFloats][numSC]
+		float* curMix;         // [L][numSC] current channel gains (mCurrentGains)
+		const float* tgtDelay; // [numSC] target delay in samples
+		const float* tgtBand;  // [4][numSC]
+		const float* tgtMix;   // [L][numSC]
+		float* rings;          // [numSC][ringSize], sample pushed at time t lives at t & ringMask
+		const float* in;       // [numSources][frames][C]
+		float* partial;        // [numCTAs][frames][L] per-CTA partial buses
+		float* perSource;      // debug: [numSources][frames][L] or nullptr
+		uint32_t numCTAs;
+	};
+
+	uint32_t RenderNumCTAs(uint32_t numSC, uint32_t srcChannels);
+	cudaError_t LaunchPush(const RenderParams& rp, cudaStream_t st);
+	cudaError_t LaunchRender(const RenderParams& rp, int mode, cudaStream_t st);
+	// bus[frames][L] (+)= sum over CTAs of partial; also writes the plain sum to `deviceBus`
+	cudaError_t LaunchBusReduce(const RenderParams& rp, float* deviceBus, float* busAccumulate, cudaStream_t st);
+	cudaError_t LaunchStateTranspose(const float* in, float* out, uint32_t rows, uint32_t cols, cudaStream_t st);
+
+	// components
+	struct XoverParams { uint32_t n, frames; float coef[27]; float* state; /* [24][n] */ };
+	cudaError_t LaunchXoverRamp(const XoverParams& xp, const float* in, const float* g0, const float* g1, float* out, int mode, cudaStream_t st);
+	cudaError_t LaunchXoverSplit(const XoverParams& xp, const float* in, float* outBands, int mode, cudaStream_t st);
+	cudaError_t LaunchDelayPush(float* rings, uint32_t n, uint32_t ringSize, uint64_t pos, const float* in, uint32_t frames, cudaStream_t st);
+	cudaError_t LaunchDelayRead(const float* rings, uint32_t n, uint32_t ringSize, uint64_t pos, const float* delays, uint32_t taps,
+								int interp, float* thiranY1, float* out, cudaStream_t st);
+	cudaError_t LaunchMixRamp(float* dest, const float* src, uint32_t n, uint32_t destCh, uint32_t srcCh, uint32_t nDest, uint32_t nSrc,
+							  uint32_t frames, const float* g0, const float* g1, cudaStream_t st);
+	cudaError_t LaunchApplyGain(float* dest, uint32_t n, uint32_t frames, const float* gains, cudaStream_t st);
+}

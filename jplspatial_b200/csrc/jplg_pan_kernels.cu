@@ -1,0 +1,329 @@
+// K1: batched VBAP / MDAP gain evaluation for sm_100a.
+//   k_point_gains_{2d,3d}  one thread per query         (GetSpeakerGains, inc/Panning/PannerBase.h:441-445)
+//   k_mdap_3d              one warp per source           (ProcessVBAPData, PannerBase.h:486-728, 3D panner)
+//   k_mdap_2d              one warp per source           (same, 2D panner)
+//   k_process_vs           one thread per virtual-source set (ProcessVirtualSources, PannerBase.h:731-804)
+// The direction -> LUT-index arithmetic is bit-exact with the reference's SSE2 build (jplg_device_math.cuh);
+// the per-speaker accumulation is done in the reference's own order, so gains are bit-exact too.
+// Compile with -fmad=false.
+#include "jplg_kernels.hpp"
+#include "jplg_device_math.cuh"
+
+namespace jplg
+{
+	using namespace dev;
+
+	//======================================================================
+	__global__ void k_point_gains_3d(const uint4* __restrict__ lut, const float* __restrict__ dirs, uint32_t n, uint32_t L, float* __restrict__ out)
+	{
+		const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+		if (i >= n) return;
+		const float x = dirs[3 * i], y = dirs[3 * i + 1], z = dirs[3 * i + 2];
+		const uint32_t code = oct_encode_scalar(x, y, z);
+		const uint4 cell = __ldg(&lut[code]);
+		float* row = out + size_t(i) * L;
+		for (uint32_t c = 0; c < L; ++c) row[c] = 0.0f;
+		// outGains[speaker[k]] = gain[k] in slot order (inc/Panning/VBAPLUT3D.h:1001-1009)
+		const uint32_t s0 = cell.w & 0xffu, s1 = (cell.w >> 8) & 0xffu, s2 = (cell.w >> 16) & 0xffu;
+		if (s0 < L) row[s0] = u2f(cell.x);
+		if (s1 < L) row[s1] = u2f(cell.y);
+		if (s2 < L) row[s2] = u2f(cell.z);
+	}
+
+	__global__ void k_point_gains_2d(const float* __restrict__ lut, const float* __restrict__ dirs, uint32_t n, uint32_t L, float* __restrict__ out)
+	{
+		const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+		if (i >= n) return;
+		// LUTQuery2D::GainsFor (inc/Panning/VBAPLUT2D.h:193-205): zero Y, normalise (exact 1/sqrt), diamond index, copy a row
+		float x = dirs[3 * i], z = dirs[3 * i + 2];
+		const float y = 0.0f;
+		const float il = invsqrt_exact(x * x + y * y + z * z);
+		x *= il; z *= il;
+		const uint32_t pos = lut2d_pos_scalar(x, z);
+		const float* src = lut + size_t(pos) * L;
+		float* row = out + size_t(i) * L;
+		for (uint32_t c = 0; c < L; ++c) row[c] = __ldg(&src[c]);
+	}
+
+	//======================================================================
+	struct MdapCommon
+	{
+		Q4 qPan;
+		float focus, tSlerp;
+		F3 target;
+	};
+
+	__device__ __forceinline__ MdapCommon mdap_prologue(const float* __restrict__ params, uint32_t src)
+	{
+		const float* p = params + size_t(src) * 5;
+		MdapCommon m;
+		m.target = { p[0], p[1], p[2] };
+		const float focusIn = p[3], spreadIn = p[4];
+		m.focus = (focusIn == 1.0f) ? 0.9999f : focusIn;          // PannerBase.h:589
+		const float spread = (spreadIn == 0.0f) ? 0.0001f : spreadIn; // :646
+		m.tSlerp = 1.0f - spread;                                  // :648
+		m.qPan = quat_look_at_world_up(m.target);                  // :495
+		return m;
+	}
+
+	// One warp per source. Shared memory per warp: ring sin/cos (2*24 floats) + per-channel entry list (numVS*3 x {speaker,value}).
+	__global__ void __launch_bounds__(JPLG_MDAP_WARPS * 32)
+	k_mdap_3d(const uint4* __restrict__ lut, const uint32_t* __restrict__ rsqTable, MdapLayoutParams lp,
+			  const float* __restrict__ params, uint32_t n, uint32_t L, float* __restrict__ out)
+	{
+		extern __shared__ __align__(16) unsigned char smemRaw[];
+		uint32_t* sRsq = reinterpret_cast<uint32_t*>(smemRaw);                       // 2048
+		float* sAzSin = reinterpret_cast<float*>(sRsq + 2048);                        // 32 (max 24 used: halfAndTail*4 <= 16)
+		float* sAzCos = sAzSin + 32;
+		float* sWarpBase = sAzCos + 32;
+		const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+		const uint32_t entriesPerWarp = lp.numVS * 3;
+		float* sRingS = sWarpBase + warp * (48 + 2 * entriesPerWarp + 2 * kMaxChannelsDev);
+		float* sRingC = sRingS + 24;
+		uint2* sEnt = reinterpret_cast<uint2*>(sRingC + 24);
+		float* sMix = reinterpret_cast<float*>(sEnt + entriesPerWarp);               // [32] mixBuffer
+		float* sGain = sMix + kMaxChannelsDev;                                        // unused tail (kept for alignment)
+		(void)sGain;
+
+		for (uint32_t i = threadIdx.x; i < 2048; i += blockDim.x) sRsq[i] = rsqTable[i];
+		if (threadIdx.x < 32) { sAzSin[threadIdx.x] = lp.azSin[threadIdx.x]; sAzCos[threadIdx.x] = lp.azCos[threadIdx.x]; }
+		__syncthreads();
+
+		const uint32_t R = lp.numRings, H = lp.halfSamples, T = lp.tail;
+		const uint32_t packsHalf = R * H;
+		const float nChF = static_cast<float>(lp.numChannels);
+
+		for (uint32_t src = blockIdx.x * JPLG_MDAP_WARPS + warp; src < n; src += gridDim.x * JPLG_MDAP_WARPS)
+		{
+			const MdapCommon m = mdap_prologue(params, src);
+
+			// GenerateSpreadCap ring centres (inc/Panning/VBAPanning3D.h:414-448): rings in groups of 4 through the
+			// SIMD SinCos, the remaining (R & 3) rings through libm
+			if (lane < R)
+			{
+				const float capSpread = 1.0f - m.focus;
+				const float phiTermS = capSpread * lp.phiTerm;
+				const float rampv = static_cast<float>((lane & 3u) + 1u);
+				float phi = phiTermS * rampv;
+				const float delta = 4.0f * phiTermS;
+				for (uint32_t g = 0; g < (lane >> 2); ++g) phi += delta;
+				float s, c;
+				if (lane < (R & ~3u)) sincos_simd(phi, s, c); else sincos_libm(phi, s, c);
+				sRingS[lane] = s; sRingC[lane] = c;
+			}
+			if (lane < L) sMix[lane] = 0.0f;
+			__syncwarp();
+
+			float* outSrc = out + size_t(src) * lp.numChannels * L;
+
+			for (uint32_t ch = 0; ch < lp.numChannels; ++ch)
+			{
+				const Q4 qc{ lp.quats[ch][0], lp.quats[ch][1], lp.quats[ch][2], lp.quats[ch][3] };
+				const B3 basis = quat_to_basis(quat_mul(m.qPan, qc)); // PannerBase.h:593-601
+
+				for (uint32_t v = lane; v < lp.numVS; v += 32)
+				{
+					const uint32_t pack = v >> 2, l4 = v & 3u;
+					uint32_t sci, azi; bool mirror = false;
+					if (pack < packsHalf) { sci = pack / H; azi = pack - sci * H; }
+					else if (pack < 2 * packsHalf) { const uint32_t p2 = pack - packsHalf; sci = p2 / H; azi = p2 - sci * H; mirror = true; }
+					else { sci = pack - 2 * packsHalf; azi = H; }
+					(void)T;
+					const float sinPhi = sRingS[sci], cosPhi = sRingC[sci];
+					F3 d;
+					d.x = sinPhi * sAzCos[azi * 4 + l4];
+					d.y = sinPhi * sAzSin[azi * 4 + l4];
+					if (mirror) d.y = 0.0f - d.y;
+					d.z = cosPhi;
+					d = basis_transform_simd(basis, d);                 // RotateChannelCap (:895-901)
+					d = slerp_simd(sRsq, d, m.target, m.tSlerp);        // SlerpChannelCap (:904-919)
+					const uint32_t code = oct_encode_simd(d.x, d.y, d.z);
+					const uint4 cell = __ldg(&lut[code]);
+					// (vsWeight * g) * g (PannerBase.h:836-839); entry order = pack*12 + lane*3 + k = v*3 + k (:846-849)
+					const float g0 = u2f(cell.x), g1 = u2f(cell.y), g2 = u2f(cell.z);
+					sEnt[v * 3 + 0] = make_uint2(cell.w & 0xffu, f2u((lp.vsWeight * g0) * g0));
+					sEnt[v * 3 + 1] = make_uint2((cell.w >> 8) & 0xffu, f2u((lp.vsWeight * g1) * g1));
+					sEnt[v * 3 + 2] = make_uint2((cell.w >> 16) & 0xffu, f2u((lp.vsWeight * g2) * g2));
+				}
+				__syncwarp();
+				// outGains[speakers[s]] += gains[s], in entry order, per speaker == lane
+				float acc = 0.0f;
+				if (lane < L)
+				{
+					#pragma unroll 4
+					for (uint32_t e = 0; e < entriesPerWarp; ++e)
+					{
+						const uint2 en = sEnt[e];
+						if (en.x == lane) acc += u2f(en.y);
+					}
+					outSrc[ch * L + lane] = acc;          // pre-normalisation value; rescaled below
+					sMix[lane] += acc;                     // mixBuffer[i] += gains[i] (:683-686)
+				}
+				__syncwarp();
+			}
+
+			// Normalise for the number of input channels (:694-713)
+			if (lane < L)
+			{
+				const float g = sMix[lane];
+				const float norm = g > 0.0f ? invsqrt_exact(g * nChF) : 0.0f;
+				for (uint32_t ch = 0; ch < lp.numChannels; ++ch) outSrc[ch * L + lane] *= norm;
+			}
+			__syncwarp();
+		}
+	}
+
+	// 2D panner MDAP: one warp per source; lanes cover (channel, virtual source) pairs (<= 32 in total)
+	__global__ void __launch_bounds__(JPLG_MDAP_WARPS * 32)
+	k_mdap_2d(const float* __restrict__ lut, const uint32_t* __restrict__ rsqTable, MdapLayoutParams lp,
+			  const float* __restrict__ params, uint32_t n, uint32_t L, float* __restrict__ out)
+	{
+		extern __shared__ __align__(16) unsigned char smemRaw[];
+		uint32_t* sRsq = reinterpret_cast<uint32_t*>(smemRaw);
+		uint32_t* sPosBase = sRsq + 2048;
+		const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+		uint32_t* sPos = sPosBase + warp * 32;
+		for (uint32_t i = threadIdx.x; i < 2048; i += blockDim.x) sRsq[i] = rsqTable[i];
+		__syncthreads();
+
+		const uint32_t numVS = lp.numVS, packs = numVS >> 2;
+		const uint32_t toMirror = packs & ~1u, tail = packs & 1u, H = toMirror >> 1, halfAndTail = H + tail;
+		const uint32_t totalVS = numVS * lp.numChannels; // <= 32 (reference buffer capacity)
+		const float nChF = static_cast<float>(lp.numChannels);
+
+		for (uint32_t src = blockIdx.x * JPLG_MDAP_WARPS + warp; src < n; src += gridDim.x * JPLG_MDAP_WARPS)
+		{
+			const MdapCommon m = mdap_prologue(params, src);
+			if (lane < totalVS)
+			{
+				const uint32_t ch = lane / numVS, v = lane - ch * numVS;
+				const uint32_t pack = v >> 2, l4 = v & 3u;
+				// GenerateSpreadCap (inc/Panning/VBAPanning2D.h:196-246)
+				const uint32_t gpack = pack < halfAndTail ? pack : pack - halfAndTail;
+				const bool mirror = pack >= halfAndTail;
+				const float spread = 1.0f - m.focus;
+				const float phiTerm = spread * lp.phiTerm;
+				const float offset = (-spread) * lp.offsetTerm;
+				const float rampv = 0.5f + static_cast<float>(l4);
+				float phi = phiTerm * rampv + offset;
+				const float delta = 4.0f * phiTerm;
+				for (uint32_t g = 0; g < gpack; ++g) phi += delta;
+				F3 d; float s, c;
+				sincos_simd(phi, s, c);
+				d.x = mirror ? (0.0f - s) : s; d.y = 0.0f; d.z = c;
+				const Q4 qc{ lp.quats[ch][0], lp.quats[ch][1], lp.quats[ch][2], lp.quats[ch][3] };
+				const B3 basis = quat_to_basis(quat_mul(m.qPan, qc));
+				d = basis_transform_simd(basis, d);
+				d = slerp_simd(sRsq, d, m.target, m.tSlerp);
+				sPos[lane] = lut2d_pos_simd(sRsq, d.x, d.z);           // LUT2D::CartesianToLUTPosition(simd) (VBAPLUT2D.h:376-385)
+			}
+			__syncwarp();
+			float* outSrc = out + size_t(src) * lp.numChannels * L;
+			if (lane < L)
+			{
+				// ProcessVirtualSourcesImplSIMD 2D branch (PannerBase.h:852-875): per pack, per speaker: (w*g*g).reduce()
+				float mix = 0.0f;
+				float gains[kMaxSourceChannelsDev];
+				for (uint32_t ch = 0; ch < lp.numChannels; ++ch)
+				{
+					float acc = 0.0f;
+					for (uint32_t pk = 0; pk < packs; ++pk)
+					{
+						float t[4];
+						#pragma unroll
+						for (uint32_t l4 = 0; l4 < 4; ++l4)
+						{
+							const float g = __ldg(&lut[size_t(sPos[ch * numVS + pk * 4 + l4]) * L + lane]);
+							t[l4] = (lp.vsWeight * g) * g;
+						}
+						acc += (t[0] + t[1]) + (t[2] + t[3]);
+					}
+					gains[ch] = acc;
+					mix += acc;
+				}
+				const float norm = mix > 0.0f ? invsqrt_exact(mix * nChF) : 0.0f;
+				for (uint32_t ch = 0; ch < lp.numChannels; ++ch) outSrc[ch * L + lane] = gains[ch] * norm;
+			}
+			__syncwarp();
+		}
+	}
+
+	//======================================================================
+	// ProcessVirtualSources: bAccumulatePow=false path + Algo::NormalizeL2 (PannerBase.h:731-804). One thread per set.
+	__global__ void k_process_vs(const uint4* __restrict__ lut3d, const float* __restrict__ lut2d, int is3D,
+								 const float* __restrict__ vs, uint32_t n, uint32_t batches, uint32_t L, float* __restrict__ out)
+	{
+		const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+		if (b >= batches) return;
+		float* o = out + size_t(b) * L;
+		const float* v = vs + size_t(b) * n * 4;
+		for (uint32_t i = 0; i < n; ++i)
+		{
+			const float x = v[4 * i], y = v[4 * i + 1], z = v[4 * i + 2], w = v[4 * i + 3];
+			if (is3D)
+			{
+				const uint4 cell = __ldg(&lut3d[oct_encode_scalar(x, y, z)]);
+				const uint32_t s0 = cell.w & 0xffu, s1 = (cell.w >> 8) & 0xffu, s2 = (cell.w >> 16) & 0xffu;
+				if (s0 < L) o[s0] += w * u2f(cell.x);
+				if (s1 < L) o[s1] += w * u2f(cell.y);
+				if (s2 < L) o[s2] += w * u2f(cell.z);
+			}
+			else
+			{
+				float xx = x, zz = z;
+				const float il = invsqrt_exact(xx * xx + 0.0f * 0.0f + zz * zz);
+				xx *= il; zz *= il;
+				const float* row = lut2d + size_t(lut2d_pos_scalar(xx, zz)) * L;
+				for (uint32_t s = 0; s < L; ++s) o[s] += w * __ldg(&row[s]);
+			}
+		}
+		float sum2 = 0.0f;
+		for (uint32_t s = 0; s < L; ++s) sum2 = sum2 + o[s] * o[s];
+		const float inv = invsqrt_exact(sum2);
+		for (uint32_t s = 0; s < L; ++s) o[s] *= inv;
+	}
+
+	//======================================================================
+	// launchers
+	cudaError_t LaunchPointGains(const PannerDev& p, const float* dirs, uint32_t n, float* out, cudaStream_t st)
+	{
+		if (n == 0) return cudaSuccess;
+		const uint32_t block = 128, grid = (n + block - 1) / block;
+		if (p.is3D) k_point_gains_3d<<<grid, block, 0, st>>>(p.lut3d, dirs, n, p.numChannels, out);
+		else k_point_gains_2d<<<grid, block, 0, st>>>(p.lut2d, dirs, n, p.numChannels, out);
+		return cudaGetLastError();
+	}
+
+	size_t MdapSmemBytes(const PannerDev& p, const MdapLayoutParams& lp)
+	{
+		if (p.is3D) return (2048 + 64) * 4 + size_t(JPLG_MDAP_WARPS) * (48 + 2 * lp.numVS * 3 + 2 * kMaxChannelsDev) * 4;
+		return (2048 + JPLG_MDAP_WARPS * 32) * 4;
+	}
+
+	cudaError_t LaunchMdap(const PannerDev& p, const MdapLayoutParams& lp, const float* params, uint32_t n, float* out, int numSMs, cudaStream_t st)
+	{
+		if (n == 0) return cudaSuccess;
+		const size_t smem = MdapSmemBytes(p, lp);
+		uint32_t grid = (n + JPLG_MDAP_WARPS - 1) / JPLG_MDAP_WARPS;
+		const uint32_t maxGrid = static_cast<uint32_t>(numSMs) * 8u; // persistent-ish: amortise the 8 KB rsqrt table load
+		if (grid > maxGrid) grid = maxGrid;
+		if (p.is3D)
+		{
+			cudaFuncSetAttribute(k_mdap_3d, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+			k_mdap_3d<<<grid, JPLG_MDAP_WARPS * 32, smem, st>>>(p.lut3d, p.rsqTable, lp, params, n, p.numChannels, out);
+		}
+		else
+		{
+			k_mdap_2d<<<grid, JPLG_MDAP_WARPS * 32, smem, st>>>(p.lut2d, p.rsqTable, lp, params, n, p.numChannels, out);
+		}
+		return cudaGetLastError();
+	}
+
+	cudaError_t LaunchProcessVS(const PannerDev& p, const float* vs, uint32_t n, uint32_t batches, float* out, cudaStream_t st)
+	{
+		if (batches == 0) return cudaSuccess;
+		const uint32_t block = 64, grid = (batches + block - 1) / block;
+		k_process_vs<<<grid, block, 0, st>>>(p.lut3d, p.lut2d, p.is3D ? 1 : 0, vs, n, batches, p.numChannels, out);
+		return cudaGetLastError();
+	}
+}

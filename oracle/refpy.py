@@ -1,0 +1,287 @@
+"""TEST INFRASTRUCTURE — ctypes wrapper over oracle/_ref/libjplref_*.so (the unmodified reference, see
+oracle/ref/ref_harness.cpp). Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / reference arm
+may import this module; the product package never does."""
+import ctypes as C
+import os
+import numpy as np
+
+_here = os.path.dirname(os.path.abspath(__file__))
+_vp, _u32, _f32 = C.c_void_p, C.c_uint32, C.c_float
+
+
+def ref_path(variant="sse2"):
+    return os.path.join(_here, "_ref", f"libjplref_{variant}.so")
+
+
+def available(variant="sse2"):
+    return os.path.exists(ref_path(variant))
+
+
+class Ref:
+    def __init__(self, variant="sse2"):
+        self.lib = L = C.CDLL(ref_path(variant))
+        for name in ("ref_panner_create", "ref_layout_create", "ref_xover_create", "ref_delay_create", "ref_dse_create"):
+            getattr(L, name).restype = _vp
+        L.ref_panner_aperture.restype = _f32
+        L.ref_smoother_alpha.restype = _f32
+        L.ref_delay_read_int.restype = _f32
+        L.ref_delay_tap_thiran.restype = _f32
+        L.ref_delay_tap_linear.restype = _f32
+        L.ref_dse_process_batch.restype = C.c_double
+        L.ref_mdap_timed.restype = C.c_double
+        L.ref_panner_create.argtypes = [_u32]
+        L.ref_layout_create.argtypes = [_vp, _u32]
+        L.ref_xover_create.argtypes = [_f32]
+        L.ref_delay_create.argtypes = [_u32]
+        L.ref_delay_read_int.argtypes = [_vp, _u32]
+        L.ref_delay_tap_thiran.argtypes = [_vp, _f32]
+        L.ref_delay_tap_linear.argtypes = [_vp, _f32]
+        L.ref_dse_create.argtypes = [_f32, _u32, _u32, _vp, _f32, _vp]
+        L.ref_dse_update.argtypes = [_vp, _vp, _f32, _vp]
+        L.ref_dse_process.argtypes = [_vp, _vp, _vp, _u32]
+        L.ref_slerp_simd.argtypes = [_vp, _vp, _f32, _u32]
+        L.ref_smoother_run.argtypes = [_f32, _f32, _u32, _u32, _vp]
+        L.ref_add_gain_ramp.argtypes = [_vp, _vp, _u32, _u32, _u32, _u32, _u32, _f32, _f32]
+        for name in ("ref_panner_destroy", "ref_layout_destroy", "ref_xover_destroy", "ref_delay_destroy", "ref_dse_destroy",
+                     "ref_panner_ok", "ref_panner_is3d", "ref_panner_num_channels", "ref_panner_aperture", "ref_layout_ok",
+                     "ref_xover_reset", "ref_delay_size"):
+            getattr(L, name).argtypes = [_vp]
+
+    # ---- panners
+    def panner(self, mask):
+        return RefPanner(self, mask)
+
+    def triangulate(self, mask):
+        v = np.zeros((32, 3), np.float32); t = np.zeros((64, 3), np.uint8); nv = C.c_int(); nt = C.c_int()
+        ok = self.lib.ref_triangulate(_u32(mask), _vp(v.ctypes.data), C.byref(nv), _vp(t.ctypes.data), C.byref(nt))
+        if not ok:
+            return None, None
+        return v[:nv.value].copy(), t[:nt.value].copy()
+
+    # ---- math primitives (n multiple of 4 for the SIMD ones)
+    def _f(self, a):
+        return np.ascontiguousarray(a, np.float32)
+
+    def sincos(self, x):
+        x = self._f(x); s = np.empty_like(x); c = np.empty_like(x)
+        self.lib.ref_sincos(_vp(x.ctypes.data), _u32(x.size), _vp(s.ctypes.data), _vp(c.ctypes.data)); return s, c
+
+    def acos(self, x):
+        x = self._f(x); o = np.empty_like(x)
+        self.lib.ref_acos(_vp(x.ctypes.data), _u32(x.size), _vp(o.ctypes.data)); return o
+
+    def tan(self, x):
+        x = self._f(x); o = np.empty_like(x)
+        self.lib.ref_tan(_vp(x.ctypes.data), _u32(x.size), _vp(o.ctypes.data)); return o
+
+    def invsqrt(self, x):
+        x = self._f(x); a = np.empty_like(x); b = np.empty_like(x); c = np.empty_like(x)
+        self.lib.ref_invsqrt(_vp(x.ctypes.data), _u32(x.size), _vp(a.ctypes.data), _vp(b.ctypes.data), _vp(c.ctypes.data)); return a, b, c
+
+    def oct_encode_simd(self, d):
+        d = self._f(d); o = np.empty(d.shape[0], np.uint32)
+        self.lib.ref_oct_encode_simd(_vp(d.ctypes.data), _u32(d.shape[0]), _vp(o.ctypes.data)); return o
+
+    def oct_encode_scalar(self, d):
+        d = self._f(d); o = np.empty(d.shape[0], np.uint32)
+        self.lib.ref_oct_encode_scalar(_vp(d.ctypes.data), _u32(d.shape[0]), _vp(o.ctypes.data)); return o
+
+    def oct_decode_scalar(self, codes):
+        c = np.ascontiguousarray(codes, np.uint32); o = np.empty((c.size, 3), np.float32)
+        self.lib.ref_oct_decode_scalar(_vp(c.ctypes.data), _u32(c.size), _vp(o.ctypes.data)); return o
+
+    def diamond_scalar(self, xy):
+        xy = self._f(xy); o = np.empty(xy.shape[0], np.float32)
+        self.lib.ref_diamond_scalar(_vp(xy.ctypes.data), _u32(xy.shape[0]), _vp(o.ctypes.data)); return o
+
+    def from_diamond(self, p):
+        p = self._f(p); o = np.empty((p.size, 2), np.float32)
+        self.lib.ref_from_diamond(_vp(p.ctypes.data), _u32(p.size), _vp(o.ctypes.data)); return o
+
+    def slerp_simd(self, v0, v1, t):
+        v0 = self._f(v0).copy(); v1 = self._f(v1)
+        self.lib.ref_slerp_simd(_vp(v0.ctypes.data), _vp(v1.ctypes.data), _f32(t), _u32(v0.shape[0])); return v0
+
+    def quat_lookat(self, d):
+        d = self._f(d); o = np.empty((d.shape[0], 4), np.float32)
+        self.lib.ref_quat_lookat(_vp(d.ctypes.data), _u32(d.shape[0]), _vp(o.ctypes.data)); return o
+
+    def smoother_alpha(self, ticks):
+        return float(self.lib.ref_smoother_alpha(_u32(ticks)))
+
+    def smoother_run(self, cur, tgt, ticks, n):
+        o = np.empty(n, np.float32)
+        self.lib.ref_smoother_run(cur, tgt, ticks, n, o.ctypes.data); return o
+
+    def add_gain_ramp(self, dest, src, dest_ch, src_ch, n_dest, n_src, frames, g0, g1):
+        d = self._f(dest).copy(); s = self._f(src)
+        self.lib.ref_add_gain_ramp(d.ctypes.data, s.ctypes.data, dest_ch, src_ch, n_dest, n_src, frames, g0, g1); return d
+
+    def crossover(self, fs=48000.0):
+        return RefCrossover(self, fs)
+
+    def delay(self, min_size):
+        return RefDelay(self, min_size)
+
+    def dse(self, fs, n_src, n_out, band_gains, delay_seconds, mix_map):
+        return RefDSE(self, fs, n_src, n_out, band_gains, delay_seconds, mix_map)
+
+    def dse_batch_process(self, effects, inp, frames, bus, threads=1):
+        """effects: list of RefDSE; inp [N][frames*C]; bus [frames*L] accumulated. Returns seconds."""
+        arr = (_vp * len(effects))(*[e.h for e in effects])
+        x = self._f(inp)
+        return float(self.lib.ref_dse_process_batch(arr, _u32(len(effects)), _vp(x.ctypes.data), _u32(frames), _vp(bus.ctypes.data), C.c_int(threads)))
+
+    def dse_batch_update(self, effects, band, delay, mix):
+        arr = (_vp * len(effects))(*[e.h for e in effects])
+        b = self._f(band); d = self._f(delay); m = self._f(mix)
+        self.lib.ref_dse_update_batch(arr, _u32(len(effects)), _vp(b.ctypes.data), _vp(d.ctypes.data), _vp(m.ctypes.data))
+
+
+class RefPanner:
+    def __init__(self, ref, mask):
+        self.ref, self.lib = ref, ref.lib
+        self.h = _vp(self.lib.ref_panner_create(mask))
+        self.ok = bool(self.lib.ref_panner_ok(self.h))
+        self.is3d = bool(self.lib.ref_panner_is3d(self.h))
+        self.L = int(self.lib.ref_panner_num_channels(self.h)) if self.ok else 0
+        self.aperture = float(self.lib.ref_panner_aperture(self.h)) if self.ok else 0.0
+
+    def lut(self):
+        if self.is3d:
+            g = np.zeros((65536, 3), np.float32); s = np.zeros((65536, 3), np.uint8)
+            self.lib.ref_panner_lut3d(self.h, _vp(g.ctypes.data), _vp(s.ctypes.data)); return g, s
+        g = np.zeros((1024, self.L), np.float32)
+        self.lib.ref_panner_lut2d(self.h, _vp(g.ctypes.data)); return g, None
+
+    def point_gains(self, dirs):
+        d = np.ascontiguousarray(dirs, np.float32); o = np.zeros((d.shape[0], self.L), np.float32)
+        self.lib.ref_point_gains(self.h, _vp(d.ctypes.data), _u32(d.shape[0]), _vp(o.ctypes.data)); return o
+
+    def layout(self, source_mask):
+        return RefLayout(self, source_mask)
+
+    def mdap(self, layout, params, threads=0):
+        p = np.ascontiguousarray(params, np.float32); o = np.zeros((p.shape[0], layout.num_channels, self.L), np.float32)
+        if threads:
+            self.last_seconds = float(self.lib.ref_mdap_timed(self.h, layout.h, _vp(p.ctypes.data), _u32(p.shape[0]), _vp(o.ctypes.data), C.c_int(threads)))
+        else:
+            self.lib.ref_mdap(self.h, layout.h, _vp(p.ctypes.data), _u32(p.shape[0]), _vp(o.ctypes.data))
+        return o
+
+    def process_virtual_sources(self, vs):
+        v = np.ascontiguousarray(vs, np.float32); o = np.zeros(self.L, np.float32)
+        self.lib.ref_process_virtual_sources(self.h, _vp(v.ctypes.data), _u32(v.shape[0]), _vp(o.ctypes.data)); return o
+
+    def __del__(self):
+        try:
+            self.lib.ref_panner_destroy(self.h)
+        except Exception:
+            pass
+
+
+class RefLayout:
+    def __init__(self, panner, source_mask):
+        self.panner, self.lib = panner, panner.lib
+        self.h = _vp(self.lib.ref_layout_create(panner.h, source_mask))
+        self.ok = bool(self.lib.ref_layout_ok(self.h))
+        if self.ok:
+            info = (_u32 * 4)(); a, b, c = _f32(), _f32(), _f32()
+            self.lib.ref_layout_info(self.h, info, C.byref(a), C.byref(b), C.byref(c))
+            self.num_channels, self.num_virtual_sources, self.num_rings, self.samples_per_ring = [int(v) for v in info]
+            self.phi_term, self.offset_term, self.vs_weight = a.value, b.value, c.value
+
+    def groups(self):
+        q = np.zeros((self.num_channels, 4), np.float32); ids = np.zeros(self.num_channels, np.uint32)
+        self.lib.ref_layout_groups(self.h, _vp(q.ctypes.data), _vp(ids.ctypes.data)); return q, ids
+
+    def azimuth(self):
+        s = np.zeros(256, np.float32); c = np.zeros(256, np.float32)
+        n = self.lib.ref_layout_azimuth(self.h, _vp(s.ctypes.data), _vp(c.ctypes.data)); return s[:4 * n].copy(), c[:4 * n].copy()
+
+    def __del__(self):
+        try:
+            self.lib.ref_layout_destroy(self.h)
+        except Exception:
+            pass
+
+
+class RefCrossover:
+    def __init__(self, ref, fs):
+        self.lib = ref.lib
+        self.h = _vp(self.lib.ref_xover_create(fs))
+
+    def coeffs(self):
+        o = np.zeros(27, np.float32); self.lib.ref_xover_coeffs(self.h, _vp(o.ctypes.data)); return o
+
+    def reset(self):
+        self.lib.ref_xover_reset(self.h)
+
+    def process_ramp(self, x, g0, g1):
+        x = np.ascontiguousarray(x, np.float32); g0 = np.ascontiguousarray(g0, np.float32); g1 = np.ascontiguousarray(g1, np.float32); o = np.empty_like(x)
+        self.lib.ref_xover_process_ramp(self.h, _vp(x.ctypes.data), _u32(x.size), _vp(g0.ctypes.data), _vp(g1.ctypes.data), _vp(o.ctypes.data)); return o
+
+    def process_gains(self, x, g):
+        x = np.ascontiguousarray(x, np.float32); g = np.ascontiguousarray(g, np.float32); o = np.empty_like(x)
+        self.lib.ref_xover_process_gains(self.h, _vp(x.ctypes.data), _u32(x.size), _vp(g.ctypes.data), _vp(o.ctypes.data)); return o
+
+    def split(self, x):
+        x = np.ascontiguousarray(x, np.float32); o = np.empty((x.size, 4), np.float32)
+        self.lib.ref_xover_split(self.h, _vp(x.ctypes.data), _u32(x.size), _vp(o.ctypes.data)); return o
+
+    def __del__(self):
+        try:
+            self.lib.ref_xover_destroy(self.h)
+        except Exception:
+            pass
+
+
+class RefDelay:
+    def __init__(self, ref, min_size):
+        self.lib = ref.lib
+        self.h = _vp(self.lib.ref_delay_create(min_size))
+
+    def size(self):
+        return int(self.lib.ref_delay_size(self.h))
+
+    def push(self, x):
+        x = np.ascontiguousarray(x, np.float32); self.lib.ref_delay_push(self.h, _vp(x.ctypes.data), _u32(x.size))
+
+    def read_int(self, d):
+        return float(self.lib.ref_delay_read_int(self.h, int(d)))
+
+    def tap_thiran(self, d):
+        return float(self.lib.ref_delay_tap_thiran(self.h, float(d)))
+
+    def tap_linear(self, d):
+        return float(self.lib.ref_delay_tap_linear(self.h, float(d)))
+
+    def __del__(self):
+        try:
+            self.lib.ref_delay_destroy(self.h)
+        except Exception:
+            pass
+
+
+class RefDSE:
+    def __init__(self, ref, fs, n_src, n_out, band_gains, delay_seconds, mix_map):
+        self.lib = ref.lib
+        self.n_src, self.n_out = n_src, n_out
+        b = np.ascontiguousarray(band_gains, np.float32); m = np.ascontiguousarray(mix_map, np.float32)
+        self.h = _vp(self.lib.ref_dse_create(fs, n_src, n_out, b.ctypes.data, float(delay_seconds), m.ctypes.data))
+
+    def update(self, band_gains, delay_seconds, mix_map):
+        b = np.ascontiguousarray(band_gains, np.float32); m = np.ascontiguousarray(mix_map, np.float32)
+        self.lib.ref_dse_update(self.h, b.ctypes.data, float(delay_seconds), m.ctypes.data)
+
+    def process(self, inp, out, frames):
+        x = np.ascontiguousarray(inp, np.float32)
+        assert out.dtype == np.float32 and out.flags.c_contiguous
+        self.lib.ref_dse_process(self.h, x.ctypes.data, out.ctypes.data, frames)
+        return out
+
+    def __del__(self):
+        try:
+            self.lib.ref_dse_destroy(self.h)
+        except Exception:
+            pass
