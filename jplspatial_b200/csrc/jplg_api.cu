@@ -483,7 +483,7 @@ jplg_status jplg_renderer_create(jplg_context ctx, const jplg_renderer_config* c
 	uint32_t ring = cfg.ring_size;
 	if (ring == 0) { const uint32_t minSize = static_cast<uint32_t>(cfg.sample_rate * 2.0f); ring = 1; while (ring < minSize) ring <<= 1; } // std::bit_ceil (DirectSound.cpp:79)
 	if (ring & (ring - 1)) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "jplg_renderer_create: ring_size must be a power of two");
-	if (ring < 2 * cfg.max_block_frames + 4) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "jplg_renderer_create: ring_size too small for max_block_frames");
+	if (ring < TotalPushes(cfg.max_block_frames) + kChunkFrames + 4) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "jplg_renderer_create: ring_size too small for max_block_frames");
 	if (cfg.split_f1 == 0.0f) cfg.split_f1 = 176.0f;
 	if (cfg.split_f2 == 0.0f) cfg.split_f2 = 775.0f;
 	if (cfg.split_f3 == 0.0f) cfg.split_f3 = 3408.0f;
@@ -575,7 +575,7 @@ static jplg_status ProcessBlock(jplg_renderer r, const float* in, float* bus, fl
 	JPLG_CUDA_TRY(ctx, LaunchPush(rp, ctx->stream)); ctx->launches++;
 	JPLG_CUDA_TRY(ctx, LaunchRender(rp, r->cfg.mode, ctx->stream)); ctx->launches++;
 	JPLG_CUDA_TRY(ctx, LaunchBusReduce(rp, r->deviceBus, dBus, ctx->stream)); ctx->launches++;
-	r->pos += frames;
+	r->pos += TotalPushes(frames);
 	if (mem == JPLG_MEM_HOST)
 	{
 		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(bus, dBus, size_t(frames) * L * 4, cudaMemcpyDeviceToHost, ctx->stream));

@@ -55,7 +55,7 @@ namespace jplg
 		uint32_t srcChannels;  // channels per source (C)
 		uint32_t L;            // output channels
 		uint32_t ringSize, ringMask;
-		uint64_t pos;          // samples pushed before this block
+		uint64_t pos;          // ring pushes before this block
 		uint32_t frames;
 		float alpha;           // exp smoothing coefficient for cScratchSize ticks
 		float coef[27];        // crossover coefficients (see jplg_host.hpp)
@@ -72,6 +72,7 @@ namespace jplg
 	};
 
 	uint32_t RenderNumCTAs(uint32_t numSC, uint32_t srcChannels);
+	uint32_t TotalPushes(uint32_t frames); // ring pushes one block of `frames` causes (reference quirk, see k_push)
 	cudaError_t LaunchPush(const RenderParams& rp, cudaStream_t st);
 	cudaError_t LaunchRender(const RenderParams& rp, int mode, cudaStream_t st);
 	// bus[frames][L] (+)= sum over CTAs of partial; also writes the plain sum to `deviceBus`

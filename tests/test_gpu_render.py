@@ -1,0 +1,226 @@
+"""GPU parity tests for stages 2-4 (delay/Doppler read, LR4 four-band filter, gain-ramped mix) through the C-ABI
+against the unmodified reference's DirectSoundEffect (oracle/_ref, SSE2 build).
+
+Bars: per-source rendered audio BIT-EXACT in parity mode; <= 1e-5 relative per sample in throughput mode
+(tolerance |d| <= 1e-5 * max(|ref|, rms_block(ref), 1e-3)); the N-source bus (re-associated sum) against the
+reference's sequential float sum and an fp64 sum with a tolerance scaled by the sum of |terms|."""
+import numpy as np
+import pytest
+
+import jplspatial_b200 as J
+from tests import util
+
+pytestmark = pytest.mark.gpu
+FS = 48000.0
+
+
+def make_scene(N, C, L, blocks, frames, seed, integer_delays=False):
+    rng_u = lambda n, k: util.uniform01(n, seed + k)
+    sc = {}
+    sc["audio"] = util.white_noise((blocks, N, frames, C), seed + 100)
+    dist0 = 1.0 + 299.0 * rng_u(N, 1)                      # metres
+    speed = (rng_u(N, 2) * 2.0 - 1.0) * 30.0               # m/s radial
+    speed[: N // 4] = 0.0                                   # static sources
+    t = (np.arange(blocks + 1, dtype=np.float32) * np.float32(frames / FS))[:, None]
+    dist = np.maximum(dist0[None, :] + speed[None, :] * t, 0.5).astype(np.float32)
+    delay = (dist / np.float32(343.2)).astype(np.float32)  # seconds (inc/SpeedOfSound.h:32)
+    if integer_delays:
+        delay = (np.round(delay * FS) / FS).astype(np.float32)
+    sc["delay"] = delay
+    sc["band"] = (0.1 + 0.9 * rng_u((blocks + 1) * N * 4, 3)).reshape(blocks + 1, N, 4).astype(np.float32)
+    mix = rng_u((blocks + 1) * N * C * L, 4).reshape(blocks + 1, N, C * L).astype(np.float32)
+    mix[:, :, 3::7] = 0.0                                   # some silent speakers (LFE-like)
+    mix[:, N // 2:, :] = mix[0:1, N // 2:, :]               # half the sources keep constant pan
+    sc["mix"] = mix
+    return sc
+
+
+def run_reference(ref, sc, N, C, L, blocks, frames):
+    fx = [ref.dse(FS, C, L, sc["band"][0, i], float(sc["delay"][0, i]), sc["mix"][0, i]) for i in range(N)]
+    per = np.zeros((blocks, N, frames, L), np.float32)
+    bus = np.zeros((blocks, frames, L), np.float32)
+    for b in range(blocks):
+        for i in range(N):
+            fx[i].update(sc["band"][b + 1, i], float(sc["delay"][b + 1, i]), sc["mix"][b + 1, i])
+            out = np.zeros((frames, L), np.float32)
+            fx[i].process(sc["audio"][b, i], out, frames)
+            per[b, i] = out
+            bus[b] += out  # the host loop of the reference: every effect adds into the same bus, in source order
+    return per, bus
+
+
+def run_gpu(ctx, sc, N, C, L, blocks, frames, mode, debug=True, ring_size=0):
+    r = J.DirectSoundBatch(ctx, FS, N, C, L, sc["band"][0], sc["delay"][0], sc["mix"][0], ring_size=ring_size,
+                           max_block_frames=max(frames, 512), mode=mode)
+    per = np.zeros((blocks, N, frames, L), np.float32)
+    bus = np.zeros((blocks, frames, L), np.float32)
+    for b in range(blocks):
+        r.UpdateParameters(sc["band"][b + 1], sc["delay"][b + 1], sc["mix"][b + 1])
+        r.ProcessInterleaved(sc["audio"][b], bus[b], frames, per_source=per[b] if debug else None)
+    return per, bus, r
+
+
+@pytest.mark.parametrize("N,C,L,blocks,frames", [
+    (96, 1, 12, 6, 512),     # mono -> 7.1.4, BASELINE config 3 shape (small N)
+    (40, 2, 12, 4, 512),     # stereo sources
+    (33, 1, 16, 3, 512),     # -> 9.1.6, ragged CTA
+    (20, 6, 16, 3, 512),     # 5.1-style 6-channel sources (C does not divide the CTA width)
+    (17, 1, 4, 3, 100),      # short blocks (single chunk, ragged tiles)
+    (9, 1, 12, 2, 1000),     # long blocks: 480 + 480 + 40
+])
+def test_per_source_bit_exact(gpu_ctx, ref, N, C, L, blocks, frames):
+    sc = make_scene(N, C, L, blocks, frames, util.SEED + N)
+    rper, rbus = run_reference(ref, sc, N, C, L, blocks, frames)
+    gper, gbus, _ = run_gpu(gpu_ctx, sc, N, C, L, blocks, frames, J.MODE_PARITY)
+    nbad = util.count_bit_mismatch(gper, rper)
+    assert nbad == 0, f"{nbad} samples differ, max abs {np.abs(gper - rper).max()}"
+    # bus: same terms, different summation order
+    exact = rper.astype(np.float64).sum(1)
+    tol = 4.0 * np.finfo(np.float32).eps * np.abs(rper.astype(np.float64)).sum(1) + 1e-12
+    assert np.all(np.abs(gbus - exact) <= tol)
+    assert np.all(np.abs(gbus - rbus) <= 2 * tol)
+
+
+def test_integer_delays_bit_exact(gpu_ctx, ref):
+    """Static sources at exactly-integer delays ring at Nyquist without decay in the reference (Thiran a = 1,
+    SURVEY §7.3-4): only a bit-exact recurrence reproduces that."""
+    N, C, L, blocks, frames = 32, 1, 12, 5, 512
+    sc = make_scene(N, C, L, blocks, frames, util.SEED + 77, integer_delays=True)
+    rper, _ = run_reference(ref, sc, N, C, L, blocks, frames)
+    gper, _, _ = run_gpu(gpu_ctx, sc, N, C, L, blocks, frames, J.MODE_PARITY)
+    assert util.count_bit_mismatch(gper, rper) == 0
+
+
+def test_throughput_mode_tolerance(gpu_ctx, ref):
+    N, C, L, blocks, frames = 64, 1, 12, 8, 512
+    sc = make_scene(N, C, L, blocks, frames, util.SEED + 5)
+    rper, rbus = run_reference(ref, sc, N, C, L, blocks, frames)
+    gper, gbus, _ = run_gpu(gpu_ctx, sc, N, C, L, blocks, frames, J.MODE_THROUGHPUT)
+    rms = np.sqrt((rper.astype(np.float64) ** 2).mean(axis=(2, 3), keepdims=True))
+    tol = 1e-5 * np.maximum(np.maximum(np.abs(rper), rms), 1e-3)
+    err = np.abs(gper.astype(np.float64) - rper)
+    assert np.all(err <= tol), f"worst ratio {np.max(err / tol)}"
+    resid_db = 10 * np.log10((err ** 2).mean() + 1e-300)
+    assert resid_db < -100.0, resid_db
+
+
+def test_bus_without_debug_matches_debug(gpu_ctx):
+    N, C, L, blocks, frames = 300, 1, 12, 3, 512
+    sc = make_scene(N, C, L, blocks, frames, util.SEED + 9)
+    _, bus_a, _ = run_gpu(gpu_ctx, sc, N, C, L, blocks, frames, J.MODE_PARITY, debug=True)
+    _, bus_b, _ = run_gpu(gpu_ctx, sc, N, C, L, blocks, frames, J.MODE_PARITY, debug=False)
+    assert util.bits_equal(bus_a, bus_b)   # deterministic reduction tree, identical in both kernels
+    _, bus_c, _ = run_gpu(gpu_ctx, sc, N, C, L, blocks, frames, J.MODE_PARITY, debug=False)
+    assert util.bits_equal(bus_b, bus_c)   # run-to-run reproducible
+
+
+def test_bus_accumulates_into_output(gpu_ctx):
+    N, C, L, frames = 8, 1, 12, 512
+    sc = make_scene(N, C, L, 1, frames, util.SEED + 13)
+    r = J.DirectSoundBatch(gpu_ctx, FS, N, C, L, sc["band"][0], sc["delay"][0], sc["mix"][0])
+    bus0 = np.zeros((frames, L), np.float32)
+    r.ProcessInterleaved(sc["audio"][0], bus0, frames)
+    r2 = J.DirectSoundBatch(gpu_ctx, FS, N, C, L, sc["band"][0], sc["delay"][0], sc["mix"][0])
+    bus1 = np.full((frames, L), 0.25, np.float32)
+    r2.ProcessInterleaved(sc["audio"][0], bus1, frames)
+    assert util.bits_equal(bus1, (np.float32(0.25) + bus0).astype(np.float32))
+
+
+def test_state_export_import_roundtrip(gpu_ctx):
+    N, C, L, frames = 24, 2, 12, 512
+    sc = make_scene(N, C, L, 4, frames, util.SEED + 17)
+    _, busA, rA = run_gpu(gpu_ctx, sc, N, C, L, 2, frames, J.MODE_PARITY, debug=False, ring_size=4096)
+    st, rings, pos = rA.state_export(with_rings=True)
+    assert pos == 2 * 544 and st.shape  # 512-frame block = 512 + 32 ring pushes (reference chunk quirk) == (N * C, J.STATE_FLOATS)
+    rB = J.DirectSoundBatch(gpu_ctx, FS, N, C, L, sc["band"][2], sc["delay"][2], sc["mix"][2], ring_size=4096)
+    rB.state_import(st, rings, pos)
+    outA = np.zeros((frames, L), np.float32)
+    outB = np.zeros((frames, L), np.float32)
+    for r, o in ((rA, outA), (rB, outB)):
+        r.UpdateParameters(sc["band"][3], sc["delay"][3], sc["mix"][3])
+        r.ProcessInterleaved(sc["audio"][2], o, frames)
+    assert util.bits_equal(outA, outB)
+
+
+def test_crossover_bank_vs_reference(gpu_ctx, ref):
+    n, frames = 37, 700
+    x = util.white_noise((n, frames), util.SEED + 41)
+    g0 = util.uniform01(n * 4, util.SEED + 42).reshape(n, 4)
+    g1 = util.uniform01(n * 4, util.SEED + 43).reshape(n, 4)
+    bank = J.CrossoverBank(gpu_ctx, n, FS)
+    y1 = bank.ProcessBlock(x, g0, g1)
+    y2 = bank.ProcessBlock(x, g1, g0)  # state carried across calls
+    for i in range(n):
+        rc = ref.crossover(FS)
+        assert util.bits_equal(y1[i], rc.process_ramp(x[i], g0[i], g1[i]))
+        assert util.bits_equal(y2[i], rc.process_ramp(x[i], g1[i], g0[i]))
+    # CrossoverFilterTest.cpp:74-123: bands of an impulse sum back with preserved energy; split == fused path
+    bank.Reset()
+    imp = np.zeros((n, 4096), np.float32); imp[:, 0] = 1.0
+    bands = bank.SplitBlock(imp)
+    rc = ref.crossover(FS)
+    assert util.bits_equal(bands[0], rc.split(imp[0]))
+    summed = bands.sum(-1)
+    assert abs(np.sqrt((summed[0].astype(np.float64) ** 2).sum()) - 1.0) < 1e-4
+
+
+def test_delay_bank_vs_reference(gpu_ctx, ref):
+    """DelayLineTest.cpp:58-215 known answers + Thiran/linear taps against the reference DelayLine."""
+    n = 5
+    bank = J.DelayBank(gpu_ctx, n, 1000)
+    assert bank.GetSize() == 1024
+    x = util.white_noise((n, 300), util.SEED + 51)
+    bank.Push(x)
+    rd = [ref.delay(1000) for _ in range(n)]
+    for i in range(n):
+        rd[i].push(x[i])
+    # zero delay = last written sample; fixed integer delays
+    d = np.tile(np.array([0, 1, 7, 299], np.float32), (n, 1))
+    out = bank.Read(d, J.DelayBank.NEAREST)
+    assert np.array_equal(out[:, 0], x[:, -1]) and np.array_equal(out[:, 1], x[:, -2]) and np.array_equal(out[:, 3], x[:, 0])
+    # linear tap 0.25 between two samples (DelayLineTest linear tap case)
+    lin = bank.Read(np.full((n, 1), 3.25, np.float32), J.DelayBank.LINEAR)
+    for i in range(n):
+        assert np.float32(lin[i, 0]) == np.float32(rd[i].tap_linear(3.25))
+    delays = (util.uniform01(n * 64, util.SEED + 52).reshape(n, 64) * 250.0).astype(np.float32)
+    th = bank.Read(delays, J.DelayBank.THIRAN1)
+    for i in range(n):
+        r = np.array([rd[i].tap_thiran(float(v)) for v in delays[i]], np.float32)
+        assert util.bits_equal(th[i], r)
+    # wrap: push past the ring size and read across the seam
+    big = util.white_noise((n, 1500), util.SEED + 53)
+    bank.Push(big[:, :1000]); bank.Push(big[:, 1000:])
+    for i in range(n):
+        rd[i].push(big[i])
+    d2 = np.tile(np.arange(0, 1000, 37, dtype=np.float32), (n, 1))
+    o2 = bank.Read(d2, J.DelayBank.NEAREST)
+    for i in range(n):
+        assert np.array_equal(o2[i], np.array([rd[i].read_int(int(v)) for v in d2[i]], np.float32))
+
+
+def test_channel_mixing_vs_reference(gpu_ctx, ref):
+    n, frames, nd, ns = 6, 333, 12, 2
+    dest = util.white_noise((n, frames, nd), util.SEED + 61)
+    src = util.white_noise((n, frames, ns), util.SEED + 62)
+    g0 = util.uniform01(n, util.SEED + 63); g1 = util.uniform01(n, util.SEED + 64)
+    out = J.add_and_apply_gain_ramp(gpu_ctx, dest, src, 5, 1, frames, g0, g1)
+    for i in range(n):
+        r = ref.add_gain_ramp(dest[i], src[i], 5, 1, nd, ns, frames, float(g0[i]), float(g1[i]))
+        assert util.bits_equal(out[i], r)
+    flat = util.white_noise((n, frames), util.SEED + 65)
+    assert util.bits_equal(J.apply_gain(gpu_ctx, flat, g0), (flat * g0[:, None]).astype(np.float32))
+
+
+def test_empty_and_error_paths(gpu_ctx):
+    p = J.VBAPanner(gpu_ctx)
+    assert not p.Initialize(J.ChannelMask.Mono)          # single target channel (VBAPanning2D.h:133-134)
+    assert not p.Initialize(0)                            # invalid map
+    assert p.Initialize(J.ChannelMask.Quad)
+    assert p.GetSpeakerGains(np.zeros((0, 3), np.float32)).shape == (0, 4)
+    with pytest.raises(J.JplgError):
+        p.InitializeSourceLayout(J.ChannelMask.Surround_5_0_2)   # source map with top channels (PannerBase.h:196-199)
+    r = J.DirectSoundBatch(gpu_ctx, FS, 4, 1, 4)
+    bus = np.zeros((0, 4), np.float32)
+    r.ProcessInterleaved(np.zeros((4, 0, 1), np.float32), bus, 0)  # zero frames is a no-op
+    with pytest.raises(J.JplgError):
+        r.ProcessInterleaved(np.zeros((4, 4096, 1), np.float32), np.zeros((4096, 4), np.float32), 4096)  # > max_block_frames
