@@ -556,7 +556,7 @@ class DelayBank:
 
 def add_and_apply_gain_ramp(ctx, dest, source, dest_channel, source_channel, frames, gain_start, gain_end):
     """AddAndApplyGainRamp (inc/Auralization/ChannelMixing.h:89-107) for n (dest, source) pairs: dest [n, frames, nDest], source [n, frames, nSrc]"""
-    d = np.ascontiguousarray(dest, np.float32)
+    d = np.array(dest, np.float32, copy=True, order="C")  # returns the mixed copy; the caller's array is left alone
     s = np.ascontiguousarray(source, np.float32)
     g0 = np.ascontiguousarray(gain_start, np.float32)
     g1 = np.ascontiguousarray(gain_end, np.float32)
@@ -566,7 +566,7 @@ def add_and_apply_gain_ramp(ctx, dest, source, dest_channel, source_channel, fra
 
 
 def apply_gain(ctx, dest, gains):
-    d = np.ascontiguousarray(dest, np.float32)
+    d = np.array(dest, np.float32, copy=True, order="C")
     g = np.ascontiguousarray(gains, np.float32)
     ctx.check(lib.jplg_mix_apply_gain(ctx.h, d.ctypes.data, d.shape[0], d.shape[1], g.ctypes.data, MEM_HOST))
     return d
