@@ -1,0 +1,397 @@
+#!/usr/bin/env python3
+"""bench.py — headline benchmark of the B200-native many-source spatial renderer.
+
+Metric (BASELINE.json): real-time sources @ 48 kHz / 512-frame blocks -> 7.1.4.
+Workload at every N: BASELINE config 3 per GPU — 16,384 mono sources, full block render
+(MDAP gains -> Doppler fractional delay -> LR4 4-band filter -> gain-ramped mix to 7.1.4), weak scaling
+(each rank owns 16,384 sources; the only collective is the reduce of the [512 x 12] speaker bus to rank 0).
+
+One "step" = one 512-frame audio block for all sources of the job:
+    (1) jplg_panner_mdap        new pan parameters for every source   -> mix maps
+    (2) jplg_renderer_update    band gains, delays, mix maps
+    (3) jplg_renderer_process_block   push + fused render + bus reduce
+    (4) N > 1: torch.distributed.reduce(bus) over NCCL
+value = sources * (block duration / step time) = how many sources this job renders in real time.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--mode parity|throughput] [--sources S]
+  python bench.py --impl reference ...     times the reference's own CPU code (oracle/_ref) on the host cores
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FS = 48000.0
+FRAMES = 512
+L_OUT = 12
+BLOCK_S = FRAMES / FS
+SOURCES_PER_GPU = 16384
+METRIC = "real-time sources @48kHz/512-frame->7.1.4 (full block render)"
+UNIT = "sources"
+# algorithmic bytes of the fused render kernel per mono source per 512-frame block, L = 12:
+# ring read 512+2 samples, params (delay 4 + band gains 16 + mix map 48), state r/w 2*(32*4) + current mix r/w 2*48
+RENDER_BYTES_PER_SOURCE = (FRAMES + 2) * 4 + 68 + 2 * 128 + 2 * 48
+# whole step (all kernels): + input read 2048 + ring write 2176 (544 pushes, reference chunk quirk) + MDAP in/out 68
+STEP_BYTES_PER_SOURCE = RENDER_BYTES_PER_SOURCE + FRAMES * 4 + 544 * 4 + 68
+
+
+def log(*a):
+    print(*a, file=sys.stderr, flush=True)
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+        self.thread = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line)
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i", str(self.gpu), "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        if self.proc is not None:
+            time.sleep(0.15)
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+            if self.thread:
+                self.thread.join(timeout=2)
+        sm, mx, reasons = [], 0.0, set()
+        for line in self.lines:
+            s = [x.strip() for x in line.split(",")]
+            try:
+                sm.append(float(s[1])); mx = max(mx, float(s[2]))
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), s[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(name)
+            except Exception:
+                pass
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm),
+                "window": "warm-up + timed region + e2e region (100 ms period)"}
+
+
+def make_inputs(n_sources, pool, seed):
+    """Synthetic scene: white noise per source, linear trajectories (1-300 m, +-30 m/s), random band gains,
+    random pan parameters per block. `pool` distinct blocks that the steps cycle through (pool * 33.5 MB > L2)."""
+    from tests import util
+    audio = util.white_noise((pool, n_sources, FRAMES, 1), seed + 1)
+    params = np.stack([util.pan_params(n_sources, seed + 10 + k, edge=False) for k in range(pool)])
+    band = (0.1 + 0.9 * util.uniform01(pool * n_sources * 4, seed + 2)).reshape(pool, n_sources, 4).astype(np.float32)
+    dist0 = 1.0 + 299.0 * util.uniform01(n_sources, seed + 3)
+    speed = (util.uniform01(n_sources, seed + 4) * 2.0 - 1.0) * 30.0
+    t = (np.arange(pool, dtype=np.float32) * np.float32(BLOCK_S))[:, None]
+    delay = (np.maximum(dist0[None] + speed[None] * t, 0.5) / np.float32(343.2)).astype(np.float32)
+    return audio, params, band, delay
+
+
+# ------------------------------------------------------------------------------------------------
+def run_reference_arm(args, rank, world):
+    """Times the reference's own CPU implementation of the path (oracle/_ref: the unmodified reference compiled from
+    /root/reference) on the host cores, all hardware threads, on a bounded sample of the same workload."""
+    if rank != 0:
+        return
+    from oracle import refpy
+    kind = "reference"
+    if not refpy.available("sse2"):
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libjplref_sse2.so not present (reference tree absent at build time)"}))
+        return
+    cores = os.cpu_count() or 1
+    n = args.ref_sources
+    ref = refpy.Ref("sse2")
+    M = __import__("jplspatial_b200").ChannelMask
+    audio, params, band, delay = make_inputs(n, 4, 0x5EED)
+    rp = ref.panner(M.Surround_7_1_4)
+    rl = rp.layout(M.Mono)
+    mix0 = rp.mdap(rl, params[0]).reshape(n, L_OUT)
+    fx = [ref.dse(FS, 1, L_OUT, band[0, i], float(delay[0, i]), mix0[i]) for i in range(n)]
+    bus = np.zeros((FRAMES, L_OUT), np.float32)
+
+    def step(k):
+        j = k % audio.shape[0]
+        mix = rp.mdap(rl, params[j], threads=cores).reshape(n, L_OUT)
+        ref.dse_batch_update(fx, band[j], delay[j], mix)
+        bus[:] = 0
+        ref.dse_batch_process(fx, audio[j].reshape(n, -1), FRAMES, bus.reshape(-1), threads=cores)
+
+    for k in range(args.warmup):
+        step(k)
+    t0 = time.perf_counter()
+    for k in range(args.steps):
+        step(args.warmup + k)
+    dt = (time.perf_counter() - t0) / args.steps
+    value = n * BLOCK_S / dt
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "BASELINE config 3: full block render, mono sources -> 7.1.4, 48 kHz / 512 frames (MDAP gains + update + render per block)",
+                   "sources_per_step": n, "note": "bounded sample of the 16,384-source workload; value = sample sources x block duration / step time"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
+                         "sample": f"{n} mono sources x {args.steps} blocks of 512 frames, {cores} std::threads, reference SSE2 build (-O2)"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+def cpu_baseline_sample(log_fn):
+    """Bounded CPU sample for the `cpu_baseline` object of the GPU arm (rank 0, N = 1)."""
+    from oracle import refpy
+    cores = os.cpu_count() or 1
+    if refpy.available("sse2"):
+        ref = refpy.Ref("sse2")
+        kind = "reference"
+    else:
+        return None
+    import jplspatial_b200 as J
+    n, blocks = 1024, 24
+    audio, params, band, delay = make_inputs(n, 4, 0xC0FFEE)
+    rp = ref.panner(J.ChannelMask.Surround_7_1_4)
+    rl = rp.layout(J.ChannelMask.Mono)
+    mix0 = rp.mdap(rl, params[0]).reshape(n, L_OUT)
+    fx = [ref.dse(FS, 1, L_OUT, band[0, i], float(delay[0, i]), mix0[i]) for i in range(n)]
+    bus = np.zeros((FRAMES, L_OUT), np.float32)
+    t0 = time.perf_counter()
+    for k in range(blocks):
+        j = k % 4
+        mix = rp.mdap(rl, params[j], threads=cores).reshape(n, L_OUT)
+        ref.dse_batch_update(fx, band[j], delay[j], mix)
+        ref.dse_batch_process(fx, audio[j].reshape(n, -1), FRAMES, bus.reshape(-1), threads=cores)
+    dt = (time.perf_counter() - t0) / blocks
+    # single-thread figure for context
+    t1 = time.perf_counter()
+    for k in range(4):
+        ref.dse_batch_process(fx[:256], audio[k % 4, :256].reshape(256, -1), FRAMES, bus.reshape(-1), threads=1)
+    us1 = (time.perf_counter() - t1) / (4 * 256) * 1e6
+    log_fn(f"cpu baseline: {dt * 1e3:.2f} ms per {n}-source block on {cores} threads; single-thread DirectSoundEffect {us1:.1f} us/source-block")
+    return {"value": n * BLOCK_S / dt, "unit": UNIT, "cores": cores, "kind": kind,
+            "sample": f"{n} mono sources x {blocks} blocks of 512 frames (MDAP + update + render), {cores} std::threads, reference SSE2 build; "
+                      f"1-thread DirectSoundEffect = {us1:.1f} us per source-block"}
+
+
+# ------------------------------------------------------------------------------------------------
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--mode", default="parity", choices=["parity", "throughput"])
+    ap.add_argument("--sources", type=int, default=SOURCES_PER_GPU, help="sources per GPU")
+    ap.add_argument("--ring", type=int, default=0, help="ring size per source (0 = reference value bit_ceil(2*fs) = 131072)")
+    ap.add_argument("--pool", type=int, default=8, help="distinct input blocks cycled through (pool x 33.5 MB > L2)")
+    ap.add_argument("--ref-sources", type=int, default=2048)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        run_reference_arm(args, rank, world)
+        return
+
+    import torch
+    import jplspatial_b200 as J
+
+    if not torch.cuda.is_available() or J.device_count() == 0:
+        raise SystemExit("bench.py: no CUDA device — this framework has no CPU fallback (use --impl reference for the CPU reference arm)")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+        dist = dist_mod
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    N = args.sources
+    mode = J.MODE_PARITY if args.mode == "parity" else J.MODE_THROUGHPUT
+    ctx = J.Context(local_rank)
+    stream = ctx.torch_stream()
+    audio, params, band, delay = make_inputs(N, args.pool, 0xB200 + rank)
+    pan = J.VBAPanner(ctx)
+    assert pan.Initialize(J.ChannelMask.Surround_7_1_4)
+    lay = pan.InitializeSourceLayout(J.ChannelMask.Mono)
+    mix0 = pan.ProcessVBAPData(lay, params[0]).reshape(N, L_OUT)
+    rend = J.DirectSoundBatch(ctx, FS, N, 1, L_OUT, band[0], delay[0], mix0, ring_size=args.ring, max_block_frames=FRAMES, mode=mode)
+    dev = torch.device("cuda", local_rank)
+
+    with torch.cuda.stream(stream):
+        d_audio = torch.from_numpy(audio).to(dev)
+        d_params = torch.from_numpy(params).to(dev)
+        d_band = torch.from_numpy(band).to(dev)
+        d_delay = torch.from_numpy(delay).to(dev)
+        d_mix = torch.empty((N, 1, L_OUT), dtype=torch.float32, device=dev)
+        d_bus = torch.zeros((FRAMES, L_OUT), dtype=torch.float32, device=dev)
+    ctx.synchronize()
+
+    def step_device(k):
+        j = k % args.pool
+        with torch.cuda.stream(stream):
+            pan.ProcessVBAPData(lay, d_params[j], out=d_mix)
+            rend.UpdateParameters(d_band[j], d_delay[j], d_mix)
+            d_bus.zero_()
+            rend.ProcessInterleaved(d_audio[j], d_bus, FRAMES)
+            if dist is not None:
+                dist.reduce(d_bus, dst=0)
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing (`value`)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    for k in range(args.warmup):
+        step_device(k)
+    barrier()
+    ctx.set_kernel_timing(True)
+    ctx.reset_kernel_timing()
+    launches0 = ctx.launch_count
+    ev0 = torch.cuda.Event(enable_timing=True)
+    ev1 = torch.cuda.Event(enable_timing=True)
+    barrier()
+    with torch.cuda.stream(stream):
+        ev0.record(stream)
+    for k in range(args.steps):
+        step_device(args.warmup + k)
+    with torch.cuda.stream(stream):
+        ev1.record(stream)
+    barrier()
+    ms_total = ev0.elapsed_time(ev1)
+    launches = ctx.launch_count - launches0  # our kernels only (torch's bus zero-fill and NCCL are not counted)
+    ktimes = {name: ctx.kernel_time(name) for name in ("mdap", "update", "push", "render", "bus_reduce")}
+    ctx.set_kernel_timing(False)
+    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if dist is not None:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_step = float(t.item()) / args.steps
+    value = N * world * BLOCK_S / (ms_step * 1e-3)
+
+    # ---- end to end through the C-ABI with HOST (pinned) buffers: H2D of the step's inputs and D2H of the bus inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        def pinned(a):
+            t_ = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+            return t_, t_.numpy()
+        keep = []
+        h_audio, h_params, h_band, h_delay = [], [], [], []
+        for j in range(args.pool):
+            for src, dst in ((audio[j], h_audio), (params[j], h_params), (band[j], h_band), (delay[j], h_delay)):
+                tt, nn = pinned(src); keep.append(tt); dst.append(nn)
+        tt, h_mix = pinned(np.zeros((N, 1, L_OUT), np.float32)); keep.append(tt)
+        tt, h_bus = pinned(np.zeros((FRAMES, L_OUT), np.float32)); keep.append(tt)
+        d_partial = torch.zeros((FRAMES, L_OUT), dtype=torch.float32, device=dev)
+
+        def step_host(k):
+            j = k % args.pool
+            pan.ProcessVBAPData(lay, h_params[j], out=h_mix)          # H2D params, D2H mix maps
+            rend.UpdateParameters(h_band[j], h_delay[j], h_mix)        # H2D
+            h_bus[:] = 0.0
+            rend.ProcessInterleaved(h_audio[j], h_bus, FRAMES)         # H2D audio + bus, D2H bus
+            if dist is not None:
+                d_partial.copy_(torch.from_numpy(h_bus))
+                dist.reduce(d_partial, dst=0)
+                if rank == 0:
+                    h_bus[:] = d_partial.cpu().numpy()
+            return float(h_bus[0, 0])
+
+        e2e_steps = max(10, min(args.steps, 50))
+        for k in range(3):
+            step_host(k)
+        barrier()
+        t0 = time.perf_counter()
+        for k in range(e2e_steps):
+            step_host(3 + k)
+        barrier()
+        dt = (time.perf_counter() - t0) / e2e_steps
+        tt2 = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if dist is not None:
+            dist.all_reduce(tt2, op=dist.ReduceOp.MAX)
+        dt = float(tt2.item())
+        h2d = N * FRAMES * 4 + N * 20 + N * 16 + N * 4 + N * L_OUT * 4 + FRAMES * L_OUT * 4
+        d2h = N * L_OUT * 4 + FRAMES * L_OUT * 4
+        e2e = {"value": N * world * BLOCK_S / dt, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+               "ms_per_step": dt * 1e3, "steps": e2e_steps}
+
+    clocks = sampler.stop()
+    if rank != 0:
+        if dist is not None:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (k_render), measured live with CUDA events on the launching stream
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak = float(json.load(open(peaks_path))["hbm_gbs"]); peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak = 6650.0; peak_src = "fallback (B200_PROFILING.md)"
+    r_ms, r_n = ktimes["render"]
+    r_avg_ms = r_ms / max(r_n, 1)
+    achieved = RENDER_BYTES_PER_SOURCE * N / (r_avg_ms * 1e-3) / 1e9
+    ncu_traffic = None
+    tpath = os.path.join(ROOT, "profiles", "render_traffic.json")
+    if os.path.exists(tpath):
+        try:
+            ncu_traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
+        except Exception:
+            pass
+    roofline = {"bound": "hbm", "kernel": "k_render", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                "traffic": ncu_traffic, "peak_source": peak_src, "avg_launch_ms": r_avg_ms,
+                "algorithmic_bytes_per_launch": RENDER_BYTES_PER_SOURCE * N,
+                "whole_step_gbs": STEP_BYTES_PER_SOURCE * N / (ms_step * 1e-3) / 1e9,
+                "note": "fused render is FP32-issue bound (~200 FP32 ops/sample in parity mode), not HBM bound: see DESIGN.md §5",
+                "kernel_ms_per_step": {k: v[0] / max(args.steps, 1) for k, v in ktimes.items()}}
+
+    cpu = None
+    if not args.no_cpu_baseline and world == 1:
+        try:
+            cpu = cpu_baseline_sample(log)
+        except Exception as e:  # the checker is optional at bench time
+            log("cpu baseline failed:", e)
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "BASELINE config 3: full block render, 16,384 mono sources per GPU -> 7.1.4, 48 kHz / 512 frames "
+                               "(MDAP gains + update + push + fused delay/LR4/mix + bus reduce per block)",
+                   "sources_per_gpu": N, "total_sources": N * world, "mode": args.mode, "ring_size": rend.ring_size,
+                   "l2_policy": f"inputs larger than L2: {args.pool} distinct 33.5 MB input blocks cycled, {N * rend.ring_size * 4 / 2**30:.1f} GiB of rings",
+                   "parallelism": f"sources sharded over {world} GPU(s); NCCL reduce of the [512x12] bus" if world > 1 else "single GPU"},
+        "clocks": clocks, "gpu_launches": launches, "e2e": e2e, "roofline": roofline, "cpu_baseline": cpu,
+    }
+    print(json.dumps(line))
+    if dist is not None:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -41,6 +41,9 @@ _sig("jplg_context_stream", _vp, [_vp])
 _sig("jplg_context_synchronize", _i32, [_vp])
 _sig("jplg_context_rsqrt_model_verified", _i32, [_vp])
 _sig("jplg_context_launch_count", _u64, [_vp])
+_sig("jplg_context_set_kernel_timing", None, [_vp, _i32])
+_sig("jplg_context_reset_kernel_timing", None, [_vp])
+_sig("jplg_context_kernel_time", _i32, [_vp, _i32, C.POINTER(C.c_double), C.POINTER(_u64)])
 _sig("jplg_channel_map_num_channels", _u32, [_u32])
 _sig("jplg_channel_map_has_lfe", _i32, [_u32])
 _sig("jplg_channel_map_has_top_channels", _i32, [_u32])
@@ -245,6 +248,20 @@ class Context:
     @property
     def launch_count(self):
         return int(lib.jplg_context_launch_count(self.h))
+
+    KERNELS = {"push": 0, "render": 1, "bus_reduce": 2, "mdap": 3, "point_gains": 4, "update": 5, "other": 6}
+
+    def set_kernel_timing(self, enabled):
+        lib.jplg_context_set_kernel_timing(self.h, 1 if enabled else 0)
+
+    def reset_kernel_timing(self):
+        lib.jplg_context_reset_kernel_timing(self.h)
+
+    def kernel_time(self, name):
+        """-> (total milliseconds, launches) of one of KERNELS since the last reset (CUDA events on the context stream)"""
+        ms, cnt = C.c_double(), _u64()
+        self.check(lib.jplg_context_kernel_time(self.h, self.KERNELS[name], C.byref(ms), C.byref(cnt)))
+        return ms.value, int(cnt.value)
 
     def close(self):
         if self.h:

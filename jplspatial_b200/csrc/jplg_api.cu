@@ -29,7 +29,49 @@ struct jplg_context_t
 	void* scratch[4] = { nullptr, nullptr, nullptr, nullptr };
 	size_t scratchBytes[4] = { 0, 0, 0, 0 };
 	std::mutex mtx;
+	// optional per-kernel timing (CUDA events on the launching stream)
+	struct Timed { int which; cudaEvent_t a, b; };
+	bool timing = false;
+	std::vector<Timed> pending;
+	std::vector<cudaEvent_t> freeEvents;
+	double totalMs[JPLG_K_COUNT] = {};
+	uint64_t counts[JPLG_K_COUNT] = {};
 };
+
+static void TimeBegin(jplg_context ctx, int which)
+{
+	if (!ctx->timing) return;
+	cudaEvent_t ev[2];
+	for (auto& e : ev)
+	{
+		if (!ctx->freeEvents.empty()) { e = ctx->freeEvents.back(); ctx->freeEvents.pop_back(); }
+		else cudaEventCreate(&e);
+	}
+	cudaEventRecord(ev[0], ctx->stream);
+	ctx->pending.push_back({ which, ev[0], ev[1] });
+}
+static void TimeEnd(jplg_context ctx)
+{
+	if (!ctx->timing || ctx->pending.empty()) return;
+	cudaEventRecord(ctx->pending.back().b, ctx->stream);
+}
+static void TimeCollect(jplg_context ctx)
+{
+	if (ctx->pending.empty()) return;
+	cudaStreamSynchronize(ctx->stream);
+	for (auto& t : ctx->pending)
+	{
+		float ms = 0.0f;
+		if (cudaEventElapsedTime(&ms, t.a, t.b) == cudaSuccess) { ctx->totalMs[t.which] += ms; ctx->counts[t.which]++; }
+		else cudaGetLastError();
+		ctx->freeEvents.push_back(t.a); ctx->freeEvents.push_back(t.b);
+	}
+	ctx->pending.clear();
+}
+// launch + count + (optionally) time one kernel
+#define JPLG_LAUNCH(ctx, which, expr) do { TimeBegin((ctx), (which)); cudaError_t _le = (expr); TimeEnd((ctx)); (ctx)->launches++; \
+	if ((ctx)->timing && (ctx)->pending.size() > 4096) TimeCollect((ctx)); \
+	if (_le != cudaSuccess) { (ctx)->sticky = true; return Fail((ctx), JPLG_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_le)); } } while (0)
 
 static jplg_status Fail(jplg_context ctx, jplg_status st, const std::string& msg)
 {
@@ -101,6 +143,8 @@ void jplg_context_destroy(jplg_context ctx)
 	{
 		cudaSetDevice(ctx->device);
 		if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+		TimeCollect(ctx);
+		for (auto& e : ctx->freeEvents) cudaEventDestroy(e);
 		for (auto& s : ctx->scratch) if (s) cudaFree(s);
 		if (ctx->dRsq) cudaFree(ctx->dRsq);
 		if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -117,6 +161,33 @@ jplg_status jplg_context_synchronize(jplg_context ctx)
 }
 int32_t jplg_context_rsqrt_model_verified(jplg_context ctx) { return ctx && ctx->rsqVerified ? 1 : 0; }
 uint64_t jplg_context_launch_count(jplg_context ctx) { return ctx ? ctx->launches : 0; }
+void jplg_context_set_kernel_timing(jplg_context ctx, int32_t enabled)
+{
+	if (!ctx || ctx->device < 0) return;
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	if (!enabled) TimeCollect(ctx);
+	ctx->timing = enabled != 0;
+}
+void jplg_context_reset_kernel_timing(jplg_context ctx)
+{
+	if (!ctx || ctx->device < 0) return;
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	TimeCollect(ctx);
+	for (int i = 0; i < JPLG_K_COUNT; ++i) { ctx->totalMs[i] = 0.0; ctx->counts[i] = 0; }
+}
+jplg_status jplg_context_kernel_time(jplg_context ctx, int32_t which, double* total_ms, uint64_t* launches)
+{
+	if (!ctx || which < 0 || which >= JPLG_K_COUNT) return JPLG_ERR_INVALID_ARGUMENT;
+	JPLG_NEED_DEVICE(ctx);
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	TimeCollect(ctx);
+	if (total_ms) *total_ms = ctx->totalMs[which];
+	if (launches) *launches = ctx->counts[which];
+	return JPLG_OK;
+}
 
 //==================================================================================================
 uint32_t jplg_channel_map_num_channels(uint32_t mask) { return NumChannels(mask); }
@@ -256,7 +327,7 @@ jplg_status jplg_panner_point_gains(jplg_panner p, const float* dirs, uint32_t n
 		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(a, dirs, size_t(n) * 3 * 4, cudaMemcpyHostToDevice, ctx->stream));
 		dDirs = static_cast<float*>(a); dOut = static_cast<float*>(b);
 	}
-	JPLG_CUDA_TRY(ctx, LaunchPointGains(p->dev, dDirs, n, dOut, ctx->stream)); ctx->launches++;
+	JPLG_LAUNCH(ctx, JPLG_K_POINT_GAINS, LaunchPointGains(p->dev, dDirs, n, dOut, ctx->stream));
 	if (mem == JPLG_MEM_HOST)
 	{
 		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(out, dOut, size_t(n) * L * 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -331,7 +402,7 @@ jplg_status jplg_panner_mdap(jplg_panner p, jplg_source_layout l, const float* p
 		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(a, params, size_t(n) * 5 * 4, cudaMemcpyHostToDevice, ctx->stream));
 		dParams = static_cast<float*>(a); dOut = static_cast<float*>(b);
 	}
-	JPLG_CUDA_TRY(ctx, LaunchMdap(p->dev, l->lp, dParams, n, dOut, ctx->numSMs, ctx->stream)); ctx->launches++;
+	JPLG_LAUNCH(ctx, JPLG_K_MDAP, LaunchMdap(p->dev, l->lp, dParams, n, dOut, ctx->numSMs, ctx->stream));
 	if (mem == JPLG_MEM_HOST)
 	{
 		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(out, dOut, outFloats * 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -359,7 +430,7 @@ jplg_status jplg_panner_process_virtual_sources(jplg_panner p, const float* vs, 
 		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(b, out, size_t(batches) * L * 4, cudaMemcpyHostToDevice, ctx->stream)); // accumulated into
 		dVs = static_cast<float*>(a); dOut = static_cast<float*>(b);
 	}
-	JPLG_CUDA_TRY(ctx, LaunchProcessVS(p->dev, dVs, n, batches, dOut, ctx->stream)); ctx->launches++;
+	JPLG_LAUNCH(ctx, JPLG_K_OTHER, LaunchProcessVS(p->dev, dVs, n, batches, dOut, ctx->stream));
 	if (mem == JPLG_MEM_HOST)
 	{
 		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(out, dOut, size_t(batches) * L * 4, cudaMemcpyDeviceToHost, ctx->stream));
@@ -462,7 +533,9 @@ static jplg_status RendererUpdateLocked(jplg_renderer r, const float* band, cons
 		if (delay) { JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(base + size_t(N) * 4, delay, size_t(N) * 4, cudaMemcpyHostToDevice, ctx->stream)); dDelay = base + size_t(N) * 4; }
 		if (mix) { JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(base + size_t(N) * 5, mix, size_t(N) * C * L * 4, cudaMemcpyHostToDevice, ctx->stream)); dMix = base + size_t(N) * 5; }
 	}
+	TimeBegin(ctx, JPLG_K_UPDATE);
 	k_update_targets<<<(r->numSC + 127) / 128, 128, 0, ctx->stream>>>(dBand, dDelay, dMix, r->numSC, C, L, r->cfg.sample_rate, r->tgtBand, r->tgtDelay, r->tgtMix);
+	TimeEnd(ctx);
 	JPLG_CUDA_TRY(ctx, cudaGetLastError()); ctx->launches++;
 	if (mem == JPLG_MEM_HOST) JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream)); // host buffers are caller-owned: safe to reuse on return
 	return JPLG_OK;
@@ -572,9 +645,9 @@ static jplg_status ProcessBlock(jplg_renderer r, const float* in, float* bus, fl
 	rp.alpha = r->alpha; std::memcpy(rp.coef, r->coef, sizeof(rp.coef));
 	rp.state = r->state; rp.curMix = r->curMix; rp.tgtDelay = r->tgtDelay; rp.tgtBand = r->tgtBand; rp.tgtMix = r->tgtMix; rp.rings = r->rings;
 	rp.in = dIn; rp.partial = r->partial; rp.perSource = dPer; rp.numCTAs = r->numCTAs;
-	JPLG_CUDA_TRY(ctx, LaunchPush(rp, ctx->stream)); ctx->launches++;
-	JPLG_CUDA_TRY(ctx, LaunchRender(rp, r->cfg.mode, ctx->stream)); ctx->launches++;
-	JPLG_CUDA_TRY(ctx, LaunchBusReduce(rp, r->deviceBus, dBus, ctx->stream)); ctx->launches++;
+	JPLG_LAUNCH(ctx, JPLG_K_PUSH, LaunchPush(rp, ctx->stream));
+	JPLG_LAUNCH(ctx, JPLG_K_RENDER, LaunchRender(rp, r->cfg.mode, ctx->stream));
+	JPLG_LAUNCH(ctx, JPLG_K_BUS_REDUCE, LaunchBusReduce(rp, r->deviceBus, dBus, ctx->stream));
 	r->pos += TotalPushes(frames);
 	if (mem == JPLG_MEM_HOST)
 	{
