@@ -23,11 +23,13 @@ void orc_sincos(const float* x, uint32_t n, float* s, float* c);          /* inc
 void orc_acos(const float* x, uint32_t n, float* out);                     /* :667-714 */
 void orc_tan(const float* x, uint32_t n, float* out);                      /* :617-665 */
 void orc_invsqrt_nr1(const float* x, uint32_t n, float* out);              /* inc/Math/SIMD.h:1700-1790 (RSQRTPS + 1 Newton step) */
+void orc_invsqrt_nr2(const float* x, uint32_t n, float* out);              /* same, 2 Newton steps (Math::InvSqrt simd) */
 void orc_oct_encode_simd(const float* dirs, uint32_t n, uint32_t* out);    /* inc/Math/DirectionEncoding.h:346-386 */
 void orc_oct_encode_scalar(const float* dirs, uint32_t n, uint32_t* out);  /* :292-343 */
 void orc_oct_decode_scalar(const uint32_t* codes, uint32_t n, float* out); /* :389-436 */
+void orc_diamond_scalar(const float* xy, uint32_t n, float* out);          /* :197-209 */
 void orc_from_diamond(const float* p, uint32_t n, float* outXY);           /* :212-227 */
-void orc_slerp_simd(float* v0, const float* v1, float t, uint32_t n);      /* inc/Math/Vec3Math.h:206-307 */
+void orc_slerp_simd(float* v0, const float* v1, float t, uint32_t n);      /* inc/Math/Vec3Math.h:206-307; v0 [n][3] in/out, v1 ONE target [3] */
 void orc_quat_lookat(const float* dirs, uint32_t n, float* out);           /* inc/Math/MinimalQuat.h:84-144 */
 
 /* ---- panner (inc/Panning/*) */
