@@ -4,7 +4,9 @@
 #include "jplg_host.hpp"
 #include "jplg_kernels.hpp"
 
+#include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstdio>
 #include <cstring>
 #include <mutex>
@@ -36,10 +38,21 @@ struct jplg_context_t
 	std::vector<cudaEvent_t> freeEvents;
 	double totalMs[JPLG_K_COUNT] = {};
 	uint64_t counts[JPLG_K_COUNT] = {};
+	// host-path pipelining (JPLG_MEM_HOST process_block): slices of sources are copied / pushed / rendered on auxiliary streams
+	// so the PCIe transfer of slice k+1 overlaps the render of slice k. Created on first use.
+	static constexpr int kAux = 4, kMaxSlices = 16;
+	cudaStream_t aux[kAux] = {};
+	cudaEvent_t evStart = nullptr, evCopied[kMaxSlices] = {}, evDone[kAux] = {};
+	bool auxReady = false;
+	// 0 (default): single stream (copy, then compute); 1: sliced DMA + concurrent slices; 2: like 1, but pinned input is read in place by k_push (zero-copy).
+	// Measured at 16,384 sources (r01b): process_block 797 / 818 / 1072 us for modes 0 / 1 / 2 against a 610 us PCIe floor (55 GB/s): the render of the
+	// last slice is as long as the render of the whole block (latency-bound per warp), so slicing only hides ~100 us and its event traffic costs as much.
+	int hostPipeline = 0;
 };
 
-static void TimeBegin(jplg_context ctx, int which)
+static void TimeBegin(jplg_context ctx, int which, cudaStream_t onStream = nullptr)
 {
+	const cudaStream_t ts = onStream ? onStream : ctx->stream;
 	if (!ctx->timing) return;
 	cudaEvent_t ev[2];
 	for (auto& e : ev)
@@ -47,18 +60,19 @@ static void TimeBegin(jplg_context ctx, int which)
 		if (!ctx->freeEvents.empty()) { e = ctx->freeEvents.back(); ctx->freeEvents.pop_back(); }
 		else cudaEventCreate(&e);
 	}
-	cudaEventRecord(ev[0], ctx->stream);
+	cudaEventRecord(ev[0], ts);
 	ctx->pending.push_back({ which, ev[0], ev[1] });
 }
-static void TimeEnd(jplg_context ctx)
+static void TimeEnd(jplg_context ctx, cudaStream_t onStream = nullptr)
 {
 	if (!ctx->timing || ctx->pending.empty()) return;
-	cudaEventRecord(ctx->pending.back().b, ctx->stream);
+	cudaEventRecord(ctx->pending.back().b, onStream ? onStream : ctx->stream);
 }
 static void TimeCollect(jplg_context ctx)
 {
 	if (ctx->pending.empty()) return;
 	cudaStreamSynchronize(ctx->stream);
+	if (ctx->auxReady) for (auto& a : ctx->aux) cudaStreamSynchronize(a);
 	for (auto& t : ctx->pending)
 	{
 		float ms = 0.0f;
@@ -69,7 +83,8 @@ static void TimeCollect(jplg_context ctx)
 	ctx->pending.clear();
 }
 // launch + count + (optionally) time one kernel
-#define JPLG_LAUNCH(ctx, which, expr) do { TimeBegin((ctx), (which)); cudaError_t _le = (expr); TimeEnd((ctx)); (ctx)->launches++; \
+#define JPLG_LAUNCH(ctx, which, expr) JPLG_LAUNCH_ON(ctx, which, nullptr, expr)
+#define JPLG_LAUNCH_ON(ctx, which, onStream, expr) do { TimeBegin((ctx), (which), (onStream)); cudaError_t _le = (expr); TimeEnd((ctx), (onStream)); (ctx)->launches++; \
 	if ((ctx)->timing && (ctx)->pending.size() > 4096) TimeCollect((ctx)); \
 	if (_le != cudaSuccess) { (ctx)->sticky = true; return Fail((ctx), JPLG_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_le)); } } while (0)
 
@@ -123,6 +138,7 @@ jplg_status jplg_context_create(int32_t device, jplg_context* out)
 		if (!sBuilt) { sVerified = BuildRsqrtTable(sTable); sBuilt = true; }
 	}
 	ctx->rsqVerified = sVerified;
+	if (const char* hp = std::getenv("JPLG_HOST_PIPELINE")) ctx->hostPipeline = std::atoi(hp); // measurement knob: 0 / 1 / 2 (see jplg_context_t)
 	if (device < 0) { ctx->device = -1; *out = ctx; return JPLG_OK; }
 	if (device >= jplg_device_count()) { delete ctx; if (gTrace) gTrace("jplg_context_create: no such CUDA device"); return JPLG_ERR_NO_DEVICE; }
 	ctx->device = device;
@@ -145,6 +161,13 @@ void jplg_context_destroy(jplg_context ctx)
 		if (ctx->stream) cudaStreamSynchronize(ctx->stream);
 		TimeCollect(ctx);
 		for (auto& e : ctx->freeEvents) cudaEventDestroy(e);
+		if (ctx->auxReady)
+		{
+			for (auto& a : ctx->aux) { cudaStreamSynchronize(a); cudaStreamDestroy(a); }
+			cudaEventDestroy(ctx->evStart);
+			for (auto& e : ctx->evCopied) cudaEventDestroy(e);
+			for (auto& e : ctx->evDone) cudaEventDestroy(e);
+		}
 		for (auto& s : ctx->scratch) if (s) cudaFree(s);
 		if (ctx->dRsq) cudaFree(ctx->dRsq);
 		if (ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -610,6 +633,17 @@ jplg_status jplg_renderer_update(jplg_renderer r, const float* band_gains, const
 	return RendererUpdateLocked(r, band_gains, delay_seconds, mix_maps, mem);
 }
 
+static jplg_status EnsureAux(jplg_context ctx)
+{
+	if (ctx->auxReady) return JPLG_OK;
+	for (auto& a : ctx->aux) JPLG_CUDA_TRY(ctx, cudaStreamCreateWithFlags(&a, cudaStreamNonBlocking));
+	JPLG_CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->evStart, cudaEventDisableTiming));
+	for (auto& e : ctx->evCopied) JPLG_CUDA_TRY(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+	for (auto& e : ctx->evDone) JPLG_CUDA_TRY(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+	ctx->auxReady = true;
+	return JPLG_OK;
+}
+
 static jplg_status ProcessBlock(jplg_renderer r, const float* in, float* bus, float* perSource, uint32_t frames, int32_t mem)
 {
 	if (!r || (frames && (!in || !bus))) return JPLG_ERR_INVALID_ARGUMENT;
@@ -622,9 +656,10 @@ static jplg_status ProcessBlock(jplg_renderer r, const float* in, float* bus, fl
 	const uint32_t N = r->cfg.num_sources, C = r->cfg.source_channels, L = r->cfg.output_channels;
 	const float* dIn = in; float* dBus = bus; float* dPer = perSource;
 	const size_t perFloats = size_t(N) * frames * L;
+	const bool pipelinedHost = mem == JPLG_MEM_HOST && ctx->hostPipeline > 0 && r->numCTAs >= 32 && !perSource;
 	if (mem == JPLG_MEM_HOST)
 	{
-		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(r->stageIn, in, size_t(N) * frames * C * 4, cudaMemcpyHostToDevice, ctx->stream));
+		if (!pipelinedHost) JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(r->stageIn, in, size_t(N) * frames * C * 4, cudaMemcpyHostToDevice, ctx->stream));
 		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(r->stageBus, bus, size_t(frames) * L * 4, cudaMemcpyHostToDevice, ctx->stream));
 		dIn = r->stageIn; dBus = r->stageBus;
 		if (perSource)
@@ -645,8 +680,50 @@ static jplg_status ProcessBlock(jplg_renderer r, const float* in, float* bus, fl
 	rp.alpha = r->alpha; std::memcpy(rp.coef, r->coef, sizeof(rp.coef));
 	rp.state = r->state; rp.curMix = r->curMix; rp.tgtDelay = r->tgtDelay; rp.tgtBand = r->tgtBand; rp.tgtMix = r->tgtMix; rp.rings = r->rings;
 	rp.in = dIn; rp.partial = r->partial; rp.perSource = dPer; rp.numCTAs = r->numCTAs;
-	JPLG_LAUNCH(ctx, JPLG_K_PUSH, LaunchPush(rp, ctx->stream));
-	JPLG_LAUNCH(ctx, JPLG_K_RENDER, LaunchRender(rp, r->cfg.mode, ctx->stream));
+	const uint32_t srcPerCTA = RenderSourcesPerCTA(C);
+	// ---- host path, pipelined: slices of CTAs; the transfer of slice k+1 overlaps push + render of slice k on other streams
+	uint32_t numSlices = 1;
+	if (pipelinedHost) numSlices = 8;
+	if (numSlices > 1)
+	{
+		jplg_status ast = EnsureAux(ctx); if (ast != JPLG_OK) return ast;
+		bool zeroCopy = false;
+		if (ctx->hostPipeline == 2)
+		{
+			cudaPointerAttributes pa{};
+			if (cudaPointerGetAttributes(&pa, in) == cudaSuccess && pa.type == cudaMemoryTypeHost && pa.devicePointer != nullptr) { zeroCopy = true; rp.in = static_cast<const float*>(pa.devicePointer); }
+			else cudaGetLastError();
+		}
+		JPLG_CUDA_TRY(ctx, cudaEventRecord(ctx->evStart, ctx->stream));
+		for (auto& a : ctx->aux) JPLG_CUDA_TRY(ctx, cudaStreamWaitEvent(a, ctx->evStart, 0));
+		const uint32_t ctasPerSlice = (r->numCTAs + numSlices - 1) / numSlices;
+		for (uint32_t k = 0; k < numSlices; ++k)
+		{
+			const uint32_t c0 = k * ctasPerSlice, c1 = std::min(r->numCTAs, c0 + ctasPerSlice);
+			if (c0 >= c1) break;
+			const uint32_t s0 = c0 * srcPerCTA, s1 = std::min(N, c1 * srcPerCTA);
+			cudaStream_t cs = ctx->aux[1 + k % (jplg_context_t::kAux - 1)];
+			if (!zeroCopy)
+			{
+				// the (re-issued) staged copy of this slice runs on the copy stream aux[0]; the first, whole-block copy above is skipped
+				JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(r->stageIn + size_t(s0) * frames * C, in + size_t(s0) * frames * C, size_t(s1 - s0) * frames * C * 4, cudaMemcpyHostToDevice, ctx->aux[0]));
+				JPLG_CUDA_TRY(ctx, cudaEventRecord(ctx->evCopied[k], ctx->aux[0]));
+				JPLG_CUDA_TRY(ctx, cudaStreamWaitEvent(cs, ctx->evCopied[k], 0));
+			}
+			JPLG_LAUNCH_ON(ctx, JPLG_K_PUSH, cs, LaunchPush(rp, s0, s1 - s0, cs));
+			JPLG_LAUNCH_ON(ctx, JPLG_K_RENDER, cs, LaunchRender(rp, r->cfg.mode, c0, c1 - c0, cs));
+		}
+		for (int a = 1; a < jplg_context_t::kAux; ++a)
+		{
+			JPLG_CUDA_TRY(ctx, cudaEventRecord(ctx->evDone[a], ctx->aux[a]));
+			JPLG_CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, ctx->evDone[a], 0));
+		}
+	}
+	else
+	{
+		JPLG_LAUNCH(ctx, JPLG_K_PUSH, LaunchPush(rp, 0, N, ctx->stream));
+		JPLG_LAUNCH(ctx, JPLG_K_RENDER, LaunchRender(rp, r->cfg.mode, 0, r->numCTAs, ctx->stream));
+	}
 	JPLG_LAUNCH(ctx, JPLG_K_BUS_REDUCE, LaunchBusReduce(rp, r->deviceBus, dBus, ctx->stream));
 	r->pos += TotalPushes(frames);
 	if (mem == JPLG_MEM_HOST)

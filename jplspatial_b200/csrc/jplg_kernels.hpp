@@ -69,12 +69,14 @@ namespace jplg
 		float* partial;        // [numCTAs][frames][L] per-CTA partial buses
 		float* perSource;      // debug: [numSources][frames][L] or nullptr
 		uint32_t numCTAs;
+		uint32_t ctaBase;      // first CTA of this launch (set by LaunchRender)
 	};
 
 	uint32_t RenderNumCTAs(uint32_t numSC, uint32_t srcChannels);
 	uint32_t TotalPushes(uint32_t frames); // ring pushes one block of `frames` causes (reference quirk, see k_push)
-	cudaError_t LaunchPush(const RenderParams& rp, cudaStream_t st);
-	cudaError_t LaunchRender(const RenderParams& rp, int mode, cudaStream_t st);
+	uint32_t RenderSourcesPerCTA(uint32_t srcChannels);
+	cudaError_t LaunchPush(const RenderParams& rp, uint32_t srcBegin, uint32_t srcCount, cudaStream_t st);
+	cudaError_t LaunchRender(const RenderParams& rp, int mode, uint32_t ctaBegin, uint32_t ctaCount, cudaStream_t st);
 	// bus[frames][L] (+)= sum over CTAs of partial; also writes the plain sum to `deviceBus`
 	cudaError_t LaunchBusReduce(const RenderParams& rp, float* deviceBus, float* busAccumulate, cudaStream_t st);
 	cudaError_t LaunchStateTranspose(const float* in, float* out, uint32_t rows, uint32_t cols, cudaStream_t st);

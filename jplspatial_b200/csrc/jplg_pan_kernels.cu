@@ -1,6 +1,6 @@
 // K1: batched VBAP / MDAP gain evaluation for sm_100a.
 //   k_point_gains_{2d,3d}  one thread per query         (GetSpeakerGains, inc/Panning/PannerBase.h:441-445)
-//   k_mdap_3d              one warp per source           (ProcessVBAPData, PannerBase.h:486-728, 3D panner)
+//   k_mdap_3d<G>           G = 16 or 32 lanes per source (ProcessVBAPData, PannerBase.h:486-728, 3D panner)
 //   k_mdap_2d              one warp per source           (same, 2D panner)
 //   k_process_vs           one thread per virtual-source set (ProcessVirtualSources, PannerBase.h:731-804)
 // The direction -> LUT-index arithmetic is bit-exact with the reference's SSE2 build (jplg_device_math.cuh);
@@ -66,7 +66,10 @@ namespace jplg
 		return m;
 	}
 
-	// One warp per source. Shared memory per warp: ring sin/cos (2*24 floats) + per-channel entry list (numVS*3 x {speaker,value}).
+	// G lanes per source (G = 16 when the target has <= 16 channels: two sources share a warp, which halves the cost of the
+	// speaker-ordered accumulation and wastes fewer lanes on the 72 = 4.5 x 16 virtual sources of mono -> 7.1.4; else G = 32).
+	// Shared memory per group: ring sin/cos (2*24 floats) + one 16-B entry per virtual source + mixBuffer.
+	template<int G>
 	__global__ void __launch_bounds__(JPLG_MDAP_WARPS * 32)
 	k_mdap_3d(const uint4* __restrict__ lut, const uint32_t* __restrict__ rsqTable, MdapLayoutParams lp,
 			  const float* __restrict__ params, uint32_t n, uint32_t L, float* __restrict__ out)
@@ -75,43 +78,44 @@ namespace jplg
 		uint32_t* sRsq = reinterpret_cast<uint32_t*>(smemRaw);                       // 2048
 		float* sAzSin = reinterpret_cast<float*>(sRsq + 2048);                        // 32 (max 24 used: halfAndTail*4 <= 16)
 		float* sAzCos = sAzSin + 32;
-		float* sWarpBase = sAzCos + 32;
-		const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-		const uint32_t entriesPerWarp = lp.numVS * 3;
-		float* sRingS = sWarpBase + warp * (48 + 2 * entriesPerWarp + 2 * kMaxChannelsDev);
+		float* sGroupBase = sAzCos + 32;
+		constexpr uint32_t kGroups = JPLG_MDAP_WARPS * 32 / G;
+		const uint32_t grp = threadIdx.x / G, gl = threadIdx.x % G;
+		// per group: ring sin/cos [24+24] | one 16-B entry per virtual source { spk0 | spk1<<8 | spk2<<16, v0, v1, v2 } | mixBuffer [32]
+		float* sRingS = sGroupBase + grp * (48 + 4 * lp.numVS + kMaxChannelsDev);
 		float* sRingC = sRingS + 24;
-		uint2* sEnt = reinterpret_cast<uint2*>(sRingC + 24);
-		float* sMix = reinterpret_cast<float*>(sEnt + entriesPerWarp);               // [32] mixBuffer
-		float* sGain = sMix + kMaxChannelsDev;                                        // unused tail (kept for alignment)
-		(void)sGain;
+		uint4* sEnt = reinterpret_cast<uint4*>(sRingC + 24);
+		float* sMix = reinterpret_cast<float*>(sEnt + lp.numVS);                      // [32] mixBuffer
 
 		for (uint32_t i = threadIdx.x; i < 2048; i += blockDim.x) sRsq[i] = rsqTable[i];
 		if (threadIdx.x < 32) { sAzSin[threadIdx.x] = lp.azSin[threadIdx.x]; sAzCos[threadIdx.x] = lp.azCos[threadIdx.x]; }
 		__syncthreads();
 
-		const uint32_t R = lp.numRings, H = lp.halfSamples, T = lp.tail;
+		const uint32_t R = lp.numRings, H = lp.halfSamples;
 		const uint32_t packsHalf = R * H;
 		const float nChF = static_cast<float>(lp.numChannels);
 
-		for (uint32_t src = blockIdx.x * JPLG_MDAP_WARPS + warp; src < n; src += gridDim.x * JPLG_MDAP_WARPS)
+		for (uint32_t srcBase = blockIdx.x * kGroups; srcBase < n; srcBase += gridDim.x * kGroups)
 		{
+			const bool valid = srcBase + grp < n;                       // a warp's groups run the same trip counts; the idle one only skips its stores
+			const uint32_t src = valid ? srcBase + grp : n - 1;
 			const MdapCommon m = mdap_prologue(params, src);
 
 			// GenerateSpreadCap ring centres (inc/Panning/VBAPanning3D.h:414-448): rings in groups of 4 through the
 			// SIMD SinCos, the remaining (R & 3) rings through libm
-			if (lane < R)
+			for (uint32_t r = gl; r < R; r += G)
 			{
 				const float capSpread = 1.0f - m.focus;
 				const float phiTermS = capSpread * lp.phiTerm;
-				const float rampv = static_cast<float>((lane & 3u) + 1u);
+				const float rampv = static_cast<float>((r & 3u) + 1u);
 				float phi = phiTermS * rampv;
 				const float delta = 4.0f * phiTermS;
-				for (uint32_t g = 0; g < (lane >> 2); ++g) phi += delta;
+				for (uint32_t g = 0; g < (r >> 2); ++g) phi += delta;
 				float s, c;
-				if (lane < (R & ~3u)) sincos_simd(phi, s, c); else sincos_libm(phi, s, c);
-				sRingS[lane] = s; sRingC[lane] = c;
+				if (r < (R & ~3u)) sincos_simd(phi, s, c); else sincos_libm(phi, s, c);
+				sRingS[r] = s; sRingC[r] = c;
 			}
-			if (lane < L) sMix[lane] = 0.0f;
+			if (gl < L) sMix[gl] = 0.0f;
 			__syncwarp();
 
 			float* outSrc = out + size_t(src) * lp.numChannels * L;
@@ -121,14 +125,13 @@ namespace jplg
 				const Q4 qc{ lp.quats[ch][0], lp.quats[ch][1], lp.quats[ch][2], lp.quats[ch][3] };
 				const B3 basis = quat_to_basis(quat_mul(m.qPan, qc)); // PannerBase.h:593-601
 
-				for (uint32_t v = lane; v < lp.numVS; v += 32)
+				for (uint32_t v = gl; v < lp.numVS; v += G)
 				{
 					const uint32_t pack = v >> 2, l4 = v & 3u;
 					uint32_t sci, azi; bool mirror = false;
 					if (pack < packsHalf) { sci = pack / H; azi = pack - sci * H; }
 					else if (pack < 2 * packsHalf) { const uint32_t p2 = pack - packsHalf; sci = p2 / H; azi = p2 - sci * H; mirror = true; }
 					else { sci = pack - 2 * packsHalf; azi = H; }
-					(void)T;
 					const float sinPhi = sRingS[sci], cosPhi = sRingC[sci];
 					F3 d;
 					d.x = sinPhi * sAzCos[azi * 4 + l4];
@@ -141,33 +144,34 @@ namespace jplg
 					const uint4 cell = __ldg(&lut[code]);
 					// (vsWeight * g) * g (PannerBase.h:836-839); entry order = pack*12 + lane*3 + k = v*3 + k (:846-849)
 					const float g0 = u2f(cell.x), g1 = u2f(cell.y), g2 = u2f(cell.z);
-					sEnt[v * 3 + 0] = make_uint2(cell.w & 0xffu, f2u((lp.vsWeight * g0) * g0));
-					sEnt[v * 3 + 1] = make_uint2((cell.w >> 8) & 0xffu, f2u((lp.vsWeight * g1) * g1));
-					sEnt[v * 3 + 2] = make_uint2((cell.w >> 16) & 0xffu, f2u((lp.vsWeight * g2) * g2));
+					sEnt[v] = make_uint4(cell.w & 0xffffffu, f2u((lp.vsWeight * g0) * g0), f2u((lp.vsWeight * g1) * g1), f2u((lp.vsWeight * g2) * g2));
 				}
 				__syncwarp();
-				// outGains[speakers[s]] += gains[s], in entry order, per speaker == lane
-				float acc = 0.0f;
-				if (lane < L)
+				// outGains[speakers[s]] += gains[s], in entry order, per speaker == lane. The three speakers of a cell are distinct
+				// (a triangle, the dummy replaced by an index not in it: VBAPLUT3D.h:803-815), so at most one of a cell's entries hits a lane.
+				if (gl < L)
 				{
+					float acc = 0.0f;
+					const uint32_t laneRep = gl * 0x010101u;
 					#pragma unroll 4
-					for (uint32_t e = 0; e < entriesPerWarp; ++e)
+					for (uint32_t e = 0; e < lp.numVS; ++e)
 					{
-						const uint2 en = sEnt[e];
-						if (en.x == lane) acc += u2f(en.y);
+						const uint4 en = sEnt[e];
+						const uint32_t mm = __vcmpeq4(en.x, laneRep);         // byte k = 0xff where speaker k == lane (top byte: 0 == 0, ignored)
+						if (mm & 0x00ffffffu) acc += u2f((mm & 0xffu) ? en.y : ((mm & 0xff00u) ? en.z : en.w));
 					}
-					outSrc[ch * L + lane] = acc;          // pre-normalisation value; rescaled below
-					sMix[lane] += acc;                     // mixBuffer[i] += gains[i] (:683-686)
+					if (valid) outSrc[ch * L + gl] = acc; // pre-normalisation value; rescaled below
+					sMix[gl] += acc;                       // mixBuffer[i] += gains[i] (:683-686)
 				}
 				__syncwarp();
 			}
 
 			// Normalise for the number of input channels (:694-713)
-			if (lane < L)
+			if (gl < L && valid)
 			{
-				const float g = sMix[lane];
+				const float g = sMix[gl];
 				const float norm = g > 0.0f ? invsqrt_exact(g * nChF) : 0.0f;
-				for (uint32_t ch = 0; ch < lp.numChannels; ++ch) outSrc[ch * L + lane] *= norm;
+				for (uint32_t ch = 0; ch < lp.numChannels; ++ch) outSrc[ch * L + gl] *= norm;
 			}
 			__syncwarp();
 		}
@@ -294,9 +298,12 @@ namespace jplg
 		return cudaGetLastError();
 	}
 
+	static uint32_t MdapLanesPerSource(const PannerDev& p) { return (p.is3D && p.numChannels <= 16) ? 16u : 32u; }
+
 	size_t MdapSmemBytes(const PannerDev& p, const MdapLayoutParams& lp)
 	{
-		if (p.is3D) return (2048 + 64) * 4 + size_t(JPLG_MDAP_WARPS) * (48 + 2 * lp.numVS * 3 + 2 * kMaxChannelsDev) * 4;
+		const uint32_t groups = JPLG_MDAP_WARPS * 32 / MdapLanesPerSource(p);
+		if (p.is3D) return (2048 + 64) * 4 + size_t(groups) * (48 + 4 * lp.numVS + kMaxChannelsDev) * 4;
 		return (2048 + JPLG_MDAP_WARPS * 32) * 4;
 	}
 
@@ -304,13 +311,15 @@ namespace jplg
 	{
 		if (n == 0) return cudaSuccess;
 		const size_t smem = MdapSmemBytes(p, lp);
-		uint32_t grid = (n + JPLG_MDAP_WARPS - 1) / JPLG_MDAP_WARPS;
+		const uint32_t groups = JPLG_MDAP_WARPS * 32 / MdapLanesPerSource(p);
+		uint32_t grid = (n + groups - 1) / groups;
 		const uint32_t maxGrid = static_cast<uint32_t>(numSMs) * 8u; // persistent-ish: amortise the 8 KB rsqrt table load
 		if (grid > maxGrid) grid = maxGrid;
 		if (p.is3D)
 		{
-			cudaFuncSetAttribute(k_mdap_3d, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
-			k_mdap_3d<<<grid, JPLG_MDAP_WARPS * 32, smem, st>>>(p.lut3d, p.rsqTable, lp, params, n, p.numChannels, out);
+			auto kernel = groups == JPLG_MDAP_WARPS ? k_mdap_3d<32> : k_mdap_3d<16>;
+			cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+			kernel<<<grid, JPLG_MDAP_WARPS * 32, smem, st>>>(p.lut3d, p.rsqTable, lp, params, n, p.numChannels, out);
 		}
 		else
 		{

@@ -224,3 +224,45 @@ def test_empty_and_error_paths(gpu_ctx):
     r.ProcessInterleaved(np.zeros((4, 0, 1), np.float32), bus, 0)  # zero frames is a no-op
     with pytest.raises(J.JplgError):
         r.ProcessInterleaved(np.zeros((4, 4096, 1), np.float32), np.zeros((4096, 4), np.float32), 4096)  # > max_block_frames
+
+
+@pytest.mark.parametrize("C,pipeline", [(1, 1), (2, 1), (1, 2), (1, 0)])
+def test_pipelined_host_path_equals_device_path(C, pipeline):
+    """JPLG_HOST_PIPELINE=1/2: JPLG_MEM_HOST blocks with >= 32 CTAs are rendered in slices on auxiliary streams (transfer of slice k+1 overlaps the
+    render of slice k; in mode 2 pinned input is read in place by k_push). The result must equal the single-launch device path bit for bit
+    (same CTA partials, same reduction tree), for pinned (torch) and pageable (numpy) host buffers."""
+    import os
+    import torch
+    os.environ["JPLG_HOST_PIPELINE"] = str(pipeline)
+    try:
+        ctx = J.Context(0)
+    finally:
+        del os.environ["JPLG_HOST_PIPELINE"]
+    N, L, blocks, frames = 4096 // C + 37, 12, 3, 512
+    sc = make_scene(N, C, L, blocks, frames, util.SEED + 77)
+    dev = torch.device("cuda", 0)
+
+    def make():
+        return J.DirectSoundBatch(ctx, FS, N, C, L, sc["band"][0], sc["delay"][0], sc["mix"][0], ring_size=4096, max_block_frames=512, mode=J.MODE_PARITY)
+
+    ra, rb, rc = make(), make(), make()
+    stream = ctx.torch_stream()
+    for b in range(blocks):
+        for r in (ra, rb, rc):
+            r.UpdateParameters(sc["band"][b + 1], sc["delay"][b + 1], sc["mix"][b + 1])
+        with torch.cuda.stream(stream):
+            d_in = torch.from_numpy(sc["audio"][b]).to(dev)
+            d_bus = torch.zeros((frames, L), dtype=torch.float32, device=dev)
+            ra.ProcessInterleaved(d_in, d_bus, frames)
+        ctx.synchronize()
+        want = d_bus.cpu().numpy()
+        pinned = torch.from_numpy(sc["audio"][b].copy()).pin_memory()
+        bus_p = torch.zeros((frames, L), dtype=torch.float32).pin_memory()
+        rb.ProcessInterleaved(pinned, bus_p, frames)
+        bus_n = np.zeros((frames, L), np.float32)
+        rc.ProcessInterleaved(sc["audio"][b], bus_n, frames)
+        assert np.abs(want).max() > 0
+        assert util.bits_equal(bus_p.numpy(), want), f"block {b}: pinned host path differs"
+        assert util.bits_equal(bus_n, want), f"block {b}: pageable host path differs"
+    for r in (ra, rb, rc):
+        r.close()
