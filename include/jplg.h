@@ -96,7 +96,8 @@ JPLG_API int32_t     jplg_context_rsqrt_model_verified(jplg_context ctx);
 /* number of kernels this context has launched so far (bench.py's gpu_launches) */
 JPLG_API uint64_t    jplg_context_launch_count(jplg_context ctx);
 /* Per-kernel device timing with CUDA events recorded on the context stream around each launch (measurement aid,
- * off by default). `which`: one of JPLG_K_*. kernel_time synchronises the stream and returns the accumulated
+ * off by default; `enabled`: 0 off, 1 every kernel, or (mask << 1) with mask bits (1 << JPLG_K_*) to bracket only those kernels
+ * so the events do not perturb the others). `which`: one of JPLG_K_*. kernel_time synchronises the stream and returns the accumulated
  * milliseconds and launch count since the last reset. */
 enum { JPLG_K_PUSH = 0, JPLG_K_RENDER = 1, JPLG_K_BUS_REDUCE = 2, JPLG_K_MDAP = 3, JPLG_K_POINT_GAINS = 4,
        JPLG_K_UPDATE = 5, JPLG_K_OTHER = 6, JPLG_K_COUNT = 7 };

@@ -211,8 +211,15 @@ class Context:
 
     KERNELS = {"push": 0, "render": 1, "bus_reduce": 2, "mdap": 3, "point_gains": 4, "update": 5, "other": 6}
 
-    def set_kernel_timing(self, enabled):
-        lib.jplg_context_set_kernel_timing(self.h, 1 if enabled else 0)
+    def set_kernel_timing(self, enabled, only=None):
+        """only: iterable of kernel names (see kernel_time) to bracket with events; default every kernel"""
+        if enabled and only:
+            mask = 0
+            for name in only:
+                mask |= 1 << self.KERNELS[name]
+            lib.jplg_context_set_kernel_timing(self.h, mask << 1)
+        else:
+            lib.jplg_context_set_kernel_timing(self.h, 1 if enabled else 0)
 
     def reset_kernel_timing(self):
         lib.jplg_context_reset_kernel_timing(self.h)

@@ -34,6 +34,8 @@ struct jplg_context_t
 	// optional per-kernel timing (CUDA events on the launching stream)
 	struct Timed { int which; cudaEvent_t a, b; };
 	bool timing = false;
+	bool timedThis = false;
+	uint32_t timingMask = 0;   // bit (1 << JPLG_K_*) = that kernel is bracketed by events
 	std::vector<Timed> pending;
 	std::vector<cudaEvent_t> freeEvents;
 	double totalMs[JPLG_K_COUNT] = {};
@@ -53,7 +55,8 @@ struct jplg_context_t
 static void TimeBegin(jplg_context ctx, int which, cudaStream_t onStream = nullptr)
 {
 	const cudaStream_t ts = onStream ? onStream : ctx->stream;
-	if (!ctx->timing) return;
+	if (!ctx->timing || !((ctx->timingMask >> which) & 1u)) { ctx->timedThis = false; return; }
+	ctx->timedThis = true;
 	cudaEvent_t ev[2];
 	for (auto& e : ev)
 	{
@@ -65,7 +68,7 @@ static void TimeBegin(jplg_context ctx, int which, cudaStream_t onStream = nullp
 }
 static void TimeEnd(jplg_context ctx, cudaStream_t onStream = nullptr)
 {
-	if (!ctx->timing || ctx->pending.empty()) return;
+	if (!ctx->timing || !ctx->timedThis || ctx->pending.empty()) return;
 	cudaEventRecord(ctx->pending.back().b, onStream ? onStream : ctx->stream);
 }
 static void TimeCollect(jplg_context ctx)
@@ -191,6 +194,7 @@ void jplg_context_set_kernel_timing(jplg_context ctx, int32_t enabled)
 	cudaSetDevice(ctx->device);
 	if (!enabled) TimeCollect(ctx);
 	ctx->timing = enabled != 0;
+	ctx->timingMask = enabled == 1 ? 0xffffffffu : static_cast<uint32_t>(enabled) >> 1;   // 1 = all kernels, else (mask << 1)
 }
 void jplg_context_reset_kernel_timing(jplg_context ctx)
 {
