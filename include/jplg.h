@@ -72,6 +72,8 @@ typedef struct jplg_source_layout_t* jplg_source_layout;
 typedef struct jplg_renderer_t*      jplg_renderer;
 typedef struct jplg_crossover_bank_t* jplg_crossover_bank;
 typedef struct jplg_delay_bank_t*    jplg_delay_bank;
+typedef struct jplg_reverb_bank_t*   jplg_reverb_bank;
+typedef struct jplg_erbus_bank_t*    jplg_erbus_bank;
 
 /* replaces: JPL::SpatialTrace (inc/ErrorReporting.h:44-47) */
 typedef void (*jplg_trace_fn)(const char* message);
@@ -100,7 +102,7 @@ JPLG_API uint64_t    jplg_context_launch_count(jplg_context ctx);
  * so the events do not perturb the others). `which`: one of JPLG_K_*. kernel_time synchronises the stream and returns the accumulated
  * milliseconds and launch count since the last reset. */
 enum { JPLG_K_PUSH = 0, JPLG_K_RENDER = 1, JPLG_K_BUS_REDUCE = 2, JPLG_K_MDAP = 3, JPLG_K_POINT_GAINS = 4,
-       JPLG_K_UPDATE = 5, JPLG_K_OTHER = 6, JPLG_K_COUNT = 7 };
+       JPLG_K_UPDATE = 5, JPLG_K_OTHER = 6, JPLG_K_FDN = 7, JPLG_K_ER_PUSH = 8, JPLG_K_COUNT = 9 };
 JPLG_API void        jplg_context_set_kernel_timing(jplg_context ctx, int32_t enabled);
 JPLG_API void        jplg_context_reset_kernel_timing(jplg_context ctx);
 JPLG_API jplg_status jplg_context_kernel_time(jplg_context ctx, int32_t which, double* total_ms, uint64_t* launches);
@@ -254,6 +256,26 @@ JPLG_API jplg_status jplg_mix_add_and_apply_gain_ramp(jplg_context ctx, float* d
                                                       uint32_t dest_num_channels, uint32_t source_num_channels,
                                                       uint32_t frames, const float* gain_start, const float* gain_end, int32_t mem); /* :89-107 */
 JPLG_API jplg_status jplg_mix_apply_gain(jplg_context ctx, float* dest, uint32_t n, uint32_t frames, const float* gains, int32_t mem); /* :50-63 */
+
+/* ---------------------------------------------------------------------------------------------- */
+/* ReverbBus x n  (replaces: inc/Auralization/LateReverb.h:34-117, src/Auralization/LateReverb.cpp:31-134;           */
+/*                 FDN inc/Auralization/ReverbDesign.h:311-349 Householder, :388-448 Hadamard, :451-492 mixers,        */
+/*                 :573-704 MultiChannelMixedFeedback<16, AttenuationFilter>)                                          */
+
+/* Prepare(sampleRate, splits) for n buses (LateReverb.cpp:42-48); f1..f3 = 0 -> reference defaults. output_channels =
+ * channel count of the `output` span of ProcessInterleaved (1..16). Initial decay slope -60 dB/s (RT60 = 1 s). */
+JPLG_API jplg_status jplg_reverb_bank_create(jplg_context ctx, uint32_t n, float sample_rate, float f1, float f2, float f3,
+                                             uint32_t output_channels, uint32_t max_block_frames, int32_t mode, jplg_reverb_bank* out);
+JPLG_API void        jplg_reverb_bank_destroy(jplg_reverb_bank b);
+/* SetRT60(newRT60Seconds) (:31-35): rt60 [n][4] seconds per band, clamped to [0.03, 10]. Visible at the next process. */
+JPLG_API jplg_status jplg_reverb_bank_set_rt60(jplg_reverb_bank b, const float* rt60_seconds, int32_t mem);
+/* SetDecaySlope(newDecaySlope) (:37-40): [n][4] dB/s, clamped to [-2000, -6] */
+JPLG_API jplg_status jplg_reverb_bank_set_decay_slope(jplg_reverb_bank b, const float* slope_db_per_second, int32_t mem);
+/* AttenuationFilter::DecayGains of every FDN channel = dBToGain(slope * delaySeconds) (LateReverb.h:64-68): host out [n][16][4] */
+JPLG_API jplg_status jplg_reverb_bank_decay_gains(jplg_reverb_bank b, float* out);
+/* ProcessInterleaved(input, output, numFrames) for all n buses (:53-134). in [n][frames] (mono: in_channels must be 1);
+ * out [n][frames][output_channels] interleaved, ACCUMULATED INTO like the reference's `output` span. */
+JPLG_API jplg_status jplg_reverb_bank_process(jplg_reverb_bank b, const float* in, uint32_t in_channels, float* out, uint32_t frames, int32_t mem);
 
 #ifdef __cplusplus
 }

@@ -8,6 +8,7 @@ reference's component interface (same names / argument meaning, batched) on top 
     VBAPanner (2D/3D), SourceLayout   inc/Panning/PannerBase.h:315-389
     DirectSoundBatch                  inc/Auralization/DirectSound.h:41-125 (N effects at once)
     CrossoverBank, DelayBank          inc/Auralization/CrossoverFilter.h, DelayLine.h
+    ReverbBusBatch                    inc/Auralization/LateReverb.h:34-117 (n FDN16 late-reverb buses)
 
 There is NO CPU fallback: without the built library the import fails, without a GPU every data-path call raises.
 """
@@ -15,7 +16,7 @@ from ._capi import (  # noqa: F401
     JplgError, lib, lib_path, device_count, version,
     MEM_HOST, MEM_DEVICE, MODE_PARITY, MODE_THROUGHPUT,
     EChannel, ChannelMask, ChannelMap,
-    Context, VBAPanner, SourceLayout, DirectSoundBatch, CrossoverBank, DelayBank,
+    Context, VBAPanner, SourceLayout, DirectSoundBatch, CrossoverBank, DelayBank, ReverbBusBatch,
     add_and_apply_gain_ramp, apply_gain, normalize_weights, get_spread_from_source_size,
     STATE_FLOATS,
 )

@@ -209,7 +209,7 @@ class Context:
     def launch_count(self):
         return int(lib.jplg_context_launch_count(self.h))
 
-    KERNELS = {"push": 0, "render": 1, "bus_reduce": 2, "mdap": 3, "point_gains": 4, "update": 5, "other": 6}
+    KERNELS = {"push": 0, "render": 1, "bus_reduce": 2, "mdap": 3, "point_gains": 4, "update": 5, "other": 6, "fdn": 7, "er_push": 8}
 
     def set_kernel_timing(self, enabled, only=None):
         """only: iterable of kernel names (see kernel_time) to bracket with events; default every kernel"""
@@ -459,6 +459,57 @@ class DirectSoundBatch:
     def __del__(self):
         try:
             self.close()
+        except Exception:
+            pass
+
+
+_sig("jplg_reverb_bank_create", _i32, [_vp, _u32, _f32, _f32, _f32, _f32, _u32, _u32, _i32, C.POINTER(_vp)])
+_sig("jplg_reverb_bank_destroy", None, [_vp])
+_sig("jplg_reverb_bank_set_rt60", _i32, [_vp, _fp, _i32])
+_sig("jplg_reverb_bank_set_decay_slope", _i32, [_vp, _fp, _i32])
+_sig("jplg_reverb_bank_decay_gains", _i32, [_vp, _fp])
+_sig("jplg_reverb_bank_process", _i32, [_vp, _fp, _u32, _fp, _u32, _i32])
+
+
+class ReverbBusBatch:
+    """n x ReverbBus (inc/Auralization/LateReverb.h:34-117): 16th-order FDN with four-band decay filters"""
+
+    def __init__(self, ctx, n, sample_rate, output_channels, splits=(0.0, 0.0, 0.0), max_block_frames=512, mode=MODE_PARITY):
+        self.ctx, self.n, self.L = ctx, int(n), int(output_channels)
+        h = _vp()
+        ctx.check(lib.jplg_reverb_bank_create(ctx.h, self.n, float(sample_rate), float(splits[0]), float(splits[1]), float(splits[2]),
+                                              self.L, int(max_block_frames), int(mode), C.byref(h)))
+        self.h = h
+
+    def SetRT60(self, rt60):
+        a, mem, _k = _arg(rt60)
+        self.ctx.check(lib.jplg_reverb_bank_set_rt60(self.h, a, mem))
+
+    def SetDecaySlope(self, slope):
+        a, mem, _k = _arg(slope)
+        self.ctx.check(lib.jplg_reverb_bank_set_decay_slope(self.h, a, mem))
+
+    def DecayGains(self):
+        out = np.zeros((self.n, 16, 4), np.float32)
+        self.ctx.check(lib.jplg_reverb_bank_decay_gains(self.h, out.ctypes.data))
+        return out
+
+    def ProcessInterleaved(self, inp, out, frames, in_channels=1):
+        """inp [n][frames] mono, out [n][frames][L] accumulated into (numpy = host buffers, torch CUDA tensors = device buffers)"""
+        a, mem_a, _k = _arg(inp)
+        if _is_torch(out):
+            o, mem_o = out.data_ptr(), (MEM_DEVICE if out.is_cuda else MEM_HOST)
+        else:
+            assert out.dtype == np.float32 and out.flags["C_CONTIGUOUS"]
+            o, mem_o = out.ctypes.data, MEM_HOST
+        assert mem_a == mem_o, "input and output must live in the same memory space"
+        self.ctx.check(lib.jplg_reverb_bank_process(self.h, a, int(in_channels), o, int(frames), mem_a))
+
+    def __del__(self):
+        try:
+            if self.h:
+                lib.jplg_reverb_bank_destroy(self.h)
+                self.h = None
         except Exception:
             pass
 

@@ -1023,4 +1023,143 @@ jplg_status jplg_mix_apply_gain(jplg_context ctx, float* dest, uint32_t n, uint3
 	return JPLG_OK;
 }
 
+//==================================================================================================
+// ReverbBus bank (LateReverb.h:34-117, LateReverb.cpp:31-134)
+struct jplg_reverb_bank_t
+{
+	jplg_context ctx; uint32_t n, L, maxFrames; int mode; float sampleRate, invSampleRate; float coef[27];
+	float *state = nullptr, *decay = nullptr, *slope = nullptr, *rings = nullptr, *stageIn = nullptr, *stageOut = nullptr;
+	uint64_t pos = 0; bool slopeDirty = true;
+};
+static void FreeReverb(jplg_reverb_bank b)
+{
+	for (float* p : { b->state, b->decay, b->slope, b->rings, b->stageIn, b->stageOut }) if (p) cudaFree(p);
+}
+jplg_status jplg_reverb_bank_create(jplg_context ctx, uint32_t n, float sample_rate, float f1, float f2, float f3,
+									uint32_t output_channels, uint32_t max_block_frames, int32_t mode, jplg_reverb_bank* out)
+{
+	if (!ctx || !out || n == 0 || !(sample_rate > 0.0f)) return JPLG_ERR_INVALID_ARGUMENT;
+	// numOutChannels <= cFDNChannels is asserted by the reference (LateReverb.cpp:66)
+	if (output_channels == 0 || output_channels > 16) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "jplg_reverb_bank_create: output_channels must be 1..16 (FDN order)");
+	if (max_block_frames == 0) max_block_frames = 512;
+	if (max_block_frames > kFdnMaxFrames) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "jplg_reverb_bank_create: max_block_frames must not exceed 1024 (shortest FDN delay is 1609 samples)");
+	JPLG_NEED_DEVICE(ctx);
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	auto* b = new jplg_reverb_bank_t{};
+	b->ctx = ctx; b->n = n; b->L = output_channels; b->maxFrames = max_block_frames; b->mode = mode; b->sampleRate = sample_rate;
+	b->invSampleRate = 1.0f / sample_rate;                                 // MultiChannelFeedbackBase::Prepare (ReverbDesign.h:598)
+	if (f1 == 0.0f) f1 = 176.0f; if (f2 == 0.0f) f2 = 775.0f; if (f3 == 0.0f) f3 = 3408.0f;
+	CrossoverCoefficients(sample_rate, f1, f2, f3, b->coef);
+	const size_t nCh = size_t(n) * 16;
+	auto alloc = [&](float** p, size_t floats) { return cudaMalloc(reinterpret_cast<void**>(p), floats * 4) == cudaSuccess; };
+	const bool ok = alloc(&b->state, nCh * 24) && alloc(&b->decay, nCh * 4) && alloc(&b->slope, size_t(n) * 4) && alloc(&b->rings, nCh * kFdnRingSize)
+		&& alloc(&b->stageIn, size_t(n) * max_block_frames) && alloc(&b->stageOut, size_t(n) * max_block_frames * output_channels);
+	if (!ok) { cudaGetLastError(); FreeReverb(b); delete b; return Fail(ctx, JPLG_ERR_OUT_OF_MEMORY, "jplg_reverb_bank_create: device allocation failed (rings need n*16*8192*4 bytes)"); }
+	JPLG_CUDA_TRY(ctx, cudaMemsetAsync(b->state, 0, nCh * 24 * 4, ctx->stream));
+	JPLG_CUDA_TRY(ctx, cudaMemsetAsync(b->rings, 0, nCh * kFdnRingSize * 4, ctx->stream));
+	k_fill<<<static_cast<uint32_t>((size_t(n) * 4 + 255) / 256), 256, 0, ctx->stream>>>(b->slope, size_t(n) * 4, -60.0f); ctx->launches++;   // mDecaySlopeDbPerSecond{ -60 / 1 } (LateReverb.h:116)
+	JPLG_CUDA_TRY(ctx, cudaGetLastError());
+	JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	*out = b;
+	return JPLG_OK;
+}
+void jplg_reverb_bank_destroy(jplg_reverb_bank b)
+{
+	if (!b) return;
+	cudaSetDevice(b->ctx->device);
+	cudaStreamSynchronize(b->ctx->stream);
+	FreeReverb(b);
+	delete b;
+}
+// slope = clamp(...) per the two setters; `rt60` selects SetRT60 (LateReverb.cpp:31-35) or SetDecaySlope (:37-40)
+__global__ void k_reverb_set_slope(const float* __restrict__ v, size_t count, int rt60, float* __restrict__ slope)
+{
+	const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+	if (i >= count) return;
+	const float cMinRT60 = 0.03f, cMaxRT60 = 10.0f;
+	if (rt60) slope[i] = -60.0f / fminf(fmaxf(v[i], cMinRT60), cMaxRT60);
+	else slope[i] = fminf(fmaxf(v[i], -60.0f / cMinRT60), -60.0f / cMaxRT60);
+}
+static jplg_status ReverbSet(jplg_reverb_bank b, const float* v, int rt60, int32_t mem)
+{
+	if (!b || !v) return JPLG_ERR_INVALID_ARGUMENT;
+	jplg_context ctx = b->ctx;
+	JPLG_NEED_DEVICE(ctx);
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	const size_t count = size_t(b->n) * 4;
+	const float* dV = v;
+	if (mem == JPLG_MEM_HOST)
+	{
+		void* a; jplg_status st = Scratch(ctx, 0, count * 4, &a); if (st) return st;
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(a, v, count * 4, cudaMemcpyHostToDevice, ctx->stream));
+		dV = static_cast<float*>(a);
+	}
+	k_reverb_set_slope<<<static_cast<uint32_t>((count + 255) / 256), 256, 0, ctx->stream>>>(dV, count, rt60, b->slope); ctx->launches++;
+	JPLG_CUDA_TRY(ctx, cudaGetLastError());
+	if (mem == JPLG_MEM_HOST) JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	b->slopeDirty = true;
+	return JPLG_OK;
+}
+jplg_status jplg_reverb_bank_set_rt60(jplg_reverb_bank b, const float* rt60_seconds, int32_t mem) { return ReverbSet(b, rt60_seconds, 1, mem); }
+jplg_status jplg_reverb_bank_set_decay_slope(jplg_reverb_bank b, const float* slope_db_per_second, int32_t mem) { return ReverbSet(b, slope_db_per_second, 0, mem); }
+
+static jplg_status ReverbRefreshDecay(jplg_reverb_bank b)
+{
+	if (!b->slopeDirty) return JPLG_OK;
+	jplg_context ctx = b->ctx;
+	// mFDN.UpdateFilterParameters(slope) at the top of every ProcessInterleaved (LateReverb.cpp:55); recomputed only when the slope changed
+	JPLG_LAUNCH(ctx, JPLG_K_OTHER, LaunchFdnDecay(b->slope, b->n, b->invSampleRate, b->decay, b->mode, ctx->stream));
+	b->slopeDirty = false;
+	return JPLG_OK;
+}
+jplg_status jplg_reverb_bank_decay_gains(jplg_reverb_bank b, float* out /* host [n][16][4] */)
+{
+	if (!b || !out) return JPLG_ERR_INVALID_ARGUMENT;
+	jplg_context ctx = b->ctx;
+	JPLG_NEED_DEVICE(ctx);
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	jplg_status st = ReverbRefreshDecay(b); if (st) return st;
+	const size_t nCh = size_t(b->n) * 16;
+	std::vector<float> soa(nCh * 4);
+	JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(soa.data(), b->decay, nCh * 16, cudaMemcpyDeviceToHost, ctx->stream));
+	JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	for (size_t i = 0; i < nCh; ++i) for (int k = 0; k < 4; ++k) out[i * 4 + k] = soa[size_t(k) * nCh + i];
+	return JPLG_OK;
+}
+jplg_status jplg_reverb_bank_process(jplg_reverb_bank b, const float* in, uint32_t in_channels, float* out, uint32_t frames, int32_t mem)
+{
+	if (!b || (frames && (!in || !out))) return JPLG_ERR_INVALID_ARGUMENT;
+	jplg_context ctx = b->ctx;
+	JPLG_NEED_DEVICE(ctx);
+	if (frames == 0) return JPLG_OK;
+	if (in_channels != 1) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "jplg_reverb_bank_process: only mono input is supported (the reference's multichannel down-mix "
+		"path over-runs its 480-frame scratch array for blocks longer than one chunk, LateReverb.cpp:86)");
+	if (frames > b->maxFrames) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "jplg_reverb_bank_process: frames exceeds max_block_frames");
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	const size_t nIn = size_t(b->n) * frames, nOut = nIn * b->L;
+	const float* dIn = in; float* dOut = out;
+	if (mem == JPLG_MEM_HOST)
+	{
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(b->stageIn, in, nIn * 4, cudaMemcpyHostToDevice, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(b->stageOut, out, nOut * 4, cudaMemcpyHostToDevice, ctx->stream));
+		dIn = b->stageIn; dOut = b->stageOut;
+	}
+	jplg_status st = ReverbRefreshDecay(b); if (st) return st;
+	FdnParams fp{}; fp.n = b->n; fp.L = b->L; fp.frames = frames; fp.pos = b->pos; std::memcpy(fp.coef, b->coef, sizeof(fp.coef));
+	fp.hadamardScale = FdnHadamardScale();
+	fp.state = b->state; fp.decay = b->decay; fp.rings = b->rings; fp.in = dIn; fp.out = dOut;
+	JPLG_LAUNCH(ctx, JPLG_K_FDN, LaunchFdn(fp, b->mode, ctx->stream));
+	b->pos += frames;
+	if (mem == JPLG_MEM_HOST)
+	{
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(out, dOut, nOut * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	}
+	return JPLG_OK;
+}
+
 } // extern "C"

@@ -91,4 +91,26 @@ namespace jplg
 	cudaError_t LaunchMixRamp(float* dest, const float* src, uint32_t n, uint32_t destCh, uint32_t srcCh, uint32_t nDest, uint32_t nSrc,
 							  uint32_t frames, const float* g0, const float* g1, cudaStream_t st);
 	cudaError_t LaunchApplyGain(float* dest, uint32_t n, uint32_t frames, const float* gains, cudaStream_t st);
+	//======================================================================
+	// ReverbBus bank (jplg_reverb_kernels.cu)
+	constexpr uint32_t kFdnRingSize = 8192;   // power of two above the longest FDN delay + 1 (4259); the reference sizes each line bit_ceil(delay + 1)
+	constexpr uint32_t kFdnMaxFrames = 1024;  // a call must not be longer than the shortest FDN delay (1609): no feedback dependency inside a call
+	struct FdnParams
+	{
+		uint32_t n, L, frames;
+		uint64_t pos;           // samples pushed into every ring so far
+		float coef[27];         // crossover coefficients (jplg_host.hpp)
+		float hadamardScale;    // Hadamard::MixInPlace scalingFactor (see FdnHadamardScale)
+		float* state;           // [24][n*16] crossover state, SoA
+		const float* decay;     // [4][n*16] per-channel decay gains b1..b4
+		float* rings;           // [n*16][kFdnRingSize]
+		const float* in;        // [n][frames] mono
+		float* out;             // [n][frames][L], accumulated into
+	};
+	// Hadamard::MixInPlace's `static constexpr Sample scalingFactor = Math::Sqrt(1.0 / Size)` (ReverbDesign.h:443-446) is evaluated at compile time
+	// by the reference's constexpr fallback on a DOUBLE (Quake-style seed + 2 Newton steps on 1/sqrt, no polish: inc/Math/Math.h:213-262), then
+	// narrowed to float: 0x3e7fffb8 = 0.249998927 for Size = 16, not 0.25. Restated on the host so the value is derived, not pasted.
+	float FdnHadamardScale();
+	cudaError_t LaunchFdnDecay(const float* slope, uint32_t n, float invSampleRate, float* decay, int mode, cudaStream_t st);
+	cudaError_t LaunchFdn(const FdnParams& fp, int mode, cudaStream_t st);
 }

@@ -1,0 +1,238 @@
+// Batched ReverbBus for sm_100a: n x 16th-order feedback delay network with four-band decay filters
+// (inc/Auralization/LateReverb.h:34-117, src/Auralization/LateReverb.cpp:53-134, inc/Auralization/ReverbDesign.h:311-349,388-492,573-704).
+//
+//   k_fdn_decay   AttenuationFilter::UpdateParameters for every (instance, FDN channel): DecayGains = dBToGain(slope * delaySeconds)
+//                 (LateReverb.h:64-68; dBToGain = SIMD exp, inc/Math/DecibelsAndGain.h:40-56, inc/Math/SIMDMath.h:270-316)
+//   k_fdn         one block of ReverbBus::ProcessInterleaved for n instances. Thread = (instance, FDN channel); the 16 channels of an
+//                 instance sit in 16 consecutive lanes, so the Householder feedback mix and the Hadamard output mix are warp shuffles.
+//                 Every FDN delay (1609..4259 samples) is longer than a block, so inside a block the only time recurrences are the 16
+//                 per-channel crossover filters; delayed samples are staged from the rings, and the new ring samples / output frames are
+//                 staged back, through shared memory with coalesced global accesses.
+//
+// Arithmetic modes as in jplg_render_kernels.cu: PARITY = every reference FMA as mul + add (the SSE2 baseline semantic), THROUGHPUT = fused.
+// Compile with -fmad=false.
+#include "jplg_kernels.hpp"
+#include <cstring>
+
+namespace jplg
+{
+	namespace
+	{
+		template<int MODE> __device__ __forceinline__ float mad(float a, float b, float c)
+		{
+			if (MODE == 0) return a * b + c;   // -fmad=false: two roundings
+			else return __fmaf_rn(a, b, c);
+		}
+
+		struct SvfP { float g, d, mrg; };
+
+		// StateVariableFilterTPT::Process / TPTSVFStageSIMD::Process (inc/Auralization/CrossoverFilter.h:64-76,154-162)
+		template<int MODE> __device__ __forceinline__ void svf(const SvfP p, const float x, float& s1, float& s2, float& yL, float& yB, float& yH)
+		{
+			yH = mad<MODE>(p.mrg, s1, x - s2) * p.d;
+			yB = mad<MODE>(p.g, yH, s1);
+			s1 = mad<MODE>(p.g, yH, yB);
+			yL = mad<MODE>(p.g, yB, s2);
+			s2 = mad<MODE>(p.g, yB, yL);
+		}
+
+		// FourBandCrossover::ProcessSample(sample, gains) (CrossoverFilter.h:440-459): SplitSample -> { b1, b2, b3, b4 } * gains, reduce()
+		// = (b1*g1 + b2*g2) + (b3*g3 + b4*g4) (simd::reduce, inc/Math/SIMD.h:938-945). st: 24 state floats in ST_FILTER order.
+		template<int MODE> __device__ __forceinline__ float xover_process_sample(const float* __restrict__ cf, float* st, const float x, const float g[4])
+		{
+			const float minusR = -1.41421356237309504880f;
+			const SvfP p2{ cf[0], cf[1], cf[2] };
+			float yL, yB, yH, yL2, yB2, yH2;
+			svf<MODE>(p2, x, st[0], st[1], yL, yB, yH);
+			svf<MODE>(p2, yL, st[2], st[3], yL2, yB2, yH2);
+			const float low = yL2;
+			const float high = mad<MODE>(minusR, yB, yL + yH - yL2);
+			float aL, aB, aH, bL, bB, bH;
+			svf<MODE>(SvfP{ cf[3], cf[7], cf[11] }, low, st[4], st[5], aL, aB, aH);
+			svf<MODE>(SvfP{ cf[4], cf[8], cf[12] }, high, st[6], st[7], bL, bB, bH);
+			float o[4], t0, t1;
+			svf<MODE>(SvfP{ cf[3], cf[7], cf[11] }, aL, st[8], st[9], o[0], t0, t1);
+			svf<MODE>(SvfP{ cf[4], cf[8], cf[12] }, bL, st[10], st[11], o[1], t0, t1);
+			svf<MODE>(SvfP{ cf[5], cf[9], cf[13] }, aH, st[12], st[13], t0, t1, o[2]);
+			svf<MODE>(SvfP{ cf[6], cf[10], cf[14] }, bH, st[14], st[15], t0, t1, o[3]);
+			float b[4];   // interleaved { b1, b3, b2, b4 }
+			#pragma unroll
+			for (int k = 0; k < 4; ++k)
+			{
+				float pL, pB, pH;
+				svf<MODE>(SvfP{ cf[15 + k], cf[19 + k], cf[23 + k] }, o[k], st[16 + 2 * k], st[17 + 2 * k], pL, pB, pH);
+				b[k] = mad<MODE>(minusR, pB, pH + pL);
+			}
+			return (b[0] * g[0] + b[2] * g[1]) + (b[1] * g[2] + b[3] * g[3]);
+		}
+
+		// JPL::exp(simd) per lane (inc/Math/SIMDMath.h:296-316) with the SSE2 floor (inc/Math/SIMD.h:1861-1879)
+		template<int MODE> __device__ __forceinline__ float exp_ref(float x)
+		{
+			x = fminf(fmaxf(x, -88.3762626647949f), 88.3762626647949f);
+			const float v = mad<MODE>(x, 1.44269504088896341f, 0.5f);
+			const float tr = static_cast<float>(static_cast<int32_t>(v));     // cvttps2dq -> cvtdq2ps
+			const float n = (v == 0.0f) ? v : tr - (tr > v ? 1.0f : 0.0f);
+			const float nC2 = n * -2.12194440e-4f;
+			x = x - mad<MODE>(n, 0.693359375f, nC2);
+			const float x2 = x * x;
+			float y = 1.9875691500e-4f;
+			y = mad<MODE>(y, x, 1.3981999507e-3f);
+			y = mad<MODE>(y, x, 8.3334519073e-3f);
+			y = mad<MODE>(y, x, 4.1665795894e-2f);
+			y = mad<MODE>(y, x, 1.6666665459e-1f);
+			y = mad<MODE>(y, x, 5.0000001201e-1f);
+			y = mad<MODE>(y, x2, x + 1.0f);
+			const float pow2n = __int_as_float((static_cast<int32_t>(n) + 0x7f) << 23);
+			return y * pow2n;
+		}
+	}
+
+	// cPrimeDelayLengths[0..15] (ReverbDesign.h:578-581)
+	__constant__ uint32_t cFdnDelays[16] = { 2927, 2593, 2273, 3697, 1877, 3877, 2477, 3461, 1609, 3779, 3541, 4259, 1669, 3539, 3637, 4013 };
+
+	template<int MODE>
+	__global__ void k_fdn_decay(const float* __restrict__ slope /*[n][4]*/, uint32_t n, float invSampleRate, float* __restrict__ decay /*[4][n*16]*/)
+	{
+		const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+		if (i >= n * 16u) return;
+		const uint32_t inst = i >> 4, c = i & 15u;
+		const float delaySeconds = static_cast<float>(cFdnDelays[c]) * invSampleRate;      // ReverbDesign.h:625
+		const float ln10div20 = 2.302585092994046f * 0.05f;                                  // DecibelsAndGain.h:47 (float product, folded like the reference's static)
+		#pragma unroll
+		for (int k = 0; k < 4; ++k)
+		{
+			const float dbLossPerLoop = slope[4 * size_t(inst) + k] * delaySeconds;           // LateReverb.h:66
+			decay[size_t(k) * n * 16u + i] = exp_ref<MODE>(ln10div20 * dbLossPerLoop);
+		}
+	}
+
+	constexpr uint32_t kFdnTile = 32;        // frames per shared-memory tile
+	constexpr uint32_t kFdnInstPerCTA = 8;   // 8 instances x 16 channels = 128 threads
+	constexpr uint32_t kFdnRow = kFdnTile + 1;
+
+	// ReverbBus::ProcessInterleaved, mono input (LateReverb.cpp:53-134), for `n` instances. The 480-frame chunking of the reference
+	// has no arithmetic effect here (the filter parameters are updated once per call, the FDN runs sample by sample).
+	template<int MODE>
+	__global__ void __launch_bounds__(kFdnInstPerCTA * 16)
+	k_fdn(const FdnParams fp)
+	{
+		__shared__ float sDel[kFdnInstPerCTA * 16][kFdnRow];   // one row per (instance, channel): the tile's delayed samples, overwritten in place by the samples to push
+		__shared__ float sIn[kFdnInstPerCTA][kFdnTile];
+		__shared__ float sOut[kFdnInstPerCTA][kFdnTile][16];   // FDN output mix per frame (first L used)
+
+		const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
+		const uint32_t c = tid & 15u;                          // FDN channel
+		const uint32_t instBase = blockIdx.x * kFdnInstPerCTA;
+		const uint32_t inst = instBase + (tid >> 4);
+		const bool active = inst < fp.n;
+		const uint32_t L = fp.L;
+		const size_t nCh = size_t(fp.n) * 16u, ch = size_t(inst) * 16u + c;
+		const uint32_t pos32 = static_cast<uint32_t>(fp.pos);
+		constexpr uint32_t ringMask = kFdnRingSize - 1;
+
+		float st[24], g[4];
+		#pragma unroll
+		for (int k = 0; k < 24; ++k) st[k] = active ? fp.state[size_t(k) * nCh + ch] : 0.0f;
+		#pragma unroll
+		for (int k = 0; k < 4; ++k) g[k] = active ? fp.decay[size_t(k) * nCh + ch] : 0.0f;
+
+		for (uint32_t t0 = 0; t0 < fp.frames; t0 += kFdnTile)
+		{
+			const uint32_t len = min(kFdnTile, fp.frames - t0);
+			// ---- stage in: warp w loads rows [32w, 32w+32): delayed[c][n] = pushed[n - 1 - D_c] (GetReadWindow<1>(D) before this frame's push)
+			for (uint32_t r = 0; r < 32; ++r)
+			{
+				const uint32_t row = warp * 32 + r, rInst = instBase + (row >> 4), rc = row & 15u;
+				if (rInst < fp.n && lane < len)
+				{
+					const float* ring = fp.rings + (size_t(rInst) * 16u + rc) * kFdnRingSize;
+					sDel[row][lane] = ring[(pos32 + t0 + lane - 1u - cFdnDelays[rc]) & ringMask];
+				}
+			}
+			for (uint32_t e = tid; e < kFdnInstPerCTA * kFdnTile; e += blockDim.x)
+			{
+				const uint32_t i = e / kFdnTile, f = e - i * kFdnTile;
+				if (instBase + i < fp.n && f < len) sIn[i][f] = fp.in[size_t(instBase + i) * fp.frames + t0 + f];
+			}
+			__syncthreads();
+
+			// ---- compute: one thread per (instance, channel), frames in order
+			for (uint32_t f = 0; f < len; ++f)
+			{
+				const float d = sDel[tid][f];
+				// Householder::MixInPlace, 16-channel special case (ReverbDesign.h:311-349): mix4 inside each group of 4, then across the groups
+				float s = d + __shfl_xor_sync(0xffffffffu, d, 1);
+				s = s + __shfl_xor_sync(0xffffffffu, s, 2);
+				float m = 2.0f * d - s;                                 // FMA(2, v, -sum): 2v is exact, one rounding in either build
+				float s2 = m + __shfl_xor_sync(0xffffffffu, m, 4);
+				s2 = s2 + __shfl_xor_sync(0xffffffffu, s2, 8);
+				m = (2.0f * m - s2) * 0.25f;
+				// FDNInput::InjectNormalized: every channel gets monoInput * sqrt(1/16) (ReverbDesign.h:455-459)
+				const float x = m + sIn[tid >> 4][f] * 0.25f;
+				sDel[tid][f] = xover_process_sample<MODE>(fp.coef, st, x, g);   // AttenuationFilter::Process, then Push (ReverbDesign.h:696-699)
+				// FDNOutputMixer::Mix (ReverbDesign.h:480-492): Hadamard of the delayed samples (RecursiveUnscaled :391-437), * sqrt(1/16)
+				float h = d;
+				#pragma unroll
+				for (uint32_t bit = 1; bit < 16; bit <<= 1)
+				{
+					const float o = __shfl_xor_sync(0xffffffffu, h, bit);
+					h = (c & bit) ? o - h : h + o;
+				}
+				sOut[tid >> 4][f][c] = h * fp.hadamardScale;
+			}
+			__syncthreads();
+
+			// ---- stage out: push the new samples (ring index = push count), fold the mixed FDN channels into the output frames
+			for (uint32_t r = 0; r < 32; ++r)
+			{
+				const uint32_t row = warp * 32 + r, rInst = instBase + (row >> 4), rc = row & 15u;
+				if (rInst < fp.n && lane < len)
+					fp.rings[(size_t(rInst) * 16u + rc) * kFdnRingSize + ((pos32 + t0 + lane) & ringMask)] = sDel[row][lane];
+			}
+			for (uint32_t e = tid; e < kFdnInstPerCTA * len * L; e += blockDim.x)
+			{
+				const uint32_t i = e / (len * L), rem = e - i * (len * L), f = rem / L, oc = rem - f * L;
+				if (instBase + i >= fp.n) continue;
+				float* o = fp.out + (size_t(instBase + i) * fp.frames + t0 + f) * L + oc;
+				float acc = *o;                                         // out[i % numOut] += fdn[i], i ascending
+				for (uint32_t k = oc; k < 16; k += L) acc += sOut[i][f][k];
+				*o = acc;
+			}
+			__syncthreads();
+		}
+
+		if (active)
+		{
+			#pragma unroll
+			for (int k = 0; k < 24; ++k) fp.state[size_t(k) * nCh + ch] = st[k];
+		}
+	}
+
+	float FdnHadamardScale()
+	{
+		const double x = 1.0 / 16.0;
+		uint64_t i; std::memcpy(&i, &x, 8);
+		i = 0x5fe6eb50c7b537a9ull - (i >> 1);              // InvSqrtInitialGuess<double> (Math.h:221-226)
+		double y; std::memcpy(&y, &i, 8);
+		const double halfx = 0.5 * x;
+		for (int k = 0; k < 2; ++k) y = y * (1.5 - halfx * y * y);   // InvSqrtNewtonRefine<double, 2> (:236-242)
+		return static_cast<float>(x * y);                  // SqrtConstevalFallback (:255), narrowed by `constexpr Sample`
+	}
+
+	cudaError_t LaunchFdnDecay(const float* slope, uint32_t n, float invSampleRate, float* decay, int mode, cudaStream_t st)
+	{
+		if (n == 0) return cudaSuccess;
+		const uint32_t total = n * 16u, grid = (total + 255) / 256;
+		if (mode == 0) k_fdn_decay<0><<<grid, 256, 0, st>>>(slope, n, invSampleRate, decay); else k_fdn_decay<1><<<grid, 256, 0, st>>>(slope, n, invSampleRate, decay);
+		return cudaGetLastError();
+	}
+
+	cudaError_t LaunchFdn(const FdnParams& fp, int mode, cudaStream_t st)
+	{
+		if (fp.n == 0 || fp.frames == 0) return cudaSuccess;
+		const uint32_t grid = (fp.n + kFdnInstPerCTA - 1) / kFdnInstPerCTA;
+		if (mode == 0) k_fdn<0><<<grid, kFdnInstPerCTA * 16, 0, st>>>(fp); else k_fdn<1><<<grid, kFdnInstPerCTA * 16, 0, st>>>(fp);
+		return cudaGetLastError();
+	}
+}

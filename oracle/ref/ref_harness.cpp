@@ -15,6 +15,9 @@
 #include <JPLSpatial/Panning/VBAPanning2D.h>
 #include <JPLSpatial/Panning/VBAPanning3D.h>
 #include <JPLSpatial/Auralization/DirectSound.h>
+#include <JPLSpatial/Auralization/LateReverb.h>
+#include <JPLSpatial/Auralization/EarlyReflectionsBus.h>
+#include <JPLSpatial/Math/DecibelsAndGain.h>
 #include <JPLSpatial/Auralization/CrossoverFilter.h>
 #include <JPLSpatial/Auralization/DelayLine.h>
 #include <JPLSpatial/Auralization/FractionalDelay.h>
@@ -514,5 +517,77 @@ extern "C"
 		auto* d0 = static_cast<RefDSE*>(effects[0]);
 		const size_t mm = size_t(d0->nSrc) * d0->nOut;
 		for (uint32_t i = 0; i < n; ++i) ref_dse_update(effects[i], bandGains + 4 * size_t(i), delaySeconds[i], mixMaps + mm * i);
+	}
+	//==========================================================================
+	// ReverbBus (LateReverb.h:84-108)
+	void* ref_reverb_create(float fs, float f1, float f2, float f3)
+	{
+		auto* r = new ReverbBus();
+		SplitFrequencies sp{}; if (f1 > 0.0f) { sp.F1 = f1; sp.F2 = f2; sp.F3 = f3; }
+		r->Prepare(fs, sp);
+		return r;
+	}
+	void ref_reverb_destroy(void* h) { delete static_cast<ReverbBus*>(h); }
+	void ref_reverb_set_rt60(void* h, const float* rt60) { static_cast<ReverbBus*>(h)->SetRT60(simd(rt60)); }
+	void ref_reverb_set_decay_slope(void* h, const float* slope) { static_cast<ReverbBus*>(h)->SetDecaySlope(simd(slope)); }
+	// in: interleaved [frames][nIn]; out: interleaved [frames][nOut], ACCUMULATED INTO (ReverbDesign.h:480-492)
+	void ref_reverb_process(void* h, const float* in, uint32_t nIn, float* out, uint32_t nOut, uint32_t frames)
+	{
+		static_cast<ReverbBus*>(h)->ProcessInterleaved(std::span<const float>(in, size_t(frames) * nIn), std::span<float>(out, size_t(frames) * nOut), frames);
+	}
+	// dBToGain on 4 lanes (DecibelsAndGain.h:40-56): the decay gains of one FDN channel = dBToGain(slope * delaySeconds)
+	void ref_db_to_gain(const float* db, float* out) { dBToGain(simd(db)).store(out); }
+	double ref_reverb_process_batch(void** buses, uint32_t n, const float* in /*[n][frames]*/, float* out /*[n][frames][nOut]*/, uint32_t nOut, uint32_t frames, int threads)
+	{
+		if (threads < 1) threads = 1;
+		const auto t0 = std::chrono::steady_clock::now();
+		std::vector<std::thread> pool;
+		for (int t = 0; t < threads; ++t)
+		{
+			const uint32_t b = uint32_t(uint64_t(n) * t / threads), e = uint32_t(uint64_t(n) * (t + 1) / threads);
+			pool.emplace_back([=] { for (uint32_t i = b; i < e; ++i) ref_reverb_process(buses[i], in + size_t(i) * frames, 1, out + size_t(i) * frames * nOut, nOut, frames); });
+		}
+		for (auto& th : pool) th.join();
+		return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+	}
+
+	//==========================================================================
+	// ERBus (EarlyReflectionsBus.h:60-88)
+	void* ref_erbus_create(float fs, uint32_t numChannels) { return new ERBus(fs, numChannels); }
+	void ref_erbus_destroy(void* h) { delete static_cast<ERBus*>(h); }
+	uint32_t ref_erbus_num_taps(void* h) { return static_cast<ERBus*>(h)->GetNumTaps(); }
+	// taps: n x { filterGains[4], delaySeconds, id (as float bits), gains[numChannels] }
+	void ref_erbus_set_taps(void* h, uint32_t n, const float* filterGains /*[n][4]*/, const float* delaySeconds /*[n]*/, const uint32_t* ids /*[n]*/, const float* gains /*[n][L]*/)
+	{
+		auto* b = static_cast<ERBus*>(h);
+		const uint32 L = b->GetNumChannels();
+		std::vector<ERBus::ERUpdateData> upd(n);
+		for (uint32_t i = 0; i < n; ++i)
+		{
+			upd[i].FilterGains = simd(filterGains + 4 * size_t(i));
+			upd[i].Gains.assign(gains + size_t(i) * L, gains + size_t(i + 1) * L);
+			upd[i].Delay = delaySeconds[i];
+			upd[i].Id = ids[i];
+		}
+		b->SetTaps(upd);
+	}
+	// in: interleaved [frames][nIn]; out: interleaved [frames][L], ACCUMULATED INTO
+	void ref_erbus_process(void* h, const float* in, uint32_t nIn, float* out, uint32_t frames)
+	{
+		auto* b = static_cast<ERBus*>(h);
+		b->ProcessInterleaved(std::span<const float>(in, size_t(frames) * nIn), std::span<float>(out, size_t(frames) * b->GetNumChannels()), nIn, frames);
+	}
+	double ref_erbus_process_batch(void** buses, uint32_t n, const float* in /*[n][frames]*/, float* out /*[n][frames][L]*/, uint32_t frames, int threads)
+	{
+		if (threads < 1) threads = 1;
+		const auto t0 = std::chrono::steady_clock::now();
+		std::vector<std::thread> pool;
+		for (int t = 0; t < threads; ++t)
+		{
+			const uint32_t b = uint32_t(uint64_t(n) * t / threads), e = uint32_t(uint64_t(n) * (t + 1) / threads);
+			pool.emplace_back([=] { for (uint32_t i = b; i < e; ++i) { const uint32 L = static_cast<ERBus*>(buses[i])->GetNumChannels(); ref_erbus_process(buses[i], in + size_t(i) * frames, 1, out + size_t(i) * frames * L, frames); } });
+		}
+		for (auto& th : pool) th.join();
+		return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 	}
 } // extern "C"

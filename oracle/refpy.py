@@ -42,10 +42,49 @@ class Ref:
         L.ref_slerp_simd.argtypes = [_vp, _vp, _f32, _u32]
         L.ref_smoother_run.argtypes = [_f32, _f32, _u32, _u32, _vp]
         L.ref_add_gain_ramp.argtypes = [_vp, _vp, _u32, _u32, _u32, _u32, _u32, _f32, _f32]
+        for name in ("ref_reverb_create", "ref_erbus_create"):
+            getattr(L, name).restype = _vp
+        L.ref_reverb_create.argtypes = [_f32, _f32, _f32, _f32]
+        L.ref_reverb_set_rt60.argtypes = [_vp, _vp]
+        L.ref_reverb_set_decay_slope.argtypes = [_vp, _vp]
+        L.ref_reverb_process.argtypes = [_vp, _vp, _u32, _vp, _u32, _u32]
+        L.ref_reverb_process_batch.restype = C.c_double
+        L.ref_reverb_process_batch.argtypes = [_vp, _u32, _vp, _vp, _u32, _u32, C.c_int]
+        L.ref_db_to_gain.argtypes = [_vp, _vp]
+        L.ref_erbus_create.argtypes = [_f32, _u32]
+        L.ref_erbus_num_taps.restype = _u32
+        L.ref_erbus_set_taps.argtypes = [_vp, _u32, _vp, _vp, _vp, _vp]
+        L.ref_erbus_process.argtypes = [_vp, _vp, _u32, _vp, _u32]
+        L.ref_erbus_process_batch.restype = C.c_double
+        L.ref_erbus_process_batch.argtypes = [_vp, _u32, _vp, _vp, _u32, C.c_int]
+        for name in ("ref_reverb_destroy", "ref_erbus_destroy", "ref_erbus_num_taps"):
+            getattr(L, name).argtypes = [_vp]
         for name in ("ref_panner_destroy", "ref_layout_destroy", "ref_xover_destroy", "ref_delay_destroy", "ref_dse_destroy",
                      "ref_panner_ok", "ref_panner_is3d", "ref_panner_num_channels", "ref_panner_aperture", "ref_layout_ok",
                      "ref_xover_reset", "ref_delay_size"):
             getattr(L, name).argtypes = [_vp]
+
+    # ---- late reverb / early reflections (BASELINE config 5)
+    def reverb(self, fs=48000.0, splits=(0.0, 0.0, 0.0)):
+        return RefReverb(self, fs, splits)
+
+    def erbus(self, fs, num_channels):
+        return RefERBus(self, fs, num_channels)
+
+    def db_to_gain(self, db):
+        d = np.ascontiguousarray(db, np.float32).reshape(-1, 4)
+        out = np.empty_like(d)
+        for i in range(d.shape[0]):
+            self.lib.ref_db_to_gain(d[i].ctypes.data, out[i].ctypes.data)
+        return out
+
+    def reverb_process_batch(self, buses, inp, out, frames, threads=1):
+        arr = (_vp * len(buses))(*[b.h for b in buses])
+        return self.lib.ref_reverb_process_batch(arr, len(buses), inp.ctypes.data, out.ctypes.data, out.shape[-1], frames, int(threads))
+
+    def erbus_process_batch(self, buses, inp, out, frames, threads=1):
+        arr = (_vp * len(buses))(*[b.h for b in buses])
+        return self.lib.ref_erbus_process_batch(arr, len(buses), inp.ctypes.data, out.ctypes.data, frames, int(threads))
 
     # ---- panners
     def panner(self, mask):
@@ -283,5 +322,66 @@ class RefDSE:
     def __del__(self):
         try:
             self.lib.ref_dse_destroy(self.h)
+        except Exception:
+            pass
+
+
+class RefReverb:
+    """ReverbBus (inc/Auralization/LateReverb.h:84-108)"""
+
+    def __init__(self, ref, fs, splits):
+        self.ref = ref
+        self.h = ref.lib.ref_reverb_create(_f32(fs), _f32(splits[0]), _f32(splits[1]), _f32(splits[2]))
+
+    def set_rt60(self, rt60):
+        a = np.ascontiguousarray(rt60, np.float32)
+        self.ref.lib.ref_reverb_set_rt60(self.h, a.ctypes.data)
+
+    def set_decay_slope(self, slope):
+        a = np.ascontiguousarray(slope, np.float32)
+        self.ref.lib.ref_reverb_set_decay_slope(self.h, a.ctypes.data)
+
+    def process(self, inp, out, frames, n_in=1):
+        """inp [frames][n_in]; out [frames][n_out] accumulated into"""
+        x = np.ascontiguousarray(inp, np.float32)
+        assert out.dtype == np.float32 and out.flags["C_CONTIGUOUS"]
+        self.ref.lib.ref_reverb_process(self.h, x.ctypes.data, n_in, out.ctypes.data, out.shape[-1], frames)
+
+    def __del__(self):
+        try:
+            if self.h:
+                self.ref.lib.ref_reverb_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+
+class RefERBus:
+    """ERBus (inc/Auralization/EarlyReflectionsBus.h:60-88)"""
+
+    def __init__(self, ref, fs, num_channels):
+        self.ref, self.L = ref, int(num_channels)
+        self.h = ref.lib.ref_erbus_create(_f32(fs), self.L)
+
+    def set_taps(self, filter_gains, delay_seconds, ids, gains):
+        fg = np.ascontiguousarray(filter_gains, np.float32).reshape(-1, 4)
+        d = np.ascontiguousarray(delay_seconds, np.float32).reshape(-1)
+        i = np.ascontiguousarray(ids, np.uint32).reshape(-1)
+        g = np.ascontiguousarray(gains, np.float32).reshape(-1, self.L) if len(i) else np.zeros((0, self.L), np.float32)
+        self.ref.lib.ref_erbus_set_taps(self.h, len(i), fg.ctypes.data, d.ctypes.data, i.ctypes.data, g.ctypes.data)
+
+    def num_taps(self):
+        return int(self.ref.lib.ref_erbus_num_taps(self.h))
+
+    def process(self, inp, out, frames, n_in=1):
+        x = np.ascontiguousarray(inp, np.float32)
+        assert out.dtype == np.float32 and out.flags["C_CONTIGUOUS"]
+        self.ref.lib.ref_erbus_process(self.h, x.ctypes.data, n_in, out.ctypes.data, frames)
+
+    def __del__(self):
+        try:
+            if self.h:
+                self.ref.lib.ref_erbus_destroy(self.h)
+                self.h = None
         except Exception:
             pass
