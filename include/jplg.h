@@ -277,6 +277,32 @@ JPLG_API jplg_status jplg_reverb_bank_decay_gains(jplg_reverb_bank b, float* out
  * out [n][frames][output_channels] interleaved, ACCUMULATED INTO like the reference's `output` span. */
 JPLG_API jplg_status jplg_reverb_bank_process(jplg_reverb_bank b, const float* in, uint32_t in_channels, float* out, uint32_t frames, int32_t mem);
 
+/* ---------------------------------------------------------------------------------------------- */
+/* ERBus x B  (replaces: inc/Auralization/EarlyReflectionsBus.h:45-249,                              */
+/*             src/Auralization/EarlyReflectionsBus.cpp:60-225 Prepare / ProcessInterleaved, :239-417 SetTaps) */
+
+/* Prepare(sampleRate, numChannels) for num_buses buses (:60-81). Every bus owns one mono ring (ring_size 0 = the reference's
+ * bit_ceil(2 * fs)) and max_taps_per_bus tap slots (rounded up to a power of two in [8, 128]; taps that are still fading
+ * out occupy a slot until the SetTaps call after their last chunk). */
+JPLG_API jplg_status jplg_erbus_bank_create(jplg_context ctx, uint32_t num_buses, uint32_t max_taps_per_bus, float sample_rate,
+                                            uint32_t output_channels, uint32_t ring_size, uint32_t max_block_frames, int32_t mode,
+                                            jplg_erbus_bank* out);
+JPLG_API void        jplg_erbus_bank_destroy(jplg_erbus_bank b);
+/* SetTaps(span<const ERUpdateData>) of bus `bus` (:239-406), host pointers: filter_gains [n][4], delay_seconds [n] (ERUpdateData::Delay),
+ * ids [n], gains [n][L]. Ids not in the list fade out over the next chunk and are then removed; new ids fade in from gain 0;
+ * known ids get new targets. Takes effect at the next process call, like the reference's RealtimeObject hand-over. */
+JPLG_API jplg_status jplg_erbus_bank_set_taps(jplg_erbus_bank b, uint32_t bus, uint32_t n, const float* filter_gains,
+                                              const float* delay_seconds, const uint32_t* ids, const float* gains);
+JPLG_API uint32_t    jplg_erbus_bank_num_taps(jplg_erbus_bank b, uint32_t bus);       /* GetNumTaps (incl. taps fading out) */
+JPLG_API uint32_t    jplg_erbus_bank_slots_per_bus(jplg_erbus_bank b);
+JPLG_API int32_t     jplg_erbus_bank_tap_slot(jplg_erbus_bank b, uint32_t bus, uint32_t id);  /* row of per_tap for this id, -1 if unknown */
+/* ProcessInterleaved(input, output, numInputChannels, numFrames) for all buses (:83-225). in [B][frames][in_channels]
+ * (down-mixed to mono per bus), out [B][frames][L] interleaved, ACCUMULATED INTO like the reference's `output` span. */
+JPLG_API jplg_status jplg_erbus_bank_process(jplg_erbus_bank b, const float* in, uint32_t in_channels, float* out, uint32_t frames, int32_t mem);
+/* Same, and every tap slot's own contribution: per_tap [B * slots_per_bus][frames][L] (overwritten; dead slots give zeros). */
+JPLG_API jplg_status jplg_erbus_bank_process_debug(jplg_erbus_bank b, const float* in, uint32_t in_channels, float* out, float* per_tap,
+                                                   uint32_t frames, int32_t mem);
+
 #ifdef __cplusplus
 }
 #endif

@@ -9,6 +9,7 @@ reference's component interface (same names / argument meaning, batched) on top 
     DirectSoundBatch                  inc/Auralization/DirectSound.h:41-125 (N effects at once)
     CrossoverBank, DelayBank          inc/Auralization/CrossoverFilter.h, DelayLine.h
     ReverbBusBatch                    inc/Auralization/LateReverb.h:34-117 (n FDN16 late-reverb buses)
+    ERBusBatch                        inc/Auralization/EarlyReflectionsBus.h:45-249 (B early-reflection buses x taps)
 
 There is NO CPU fallback: without the built library the import fails, without a GPU every data-path call raises.
 """
@@ -16,7 +17,7 @@ from ._capi import (  # noqa: F401
     JplgError, lib, lib_path, device_count, version,
     MEM_HOST, MEM_DEVICE, MODE_PARITY, MODE_THROUGHPUT,
     EChannel, ChannelMask, ChannelMap,
-    Context, VBAPanner, SourceLayout, DirectSoundBatch, CrossoverBank, DelayBank, ReverbBusBatch,
+    Context, VBAPanner, SourceLayout, DirectSoundBatch, CrossoverBank, DelayBank, ReverbBusBatch, ERBusBatch,
     add_and_apply_gain_ramp, apply_gain, normalize_weights, get_spread_from_source_size,
     STATE_FLOATS,
 )

@@ -514,6 +514,70 @@ class ReverbBusBatch:
             pass
 
 
+_sig("jplg_erbus_bank_create", _i32, [_vp, _u32, _u32, _f32, _u32, _u32, _u32, _i32, C.POINTER(_vp)])
+_sig("jplg_erbus_bank_destroy", None, [_vp])
+_sig("jplg_erbus_bank_set_taps", _i32, [_vp, _u32, _u32, _fp, _fp, _vp, _fp])
+_sig("jplg_erbus_bank_num_taps", _u32, [_vp, _u32])
+_sig("jplg_erbus_bank_slots_per_bus", _u32, [_vp])
+_sig("jplg_erbus_bank_tap_slot", _i32, [_vp, _u32, _u32])
+_sig("jplg_erbus_bank_process", _i32, [_vp, _fp, _u32, _fp, _u32, _i32])
+_sig("jplg_erbus_bank_process_debug", _i32, [_vp, _fp, _u32, _fp, _fp, _u32, _i32])
+
+
+def _out_arg(out):
+    if _is_torch(out):
+        assert out.is_contiguous()
+        return out.data_ptr(), (MEM_DEVICE if out.is_cuda else MEM_HOST)
+    assert out.dtype == np.float32 and out.flags["C_CONTIGUOUS"]
+    return out.ctypes.data, MEM_HOST
+
+
+class ERBusBatch:
+    """B x ERBus (inc/Auralization/EarlyReflectionsBus.h:45-249): early-reflection taps on one mono delay line per bus"""
+
+    def __init__(self, ctx, num_buses, max_taps_per_bus, sample_rate, num_channels, ring_size=0, max_block_frames=512, mode=MODE_PARITY):
+        self.ctx, self.B, self.L = ctx, int(num_buses), int(num_channels)
+        h = _vp()
+        ctx.check(lib.jplg_erbus_bank_create(ctx.h, self.B, int(max_taps_per_bus), float(sample_rate), self.L, int(ring_size),
+                                             int(max_block_frames), int(mode), C.byref(h)))
+        self.h = h
+        self.slots_per_bus = int(lib.jplg_erbus_bank_slots_per_bus(h))
+
+    def SetTaps(self, bus, filter_gains, delay_seconds, ids, gains):
+        ids = np.ascontiguousarray(ids, np.uint32).reshape(-1)
+        n = len(ids)
+        fg = np.ascontiguousarray(filter_gains, np.float32).reshape(n, 4) if n else np.zeros((0, 4), np.float32)
+        d = np.ascontiguousarray(delay_seconds, np.float32).reshape(n) if n else np.zeros(0, np.float32)
+        g = np.ascontiguousarray(gains, np.float32).reshape(n, self.L) if n else np.zeros((0, self.L), np.float32)
+        self.ctx.check(lib.jplg_erbus_bank_set_taps(self.h, int(bus), n, fg.ctypes.data, d.ctypes.data, ids.ctypes.data, g.ctypes.data))
+
+    def GetNumTaps(self, bus):
+        return int(lib.jplg_erbus_bank_num_taps(self.h, int(bus)))
+
+    def tap_slot(self, bus, tap_id):
+        return int(lib.jplg_erbus_bank_tap_slot(self.h, int(bus), int(tap_id)))
+
+    def ProcessInterleaved(self, inp, out, frames, in_channels=1, per_tap=None):
+        """inp [B][frames][in_channels], out [B][frames][L] accumulated into; per_tap [B*slots_per_bus][frames][L] (debug)"""
+        a, mem_a, _k = _arg(inp)
+        o, mem_o = _out_arg(out)
+        assert mem_a == mem_o, "input and output must live in the same memory space"
+        if per_tap is None:
+            self.ctx.check(lib.jplg_erbus_bank_process(self.h, a, int(in_channels), o, int(frames), mem_a))
+        else:
+            p, mem_p = _out_arg(per_tap)
+            assert mem_p == mem_a
+            self.ctx.check(lib.jplg_erbus_bank_process_debug(self.h, a, int(in_channels), o, p, int(frames), mem_a))
+
+    def __del__(self):
+        try:
+            if self.h:
+                lib.jplg_erbus_bank_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+
 class CrossoverBank:
     """n x FourBandCrossover (inc/Auralization/CrossoverFilter.h:416-535)"""
 

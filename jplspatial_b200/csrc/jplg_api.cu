@@ -1162,4 +1162,259 @@ jplg_status jplg_reverb_bank_process(jplg_reverb_bank b, const float* in, uint32
 	return JPLG_OK;
 }
 
+//==================================================================================================
+// ERBus bank (EarlyReflectionsBus.h:45-249, EarlyReflectionsBus.cpp:83-417): B buses x up to T taps, every tap = smoothed fractional
+// delay + four-band filter + gain-ramped pan reading the bus' ONE mono ring. The taps run through k_render (scPerRing = T,
+// plain pushes, one mix group per bus); this layer restates SetTaps' add / update / fade-out bookkeeping on slots.
+struct ErTap { uint32_t id, slot; int state; };          // state: 1 Rendering, 2 FadingOut, 0 Stopped (realtime side finished the fade)
+struct jplg_erbus_bank_t
+{
+	jplg_context ctx; uint32_t B, T, L, ringSize, maxFrames; int mode; float sampleRate, alpha, coef[27];
+	float *state = nullptr, *curMix = nullptr, *tgtMix = nullptr, *tgtDelay = nullptr, *tgtBand = nullptr, *rings = nullptr, *busOut = nullptr,
+		  *stageIn = nullptr, *stageOut = nullptr, *stagePer = nullptr;
+	uint8_t* flags = nullptr; uint32_t* initList = nullptr;
+	size_t stagePerFloats = 0, stageInFloats = 0;
+	uint64_t pos = 0;
+	// host mirrors (SoA like the device arrays) + per-bus tap tables
+	std::vector<float> hMix, hDelay, hBand; std::vector<uint8_t> hFlags; std::vector<uint32_t> hInit;
+	std::vector<std::vector<ErTap>> taps; std::vector<std::vector<uint32_t>> freeSlots;
+	bool dirty = true;
+};
+static void FreeErBus(jplg_erbus_bank b)
+{
+	for (float* p : { b->state, b->curMix, b->tgtMix, b->tgtDelay, b->tgtBand, b->rings, b->busOut, b->stageIn, b->stageOut, b->stagePer }) if (p) cudaFree(p);
+	if (b->flags) cudaFree(b->flags);
+	if (b->initList) cudaFree(b->initList);
+}
+static uint32_t BitCeil(uint32_t v) { uint32_t p = 1; while (p < v) p <<= 1; return p; }
+
+jplg_status jplg_erbus_bank_create(jplg_context ctx, uint32_t num_buses, uint32_t max_taps_per_bus, float sample_rate, uint32_t output_channels,
+								   uint32_t ring_size, uint32_t max_block_frames, int32_t mode, jplg_erbus_bank* out)
+{
+	if (!ctx || !out || num_buses == 0 || max_taps_per_bus == 0 || !(sample_rate > 0.0f)) return JPLG_ERR_INVALID_ARGUMENT;
+	if (output_channels == 0 || output_channels > kMaxChannelsDev) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "jplg_erbus_bank_create: output_channels must be 1..32");
+	if (max_taps_per_bus > 128) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "jplg_erbus_bank_create: at most 128 taps per bus (one CTA renders a whole bus)");
+	if (ring_size && (ring_size & (ring_size - 1))) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "jplg_erbus_bank_create: ring_size must be a power of two");
+	JPLG_NEED_DEVICE(ctx);
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	auto* b = new jplg_erbus_bank_t{};
+	b->ctx = ctx; b->B = num_buses; b->L = output_channels; b->mode = mode; b->sampleRate = sample_rate;
+	// slots per bus: a power of two so that 128 / T buses share a CTA; at least 8 so every bus gets its own mix subset
+	b->T = std::max(8u, BitCeil(max_taps_per_bus));
+	b->ringSize = ring_size ? ring_size : BitCeil(static_cast<uint32_t>(sample_rate * 2.0f));   // DelayLineType(sampleRate * 2) (EarlyReflectionsBus.cpp:74)
+	b->maxFrames = max_block_frames ? max_block_frames : 512;
+	b->alpha = ExpAlpha(kChunkFrames);                                   // CreateExpSmoothing(d, d, cScratchSize) (:452)
+	CrossoverCoefficients(sample_rate, 176.0f, 775.0f, 3408.0f, b->coef); // Filter.Prepare(mSampleRate) (:450)
+	const size_t nsc = size_t(b->B) * b->T, L = b->L;
+	auto alloc = [&](float** p, size_t floats) { return cudaMalloc(reinterpret_cast<void**>(p), floats * 4) == cudaSuccess; };
+	const bool ok = alloc(&b->state, nsc * kStateFloats) && alloc(&b->curMix, nsc * L) && alloc(&b->tgtMix, nsc * L) && alloc(&b->tgtDelay, nsc) && alloc(&b->tgtBand, nsc * 4)
+		&& alloc(&b->rings, size_t(b->B) * b->ringSize) && alloc(&b->busOut, size_t(b->B) * b->maxFrames * L) && alloc(&b->stageOut, size_t(b->B) * b->maxFrames * L)
+		&& cudaMalloc(reinterpret_cast<void**>(&b->flags), nsc) == cudaSuccess && cudaMalloc(reinterpret_cast<void**>(&b->initList), nsc * 4) == cudaSuccess;
+	if (!ok) { cudaGetLastError(); FreeErBus(b); delete b; return Fail(ctx, JPLG_ERR_OUT_OF_MEMORY, "jplg_erbus_bank_create: device allocation failed"); }
+	JPLG_CUDA_TRY(ctx, cudaMemsetAsync(b->state, 0, nsc * kStateFloats * 4, ctx->stream));
+	JPLG_CUDA_TRY(ctx, cudaMemsetAsync(b->curMix, 0, nsc * L * 4, ctx->stream));
+	JPLG_CUDA_TRY(ctx, cudaMemsetAsync(b->rings, 0, size_t(b->B) * b->ringSize * 4, ctx->stream));
+	JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	b->hMix.assign(nsc * L, 0.0f); b->hDelay.assign(nsc, 0.0f); b->hBand.assign(nsc * 4, 1.0f); b->hFlags.assign(nsc, 0);
+	b->taps.resize(b->B); b->freeSlots.resize(b->B);
+	for (uint32_t i = 0; i < b->B; ++i) for (uint32_t t = b->T; t-- > 0;) b->freeSlots[i].push_back(t);
+	*out = b;
+	return JPLG_OK;
+}
+void jplg_erbus_bank_destroy(jplg_erbus_bank b)
+{
+	if (!b) return;
+	cudaSetDevice(b->ctx->device);
+	cudaStreamSynchronize(b->ctx->stream);
+	FreeErBus(b);
+	delete b;
+}
+uint32_t jplg_erbus_bank_num_taps(jplg_erbus_bank b, uint32_t bus) { return (b && bus < b->B) ? static_cast<uint32_t>(b->taps[bus].size()) : 0; }
+uint32_t jplg_erbus_bank_slots_per_bus(jplg_erbus_bank b) { return b ? b->T : 0; }
+
+// ERBus::SetTaps (EarlyReflectionsBus.cpp:239-406) for one bus; host pointers.
+jplg_status jplg_erbus_bank_set_taps(jplg_erbus_bank b, uint32_t bus, uint32_t n, const float* filter_gains, const float* delay_seconds,
+									 const uint32_t* ids, const float* gains)
+{
+	if (!b || bus >= b->B || (n && (!filter_gains || !delay_seconds || !ids || !gains))) return JPLG_ERR_INVALID_ARGUMENT;
+	jplg_context ctx = b->ctx;
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	const size_t nsc = size_t(b->B) * b->T; const uint32_t L = b->L;
+	auto& taps = b->taps[bus];
+	auto slotIndex = [&](uint32_t slot) { return size_t(bus) * b->T + slot; };
+	// 1.-2. taps whose fade-out has been rendered are erased and their slot is released (:246-322)
+	for (size_t i = 0; i < taps.size();)
+	{
+		if (taps[i].state == 0) { b->hFlags[slotIndex(taps[i].slot)] = 0; b->freeSlots[bus].push_back(taps[i].slot); taps.erase(taps.begin() + i); }
+		else ++i;
+	}
+	auto inNew = [&](uint32_t id) { for (uint32_t k = 0; k < n; ++k) if (ids[k] == id) return true; return false; };
+	// 3. taps that are no longer requested fade out: target channel gains 0, one more chunk is rendered (:329-343)
+	for (auto& t : taps)
+	{
+		if (inNew(t.id) || t.state == 2) continue;
+		const size_t sc = slotIndex(t.slot);
+		for (uint32_t c = 0; c < L; ++c) b->hMix[size_t(c) * nsc + sc] = 0.0f;
+		t.state = 2; b->hFlags[sc] = 1 | 2;
+	}
+	// 4.-6. update existing taps, create new ones (:352-400)
+	uint32_t needed = 0;
+	for (uint32_t k = 0; k < n; ++k) { bool found = false; for (auto& t : taps) if (t.id == ids[k]) found = true; if (!found) ++needed; }
+	if (needed > b->freeSlots[bus].size())
+		return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "jplg_erbus_bank_set_taps: more simultaneous taps (incl. taps still fading out) than slots per bus");
+	for (uint32_t k = 0; k < n; ++k)
+	{
+		ErTap* hit = nullptr;
+		for (auto& t : taps) if (t.id == ids[k]) { hit = &t; break; }
+		if (hit && hit->state == 2) continue;   // a fading tap cannot be restarted (the reference asserts this path dead, :366-376); it is re-created once erased
+		if (!hit)
+		{
+			const uint32_t slot = b->freeSlots[bus].back(); b->freeSlots[bus].pop_back();
+			taps.push_back({ ids[k], slot, 1 });
+			hit = &taps.back();
+			b->hInit.push_back(static_cast<uint32_t>(slotIndex(slot)));   // AllocateRTData: current = target delay / filter gains, channel gains 0 (:421-455)
+		}
+		const size_t sc = slotIndex(hit->slot);
+		for (uint32_t q = 0; q < 4; ++q) b->hBand[size_t(q) * nsc + sc] = filter_gains[4 * size_t(k) + q];
+		for (uint32_t c = 0; c < L; ++c) b->hMix[size_t(c) * nsc + sc] = gains[size_t(k) * L + c];
+		b->hDelay[sc] = delay_seconds[k] * b->sampleRate;                 // newER.Delay * mSampleRate (:383,393)
+		b->hFlags[sc] = 1;
+	}
+	b->dirty = true;
+	return JPLG_OK;
+}
+
+// new slots: the realtime state AllocateRTData builds (EarlyReflectionsBus.cpp:421-455)
+__global__ void k_er_init_slots(const uint32_t* __restrict__ slots, uint32_t n, uint32_t numSC, uint32_t L, const float* __restrict__ tgtDelay,
+								const float* __restrict__ tgtBand, float* __restrict__ state, float* __restrict__ curMix)
+{
+	const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	const uint32_t sc = slots[i];
+	for (uint32_t k = 0; k < kStateFloats; ++k) state[size_t(k) * numSC + sc] = 0.0f;             // Filter.Prepare, CreateTap: zero state
+	state[size_t(ST_DELAY) * numSC + sc] = tgtDelay[sc];                                           // CreateExpSmoothing(delay, delay, ..)
+	for (uint32_t q = 0; q < 4; ++q) state[size_t(ST_BAND + q) * numSC + sc] = tgtBand[size_t(q) * numSC + sc];   // FilterGains = filterGains
+	for (uint32_t c = 0; c < L; ++c) curMix[size_t(c) * numSC + sc] = 0.0f;                        // ChannelGains filled with 0: the tap fades in
+}
+// ERBus::ProcessInterleaved head (EarlyReflectionsBus.cpp:100-122): down-mix to mono, ApplyGain(1 / numInputChannels), push
+__global__ void k_er_push(float* __restrict__ rings, const float* __restrict__ in, uint32_t numBuses, uint32_t inCh, uint32_t frames,
+						  uint32_t ringSize, uint64_t pos)
+{
+	const uint64_t idx = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+	if (idx >= uint64_t(numBuses) * frames) return;
+	const uint32_t bus = static_cast<uint32_t>(idx / frames), f = static_cast<uint32_t>(idx - uint64_t(bus) * frames);
+	const float* x = in + (size_t(bus) * frames + f) * inCh;
+	float sample = 0.0f;
+	for (uint32_t ch = 0; ch < inCh; ++ch) sample += x[ch];
+	sample *= 1.0f / static_cast<float>(inCh);
+	rings[size_t(bus) * ringSize + (static_cast<uint32_t>(pos + f) & (ringSize - 1))] = sample;
+}
+__global__ void k_accumulate(float* __restrict__ dst, const float* __restrict__ src, size_t n)
+{
+	const size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+	if (i < n) dst[i] += src[i];
+}
+
+static jplg_status ErProcess(jplg_erbus_bank b, const float* in, uint32_t in_channels, float* out, float* perTap, uint32_t frames, int32_t mem)
+{
+	if (!b || (frames && (!in || !out)) || in_channels == 0) return JPLG_ERR_INVALID_ARGUMENT;
+	jplg_context ctx = b->ctx;
+	JPLG_NEED_DEVICE(ctx);
+	if (frames == 0) return JPLG_OK;
+	if (frames > b->maxFrames) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "jplg_erbus_bank_process: frames exceeds max_block_frames");
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	const uint32_t numSC = b->B * b->T, L = b->L;
+	const size_t nIn = size_t(b->B) * frames * in_channels, nOut = size_t(b->B) * frames * L, nPer = size_t(numSC) * frames * L;
+	// ---- SafeERsRead: the audio thread picks up the latest tap data (:141-143)
+	if (b->dirty)
+	{
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(b->tgtMix, b->hMix.data(), size_t(numSC) * L * 4, cudaMemcpyHostToDevice, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(b->tgtDelay, b->hDelay.data(), size_t(numSC) * 4, cudaMemcpyHostToDevice, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(b->tgtBand, b->hBand.data(), size_t(numSC) * 16, cudaMemcpyHostToDevice, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(b->flags, b->hFlags.data(), numSC, cudaMemcpyHostToDevice, ctx->stream));
+		if (!b->hInit.empty())
+		{
+			const uint32_t n = static_cast<uint32_t>(b->hInit.size());
+			JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(b->initList, b->hInit.data(), size_t(n) * 4, cudaMemcpyHostToDevice, ctx->stream));
+			k_er_init_slots<<<(n + 127) / 128, 128, 0, ctx->stream>>>(b->initList, n, numSC, L, b->tgtDelay, b->tgtBand, b->state, b->curMix); ctx->launches++;
+			JPLG_CUDA_TRY(ctx, cudaGetLastError());
+		}
+		JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));   // the host mirrors may be rewritten by the next set_taps
+		b->hInit.clear();
+		b->dirty = false;
+	}
+	const float* dIn = in; float* dOut = out; float* dPer = perTap;
+	if (mem == JPLG_MEM_HOST)
+	{
+		if (nIn > b->stageInFloats)
+		{
+			if (b->stageIn) cudaFree(b->stageIn);
+			b->stageIn = nullptr; b->stageInFloats = 0;
+			if (cudaMalloc(reinterpret_cast<void**>(&b->stageIn), nIn * 4) != cudaSuccess) { cudaGetLastError(); return Fail(ctx, JPLG_ERR_OUT_OF_MEMORY, "erbus input staging allocation failed"); }
+			b->stageInFloats = nIn;
+		}
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(b->stageIn, in, nIn * 4, cudaMemcpyHostToDevice, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(b->stageOut, out, nOut * 4, cudaMemcpyHostToDevice, ctx->stream));
+		dIn = b->stageIn; dOut = b->stageOut;
+		if (perTap)
+		{
+			if (nPer > b->stagePerFloats)
+			{
+				if (b->stagePer) cudaFree(b->stagePer);
+				b->stagePer = nullptr; b->stagePerFloats = 0;
+				if (cudaMalloc(reinterpret_cast<void**>(&b->stagePer), nPer * 4) != cudaSuccess) { cudaGetLastError(); return Fail(ctx, JPLG_ERR_OUT_OF_MEMORY, "per-tap debug buffer allocation failed"); }
+				b->stagePerFloats = nPer;
+			}
+			dPer = b->stagePer;
+		}
+	}
+	{
+		const uint64_t total = uint64_t(b->B) * frames;
+		TimeBegin(ctx, JPLG_K_ER_PUSH);
+		k_er_push<<<static_cast<uint32_t>((total + 255) / 256), 256, 0, ctx->stream>>>(b->rings, dIn, b->B, in_channels, frames, b->ringSize, b->pos);
+		TimeEnd(ctx); ctx->launches++;
+		JPLG_CUDA_TRY(ctx, cudaGetLastError());
+	}
+	RenderParams rp{};
+	rp.numSC = numSC; rp.srcChannels = 1; rp.L = L; rp.ringSize = b->ringSize; rp.ringMask = b->ringSize - 1; rp.pos = b->pos; rp.frames = frames;
+	rp.alpha = b->alpha; std::memcpy(rp.coef, b->coef, sizeof(rp.coef));
+	rp.state = b->state; rp.curMix = b->curMix; rp.tgtDelay = b->tgtDelay; rp.tgtBand = b->tgtBand; rp.tgtMix = b->tgtMix; rp.rings = b->rings;
+	rp.in = nullptr; rp.partial = b->busOut; rp.perSource = dPer;
+	rp.numCTAs = RenderNumCTAs(numSC, 1);
+	rp.scPerRing = b->T; rp.plainPush = 1; rp.groupsPerCTA = 128 / b->T; rp.numGroups = b->B; rp.flags = b->flags;
+	JPLG_LAUNCH(ctx, JPLG_K_RENDER, LaunchRender(rp, b->mode, 0, rp.numCTAs, ctx->stream));
+	k_accumulate<<<static_cast<uint32_t>((nOut + 255) / 256), 256, 0, ctx->stream>>>(dOut, b->busOut, nOut); ctx->launches++;   // the bus adds into `output`
+	JPLG_CUDA_TRY(ctx, cudaGetLastError());
+	b->pos += frames;
+	// a tap that was fading out has rendered its last chunk: realtime state Stopped (:218-220); SetTaps erases it next time
+	for (uint32_t bus = 0; bus < b->B; ++bus)
+		for (auto& t : b->taps[bus])
+			if (t.state == 2) { t.state = 0; b->hFlags[size_t(bus) * b->T + t.slot] = 0; b->dirty = true; }
+	if (mem == JPLG_MEM_HOST)
+	{
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(out, dOut, nOut * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		if (perTap) JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(perTap, dPer, nPer * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	}
+	return JPLG_OK;
+}
+jplg_status jplg_erbus_bank_process(jplg_erbus_bank b, const float* in, uint32_t in_channels, float* out, uint32_t frames, int32_t mem)
+{
+	return ErProcess(b, in, in_channels, out, nullptr, frames, mem);
+}
+jplg_status jplg_erbus_bank_process_debug(jplg_erbus_bank b, const float* in, uint32_t in_channels, float* out, float* per_tap, uint32_t frames, int32_t mem)
+{
+	if (!per_tap) return JPLG_ERR_INVALID_ARGUMENT;
+	return ErProcess(b, in, in_channels, out, per_tap, frames, mem);
+}
+// slot (row of per_tap) of the tap with this id, or -1
+int32_t jplg_erbus_bank_tap_slot(jplg_erbus_bank b, uint32_t bus, uint32_t id)
+{
+	if (!b || bus >= b->B) return -1;
+	for (auto& t : b->taps[bus]) if (t.id == id) return static_cast<int32_t>(bus * b->T + t.slot);
+	return -1;
+}
+
 } // extern "C"

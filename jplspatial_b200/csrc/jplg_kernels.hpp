@@ -70,6 +70,12 @@ namespace jplg
 		float* perSource;      // debug: [numSources][frames][L] or nullptr
 		uint32_t numCTAs;
 		uint32_t ctaBase;      // first CTA of this launch (set by LaunchRender)
+		// ---- generalisations used by the ERBus bank (all zero / null for N x DirectSoundEffect)
+		uint32_t scPerRing;    // consecutive source-channels that read the SAME ring (ER taps of one bus); 0 or 1 = one ring each
+		uint32_t plainPush;    // 1: a chunk pushes only its own frames (ERBus, EarlyReflectionsBus.cpp:119-122); 0: DirectSoundEffect's quirk
+		uint32_t groupsPerCTA; // mix groups per CTA (ER: buses per CTA = 128 / taps per bus), each with its own partial bus; 0 or 1 = one
+		uint32_t numGroups;    // total number of partial buses (groups) when groupsPerCTA > 1
+		const uint8_t* flags;  // per source-channel: bit 0 = live, bit 1 = fading out (rendered for the first chunk of the block only); null = all live
 	};
 
 	uint32_t RenderNumCTAs(uint32_t numSC, uint32_t srcChannels);
