@@ -140,15 +140,21 @@ namespace jplg
 		for (uint32_t t0 = 0; t0 < fp.frames; t0 += kFdnTile)
 		{
 			const uint32_t len = min(kFdnTile, fp.frames - t0);
-			// ---- stage in: warp w loads rows [32w, 32w+32): delayed[c][n] = pushed[n - 1 - D_c] (GetReadWindow<1>(D) before this frame's push)
-			for (uint32_t r = 0; r < 32; ++r)
+			// ---- stage in: warp w loads rows [32w, 32w+32): delayed[c][n] = pushed[n - 1 - D_c] (GetReadWindow<1>(D) before this frame's push).
+			// Eight independent loads are issued before the first dependent shared-memory store (DRAM latency is paid once per batch).
+			for (uint32_t r0 = 0; r0 < 32; r0 += 8)
 			{
-				const uint32_t row = warp * 32 + r, rInst = instBase + (row >> 4), rc = row & 15u;
-				if (rInst < fp.n && lane < len)
+				float v[8];
+				#pragma unroll
+				for (uint32_t r = 0; r < 8; ++r)
 				{
-					const float* ring = fp.rings + (size_t(rInst) * 16u + rc) * kFdnRingSize;
-					sDel[row][lane] = ring[(pos32 + t0 + lane - 1u - cFdnDelays[rc]) & ringMask];
+					const uint32_t row = warp * 32 + r0 + r, rInst = instBase + (row >> 4), rc = row & 15u;
+					v[r] = 0.0f;
+					if (rInst < fp.n && lane < len)
+						v[r] = __ldcs(fp.rings + (size_t(rInst) * 16u + rc) * kFdnRingSize + ((pos32 + t0 + lane - 1u - cFdnDelays[rc]) & ringMask));
 				}
+				#pragma unroll
+				for (uint32_t r = 0; r < 8; ++r) sDel[warp * 32 + r0 + r][lane] = v[r];
 			}
 			for (uint32_t e = tid; e < kFdnInstPerCTA * kFdnTile; e += blockDim.x)
 			{
@@ -190,14 +196,30 @@ namespace jplg
 				if (rInst < fp.n && lane < len)
 					fp.rings[(size_t(rInst) * 16u + rc) * kFdnRingSize + ((pos32 + t0 + lane) & ringMask)] = sDel[row][lane];
 			}
-			for (uint32_t e = tid; e < kFdnInstPerCTA * len * L; e += blockDim.x)
+			const uint32_t perInst = len * L, total = kFdnInstPerCTA * perInst;
+			for (uint32_t e0 = tid; e0 < total; e0 += blockDim.x * 4)
 			{
-				const uint32_t i = e / (len * L), rem = e - i * (len * L), f = rem / L, oc = rem - f * L;
-				if (instBase + i >= fp.n) continue;
-				float* o = fp.out + (size_t(instBase + i) * fp.frames + t0 + f) * L + oc;
-				float acc = *o;                                         // out[i % numOut] += fdn[i], i ascending
-				for (uint32_t k = oc; k < 16; k += L) acc += sOut[i][f][k];
-				*o = acc;
+				// four independent read-modify-writes in flight per thread
+				float prev[4]; float* ptr[4]; uint32_t ii[4], ff[4], oc[4];
+				#pragma unroll
+				for (uint32_t q = 0; q < 4; ++q)
+				{
+					const uint32_t e = e0 + q * blockDim.x;
+					ptr[q] = nullptr;
+					if (e >= total) continue;
+					ii[q] = e / perInst; const uint32_t rem = e - ii[q] * perInst; ff[q] = rem / L; oc[q] = rem - ff[q] * L;
+					if (instBase + ii[q] >= fp.n) continue;
+					ptr[q] = fp.out + (size_t(instBase + ii[q]) * fp.frames + t0 + ff[q]) * L + oc[q];
+					prev[q] = *ptr[q];
+				}
+				#pragma unroll
+				for (uint32_t q = 0; q < 4; ++q)
+				{
+					if (!ptr[q]) continue;
+					float acc = prev[q];                                 // out[i % numOut] += fdn[i], i ascending
+					for (uint32_t k = oc[q]; k < 16; k += L) acc += sOut[ii[q]][ff[q]][k];
+					*ptr[q] = acc;
+				}
 			}
 			__syncthreads();
 		}
