@@ -137,6 +137,7 @@ namespace jplg
 		#pragma unroll
 		for (int k = 0; k < 4; ++k) g[k] = active ? fp.decay[size_t(k) * nCh + ch] : 0.0f;
 
+		const uint32_t oFrame0 = tid / L, oChan0 = tid - oFrame0 * L, oStepFrame = (kFdnInstPerCTA * 16) / L, oStepChan = (kFdnInstPerCTA * 16) - oStepFrame * L;
 		for (uint32_t t0 = 0; t0 < fp.frames; t0 += kFdnTile)
 		{
 			const uint32_t len = min(kFdnTile, fp.frames - t0);
@@ -163,7 +164,8 @@ namespace jplg
 			}
 			__syncthreads();
 
-			// ---- compute: one thread per (instance, channel), frames in order
+			// ---- compute, pass 1 (no time recurrence): the feedback mix and the output mix only need the delayed samples, so every
+			//      frame of the tile is independent here. x[f] overwrites the delayed sample in place.
 			for (uint32_t f = 0; f < len; ++f)
 			{
 				const float d = sDel[tid][f];
@@ -175,9 +177,8 @@ namespace jplg
 				s2 = s2 + __shfl_xor_sync(0xffffffffu, s2, 8);
 				m = (2.0f * m - s2) * 0.25f;
 				// FDNInput::InjectNormalized: every channel gets monoInput * sqrt(1/16) (ReverbDesign.h:455-459)
-				const float x = m + sIn[tid >> 4][f] * 0.25f;
-				sDel[tid][f] = xover_process_sample<MODE>(fp.coef, st, x, g);   // AttenuationFilter::Process, then Push (ReverbDesign.h:696-699)
-				// FDNOutputMixer::Mix (ReverbDesign.h:480-492): Hadamard of the delayed samples (RecursiveUnscaled :391-437), * sqrt(1/16)
+				sDel[tid][f] = m + sIn[tid >> 4][f] * 0.25f;
+				// FDNOutputMixer::Mix (ReverbDesign.h:480-492): Hadamard of the delayed samples (RecursiveUnscaled :391-437), * scalingFactor
 				float h = d;
 				#pragma unroll
 				for (uint32_t bit = 1; bit < 16; bit <<= 1)
@@ -187,6 +188,14 @@ namespace jplg
 				}
 				sOut[tid >> 4][f][c] = h * fp.hadamardScale;
 			}
+			// ---- pass 2: AttenuationFilter::Process per channel, frames in order (the only time recurrence); unrolled so the filter
+			//      stages of neighbouring frames overlap. The result is the sample Push()ed into the ring (ReverbDesign.h:696-699).
+			if (len == kFdnTile)
+			{
+				#pragma unroll 8
+				for (uint32_t f = 0; f < kFdnTile; ++f) sDel[tid][f] = xover_process_sample<MODE>(fp.coef, st, sDel[tid][f], g);
+			}
+			else for (uint32_t f = 0; f < len; ++f) sDel[tid][f] = xover_process_sample<MODE>(fp.coef, st, sDel[tid][f], g);
 			__syncthreads();
 
 			// ---- stage out: push the new samples (ring index = push count), fold the mixed FDN channels into the output frames
@@ -196,30 +205,26 @@ namespace jplg
 				if (rInst < fp.n && lane < len)
 					fp.rings[(size_t(rInst) * 16u + rc) * kFdnRingSize + ((pos32 + t0 + lane) & ringMask)] = sDel[row][lane];
 			}
-			const uint32_t perInst = len * L, total = kFdnInstPerCTA * perInst;
-			for (uint32_t e0 = tid; e0 < total; e0 += blockDim.x * 4)
+			// an instance's tile of output frames is one contiguous run of len * L floats: thread -> elements tid, tid + 128, ... of every
+			// instance ((frame, channel) advance incrementally, no divisions); the 8 instances' read-modify-writes are independent
+			const uint32_t perInst = len * L;
+			uint32_t ff = oFrame0, oc = oChan0;
+			for (uint32_t idx = tid; idx < perInst; idx += kFdnInstPerCTA * 16)
 			{
-				// four independent read-modify-writes in flight per thread
-				float prev[4]; float* ptr[4]; uint32_t ii[4], ff[4], oc[4];
+				float prev[kFdnInstPerCTA];
 				#pragma unroll
-				for (uint32_t q = 0; q < 4; ++q)
-				{
-					const uint32_t e = e0 + q * blockDim.x;
-					ptr[q] = nullptr;
-					if (e >= total) continue;
-					ii[q] = e / perInst; const uint32_t rem = e - ii[q] * perInst; ff[q] = rem / L; oc[q] = rem - ff[q] * L;
-					if (instBase + ii[q] >= fp.n) continue;
-					ptr[q] = fp.out + (size_t(instBase + ii[q]) * fp.frames + t0 + ff[q]) * L + oc[q];
-					prev[q] = *ptr[q];
-				}
+				for (uint32_t i = 0; i < kFdnInstPerCTA; ++i)
+					if (instBase + i < fp.n) prev[i] = fp.out[(size_t(instBase + i) * fp.frames + t0) * L + idx];
 				#pragma unroll
-				for (uint32_t q = 0; q < 4; ++q)
+				for (uint32_t i = 0; i < kFdnInstPerCTA; ++i)
 				{
-					if (!ptr[q]) continue;
-					float acc = prev[q];                                 // out[i % numOut] += fdn[i], i ascending
-					for (uint32_t k = oc[q]; k < 16; k += L) acc += sOut[ii[q]][ff[q]][k];
-					*ptr[q] = acc;
+					if (instBase + i >= fp.n) continue;
+					float acc = prev[i];                                 // out[i % numOut] += fdn[i], i ascending
+					for (uint32_t k = oc; k < 16; k += L) acc += sOut[i][ff][k];
+					fp.out[(size_t(instBase + i) * fp.frames + t0) * L + idx] = acc;
 				}
+				ff += oStepFrame; oc += oStepChan;
+				if (oc >= L) { oc -= L; ++ff; }
 			}
 			__syncthreads();
 		}
