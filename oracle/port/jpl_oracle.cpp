@@ -960,4 +960,185 @@ extern "C"
 		for (uint32_t t = 0; t < T; ++t) for (size_t k = 0; k < part[t].size(); ++k) bus[k] += part[t][k];
 		return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 	}
+	/* ================================================================================================
+	 * ReverbBus (src/Auralization/LateReverb.cpp:31-134) + MultiChannelMixedFeedback<16> (inc/Auralization/ReverbDesign.h:573-704) */
+
+	/* JPL::exp(simd), one lane (inc/Math/SIMDMath.h:296-316; SSE2 floor inc/Math/SIMD.h:1861-1879); FMA call sites unfused (SSE2 build) */
+	static float expLane(float x)
+	{
+		x = std::min(std::max(x, -88.3762626647949f), 88.3762626647949f);
+		const float v = x * 1.44269504088896341f + 0.5f;
+		const float tr = float(int32_t(v));
+		const float n = (v == 0.0f) ? v : tr - (tr > v ? 1.0f : 0.0f);
+		x = x - (n * 0.693359375f + n * -2.12194440e-4f);
+		const float x2 = x * x;
+		float y = 1.9875691500e-4f;
+		y = y * x + 1.3981999507e-3f; y = y * x + 8.3334519073e-3f; y = y * x + 4.1665795894e-2f;
+		y = y * x + 1.6666665459e-1f; y = y * x + 5.0000001201e-1f;
+		y = y * x2 + (x + 1.0f);
+		const int32_t e = (int32_t(n) + 0x7f) << 23;
+		float p; std::memcpy(&p, &e, 4);
+		return y * p;
+	}
+	void orc_db_to_gain(const float* db, uint32_t n, float* out) /* inc/Math/DecibelsAndGain.h:40-56 */
+	{
+		const float ln10div20 = 2.302585092994046f * 0.05f;
+		for (uint32_t i = 0; i < n; ++i) out[i] = expLane(ln10div20 * db[i]);
+	}
+	/* Math::Sqrt<double, 2> as evaluated at compile time for Hadamard's scalingFactor (inc/Math/Math.h:213-262; ReverbDesign.h:443-446) */
+	static float hadamardScale16()
+	{
+		const double x = 1.0 / 16.0; uint64_t i; std::memcpy(&i, &x, 8);
+		i = 0x5fe6eb50c7b537a9ull - (i >> 1);
+		double y; std::memcpy(&y, &i, 8);
+		for (int k = 0; k < 2; ++k) y = y * (1.5 - 0.5 * x * y * y);
+		return float(x * y);
+	}
+	static const uint32_t kFdnDelays[16] = { 2927, 2593, 2273, 3697, 1877, 3877, 2477, 3461, 1609, 3779, 3541, 4259, 1669, 3539, 3637, 4013 }; /* ReverbDesign.h:578-581 */
+
+	struct orc_reverb
+	{
+		float fs, invFs, coef[27], slope[4], gains[16][4], st[16][24];
+		std::vector<float> ring[16]; uint32_t w[16];
+	};
+	orc_reverb* orc_reverb_create(float fs, float f1, float f2, float f3) /* Prepare (LateReverb.cpp:42-48) */
+	{
+		auto* r = new orc_reverb();
+		r->fs = fs; r->invFs = 1.0f / fs;
+		orc_xover_coeffs(fs, f1 > 0 ? f1 : 176.0f, f2 > 0 ? f2 : 775.0f, f3 > 0 ? f3 : 3408.0f, r->coef);
+		for (int c = 0; c < 16; ++c) { r->ring[c].assign(8192, 0.0f); r->w[c] = 0; std::memset(r->st[c], 0, sizeof(r->st[c])); }
+		for (int k = 0; k < 4; ++k) r->slope[k] = -60.0f;
+		return r;
+	}
+	void orc_reverb_destroy(orc_reverb* r) { delete r; }
+	void orc_reverb_set_rt60(orc_reverb* r, const float rt60[4]) { for (int k = 0; k < 4; ++k) r->slope[k] = -60.0f / std::min(std::max(rt60[k], 0.03f), 10.0f); } /* :31-35 */
+	void orc_reverb_set_decay_slope(orc_reverb* r, const float s[4]) { for (int k = 0; k < 4; ++k) r->slope[k] = std::min(std::max(s[k], -60.0f / 0.03f), -60.0f / 10.0f); } /* :37-40 */
+	/* mono in [frames]; out [frames][nOut] accumulated into */
+	void orc_reverb_process(orc_reverb* r, const float* in, float* out, uint32_t nOut, uint32_t frames)
+	{
+		for (int c = 0; c < 16; ++c) /* UpdateFilterParameters (ReverbDesign.h:619-628, LateReverb.h:64-68) */
+		{
+			const float delaySeconds = float(kFdnDelays[c]) * r->invFs;
+			float db[4]; for (int k = 0; k < 4; ++k) db[k] = r->slope[k] * delaySeconds;
+			orc_db_to_gain(db, 4, r->gains[c]);
+		}
+		const float hs = hadamardScale16();
+		for (uint32_t f = 0; f < frames; ++f)
+		{
+			const float inj = in[f] * 0.25f; /* InjectNormalized (ReverbDesign.h:455-459) */
+			float delayed[16], mixed[16];
+			for (int c = 0; c < 16; ++c) delayed[c] = r->ring[c][(r->w[c] - 1u - kFdnDelays[c]) & 8191u]; /* GetReadWindow<1>(D) */
+			/* Householder::MixInPlace 16-special (:311-349) */
+			for (int c = 0; c < 16; ++c) mixed[c] = delayed[c];
+			for (int g = 0; g < 16; g += 4) { const float sum = (mixed[g] + mixed[g + 1]) + (mixed[g + 2] + mixed[g + 3]); for (int k = 0; k < 4; ++k) mixed[g + k] = 2.0f * mixed[g + k] + (-sum); }
+			for (int lane = 0; lane < 4; ++lane)
+			{
+				float v[4] = { mixed[lane], mixed[lane + 4], mixed[lane + 8], mixed[lane + 12] };
+				const float sum = (v[0] + v[1]) + (v[2] + v[3]);
+				for (int k = 0; k < 4; ++k) mixed[lane + 4 * k] = (2.0f * v[k] + (-sum)) * 0.25f;
+			}
+			for (int c = 0; c < 16; ++c) /* AttenuationFilter::Process = FourBandCrossover::ProcessSample, then Push (:696-699) */
+			{
+				const float x = mixed[c] + inj;
+				float b[4]; orc_xover_split(r->coef, r->st[c], &x, 1, b);
+				const float* g = r->gains[c];
+				const float sum = (b[0] * g[0] + b[1] * g[1]) + (b[2] * g[2] + b[3] * g[3]);
+				r->ring[c][r->w[c] & 8191u] = sum; ++r->w[c];
+			}
+			/* FDNOutputMixer::Mix (:480-492): Hadamard::RecursiveUnscaled (:391-437), scale, fold */
+			float h[16]; for (int c = 0; c < 16; ++c) h[c] = delayed[c];
+			for (int half = 1; half < 16; half <<= 1)
+				for (int base = 0; base < 16; base += 2 * half)
+					for (int i = 0; i < half; ++i) { const float a = h[base + i], bb = h[base + i + half]; h[base + i] = a + bb; h[base + i + half] = a - bb; }
+			for (int i = 0; i < 16; ++i) out[size_t(f) * nOut + (i % nOut)] += h[i] * hs;
+		}
+	}
+
+	/* ================================================================================================
+	 * ERBus (src/Auralization/EarlyReflectionsBus.cpp:83-417) */
+	struct orc_er_tap { uint32_t id; int tgtState, rtState; float tgtBand[4], curBand[4], tgtDelay, curDelay, y1, st[24]; std::vector<float> tgtMix, curMix; };
+	struct orc_erbus { float fs, alpha, coef[27]; uint32_t L, ringSize, w; std::vector<float> ring; std::vector<orc_er_tap> taps; };
+	orc_erbus* orc_erbus_create(float fs, uint32_t L)
+	{
+		auto* b = new orc_erbus();
+		b->fs = fs; b->L = L; b->alpha = orc_smoother_alpha(480);
+		orc_xover_coeffs(fs, 176.0f, 775.0f, 3408.0f, b->coef);
+		uint32_t sz = 1; while (sz < uint32_t(fs * 2.0f)) sz <<= 1; /* DelayLineType(sampleRate * 2) (:74) */
+		b->ringSize = sz; b->ring.assign(sz, 0.0f); b->w = 0;
+		return b;
+	}
+	void orc_erbus_destroy(orc_erbus* b) { delete b; }
+	uint32_t orc_erbus_num_taps(const orc_erbus* b) { return uint32_t(b->taps.size()); }
+	/* SetTaps (:239-406); states: 0 Stopped, 1 Rendering, 2 FadingOut */
+	void orc_erbus_set_taps(orc_erbus* b, uint32_t n, const float* filterGains, const float* delaySeconds, const uint32_t* ids, const float* gains)
+	{
+		const uint32_t L = b->L;
+		/* :246-322: taps whose fade-out has been rendered are dropped; EraseIf (:616-633) is a std::partition + erase of the tail, so it
+		 * reorders the survivors the way the library algorithm does */
+		b->taps.erase(std::partition(b->taps.begin(), b->taps.end(), [](const orc_er_tap& t) { return t.rtState != 0; }), b->taps.end());
+		auto wanted = [&](uint32_t id) { for (uint32_t k = 0; k < n; ++k) if (ids[k] == id) return true; return false; };
+		/* PartitionERs (:556-566): std::partition reorders the taps (requested ones first); the order is observable because every tap
+		 * adds into the output in vector order (float sums are not associative), so the same library algorithm is used here */
+		std::partition(b->taps.begin(), b->taps.end(), [&](const orc_er_tap& t) { return wanted(t.id); });
+		for (auto& t : b->taps) /* stale taps fade out (:329-343) */
+			if (!wanted(t.id) && t.rtState != 2 && t.tgtState != 2) { std::fill(t.tgtMix.begin(), t.tgtMix.end(), 0.0f); t.tgtState = 2; }
+		for (uint32_t k = 0; k < n; ++k)
+		{
+			orc_er_tap* hit = nullptr;
+			for (auto& t : b->taps) if (t.id == ids[k]) { hit = &t; break; }
+			if (hit && hit->tgtState == 2) continue; /* dead path in the reference (:366-376) */
+			if (!hit)
+			{
+				orc_er_tap t{}; t.id = ids[k]; t.tgtState = 1; t.rtState = 1;
+				t.curMix.assign(L, 0.0f); t.tgtMix.assign(L, 0.0f);
+				std::memcpy(t.curBand, filterGains + 4 * size_t(k), 16);
+				t.curDelay = delaySeconds[k] * b->fs; t.y1 = 0.0f; std::memset(t.st, 0, sizeof(t.st)); /* AllocateRTData (:421-455) */
+				b->taps.push_back(t); hit = &b->taps.back();
+			}
+			std::memcpy(hit->tgtBand, filterGains + 4 * size_t(k), 16);
+			std::copy(gains + size_t(k) * L, gains + size_t(k + 1) * L, hit->tgtMix.begin());
+			hit->tgtDelay = delaySeconds[k] * b->fs;
+		}
+	}
+	/* in [frames][nIn]; out [frames][L] accumulated into (:83-225) */
+	void orc_erbus_process(orc_erbus* b, const float* in, uint32_t nIn, float* out, uint32_t frames)
+	{
+		const uint32_t L = b->L, mask = b->ringSize - 1;
+		const float norm = 1.0f / float(nIn);
+		uint32_t done = 0, left = frames;
+		std::vector<float> buf(480);
+		while (left > 0)
+		{
+			const uint32_t n = std::min(left, 480u);
+			const float* chunk = in + size_t(done) * nIn;
+			float* o = out + size_t(done) * L;
+			done += n;
+			for (uint32_t s = 0; s < n; ++s) { float smp = 0.0f; for (uint32_t c = 0; c < nIn; ++c) smp += chunk[size_t(s) * nIn + c]; buf[s] = smp; }
+			for (uint32_t s = 0; s < n; ++s) buf[s] *= norm;
+			for (uint32_t s = 0; s < n; ++s) { b->ring[b->w & mask] = buf[s]; ++b->w; }
+			for (auto& t : b->taps)
+			{
+				if (t.tgtState == 0 && t.rtState == 0) continue;
+				if (t.rtState == 0) continue;
+				t.rtState = t.tgtState;
+				for (uint32_t s = 0; s < n; ++s)
+				{
+					t.curDelay = b->alpha * (t.tgtDelay - t.curDelay) + t.curDelay;
+					const float d = float(int(n) - int(s)) + t.curDelay;
+					const uint32_t D = uint32_t(d);
+					const float fr = d - float(D);
+					const float a = (1.0f - fr) / (1.0f + fr);
+					const float x0 = b->ring[(b->w - 1u - D) & mask], x1 = b->ring[(b->w - 2u - D) & mask];
+					const float y = a * (x0 - t.y1) + x1;
+					t.y1 = y; buf[s] = y;
+				}
+				orc_xover_process_ramp(b->coef, t.st, buf.data(), n, t.curBand, t.tgtBand, buf.data());
+				std::memcpy(t.curBand, t.tgtBand, 16);
+				for (uint32_t k = 0; k < L; ++k) { orc_add_gain_ramp(o, buf.data(), k, 0, L, 1, n, t.curMix[k], t.tgtMix[k]); t.curMix[k] = t.tgtMix[k]; }
+				if (t.rtState == 2) t.rtState = 0; /* FadingOut -> Stopped after one chunk (:218-220) */
+				/* the scratch buffer keeps this tap's output: the next tap overwrites it (buffer[s] = Tap.Process) */
+			}
+			left -= n;
+		}
+	}
 }

@@ -64,6 +64,24 @@ void     orc_dse_process(orc_dse*, const float* in, float* out, uint32_t frames)
 /* n effects, one block each, sources partitioned over `threads`; returns seconds (CPU baseline "port") */
 double   orc_dse_process_batch(orc_dse** fx, uint32_t n, const float* in, uint32_t frames, float* bus, int threads);
 
+
+/* ---- ReverbBus (src/Auralization/LateReverb.cpp:31-134, inc/Auralization/ReverbDesign.h:311-349,388-492,573-704) */
+typedef struct orc_reverb orc_reverb;
+void        orc_db_to_gain(const float* db, uint32_t n, float* out);                                   /* inc/Math/DecibelsAndGain.h:40-56 (SIMD exp, SIMDMath.h:296-316) */
+orc_reverb* orc_reverb_create(float fs, float f1, float f2, float f3);
+void        orc_reverb_destroy(orc_reverb*);
+void        orc_reverb_set_rt60(orc_reverb*, const float rt60[4]);
+void        orc_reverb_set_decay_slope(orc_reverb*, const float slope[4]);
+void        orc_reverb_process(orc_reverb*, const float* in_mono, float* out, uint32_t n_out, uint32_t frames); /* out accumulated into */
+
+/* ---- ERBus (src/Auralization/EarlyReflectionsBus.cpp:83-417) */
+typedef struct orc_erbus orc_erbus;
+orc_erbus*  orc_erbus_create(float fs, uint32_t num_channels);
+void        orc_erbus_destroy(orc_erbus*);
+uint32_t    orc_erbus_num_taps(const orc_erbus*);
+void        orc_erbus_set_taps(orc_erbus*, uint32_t n, const float* filter_gains, const float* delay_seconds, const uint32_t* ids, const float* gains);
+void        orc_erbus_process(orc_erbus*, const float* in, uint32_t n_in, float* out, uint32_t frames);          /* out accumulated into */
+
 #ifdef __cplusplus
 }
 #endif

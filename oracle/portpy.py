@@ -59,7 +59,34 @@ class Port:
         L.orc_layout_info.argtypes = [_vp, _u32, _vp, _vp, _vp, _vp, _vp, _vp]
         L.orc_mdap.argtypes = [_vp, _u32, _vp, _u32, _vp]
         L.orc_process_virtual_sources.argtypes = [_vp, _vp, _u32, _vp]
+        L.orc_reverb_create.restype = _vp
+        L.orc_reverb_create.argtypes = [_f32, _f32, _f32, _f32]
+        L.orc_reverb_set_rt60.argtypes = [_vp, _vp]
+        L.orc_reverb_set_decay_slope.argtypes = [_vp, _vp]
+        L.orc_reverb_process.argtypes = [_vp, _vp, _vp, _u32, _u32]
+        L.orc_reverb_destroy.argtypes = [_vp]
+        L.orc_db_to_gain.argtypes = [_vp, _u32, _vp]
+        L.orc_erbus_create.restype = _vp
+        L.orc_erbus_create.argtypes = [_f32, _u32]
+        L.orc_erbus_destroy.argtypes = [_vp]
+        L.orc_erbus_num_taps.restype = _u32
+        L.orc_erbus_num_taps.argtypes = [_vp]
+        L.orc_erbus_set_taps.argtypes = [_vp, _u32, _vp, _vp, _vp, _vp]
+        L.orc_erbus_process.argtypes = [_vp, _vp, _u32, _vp, _u32]
         self._panners = {}
+
+    # ---- late reverb / early reflections
+    def reverb(self, fs=48000.0, splits=(0.0, 0.0, 0.0)):
+        return PortReverb(self, fs, splits)
+
+    def erbus(self, fs, num_channels):
+        return PortERBus(self, fs, num_channels)
+
+    def db_to_gain(self, db):
+        d = np.ascontiguousarray(db, np.float32)
+        out = np.empty_like(d)
+        self.lib.orc_db_to_gain(d.ctypes.data, d.size, out.ctypes.data)
+        return out
 
     # ---- math primitives
     def _map1(self, fn, x):
@@ -228,5 +255,66 @@ class PortDSE:
     def __del__(self):
         try:
             self.lib.orc_dse_destroy(self.h)
+        except Exception:
+            pass
+
+
+class PortReverb:
+    """restatement of ReverbBus; same interface as oracle.refpy.RefReverb"""
+
+    def __init__(self, port, fs, splits):
+        self.port = port
+        self.h = port.lib.orc_reverb_create(_f32(fs), _f32(splits[0]), _f32(splits[1]), _f32(splits[2]))
+
+    def set_rt60(self, rt60):
+        a = np.ascontiguousarray(rt60, np.float32)
+        self.port.lib.orc_reverb_set_rt60(self.h, a.ctypes.data)
+
+    def set_decay_slope(self, slope):
+        a = np.ascontiguousarray(slope, np.float32)
+        self.port.lib.orc_reverb_set_decay_slope(self.h, a.ctypes.data)
+
+    def process(self, inp, out, frames, n_in=1):
+        assert n_in == 1
+        x = np.ascontiguousarray(inp, np.float32)
+        assert out.dtype == np.float32 and out.flags["C_CONTIGUOUS"]
+        self.port.lib.orc_reverb_process(self.h, x.ctypes.data, out.ctypes.data, out.shape[-1], frames)
+
+    def __del__(self):
+        try:
+            if self.h:
+                self.port.lib.orc_reverb_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+
+class PortERBus:
+    """restatement of ERBus; same interface as oracle.refpy.RefERBus"""
+
+    def __init__(self, port, fs, num_channels):
+        self.port, self.L = port, int(num_channels)
+        self.h = port.lib.orc_erbus_create(_f32(fs), self.L)
+
+    def set_taps(self, filter_gains, delay_seconds, ids, gains):
+        i = np.ascontiguousarray(ids, np.uint32).reshape(-1)
+        fg = np.ascontiguousarray(filter_gains, np.float32).reshape(-1, 4) if len(i) else np.zeros((0, 4), np.float32)
+        d = np.ascontiguousarray(delay_seconds, np.float32).reshape(-1) if len(i) else np.zeros(0, np.float32)
+        g = np.ascontiguousarray(gains, np.float32).reshape(-1, self.L) if len(i) else np.zeros((0, self.L), np.float32)
+        self.port.lib.orc_erbus_set_taps(self.h, len(i), fg.ctypes.data, d.ctypes.data, i.ctypes.data, g.ctypes.data)
+
+    def num_taps(self):
+        return int(self.port.lib.orc_erbus_num_taps(self.h))
+
+    def process(self, inp, out, frames, n_in=1):
+        x = np.ascontiguousarray(inp, np.float32)
+        assert out.dtype == np.float32 and out.flags["C_CONTIGUOUS"]
+        self.port.lib.orc_erbus_process(self.h, x.ctypes.data, n_in, out.ctypes.data, frames)
+
+    def __del__(self):
+        try:
+            if self.h:
+                self.port.lib.orc_erbus_destroy(self.h)
+                self.h = None
         except Exception:
             pass

@@ -184,5 +184,33 @@ for tag, smask, tmask, nsrc in (("mono_714", M.Mono, M.Surround_7_1_4, 3), ("ste
         rz[f"{tag}_in{b}"] = audio[b]; rz[f"{tag}_out{b}"] = out
 np.savez_compressed(os.path.join(OUT, "render.npz"), **rz)
 
+# ---- ReverbBus + ERBus (BASELINE config 5)
+vz = {}
+FDN_DELAYS = np.array([2927, 2593, 2273, 3697, 1877, 3877, 2477, 3461, 1609, 3779, 3541, 4259, 1669, 3539, 3637, 4013], np.float32)
+vz["db"] = (-60.0 * util.uniform01(64, util.SEED + 700)).astype(np.float32)
+vz["db_gain"] = ref.db_to_gain(vz["db"]).reshape(-1)
+rv = ref.reverb(48000.0)
+rt = np.array([[0.4, 1.5, 2.5, 0.8], [0.01, 20.0, 1.0, 0.2]], np.float32)
+vz["rev_rt60"] = rt
+vz["rev_in"] = (util.white_noise((7, 512), util.SEED + 701) * np.float32(0.5)); vz["rev_in"][0, 0] += 1.0; vz["rev_in"][5:] = 0.0
+outs = []
+for b in range(7):
+    if b == 0: rv.set_rt60(rt[0])
+    if b == 4: rv.set_rt60(rt[1])
+    o = np.zeros((512, 4), np.float32); rv.process(vz["rev_in"][b].reshape(512, 1), o, 512); outs.append(o)
+vz["rev_out"] = np.stack(outs)
+eb = ref.erbus(48000.0, 4)
+sched = [[1, 2, 3], [1, 2, 3], [2, 3, 7], [2, 3, 7], [3, 7, 1], [3, 7, 1]]
+vz["er_in"] = util.white_noise((6, 512, 2), util.SEED + 702)
+eouts, ntaps = [], []
+for b, ids in enumerate(sched):
+    u = util.uniform01(len(ids) * 9, util.SEED + 710 + b).reshape(len(ids), 9)
+    fg = (0.1 + 0.9 * u[:, :4]).astype(np.float32); d = (0.002 + 0.05 * np.array(ids, np.float32) / 10.0 + 0.0002 * u[:, 4]).astype(np.float32); g = u[:, 5:9].astype(np.float32)
+    vz[f"er_fg{b}"] = fg; vz[f"er_delay{b}"] = d; vz[f"er_ids{b}"] = np.array(ids, np.uint32); vz[f"er_gains{b}"] = g
+    eb.set_taps(fg, d, ids, g); ntaps.append(eb.num_taps())
+    o = np.zeros((512, 4), np.float32); eb.process(vz["er_in"][b], o, 512, n_in=2); eouts.append(o)
+vz["er_out"] = np.stack(eouts); vz["er_num_taps"] = np.array(ntaps, np.uint32)
+np.savez_compressed(os.path.join(OUT, "reverb_er.npz"), **vz)
+
 total = sum(os.path.getsize(os.path.join(OUT, f)) for f in os.listdir(OUT))
 print("wrote", sorted(os.listdir(OUT)), f"{total / 1024:.0f} KiB")

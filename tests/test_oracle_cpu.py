@@ -168,7 +168,67 @@ def test_render_matches_golden(port):
         assert b == 4
 
 
+def _run_reverb_er_golden(make_reverb, make_erbus, db_to_gain):
+    g = gold("reverb_er.npz")
+    same(np.asarray(db_to_gain(g["db"])).reshape(-1), g["db_gain"])
+    rv = make_reverb(48000.0)
+    for b in range(7):
+        if b == 0: rv.set_rt60(g["rev_rt60"][0])
+        if b == 4: rv.set_rt60(g["rev_rt60"][1])
+        o = np.zeros((512, 4), np.float32)
+        rv.process(g["rev_in"][b].reshape(512, 1), o, 512)
+        same(o, g["rev_out"][b])
+    assert np.abs(g["rev_out"][6]).max() > 1e-4
+    eb = make_erbus(48000.0, 4)
+    for b in range(6):
+        eb.set_taps(g[f"er_fg{b}"], g[f"er_delay{b}"], g[f"er_ids{b}"], g[f"er_gains{b}"])
+        assert eb.num_taps() == int(g["er_num_taps"][b])
+        o = np.zeros((512, 4), np.float32)
+        eb.process(g["er_in"][b], o, 512, n_in=2)
+        same(o, g["er_out"][b])
+
+
+def test_reverb_and_erbus_match_golden(port):
+    """ReverbBus (FDN16: Householder feedback, per-channel four-band decay, Hadamard output fold) and ERBus (shared mono ring,
+    tap add / update / fade-out life cycle, sequential per-tap accumulation) against fixtures made by the unmodified reference."""
+    _run_reverb_er_golden(port.reverb, port.erbus, port.db_to_gain)
+
+
 # ------------------------------------------------------------------------------------------------ 2. live reference
+def test_reverb_erbus_golden_is_current(ref):
+    _run_reverb_er_golden(ref.reverb, ref.erbus, ref.db_to_gain)
+
+
+def test_port_reverb_erbus_equal_reference_build(port, ref):
+    """longer seeded runs of the restated ReverbBus / ERBus against the live reference build (bit-exact)"""
+    n_blocks, frames = 16, 512
+    x = util.white_noise((n_blocks, frames), util.SEED + 950) * np.float32(0.5)
+    for L in (12, 2, 16):
+        a, b = ref.reverb(48000.0), port.reverb(48000.0)
+        for blk in range(n_blocks):
+            if blk % 5 == 0:
+                rt = (0.05 + 4.0 * util.uniform01(4, util.SEED + 951 + blk)).astype(np.float32)
+                a.set_rt60(rt); b.set_rt60(rt)
+            oa = np.zeros((frames, L), np.float32); ob = np.zeros((frames, L), np.float32)
+            a.process(x[blk].reshape(frames, 1), oa, frames); b.process(x[blk].reshape(frames, 1), ob, frames)
+            same(ob, oa)
+    L = 12
+    a, b = ref.erbus(48000.0, L), port.erbus(48000.0, L)
+    ids = list(range(1, 9))
+    for blk in range(12):
+        if blk % 3 == 2:
+            ids = ids[2:] + [100 + blk, 200 + blk]
+        u = util.uniform01(len(ids) * (5 + L), util.SEED + 960 + blk).reshape(len(ids), 5 + L)
+        fg, d, gn = 0.1 + 0.9 * u[:, :4], 0.002 + 0.078 * u[:, 4], u[:, 5:]
+        a.set_taps(fg, d, ids, gn); b.set_taps(fg, d, ids, gn)
+        assert a.num_taps() == b.num_taps()
+        xin = util.white_noise((100 if blk == 7 else frames, 1), util.SEED + 970 + blk)
+        f = xin.shape[0]
+        oa = np.zeros((f, L), np.float32); ob = np.zeros((f, L), np.float32)
+        a.process(xin, oa, f); b.process(xin, ob, f)
+        same(ob, oa)
+
+
 def test_port_equals_reference_build_large(port, ref):
     """65,536-source MDAP (BASELINE config 2's shape, reduced to 8,192 here for CPU time) + 64 sources x 6 blocks of render."""
     M, _ = _masks()
