@@ -59,3 +59,53 @@ def reduce_bus(bus, dst: int = 0, group=None, all_ranks: bool = False):
     else:
         dist.reduce(bus, dst=dst, op=dist.ReduceOp.SUM, group=group)
     return bus
+
+
+class PipelinedBusReduce:
+    """Overlaps the reduce of block k's bus with the render of block k+1 (SURVEY.md §8e): `depth` bus buffers are used in turn;
+    `begin(k)` hands out a zeroed buffer once the reduce that last used it has completed (stream-ordered, no host sync),
+    `submit(k)` starts the asynchronous reduce of that buffer (NCCL runs it on its own stream after the work enqueued so far).
+    The per-block latency still contains the reduce; the throughput does not. With one rank it degenerates to plain buffers."""
+
+    def __init__(self, frames: int, channels: int, device, depth: int = 2, dst: int = 0, group=None, all_ranks: bool = False):
+        import torch
+        self.buses = [torch.zeros((frames, channels), dtype=torch.float32, device=device) for _ in range(max(1, depth))]
+        self.pending = [None] * len(self.buses)
+        self.dst, self.group, self.all_ranks = dst, group, all_ranks
+
+    def _active(self):
+        import torch.distributed as dist
+        return dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1
+
+    def begin(self, k: int):
+        j = k % len(self.buses)
+        if self.pending[j] is not None:
+            self.pending[j].wait()          # the current stream waits for that reduce; the host does not block (NCCL) / blocks briefly (gloo)
+            self.pending[j] = None
+        self.buses[j].zero_()
+        return self.buses[j]
+
+    def submit(self, k: int):
+        j = k % len(self.buses)
+        if not self._active():
+            return None
+        import torch.distributed as dist
+        if self.all_ranks:
+            self.pending[j] = dist.all_reduce(self.buses[j], op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+        else:
+            self.pending[j] = dist.reduce(self.buses[j], dst=self.dst, op=dist.ReduceOp.SUM, group=self.group, async_op=True)
+        return self.pending[j]
+
+    def result(self, k: int):
+        """the reduced bus of block k (valid on `dst`, or everywhere with all_ranks) once its reduce has completed"""
+        j = k % len(self.buses)
+        if self.pending[j] is not None:
+            self.pending[j].wait()
+            self.pending[j] = None
+        return self.buses[j]
+
+    def drain(self):
+        for j, w in enumerate(self.pending):
+            if w is not None:
+                w.wait()
+                self.pending[j] = None

@@ -91,3 +91,40 @@ def test_two_rank_gloo_reduce_equals_unsharded_bus(tmp_path):
     assert np.abs(b).max() > 0.1
     # the two-rank sum re-associates the fp32 additions: (s0 + ... + s23) + (s24 + ... + s47) vs sequential
     np.testing.assert_allclose(a, b, rtol=0, atol=48 * np.finfo(np.float32).eps * np.abs(b).max())
+
+
+def _worker_pipelined(rank, world, port, out_path):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    from jplspatial_b200.sharding import PipelinedBusReduce
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        frames, L, blocks = 64, 12, 7
+        red = PipelinedBusReduce(frames, L, torch.device("cpu"), depth=2, dst=0)
+        got = []
+        for k in range(blocks):
+            bus = red.begin(k)
+            assert not bus.any(), "a recycled bus buffer must come back zeroed"
+            bus += float((rank + 1) * (k + 1))          # this rank's partial bus of block k
+            red.submit(k)
+            if k >= 1:
+                got.append(red.result(k - 1).clone())   # block k-1's reduce was in flight while block k was produced
+        got.append(red.result(blocks - 1).clone())
+        red.drain()
+        if rank == 0:
+            np.save(out_path, torch.stack(got).numpy())
+    finally:
+        dist.destroy_process_group()
+
+
+def test_pipelined_bus_reduce_two_ranks(tmp_path):
+    """double-buffered asynchronous reduce: every block's bus arrives complete and in order on the destination rank"""
+    import torch.multiprocessing as mp
+    out = str(tmp_path / "pipe.npy")
+    mp.spawn(_worker_pipelined, args=(2, _free_port(), out), nprocs=2, join=True)
+    a = np.load(out)
+    assert a.shape == (7, 64, 12)
+    for k in range(7):
+        assert np.all(a[k] == 3.0 * (k + 1))             # (1 + 2) * (k + 1)
