@@ -74,6 +74,7 @@ typedef struct jplg_crossover_bank_t* jplg_crossover_bank;
 typedef struct jplg_delay_bank_t*    jplg_delay_bank;
 typedef struct jplg_reverb_bank_t*   jplg_reverb_bank;
 typedef struct jplg_erbus_bank_t*    jplg_erbus_bank;
+typedef struct jplg_frontend_t*      jplg_frontend;
 
 /* replaces: JPL::SpatialTrace (inc/ErrorReporting.h:44-47) */
 typedef void (*jplg_trace_fn)(const char* message);
@@ -102,7 +103,7 @@ JPLG_API uint64_t    jplg_context_launch_count(jplg_context ctx);
  * so the events do not perturb the others). `which`: one of JPLG_K_*. kernel_time synchronises the stream and returns the accumulated
  * milliseconds and launch count since the last reset. */
 enum { JPLG_K_PUSH = 0, JPLG_K_RENDER = 1, JPLG_K_BUS_REDUCE = 2, JPLG_K_MDAP = 3, JPLG_K_POINT_GAINS = 4,
-       JPLG_K_UPDATE = 5, JPLG_K_OTHER = 6, JPLG_K_FDN = 7, JPLG_K_ER_PUSH = 8, JPLG_K_COUNT = 9 };
+       JPLG_K_UPDATE = 5, JPLG_K_OTHER = 6, JPLG_K_FDN = 7, JPLG_K_ER_PUSH = 8, JPLG_K_FRONTEND = 9, JPLG_K_COUNT = 10 };
 JPLG_API void        jplg_context_set_kernel_timing(jplg_context ctx, int32_t enabled);
 JPLG_API void        jplg_context_reset_kernel_timing(jplg_context ctx);
 JPLG_API jplg_status jplg_context_kernel_time(jplg_context ctx, int32_t which, double* total_ms, uint64_t* launches);
@@ -159,6 +160,10 @@ JPLG_API void        jplg_source_layout_groups(jplg_source_layout l, float* out_
 /* ProcessVBAPData(sourceLayout, PanUpdateData, outChannelMixMap) batched (:369,486-500).
  * params [n][5] = { dir.x, dir.y, dir.z, focus, spread } ; out [n][channels*L]. */
 JPLG_API jplg_status jplg_panner_mdap(jplg_panner p, jplg_source_layout l, const float* params, uint32_t n, float* out, int32_t mem);
+/* ProcessVBAPData(sourceLayout, PanUpdateDataWithOrientation, outChannelMixMap) batched (:375,501-515): the pan rotation is
+ * QuatFromUpAndForward(Orientation.Up, Orientation.Forward) instead of QuatLookAt(SourceDirection).
+ * params [n][11] = { dir.xyz, focus, spread, up.xyz, forward.xyz } ; out [n][channels*L]. */
+JPLG_API jplg_status jplg_panner_mdap_oriented(jplg_panner p, jplg_source_layout l, const float* params, uint32_t n, float* out, int32_t mem);
 
 /* ProcessVirtualSources(span<VirtualSource>, outGains) (:385,731-742): ONE gain vector from n weighted
  * directions. vs [n][4] = { dir.x, dir.y, dir.z, weight }; out [L] is ACCUMULATED INTO and then L2-normalised,
@@ -302,6 +307,85 @@ JPLG_API jplg_status jplg_erbus_bank_process(jplg_erbus_bank b, const float* in,
 /* Same, and every tap slot's own contribution: per_tap [B * slots_per_bus][frames][L] (overwritten; dead slots give zeros). */
 JPLG_API jplg_status jplg_erbus_bank_process_debug(jplg_erbus_bank b, const float* in, uint32_t in_channels, float* out, float* per_tap,
                                                    uint32_t frames, int32_t mem);
+
+/* ---------------------------------------------------------------------------------------------- */
+/* Scene front-end: the per-source body of SpatialManager::AdvanceSimulation batched               */
+/* (replaces: inc/SpatialManager.h:374-420 and the services it calls)                              */
+/*   DirectPathService::ProcessDirectPath / EvaluateDistance / EvaluateDirection                   */
+/*                                     inc/Services/DirectPathService.h:232-364                    */
+/*   AttenuationBaseModel / AttenuationCurve ::Evaluate   inc/DistanceAttenuation.h:66-119,172-215 */
+/*   GetSpreadFromSourceSize           inc/SpatialManager.h:617-623 (inc/Panning/PannerBase.h:69-74) */
+/*   Impl::SanitizeSourceDir           inc/Services/PanningService.h:480-495                       */
+/*   AirAbsorption::CacheParameters / ComputeForDistance    inc/AirAbsorption.h:179-234            */
+/*   dBToGain(simd)                    inc/Math/DecibelsAndGain.h:40-50                            */
+/*   SpeedOfSound                      inc/SpeedOfSound.h:24-47                                    */
+/* Positions are 9 floats: Location, Orientation.Up, Orientation.Forward (inc/Math/Position.h:31-83). */
+
+/* one AttenuationFunction */
+typedef struct jplg_attenuation_function {
+    int32_t  kind;          /* 0: AttenuationBaseModel, 1: AttenuationCurve */
+    int32_t  model;         /* AttenuationModel: 0 None, 1 Inverse, 2 Linear, 3 Exponential (base model only) */
+    float    min_distance, max_distance, rolloff;   /* DistanceAttenuationParameters */
+    uint32_t first_point, num_points;               /* curve: its range in `points` */
+} jplg_attenuation_function;
+
+/* AirAbsorptionCache (inc/AirAbsorption.h:51-87) */
+typedef struct jplg_air_absorption_cache {
+    float    band_centers[4], lower_third_centers[4];
+    float    center_db[4], lower_third_db[4], weighted_db[4], decay_slope[4];
+    float    distance_to_knee[4], linearized_loss_factor[4];
+    uint32_t has_knee[4];
+} jplg_air_absorption_cache;
+
+/* Host builders (no device needed; the reference also runs these once per environment on the CPU). */
+/* AirAbsorption::CacheParameters(frequencyBands, params, nyquist); bands NULL = cBandCenters (inc/FrequencyBands.h:68). */
+JPLG_API void  jplg_air_absorption_cache_build(const float* bands, float temperature_c, float humidity_percent, float pressure_kpa,
+                                               float nyquist, jplg_air_absorption_cache* out);
+JPLG_API void  jplg_default_band_centers(float out[4]);
+JPLG_API float jplg_speed_of_sound_for_temperature(float temperature_c);   /* SpeedOfSound::ForTemperature */
+
+typedef struct jplg_frontend_config {
+    const jplg_attenuation_function* functions;  /* attenuation function table (may be NULL / 0) */
+    uint32_t num_functions;
+    const float* points;                         /* [num_points][3] = Distance, Value, Curve::EType (inc/Math/Curves.h:40-52) */
+    uint32_t num_points;
+    int32_t  sort_points;                        /* 1: sort every curve's points by distance first (AttenuationCurve::SortPoints) */
+    const jplg_air_absorption_cache* air;        /* NULL = cDefaultAirAbsCache (20 C, 50 %, 101.325 kPa, default bands) */
+    float    speed_of_sound;                     /* 0 = SpeedOfSound::cReference (343.2 m/s); delay = distance * (1 / c) */
+    int32_t  spread_flavour;                     /* 0: SpatialManager::GetSpreadFromSourceSize, 1: the free function of PannerBase.h */
+} jplg_frontend_config;
+
+/* Arrays of one call; inputs and outputs may each be NULL (= absent / not wanted). All arrays live where `mem` says. */
+typedef struct jplg_frontend_io {
+    uint32_t n;                      /* sources */
+    uint32_t num_listeners;
+    const float*    sources;         /* [n][9] world-space Position of every source */
+    const float*    listeners;       /* [num_listeners][9] */
+    const uint32_t* listener_index;  /* [n], NULL = listener 0 */
+    const float*    distance_in;     /* [n] distances to evaluate when sources == NULL (EvaluateDistance / ComputeForDistance on their own) */
+    const float*    dot_in;          /* [n] direction cosines when sources == NULL (ProcessAngleAttenuation on its own) */
+    const float*    cones;           /* [n][2] AttenuationCone: InnerAngle, OuterAngle (radians) */
+    const float*    object_sizes;    /* [n] SourceData::ObjectSize; < 0 = none (spread stays as given) */
+    const float*    focus_spread;    /* [n][2] PanEffectParameters; NULL = focus / spread below */
+    float           focus, spread;
+    const uint32_t* function_index;  /* [n] attenuation function per source, NULL = function 0 */
+    uint32_t        pan_stride;      /* 5: PanUpdateData rows, 11: PanUpdateDataWithOrientation rows */
+    float* direct;        /* [n][4] Distance, DirectionDot, InvDirectionDot, cone factor (ProcessAngleAttenuationImpl(InvDirectionDot, cone)) */
+    float* relative;      /* [n][9] DirectPathResult::Position */
+    float* pan_params;    /* [n][pan_stride]: what jplg_panner_mdap / jplg_panner_mdap_oriented consume */
+    float* distance_attenuation; /* [n] AttenuationFunction::Evaluate(Distance) */
+    float* air_db;        /* [n][4] AirAbsorption::ComputeForDistance */
+    float* band_gains;    /* [n][4] dBToGain(-air_db): the filterGains of jplg_renderer_update */
+    float* delay_seconds; /* [n] Distance / speed of sound: the delaySeconds of jplg_renderer_update */
+} jplg_frontend_io;
+
+JPLG_API jplg_status jplg_frontend_create(jplg_context ctx, const jplg_frontend_config* cfg, jplg_frontend* out);
+JPLG_API void        jplg_frontend_destroy(jplg_frontend f);
+/* One kernel launch for all n sources. JPLG_MEM_DEVICE: asynchronous on the context stream (outputs can feed
+ * jplg_panner_mdap / jplg_renderer_update directly); JPLG_MEM_HOST: staged and synchronous. */
+JPLG_API jplg_status jplg_frontend_process(jplg_frontend f, const jplg_frontend_io* io, int32_t mem);
+/* the fallback direction SanitizeSourceDir substitutes for straight-up / straight-down sources */
+JPLG_API void        jplg_sanitize_fallback_dir(float out[3]);
 
 #ifdef __cplusplus
 }

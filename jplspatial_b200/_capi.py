@@ -67,6 +67,7 @@ _sig("jplg_source_layout_num_virtual_sources", _u32, [_vp])
 _sig("jplg_source_layout_info", None, [_vp, C.POINTER(_u32), C.POINTER(_f32), C.POINTER(_f32), C.POINTER(_f32)])
 _sig("jplg_source_layout_groups", None, [_vp, _fp, _vp])
 _sig("jplg_panner_mdap", _i32, [_vp, _vp, _fp, _u32, _fp, _i32])
+_sig("jplg_panner_mdap_oriented", _i32, [_vp, _vp, _fp, _u32, _fp, _i32])
 _sig("jplg_panner_process_virtual_sources", _i32, [_vp, _fp, _u32, _u32, _fp, _i32])
 _sig("jplg_normalize_weights", None, [_fp, _u32])
 _sig("jplg_spread_from_source_size", _f32, [_f32, _f32])
@@ -209,7 +210,7 @@ class Context:
     def launch_count(self):
         return int(lib.jplg_context_launch_count(self.h))
 
-    KERNELS = {"push": 0, "render": 1, "bus_reduce": 2, "mdap": 3, "point_gains": 4, "update": 5, "other": 6, "fdn": 7, "er_push": 8}
+    KERNELS = {"push": 0, "render": 1, "bus_reduce": 2, "mdap": 3, "point_gains": 4, "update": 5, "other": 6, "fdn": 7, "er_push": 8, "frontend": 9}
 
     def set_kernel_timing(self, enabled, only=None):
         """only: iterable of kernel names (see kernel_time) to bracket with events; default every kernel"""
@@ -364,6 +365,23 @@ class VBAPanner:
         o, omem, okeep = _arg(out)
         assert omem == mem
         self.ctx.check(lib.jplg_panner_mdap(self.h, layout.h, p, n, o, mem))
+        return out
+
+    def ProcessVBAPDataOriented(self, layout, params, out=None):
+        """PanUpdateDataWithOrientation overload (PannerBase.h:375): params [n,11] = {dir.xyz, focus, spread, up.xyz, forward.xyz}"""
+        p, mem, keep = _arg(params)
+        n = keep.shape[0]
+        assert keep.shape[-1] == 11
+        L = self.GetNumChannels()
+        if out is None:
+            if mem == MEM_DEVICE:
+                import torch
+                out = torch.empty((n, layout.num_channels, L), dtype=torch.float32, device=keep.device)
+            else:
+                out = np.empty((n, layout.num_channels, L), np.float32)
+        o, omem, okeep = _arg(out)
+        assert omem == mem
+        self.ctx.check(lib.jplg_panner_mdap_oriented(self.h, layout.h, p, n, o, mem))
         return out
 
     def ProcessVirtualSources(self, virtual_sources, out=None):
@@ -669,3 +687,140 @@ def apply_gain(ctx, dest, gains):
     g = np.ascontiguousarray(gains, np.float32)
     ctx.check(lib.jplg_mix_apply_gain(ctx.h, d.ctypes.data, d.shape[0], d.shape[1], g.ctypes.data, MEM_HOST))
     return d
+
+
+# ------------------------------------------------------------------------------------------------
+# Scene front-end (inc/SpatialManager.h:374-420 batched)
+class AttenuationFunction(C.Structure):
+    _fields_ = [("kind", _i32), ("model", _i32), ("min_distance", _f32), ("max_distance", _f32), ("rolloff", _f32),
+                ("first_point", _u32), ("num_points", _u32)]
+
+
+class AirAbsorptionCache(C.Structure):
+    """inc/AirAbsorption.h:51-87"""
+    _fields_ = [(k, _f32 * 4) for k in ("band_centers", "lower_third_centers", "center_db", "lower_third_db", "weighted_db",
+                                        "decay_slope", "distance_to_knee", "linearized_loss_factor")] + [("has_knee", _u32 * 4)]
+
+    @staticmethod
+    def CacheParameters(bands=None, temperature_c=20.0, humidity_percent=50.0, pressure_kpa=101.325, nyquist=22050.0):
+        c = AirAbsorptionCache()
+        b = None if bands is None else np.ascontiguousarray(bands, np.float32)
+        lib.jplg_air_absorption_cache_build(None if b is None else b.ctypes.data, temperature_c, humidity_percent, pressure_kpa, nyquist, C.byref(c))
+        return c
+
+    def as_dict(self):
+        return {k: np.array(getattr(self, k)) for k, _ in self._fields_}
+
+
+class FrontendConfig(C.Structure):
+    _fields_ = [("functions", C.POINTER(AttenuationFunction)), ("num_functions", _u32), ("points", _fp), ("num_points", _u32),
+                ("sort_points", _i32), ("air", C.POINTER(AirAbsorptionCache)), ("speed_of_sound", _f32), ("spread_flavour", _i32)]
+
+
+class FrontendIO(C.Structure):
+    _fields_ = [("n", _u32), ("num_listeners", _u32), ("sources", _fp), ("listeners", _fp), ("listener_index", _fp),
+                ("distance_in", _fp), ("dot_in", _fp), ("cones", _fp), ("object_sizes", _fp), ("focus_spread", _fp),
+                ("focus", _f32), ("spread", _f32), ("function_index", _fp), ("pan_stride", _u32),
+                ("direct", _fp), ("relative", _fp), ("pan_params", _fp), ("distance_attenuation", _fp), ("air_db", _fp),
+                ("band_gains", _fp), ("delay_seconds", _fp)]
+
+
+_sig("jplg_air_absorption_cache_build", None, [_fp, _f32, _f32, _f32, _f32, C.POINTER(AirAbsorptionCache)])
+_sig("jplg_default_band_centers", None, [_fp])
+_sig("jplg_speed_of_sound_for_temperature", _f32, [_f32])
+_sig("jplg_sanitize_fallback_dir", None, [_fp])
+_sig("jplg_frontend_create", _i32, [_vp, C.POINTER(FrontendConfig), C.POINTER(_vp)])
+_sig("jplg_frontend_destroy", None, [_vp])
+_sig("jplg_frontend_process", _i32, [_vp, C.POINTER(FrontendIO), _i32])
+DECLARED_SYMBOLS = [n for n in dir(lib) if n.startswith("jplg_")]
+
+MODEL_NONE, MODEL_INVERSE, MODEL_LINEAR, MODEL_EXPONENTIAL = 0, 1, 2, 3
+(CURVE_CONSTANT, CURVE_LINEAR, CURVE_SINE_FADE_IN, CURVE_SINE_FADE_OUT, CURVE_SCURVE, CURVE_LOG_1_41, CURVE_LOG_3,
+ CURVE_EXP_1_41, CURVE_EXP_3) = range(9)
+
+
+def default_band_centers():
+    out = np.zeros(4, np.float32)
+    lib.jplg_default_band_centers(out.ctypes.data)
+    return out
+
+
+def speed_of_sound_for_temperature(t):
+    return float(lib.jplg_speed_of_sound_for_temperature(t))
+
+
+def sanitize_fallback_dir():
+    out = np.zeros(3, np.float32)
+    lib.jplg_sanitize_fallback_dir(out.ctypes.data)
+    return out
+
+
+class DirectPathBatch:
+    """Batched DirectPathService + PanningService::EvaluateDirection glue + parameter producers (the per-source body of
+    SpatialManager::AdvanceSimulation). `functions`: list of ("model", model, min, max, rolloff) or ("curve", [(distance, value, type), ...])."""
+
+    _OUT = {"direct": 4, "relative": 9, "pan_params": None, "distance_attenuation": 1, "air_db": 4, "band_gains": 4, "delay_seconds": 1}
+
+    def __init__(self, ctx, functions=(), sort_points=True, air=None, speed_of_sound=0.0, spread_flavour=0):
+        self.ctx = ctx
+        funcs = (AttenuationFunction * max(len(functions), 1))()
+        pts = []
+        for i, f in enumerate(functions):
+            if f[0] == "model":
+                funcs[i] = AttenuationFunction(0, int(f[1]), float(f[2]), float(f[3]), float(f[4]), 0, 0)
+            else:
+                funcs[i] = AttenuationFunction(1, 0, 0.0, 0.0, 0.0, len(pts), len(f[1]))
+                pts.extend(f[1])
+        p = np.ascontiguousarray(np.array(pts, np.float32).reshape(-1, 3))
+        cfg = FrontendConfig(funcs, len(functions), p.ctypes.data if len(pts) else None, len(pts), 1 if sort_points else 0,
+                             C.pointer(air) if air is not None else None, float(speed_of_sound), int(spread_flavour))
+        self.h = _vp()
+        ctx.check(lib.jplg_frontend_create(ctx.h, C.byref(cfg), C.byref(self.h)))
+
+    def Process(self, n, want, sources=None, listeners=None, listener_index=None, distance_in=None, dot_in=None, cones=None,
+                object_sizes=None, focus_spread=None, focus=1.0, spread=0.0, function_index=None, pan_stride=5, out=None):
+        """`want`: names of the outputs (see jplg_frontend_io). numpy inputs -> numpy outputs (staged); CUDA torch inputs -> torch outputs
+        on the context stream. Returns a dict."""
+        io = FrontendIO()
+        io.n = n
+        io.focus, io.spread, io.pan_stride = focus, spread, pan_stride
+        keep, mems = [], set()
+
+        def put(name, x, dtype=np.float32):
+            if x is None:
+                return
+            a, mem, k = _arg(x, dtype)
+            setattr(io, name, a)
+            keep.append(k)
+            mems.add(mem)
+        put("sources", sources); put("listeners", listeners); put("listener_index", listener_index, np.uint32)
+        put("distance_in", distance_in); put("dot_in", dot_in); put("cones", cones); put("object_sizes", object_sizes)
+        put("focus_spread", focus_spread); put("function_index", function_index, np.uint32)
+        io.num_listeners = 0 if listeners is None else int(np.prod(listeners.shape) // 9)
+        assert len(mems) == 1, "all front-end arrays must live in the same memory space"
+        mem = mems.pop()
+        res = {} if out is None else dict(out)
+        for name in want:
+            w = self._OUT[name]
+            w = pan_stride if w is None else w
+            if name not in res:
+                if mem == MEM_DEVICE:
+                    import torch
+                    res[name] = torch.empty((n, w), dtype=torch.float32, device=next(k for k in keep if _is_torch(k)).device)
+                else:
+                    res[name] = np.empty((n, w), np.float32)
+            a, omem, k = _arg(res[name])
+            assert omem == mem
+            if not _is_torch(res[name]):
+                res[name] = k
+            setattr(io, name, a)
+        self.ctx.check(lib.jplg_frontend_process(self.h, C.byref(io), mem))
+        return res
+
+    def __del__(self):
+        try:
+            if self.h:
+                lib.jplg_frontend_destroy(self.h)
+                self.h = None
+        except Exception:
+            pass

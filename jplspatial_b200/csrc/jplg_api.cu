@@ -411,7 +411,7 @@ void jplg_source_layout_groups(jplg_source_layout l, float* out_quats, uint32_t*
 	}
 }
 
-jplg_status jplg_panner_mdap(jplg_panner p, jplg_source_layout l, const float* params, uint32_t n, float* out, int32_t mem)
+static jplg_status MdapImpl(jplg_panner p, jplg_source_layout l, const float* params, uint32_t stride, uint32_t n, float* out, int32_t mem)
 {
 	if (!p || !l || l->panner != p || (n && (!params || !out))) return JPLG_ERR_INVALID_ARGUMENT;
 	jplg_context ctx = p->ctx;
@@ -424,18 +424,26 @@ jplg_status jplg_panner_mdap(jplg_panner p, jplg_source_layout l, const float* p
 	if (mem == JPLG_MEM_HOST)
 	{
 		void *a, *b;
-		jplg_status st = Scratch(ctx, 0, size_t(n) * 5 * 4, &a); if (st) return st;
+		jplg_status st = Scratch(ctx, 0, size_t(n) * stride * 4, &a); if (st) return st;
 		st = Scratch(ctx, 1, outFloats * 4, &b); if (st) return st;
-		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(a, params, size_t(n) * 5 * 4, cudaMemcpyHostToDevice, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(a, params, size_t(n) * stride * 4, cudaMemcpyHostToDevice, ctx->stream));
 		dParams = static_cast<float*>(a); dOut = static_cast<float*>(b);
 	}
-	JPLG_LAUNCH(ctx, JPLG_K_MDAP, LaunchMdap(p->dev, l->lp, dParams, n, dOut, ctx->numSMs, ctx->stream));
+	JPLG_LAUNCH(ctx, JPLG_K_MDAP, LaunchMdap(p->dev, l->lp, dParams, stride, n, dOut, ctx->numSMs, ctx->stream));
 	if (mem == JPLG_MEM_HOST)
 	{
 		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(out, dOut, outFloats * 4, cudaMemcpyDeviceToHost, ctx->stream));
 		JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
 	}
 	return JPLG_OK;
+}
+jplg_status jplg_panner_mdap(jplg_panner p, jplg_source_layout l, const float* params, uint32_t n, float* out, int32_t mem)
+{
+	return MdapImpl(p, l, params, 5, n, out, mem);
+}
+jplg_status jplg_panner_mdap_oriented(jplg_panner p, jplg_source_layout l, const float* params, uint32_t n, float* out, int32_t mem)
+{
+	return MdapImpl(p, l, params, 11, n, out, mem);
 }
 
 jplg_status jplg_panner_process_virtual_sources(jplg_panner p, const float* vs, uint32_t n, uint32_t batches, float* out, int32_t mem)
@@ -1416,5 +1424,7 @@ int32_t jplg_erbus_bank_tap_slot(jplg_erbus_bank b, uint32_t bus, uint32_t id)
 	for (auto& t : b->taps[bus]) if (t.id == id) return static_cast<int32_t>(bus * b->T + t.slot);
 	return -1;
 }
+
+#include "jplg_api_frontend.inl"
 
 } // extern "C"

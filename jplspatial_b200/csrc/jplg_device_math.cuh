@@ -204,12 +204,12 @@ __device__ __forceinline__ uint32_t lut2d_pos_simd(const uint32_t* __restrict__ 
 	return static_cast<uint32_t>(cvtt(p * 1024.0f + 0.5f)) & 1023u;
 }
 
-// Math::QuatLookAt(direction, up=(0,1,0)) = Quat::FromBasis(Basis::FromUpAndForward(up, direction))
-// (inc/Math/MinimalQuat.h:84-144, inc/Math/MinimalBasis.h:60-71); scalar IEEE
-__device__ __forceinline__ Q4 quat_look_at_world_up(const F3& dir)
+// Math::QuatFromUpAndForward(up, forward) = Quat::FromBasis(Basis::FromUpAndForward(up, forward)); QuatLookAt(direction, up) is the
+// same call with forward = direction (inc/Math/MinimalQuat.h:84-144, inc/Math/MinimalBasis.h:60-71); scalar IEEE
+__device__ __forceinline__ Q4 quat_from_up_and_forward(const F3& up, const F3& forward)
 {
-	F3 Y{ 0.0f, 1.0f, 0.0f };
-	const F3 Z = dir;
+	F3 Y = up;
+	const F3 Z = forward;
 	const float dYZ = dot3(Y, Z);
 	const float ad = dYZ < 0 ? -dYZ : dYZ;
 	const float diff = ad - 1.0f;

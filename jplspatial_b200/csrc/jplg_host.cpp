@@ -745,4 +745,139 @@ namespace jplg
 		const float rev[4] = { freq[3], freq[2], freq[1], freq[0] };
 		prep(rev, out + 15, out + 19, out + 23);
 	}
+	//======================================================================
+	// Scene front-end builders
+	namespace
+	{
+		inline uint32_t FBits(float f) { uint32_t u; std::memcpy(&u, &f, 4); return u; }
+		inline float BitsF(uint32_t u) { float f; std::memcpy(&f, &u, 4); return f; }
+
+		// JPL::exp(simd), one lane, SSE2 semantic: fma = multiply then add (inc/Math/SIMDMath.h:296-316; floor inc/Math/SIMD.h:1861-1879)
+		float ExpSimdLane(float x)
+		{
+			x = std::min(std::max(x, -88.3762626647949f), 88.3762626647949f);
+			const float v = x * 1.44269504088896341f + 0.5f;
+			const float tr = static_cast<float>(static_cast<int32_t>(v));
+			const float n = (v == 0.0f) ? v : tr - (tr > v ? 1.0f : 0.0f);
+			const float nC2 = n * -2.12194440e-4f;
+			x = x - (n * 0.693359375f + nC2);
+			const float x2 = x * x;
+			float y = 1.9875691500e-4f;
+			y = y * x + 1.3981999507e-3f;
+			y = y * x + 8.3334519073e-3f;
+			y = y * x + 4.1665795894e-2f;
+			y = y * x + 1.6666665459e-1f;
+			y = y * x + 5.0000001201e-1f;
+			y = y * x2 + (x + 1.0f);
+			return y * BitsF(static_cast<uint32_t>((static_cast<int32_t>(n) + 0x7f) << 23));
+		}
+		// JPL::log(simd), one lane, for x > 0 (inc/Math/SIMDMath.h:191-226)
+		float LogSimdLane(float x)
+		{
+			x = std::max(x, BitsF(0x00800000u));
+			const int32_t emm0 = static_cast<int32_t>(FBits(x) >> 23) - 0x7f;
+			float e = static_cast<float>(emm0) + 1.0f;
+			x = BitsF((FBits(x) & ~0x7f800000u) | FBits(0.5f));
+			const bool below = x < 0.707106781186547524f;
+			e -= below ? 1.0f : 0.0f;
+			x += (below ? x : 0.0f) - 1.0f;
+			float y = 7.0376836292e-2f;
+			y = y * x + -1.1514610310e-1f;
+			y = y * x + 1.1676998740e-1f;
+			y = y * x + -1.2420140846e-1f;
+			y = y * x + 1.4249322787e-1f;
+			y = y * x + -1.6668057665e-1f;
+			y = y * x + 2.0000714765e-1f;
+			y = y * x + -2.4999993993e-1f;
+			y = y * x + 3.3333331174e-1f;
+			y *= x;
+			const float x2 = x * x;
+			y = (e * -2.12194440e-4f + y * x2) - x2 * 0.5f;
+			return e * 0.693359375f + (x + y);
+		}
+		// pow(simd, simd) for finite x > 0, x != 1, finite y != 0: exp(y * log(|x|)) (SIMDMath.h:372-379; the rest of the function only patches special values)
+		float PowSimdLane(float x, float y) { return ExpSimdLane(y * LogSimdLane(x)); }
+		// round(simd), SSE2 path: trunc(x + copysign(0.5, x)) (inc/Math/SIMD.h:1934-1937)
+		float RoundSimdLane(float x) { return static_cast<float>(static_cast<int32_t>(x + BitsF(FBits(0.5f) | (FBits(x) & 0x80000000u)))); }
+
+		void LowerThirdCenters(float f1, float f2, float f3, float out[4])
+		{
+			const float lower[4] = { 20.0f, f1, f2, f3 }, upper[4] = { f1, f2, f3, 22050.0f };
+			for (int i = 0; i < 4; ++i) out[i] = lower[i] * PowSimdLane(upper[i] / lower[i], 1.0f / 6.0f);
+		}
+	}
+
+	void DefaultBandCenters(float out[4])
+	{
+		const float lower[4] = { 20.0f, 176.0f, 775.0f, 3408.0f }, upper[4] = { 176.0f, 775.0f, 3408.0f, 22050.0f };
+		for (int i = 0; i < 4; ++i) out[i] = RoundSimdLane(std::sqrt(lower[i] * upper[i]));
+	}
+
+	float SpeedOfSoundForTemperature(float temperatureC)
+	{
+		constexpr float zeroK = 273.15f;
+		constexpr float invRefTemp = 1.0f / (20.0f + zeroK);
+		return 343.2f * std::sqrt((zeroK + temperatureC) * invRefTemp);
+	}
+
+	void BuildAirAbsorptionCache(const float bands[4], float temperatureC, float humidityPercent, float pressureKPa, float nyquist, AirCacheHost& out)
+	{
+		// ---- AirAbsorption ctor (ISO 9613-1 terms). The reference calls the C functions ::pow / ::exp / ::sqrt, i.e. the DOUBLE versions, on float
+		// arguments; the mixed float / double promotions below follow its expressions term by term.
+		const float pRef = 101.325f;
+		const float tK = temperatureC + 273.15f;
+		const float tRef = 293.15f;
+		const float tTriple = 273.16f;
+		const float tRel = tK / tRef;
+		const float pRel = pressureKPa / pRef;
+		const float pSat = pRef * ::pow(10.0f, -6.8346f * ::pow(tTriple / tK, 1.261f) + 4.6151f);
+		const float h = humidityPercent * (pSat / pressureKPa);
+		const float frO = pRel * (24.0f + 4.04e4f * h * ((0.02f + h) / (0.391f + h)));
+		const float frN = pRel * ::pow(tRel, -0.5f) * (9.0f + 280.0f * h * ::exp(-4.170f * (::pow(tRel, -1.0f / 3.0f) - 1.0f)));
+		const float classical = 1.84e-11f * ::pow(pRel, -1.0f) * ::sqrt(tRel);
+		const float relaxScale = ::pow(tRel, -2.5f);
+		const float cO = 0.01275f * ::exp(-2239.1f / tK);
+		const float cN = 0.1068f * ::exp(-3352.0f / tK);
+		const float frOInv = 1.0f / frO, frNInv = 1.0f / frN;
+		auto perMeter = [&](float f) // ComputeAbsorptionPerMeter(simd) lane; Math::FMA = multiply, add in the SSE2 build
+		{
+			const float f2 = f * f;
+			const float o = cO / (f2 * frOInv + frO);
+			const float n = cN / (f2 * frNInv + frN);
+			const float mol = relaxScale * (o + n);
+			const float total = classical + mol;
+			return (8.68588963807f * f2) * total;
+		};
+		// ---- CacheParameters
+		float c2[4];
+		for (int i = 0; i < 4; ++i) c2[i] = bands[i] * bands[i];
+		const float f3 = c2[3] / nyquist, f2 = c2[2] / f3, f1 = c2[1] / f2;   // SplitFrequenciesFromBandCenters
+		LowerThirdCenters(f1, f2, f3, out.lowerThirdCenters);
+		for (int i = 0; i < 4; ++i)
+		{
+			out.centers[i] = bands[i];
+			const float weighted = bands[i] >= 1000.0f ? out.lowerThirdCenters[i] : bands[i];
+			out.centerDb[i] = perMeter(bands[i]);
+			out.lowerThirdDb[i] = perMeter(out.lowerThirdCenters[i]);
+			out.weightedDb[i] = perMeter(weighted);
+			out.hasKnee[i] = bands[i] > 400.0f ? 1u : 0u;
+			const float deltaLk = bands[i] >= 1000.0f ? 14.0f : 6.0f;
+			out.distanceToKnee[i] = deltaLk / out.centerDb[i];
+			out.linFactor[i] = out.distanceToKnee[i] * (out.centerDb[i] - out.lowerThirdDb[i]);
+			out.decaySlope[i] = out.weightedDb[i] * SpeedOfSoundForTemperature(temperatureC);
+		}
+	}
+
+	void SanitizeFallbackDir(float out[3])
+	{
+		// Normalized(Vec3(0, 1, -5e-2)) with Math::InvSqrt evaluated at compile time: 1 / SqrtConstevalFallback<float, 2>(x)
+		const float x = 0.0f * 0.0f + 1.0f * 1.0f + -5e-2f * -5e-2f;
+		float y = BitsF(0x5f3759dfu - (FBits(x) >> 1));
+		const float halfx = 0.5f * x;
+		for (int i = 0; i < 2; ++i) y = y * (1.5f - halfx * y * y);
+		float r = x * y;
+		r = 0.5f * (r + x / r);
+		const float inv = 1.0f / r;
+		out[0] = 0.0f * inv; out[1] = 1.0f * inv; out[2] = -5e-2f * inv;
+	}
 }

@@ -98,4 +98,21 @@ namespace jplg
 	float TanSimd(float x);                         // :643-665
 	V2 FromDiamond(float p);                        // inc/Math/DirectionEncoding.h:212-227
 	V3 OctDecode(uint32_t code);                    // :389-436 (scalar Decode<Vec3>)
+	//======================================================================
+	// Scene front-end builders (host, once per environment, like the reference)
+	// AirAbsorption::CacheParameters (inc/AirAbsorption.h:179-210, ctor :297-343, ComputeAbsorptionPerMeter(simd) :358-368,
+	// band helpers inc/FrequencyBands.h:40-66 incl. the SIMD pow = exp(y * log(x)) of inc/Math/SIMDMath.h:191-226,296-316,372-379)
+	struct AirCacheHost
+	{
+		float centers[4], lowerThirdCenters[4];
+		float centerDb[4], lowerThirdDb[4], weightedDb[4], decaySlope[4];
+		float distanceToKnee[4], linFactor[4];
+		uint32_t hasKnee[4];
+	};
+	void BuildAirAbsorptionCache(const float bands[4], float temperatureC, float humidityPercent, float pressureKPa, float nyquist, AirCacheHost& out);
+	void DefaultBandCenters(float out[4]);               // cBandCenters = round(ComputeBandCenters(cDefaultFrequencySplits)) (FrequencyBands.h:68)
+	float SpeedOfSoundForTemperature(float temperatureC); // SpeedOfSound::ForTemperature (inc/SpeedOfSound.h:38-47)
+	// Impl::SanitizeSourceDir's `static const fallbackDir = Normalized(Vec3(0, 1, -5e-2))` (inc/Services/PanningService.h:487) is constant-initialised,
+	// i.e. evaluated by the reference's constexpr sqrt fallback (inc/Math/Math.h:213-262,283-289), not by the runtime 1/sqrt: restated here.
+	void SanitizeFallbackDir(float out[3]);
 }

@@ -26,12 +26,13 @@ namespace jplg
 	{
 		uint32_t numChannels, numVS, numRings, samplesPerRing, halfSamples, tail;
 		float phiTerm, offsetTerm, vsWeight;
+		uint32_t paramStride;   // 5 or 11 floats per source (set by LaunchMdap)
 		float quats[kMaxSourceChannelsDev][4];
 		float azSin[kMaxAzimuthFloats], azCos[kMaxAzimuthFloats];
 	};
 
 	cudaError_t LaunchPointGains(const PannerDev& p, const float* dirs, uint32_t n, float* out, cudaStream_t st);
-	cudaError_t LaunchMdap(const PannerDev& p, const MdapLayoutParams& lp, const float* params, uint32_t n, float* out, int numSMs, cudaStream_t st);
+	cudaError_t LaunchMdap(const PannerDev& p, const MdapLayoutParams& lp, const float* params, uint32_t paramStride, uint32_t n, float* out, int numSMs, cudaStream_t st);
 	cudaError_t LaunchProcessVS(const PannerDev& p, const float* vs, uint32_t n, uint32_t batches, float* out, cudaStream_t st);
 
 	//======================================================================
@@ -119,4 +120,51 @@ namespace jplg
 	float FdnHadamardScale();
 	cudaError_t LaunchFdnDecay(const float* slope, uint32_t n, float invSampleRate, float* decay, int mode, cudaStream_t st);
 	cudaError_t LaunchFdn(const FdnParams& fp, int mode, cudaStream_t st);
+	//======================================================================
+	// Scene front-end (jplg_frontend_kernels.cu): the per-source body of SpatialManager::AdvanceSimulation
+	// (inc/SpatialManager.h:374-420) plus the parameter producers that sit between it and stages 1-3.
+	struct AttFunctionDev     // one AttenuationFunction (inc/DistanceAttenuation.h:41-162)
+	{
+		int32_t kind;          // 0: AttenuationBaseModel, 1: AttenuationCurve
+		int32_t model;         // AttenuationModel
+		float minDistance, maxDistance, rolloff;
+		uint32_t firstPoint, numPoints; // curve: range in the point table (sorted by distance)
+	};
+	struct AirCacheDev        // the fields of AirAbsorptionCache that ComputeForDistance reads (inc/AirAbsorption.h:212-234)
+	{
+		float centerDb[4], lowerThirdDb[4], distanceToKnee[4], linFactor[4];
+		uint32_t hasKnee[4];
+	};
+	struct FrontendArgs
+	{
+		uint32_t n;
+		// ---- inputs (null = absent)
+		const float* sources;          // [n][9] Position: location, up, forward
+		const float* listeners;        // [m][9]
+		const uint32_t* listenerIndex; // [n] (null: listener 0)
+		const float* distanceIn;       // [n] used instead of the direct path when sources == null
+		const float* dotIn;            // [n] cone input (InvDirectionDot) when sources == null
+		const float* cones;            // [n][2] inner, outer angle (radians)
+		const float* sizes;            // [n] object size; < 0 = the source has none (spread unchanged)
+		const float* focusSpread;      // [n][2] PanEffectParameters (null: focusConst / spreadConst)
+		float focusConst, spreadConst;
+		const uint32_t* attIndex;      // [n] index into att (null: 0)
+		const AttFunctionDev* att;     // attenuation function table
+		uint32_t numAtt;
+		const float* attPoints;        // [p][3] distance, value, Curve::EType
+		AirCacheDev air;
+		float invSpeedOfSound;         // SpeedOfSound::cInvReference or 1 / ForTemperature(T)
+		float fallbackDir[3];          // SanitizeSourceDir's fallback (PanningService.h:487)
+		int32_t spreadFlavour;         // 0: SpatialManager::GetSpreadFromSourceSize (SpatialManager.h:617-623); 1: the free function (PannerBase.h:69-74)
+		// ---- outputs (null = not wanted)
+		float* direct;     // [n][4] distance, directionDot, invDirectionDot, cone factor
+		float* rel;        // [n][9] DirectPathResult::Position (direction, up, forward in the listener's frame)
+		float* pan;        // [n][panStride] {sanitised dir, focus, spread} (+ {up, forward} when panStride == 11): the input of LaunchMdap
+		uint32_t panStride;
+		float* distAtt;    // [n]
+		float* airDb;      // [n][4] ComputeForDistance
+		float* bandGains;  // [n][4] dBToGain(-airDb) (simd flavour): DirectSoundEffect's filterGains
+		float* delay;      // [n] seconds
+	};
+	cudaError_t LaunchFrontend(const FrontendArgs& fa, int numSMs, cudaStream_t st);
 }

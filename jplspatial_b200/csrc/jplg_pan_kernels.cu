@@ -53,16 +53,19 @@ namespace jplg
 		F3 target;
 	};
 
-	__device__ __forceinline__ MdapCommon mdap_prologue(const float* __restrict__ params, uint32_t src)
+	// stride 5: PanUpdateData {dir, focus, spread}; stride 11: PanUpdateDataWithOrientation {dir, focus, spread, up, forward}
+	// (PannerBase.h:486-500 vs :501-515: only the pan quaternion differs)
+	__device__ __forceinline__ MdapCommon mdap_prologue(const float* __restrict__ params, uint32_t src, uint32_t stride)
 	{
-		const float* p = params + size_t(src) * 5;
+		const float* p = params + size_t(src) * stride;
 		MdapCommon m;
 		m.target = { p[0], p[1], p[2] };
 		const float focusIn = p[3], spreadIn = p[4];
 		m.focus = (focusIn == 1.0f) ? 0.9999f : focusIn;          // PannerBase.h:589
 		const float spread = (spreadIn == 0.0f) ? 0.0001f : spreadIn; // :646
 		m.tSlerp = 1.0f - spread;                                  // :648
-		m.qPan = quat_look_at_world_up(m.target);                  // :495
+		m.qPan = stride == 11 ? quat_from_up_and_forward(F3{ p[5], p[6], p[7] }, F3{ p[8], p[9], p[10] })  // :509 QuatFromUpAndForward(Orientation.Up, Orientation.Forward)
+		                      : quat_from_up_and_forward(F3{ 0.0f, 1.0f, 0.0f }, m.target);                // :495 QuatLookAt(SourceDirection, world up)
 		return m;
 	}
 
@@ -99,7 +102,7 @@ namespace jplg
 		{
 			const bool valid = srcBase + grp < n;                       // a warp's groups run the same trip counts; the idle one only skips its stores
 			const uint32_t src = valid ? srcBase + grp : n - 1;
-			const MdapCommon m = mdap_prologue(params, src);
+			const MdapCommon m = mdap_prologue(params, src, lp.paramStride);
 
 			// GenerateSpreadCap ring centres (inc/Panning/VBAPanning3D.h:414-448): rings in groups of 4 through the
 			// SIMD SinCos, the remaining (R & 3) rings through libm
@@ -197,7 +200,7 @@ namespace jplg
 
 		for (uint32_t src = blockIdx.x * JPLG_MDAP_WARPS + warp; src < n; src += gridDim.x * JPLG_MDAP_WARPS)
 		{
-			const MdapCommon m = mdap_prologue(params, src);
+			const MdapCommon m = mdap_prologue(params, src, lp.paramStride);
 			if (lane < totalVS)
 			{
 				const uint32_t ch = lane / numVS, v = lane - ch * numVS;
@@ -307,8 +310,10 @@ namespace jplg
 		return (2048 + JPLG_MDAP_WARPS * 32) * 4;
 	}
 
-	cudaError_t LaunchMdap(const PannerDev& p, const MdapLayoutParams& lp, const float* params, uint32_t n, float* out, int numSMs, cudaStream_t st)
+	cudaError_t LaunchMdap(const PannerDev& p, const MdapLayoutParams& lpIn, const float* params, uint32_t paramStride, uint32_t n, float* out, int numSMs, cudaStream_t st)
 	{
+		MdapLayoutParams lp = lpIn;
+		lp.paramStride = paramStride;
 		if (n == 0) return cudaSuccess;
 		const size_t smem = MdapSmemBytes(p, lp);
 		const uint32_t groups = JPLG_MDAP_WARPS * 32 / MdapLanesPerSource(p);

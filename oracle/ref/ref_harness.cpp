@@ -27,6 +27,13 @@
 #include <JPLSpatial/Math/SIMDMath.h>
 #include <JPLSpatial/Math/Vec3Math.h>
 #include <JPLSpatial/Utilities/SmoothedValue.h>
+#include <JPLSpatial/Math/MinimalVec3.h>
+#include <JPLSpatial/Services/DirectPathService.h>
+#include <JPLSpatial/Services/PanningService.h>
+#include <JPLSpatial/SpatialManager.h>
+#include <JPLSpatial/DistanceAttenuation.h>
+#include <JPLSpatial/AirAbsorption.h>
+#include <JPLSpatial/SpeedOfSound.h>
 
 #include <atomic>
 #include <chrono>
@@ -589,5 +596,149 @@ extern "C"
 		}
 		for (auto& th : pool) th.join();
 		return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+	}
+	//==========================================================================
+	// Scene front-end: DirectPathService, SanitizeSourceDir, spread-from-size,
+	// distance attenuation, air absorption, speed of sound. Positions are 9 floats: location, up, forward.
+	static Position<MinimalVec3> ToPos(const float* p)
+	{
+		return Position<MinimalVec3>{ .Location = MinimalVec3(p[0], p[1], p[2]),
+			.Orientation = { .Up = MinimalVec3(p[3], p[4], p[5]), .Forward = MinimalVec3(p[6], p[7], p[8]) } };
+	}
+
+	// out [n][12] = distance, directionDot, invDirectionDot, location[3], up[3], forward[3]
+	void ref_direct_path(const float* sources, const float* listeners, const uint32_t* listenerIndex, uint32_t n, float* out)
+	{
+		for (uint32_t i = 0; i < n; ++i)
+		{
+			const auto r = DirectPathService::ProcessDirectPath(ToPos(sources + size_t(i) * 9), ToPos(listeners + size_t(listenerIndex ? listenerIndex[i] : 0) * 9));
+			float* o = out + size_t(i) * 12;
+			o[0] = r.Distance; o[1] = r.DirectionDot; o[2] = r.InvDirectionDot;
+			o[3] = r.Position.Location.X; o[4] = r.Position.Location.Y; o[5] = r.Position.Location.Z;
+			o[6] = r.Position.Orientation.Up.X; o[7] = r.Position.Orientation.Up.Y; o[8] = r.Position.Orientation.Up.Z;
+			o[9] = r.Position.Orientation.Forward.X; o[10] = r.Position.Orientation.Forward.Y; o[11] = r.Position.Orientation.Forward.Z;
+		}
+	}
+	// kind 0: ProcessAngleAttenuationImpl(dot, cone) (what EvaluateDirection caches); 1: azimuth overload; 2: position overload (x = [n][3], refPoint [9])
+	void ref_angle_attenuation(int kind, const float* x, const float* refPoint, const float* cones, uint32_t n, float* out)
+	{
+		for (uint32_t i = 0; i < n; ++i)
+		{
+			const AttenuationCone cone{ cones[2 * i], cones[2 * i + 1] };
+			if (kind == 0) out[i] = DirectPathService::ProcessAngleAttenuationImpl(x[i], cone);
+			else if (kind == 1) out[i] = DirectPathService::ProcessAngleAttenuation(x[i], cone);
+			else out[i] = DirectPathService::ProcessAngleAttenuation(MinimalVec3(x[3 * i], x[3 * i + 1], x[3 * i + 2]), ToPos(refPoint), cone);
+		}
+	}
+	void ref_attenuation_model(int model, float minDistance, float maxDistance, float rolloff, const float* distance, uint32_t n, float* out)
+	{
+		AttenuationBaseModel m;
+		m.Model = static_cast<AttenuationModel>(model);
+		m.Parameters = { minDistance, maxDistance, rolloff };
+		const AttenuationFunction& f = m;
+		for (uint32_t i = 0; i < n; ++i) out[i] = f.Evaluate(distance[i]);
+	}
+	// points [k][3] = distance, value, Curve::EType (as float)
+	void ref_attenuation_curve(const float* points, uint32_t k, int sortPoints, const float* distance, uint32_t n, float* out)
+	{
+		AttenuationCurve c;
+		for (uint32_t j = 0; j < k; ++j)
+		{
+			AttenuationCurve::Point p;
+			p.Distance = points[3 * j]; p.Value = points[3 * j + 1]; p.FunctionType = static_cast<Curve::EType>(int(points[3 * j + 2]));
+			c.Points.push_back(p);
+		}
+		if (sortPoints) c.SortPoints();
+		const AttenuationFunction& f = c;
+		for (uint32_t i = 0; i < n; ++i) out[i] = f.Evaluate(distance[i]);
+	}
+	// out [32]: centres, lowerThirdCentres, centre dB, lowerThird dB, weighted dB, decay slope, distanceToKnee, linearised factor; knee mask [4]
+	void ref_air_cache(const float* bands, float tempC, float humidity, float pressureKPa, float nyquist, float* out, uint32_t* kneeMask)
+	{
+		const AirAbsorptionCache c = AirAbsorption::CacheParameters(simd(bands[0], bands[1], bands[2], bands[3]), AirAbsorptionParams{ tempC, humidity, pressureKPa }, nyquist);
+		c.FrequencyBandCenters.store(out); c.FrequencyBandLowerThirdCenters.store(out + 4);
+		c.CenterFrequencyAbsorption_dB.store(out + 8); c.LowerThirdBandAbsorption_dB.store(out + 12);
+		c.HighFreqWeightedAbsorption_dB.store(out + 16); c.FrequencyDecaySlope.store(out + 20);
+		c.LinAprox.DistanceToKnee.store(out + 24); c.LinAprox.LinearizedHFLossFactor.store(out + 28);
+		float m[4]; simd::select(c.LinAprox.HasKnee, simd(1.0f), simd(0.0f)).store(m);
+		for (int i = 0; i < 4; ++i) kneeMask[i] = m[i] != 0.0f;
+	}
+	void ref_default_bands(float* out) { JPL::cBandCenters.store(out); }
+	// ComputeForDistance -> dB loss [n][4]; gains [n][4] = dBToGain(-loss) (simd flavour) when non-null
+	void ref_air_for_distance(const float* bands, float tempC, float humidity, float pressureKPa, float nyquist, const float* distance, uint32_t n, float* outDb, float* outGain)
+	{
+		const AirAbsorptionCache c = AirAbsorption::CacheParameters(simd(bands[0], bands[1], bands[2], bands[3]), AirAbsorptionParams{ tempC, humidity, pressureKPa }, nyquist);
+		for (uint32_t i = 0; i < n; ++i)
+		{
+			const simd loss = AirAbsorption::ComputeForDistance(distance[i], c);
+			loss.store(outDb + size_t(i) * 4);
+			if (outGain) dBToGain(simd(0.0f) - loss).store(outGain + size_t(i) * 4);
+		}
+	}
+	float ref_air_for_frequency(float f, float tempC, float humidity, float pressureKPa) { return AirAbsorption::ComputeForFrequency(f, AirAbsorptionParams{ tempC, humidity, pressureKPa }); }
+	float ref_speed_of_sound(float tempC) { return SpeedOfSound::ForTemperature(tempC); }
+	float ref_speed_of_sound_reference(int inverse) { return inverse ? SpeedOfSound::cInvReference : SpeedOfSound::cReference; }
+	void ref_sanitize_source_dir(const float* dirs, uint32_t n, float* out)
+	{
+		for (uint32_t i = 0; i < n; ++i)
+		{
+			const MinimalVec3 d = Impl::SanitizeSourceDir(MinimalVec3(dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2]));
+			out[3 * i] = d.X; out[3 * i + 1] = d.Y; out[3 * i + 2] = d.Z;
+		}
+	}
+	// flavour 0: SpatialManager::GetSpreadFromSourceSize (atan * 1/pi, what AdvanceSimulation calls); 1: the free function of PannerBase.h:69-74 (atanf * 2/pi)
+	void ref_spread_from_size(int flavour, const float* size, const float* distance, uint32_t n, float* out)
+	{
+		for (uint32_t i = 0; i < n; ++i)
+			out[i] = flavour == 0 ? Spatial::SpatialManager<MinimalVec3>::GetSpreadFromSourceSize(size[i], distance[i]) : JPL::GetSpreadFromSourceSize(size[i], distance[i]);
+	}
+	// The per-source body of SpatialManager::AdvanceSimulation (inc/SpatialManager.h:374-420) with the engine-side glue spelled out:
+	// direct path -> curve -> cone -> spread from size -> sanitised direction; air absorption and delay from the distance.
+	// Timed (single thread x `threads`), returns seconds; outputs like the GPU front-end.
+	double ref_frontend_timed(const float* sources, const float* listeners, uint32_t n, const float* cones, const float* sizes, const float* model /* [4] */,
+							  float* outDirect /* [n][4] */, float* outPan /* [n][5] */, float* outBand /* [n][4] */, float* outDelay, float* outAtt, float focus, int threads)
+	{
+		const AirAbsorptionCache& c = cDefaultAirAbsCache;
+		AttenuationBaseModel m; m.Model = static_cast<AttenuationModel>(int(model[0])); m.Parameters = { model[1], model[2], model[3] };
+		const auto t0 = std::chrono::steady_clock::now();
+		std::vector<std::thread> pool;
+		for (int t = 0; t < threads; ++t)
+		{
+			const uint32_t b = uint32_t(uint64_t(n) * t / threads), e = uint32_t(uint64_t(n) * (t + 1) / threads);
+			pool.emplace_back([=, &c, &m] {
+				const Position<MinimalVec3> lis = ToPos(listeners);
+				for (uint32_t i = b; i < e; ++i)
+				{
+					const auto r = DirectPathService::ProcessDirectPath(ToPos(sources + size_t(i) * 9), lis);
+					outDirect[4 * i] = r.Distance; outDirect[4 * i + 1] = r.DirectionDot; outDirect[4 * i + 2] = r.InvDirectionDot;
+					outDirect[4 * i + 3] = DirectPathService::ProcessAngleAttenuationImpl(r.InvDirectionDot, AttenuationCone{ cones[2 * i], cones[2 * i + 1] });
+					outAtt[i] = static_cast<const AttenuationFunction&>(m).Evaluate(r.Distance);
+					const float spread = Spatial::SpatialManager<MinimalVec3>::GetSpreadFromSourceSize(sizes[i], r.Distance);
+					const MinimalVec3 d = Impl::SanitizeSourceDir(r.Position.Location);
+					outPan[5 * i] = d.X; outPan[5 * i + 1] = d.Y; outPan[5 * i + 2] = d.Z; outPan[5 * i + 3] = focus; outPan[5 * i + 4] = spread;
+					dBToGain(simd(0.0f) - AirAbsorption::ComputeForDistance(r.Distance, c)).store(outBand + size_t(i) * 4);
+					outDelay[i] = r.Distance * SpeedOfSound::cInvReference;
+				}
+			});
+		}
+		for (auto& th : pool) th.join();
+		return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+	}
+
+	// ProcessVBAPData(sourceLayout, PanUpdateDataWithOrientation, out) (PannerBase.h:375,501-515); params [n][11] = dir, focus, spread, up, forward
+	void ref_mdap_oriented(void* panner, void* layout, const float* params, uint32_t n, float* out)
+	{
+		auto* p = static_cast<RefPanner*>(panner);
+		auto* l = static_cast<RefLayout*>(layout);
+		if (!p->is3D) return;
+		const uint32_t row = static_cast<uint32_t>(l->l3.ChannelGroups.size()) * p->p3.GetNumChannels();
+		for (uint32_t i = 0; i < n; ++i)
+		{
+			const float* q = params + size_t(i) * 11;
+			typename Panner3D::PanUpdateDataWithOrientation u{
+				.Pan = { .SourceDirection = MinimalVec3(q[0], q[1], q[2]), .Focus = q[3], .Spread = q[4] },
+				.Orientation = { .Up = MinimalVec3(q[5], q[6], q[7]), .Forward = MinimalVec3(q[8], q[9], q[10]) } };
+			p->p3.ProcessVBAPData(l->l3, u, std::span<float>(out + size_t(i) * row, row));
+		}
 	}
 } // extern "C"

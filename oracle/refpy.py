@@ -86,6 +86,82 @@ class Ref:
         arr = (_vp * len(buses))(*[b.h for b in buses])
         return self.lib.ref_erbus_process_batch(arr, len(buses), inp.ctypes.data, out.ctypes.data, frames, int(threads))
 
+    # ---- scene front-end; positions are [.,9] = location, up, forward
+    def _p(self, a, dtype=np.float32):
+        return None if a is None else np.ascontiguousarray(a, dtype)
+
+    def direct_path(self, sources, listeners, listener_index=None):
+        s = self._p(sources).reshape(-1, 9); l = self._p(listeners).reshape(-1, 9); li = self._p(listener_index, np.uint32)
+        out = np.empty((s.shape[0], 12), np.float32)
+        self.lib.ref_direct_path(_vp(s.ctypes.data), _vp(l.ctypes.data), _vp(None if li is None else li.ctypes.data), _u32(s.shape[0]), _vp(out.ctypes.data))
+        return out
+
+    def angle_attenuation(self, kind, x, cones, ref_point=None):
+        x = self._p(x); c = self._p(cones).reshape(-1, 2); r = self._p(ref_point)
+        out = np.empty(c.shape[0], np.float32)
+        self.lib.ref_angle_attenuation(C.c_int(kind), _vp(x.ctypes.data), _vp(None if r is None else r.ctypes.data), _vp(c.ctypes.data), _u32(c.shape[0]), _vp(out.ctypes.data))
+        return out
+
+    def attenuation_model(self, model, min_d, max_d, rolloff, distance):
+        d = self._p(distance); out = np.empty_like(d)
+        self.lib.ref_attenuation_model(C.c_int(model), _f32(min_d), _f32(max_d), _f32(rolloff), _vp(d.ctypes.data), _u32(d.size), _vp(out.ctypes.data))
+        return out
+
+    def attenuation_curve(self, points, distance, sort_points=True):
+        p = self._p(points).reshape(-1, 3); d = self._p(distance); out = np.empty_like(d)
+        self.lib.ref_attenuation_curve(_vp(p.ctypes.data), _u32(p.shape[0]), C.c_int(1 if sort_points else 0), _vp(d.ctypes.data), _u32(d.size), _vp(out.ctypes.data))
+        return out
+
+    def default_bands(self):
+        out = np.empty(4, np.float32); self.lib.ref_default_bands(_vp(out.ctypes.data)); return out
+
+    def air_cache(self, bands=None, temp_c=20.0, humidity=50.0, pressure=101.325, nyquist=22050.0):
+        b = self.default_bands() if bands is None else self._p(bands)
+        out = np.empty(32, np.float32); knee = np.empty(4, np.uint32)
+        self.lib.ref_air_cache(_vp(b.ctypes.data), _f32(temp_c), _f32(humidity), _f32(pressure), _f32(nyquist), _vp(out.ctypes.data), _vp(knee.ctypes.data))
+        names = ("band_centers", "lower_third_centers", "center_db", "lower_third_db", "weighted_db", "decay_slope", "distance_to_knee", "linearized_loss_factor")
+        d = {k: out[4 * i:4 * i + 4].copy() for i, k in enumerate(names)}
+        d["has_knee"] = knee
+        return d
+
+    def air_for_distance(self, distance, bands=None, temp_c=20.0, humidity=50.0, pressure=101.325, nyquist=22050.0):
+        b = self.default_bands() if bands is None else self._p(bands)
+        d = self._p(distance); db = np.empty((d.size, 4), np.float32); g = np.empty((d.size, 4), np.float32)
+        self.lib.ref_air_for_distance(_vp(b.ctypes.data), _f32(temp_c), _f32(humidity), _f32(pressure), _f32(nyquist), _vp(d.ctypes.data), _u32(d.size), _vp(db.ctypes.data), _vp(g.ctypes.data))
+        return db, g
+
+    def air_for_frequency(self, f, temp_c=20.0, humidity=50.0, pressure=101.325):
+        self.lib.ref_air_for_frequency.restype = _f32
+        return float(self.lib.ref_air_for_frequency(_f32(f), _f32(temp_c), _f32(humidity), _f32(pressure)))
+
+    def speed_of_sound(self, temp_c=None):
+        self.lib.ref_speed_of_sound.restype = _f32; self.lib.ref_speed_of_sound_reference.restype = _f32
+        return float(self.lib.ref_speed_of_sound_reference(C.c_int(0))) if temp_c is None else float(self.lib.ref_speed_of_sound(_f32(temp_c)))
+
+    def inv_speed_of_sound(self):
+        self.lib.ref_speed_of_sound_reference.restype = _f32
+        return float(self.lib.ref_speed_of_sound_reference(C.c_int(1)))
+
+    def sanitize_source_dir(self, dirs):
+        d = self._p(dirs).reshape(-1, 3); out = np.empty_like(d)
+        self.lib.ref_sanitize_source_dir(_vp(d.ctypes.data), _u32(d.shape[0]), _vp(out.ctypes.data)); return out
+
+    def spread_from_size(self, flavour, size, distance):
+        s = self._p(size); d = self._p(distance); out = np.empty_like(s)
+        self.lib.ref_spread_from_size(C.c_int(flavour), _vp(s.ctypes.data), _vp(d.ctypes.data), _u32(s.size), _vp(out.ctypes.data)); return out
+
+    def frontend_timed(self, sources, listener, cones, sizes, model, focus=1.0, threads=1):
+        """-> (seconds, dict of outputs): the per-source body of AdvanceSimulation + producers on `threads` std::threads"""
+        s = self._p(sources).reshape(-1, 9); n = s.shape[0]
+        l = self._p(listener).reshape(-1, 9); c = self._p(cones).reshape(-1, 2); z = self._p(sizes); m = self._p(model)
+        o = {"direct": np.empty((n, 4), np.float32), "pan_params": np.empty((n, 5), np.float32), "band_gains": np.empty((n, 4), np.float32),
+             "delay_seconds": np.empty(n, np.float32), "distance_attenuation": np.empty(n, np.float32)}
+        self.lib.ref_frontend_timed.restype = C.c_double
+        t = self.lib.ref_frontend_timed(_vp(s.ctypes.data), _vp(l.ctypes.data), _u32(n), _vp(c.ctypes.data), _vp(z.ctypes.data), _vp(m.ctypes.data),
+                                        _vp(o["direct"].ctypes.data), _vp(o["pan_params"].ctypes.data), _vp(o["band_gains"].ctypes.data),
+                                        _vp(o["delay_seconds"].ctypes.data), _vp(o["distance_attenuation"].ctypes.data), _f32(focus), C.c_int(threads))
+        return float(t), o
+
     # ---- panners
     def panner(self, mask):
         return RefPanner(self, mask)
@@ -207,6 +283,13 @@ class RefPanner:
         else:
             self.lib.ref_mdap(self.h, layout.h, _vp(p.ctypes.data), _u32(p.shape[0]), _vp(o.ctypes.data))
         return o
+
+    def mdap_oriented(self, layout, params):
+        """params [n,11] = dir, focus, spread, up, forward (3D panners)"""
+        p = np.ascontiguousarray(params, np.float32).reshape(-1, 11)
+        out = np.zeros((p.shape[0], layout.num_channels, self.L), np.float32)
+        self.lib.ref_mdap_oriented(self.h, layout.h, _vp(p.ctypes.data), _u32(p.shape[0]), _vp(out.ctypes.data))
+        return out
 
     def process_virtual_sources(self, vs):
         v = np.ascontiguousarray(vs, np.float32); o = np.zeros(self.L, np.float32)
