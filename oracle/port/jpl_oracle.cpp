@@ -227,9 +227,11 @@ namespace
 	}
 
 	/* Math::QuatLookAt(dir, worldUp) = Quat::FromBasis(Basis::FromUpAndForward) (inc/Math/MinimalQuat.h:84-144, MinimalBasis.h:60-71) */
-	Quat quatLookAt(const Vec3& fwd)
+	Quat quatFromUpAndForward(Vec3 up, const Vec3& fwd);
+	Quat quatLookAt(const Vec3& fwd) { return quatFromUpAndForward(Vec3{ 0, 1, 0 }, fwd); }
+	/* Math::QuatFromUpAndForward(up, forward) (inc/Math/MinimalQuat.h:136-139) */
+	Quat quatFromUpAndForward(Vec3 up, const Vec3& fwd)
 	{
-		Vec3 up{ 0, 1, 0 };
 		if (std::fabs(std::fabs(dot(up, fwd)) - 1.0f) <= 1e-6f) up = std::fabs(fwd.z) < 0.999f ? Vec3{ 0, 0, 1 } : Vec3{ 1, 0, 0 };
 		const Vec3 X = normalizedExact(cross(up, fwd));
 		const Vec3 Y = cross(fwd, X);
@@ -617,13 +619,14 @@ namespace
 	}
 
 	/* ProcessVBAPDataImpl for one source (inc/Panning/PannerBase.h:520-728) */
-	void mdapOne(const orc_panner& p, const Layout& lay, const float* prm, float* out)
+	void mdapOne(const orc_panner& p, const Layout& lay, const float* prm, float* out, bool oriented = false)
 	{
 		const uint32_t L = p.L;
 		const Vec3 target{ prm[0], prm[1], prm[2] };
 		const float focus = prm[3] == 1.0f ? 0.9999f : prm[3];    /* :589 */
 		const float spread = prm[4] == 0.0f ? 0.0001f : prm[4];   /* :646 */
-		const Quat pan = quatLookAt(target);                      /* :495 */
+		const Quat pan = oriented ? quatFromUpAndForward(Vec3{ prm[5], prm[6], prm[7] }, Vec3{ prm[8], prm[9], prm[10] })  /* :509 */
+		                          : quatLookAt(target);            /* :495 */
 		std::vector<Vec3> cap; spreadCap(p, lay, focus, cap);
 		std::fill(out, out + size_t(lay.channels) * L, 0.0f);
 		float mix[32] = { 0 };
@@ -1140,5 +1143,155 @@ extern "C"
 			}
 			left -= n;
 		}
+	}
+	/* ================================================================================================
+	 * Scene front-end: the per-source body of SpatialManager::AdvanceSimulation (inc/SpatialManager.h:374-420)
+	 * and the parameter producers. Positions: 9 floats = location, up, forward. libm calls are the reference's own (this is CPU code). */
+	int orc_mdap_oriented(const orc_panner* p, uint32_t src, const float* params, uint32_t n, float* out) /* PannerBase.h:501-515 */
+	{
+		Layout l;
+		if (!makeLayout(*p, src, l)) return 0;
+		for (uint32_t i = 0; i < n; ++i) mdapOne(*p, l, params + size_t(i) * 11, out + size_t(i) * l.channels * p->L, true);
+		return 1;
+	}
+	/* DirectPathService::ProcessDirectPath (inc/Services/DirectPathService.h:280-338); out [12] = distance, dot, inverse dot, location, up, forward */
+	void orc_direct_path(const float* s, const float* l, float* out)
+	{
+		const Vec3 sLoc{ s[0], s[1], s[2] }, sUp{ s[3], s[4], s[5] }, sFwd{ s[6], s[7], s[8] };
+		const Vec3 lLoc{ l[0], l[1], l[2] }, lY{ l[3], l[4], l[5] }, lZ{ -l[6], -l[7], -l[8] };   /* ToBasisUnsafe (inc/Math/Position.h:58-68) */
+		const Vec3 lX = cross(lY, lZ);
+		auto inv = [&](const Vec3& v) { return Vec3{ dot(v, lX), dot(v, lY), dot(v, lZ) }; };  /* Basis::InverseTransform (MinimalBasis.h:99-106) */
+		Vec3 p = inv(Vec3{ sLoc.x - lLoc.x, sLoc.y - lLoc.y, sLoc.z - lLoc.z });
+		if (std::fabs(p.x) <= 1e-6f && std::fabs(p.z) <= 1e-6f) { p.x += 0.0f * 1e-5f; p.y += 0.0f * 1e-5f; p.z += -1.0f * 1e-5f; }  /* :291-294 */
+		const float distance = std::sqrt(p.x * p.x + p.y * p.y + p.z * p.z);
+		const Vec3 dir{ p.x / distance, p.y / distance, p.z / distance };
+		out[0] = distance;
+		out[1] = dir.x * 0.0f + dir.y * 0.0f + dir.z * -1.0f;
+		out[2] = dot(sFwd, inv(Vec3{ -dir.x, -dir.y, -dir.z }));
+		const Vec3 up = inv(sUp), fwd = inv(Vec3{ -sFwd.x, -sFwd.y, -sFwd.z });
+		out[3] = dir.x; out[4] = dir.y; out[5] = dir.z; out[6] = up.x; out[7] = up.y; out[8] = up.z; out[9] = fwd.x; out[10] = fwd.y; out[11] = fwd.z;
+	}
+	float orc_angle_attenuation(float azimuthCos, float inner, float outer) /* ProcessAngleAttenuationImpl (:340-364) */
+	{
+		const float ci = std::cos(inner * 0.5f), co = std::cos(outer * 0.5f);
+		if (azimuthCos > ci) return 0.0f;
+		if (azimuthCos > co) return (ci - azimuthCos) / (ci - co);
+		return 1.0f;
+	}
+	float orc_attenuation_model(int model, float mn, float mx, float rolloff, float d) /* AttenuationBaseModel::Evaluate (inc/DistanceAttenuation.h:66-119) */
+	{
+		const bool valid = mn < mx;
+		const float dc = d < mn ? mn : (mx < d ? mx : d);
+		switch (model)
+		{
+		case 1: return valid ? mn / (mn + rolloff * (dc - mn)) : 1.0f;
+		case 2: return valid ? 1.0f - rolloff * (dc - mn) / (mx - mn) : 1.0f;
+		case 3: return valid ? std::pow(dc / mn, -rolloff) : 1.0f;
+		default: return 1.0f;
+		}
+	}
+	static float curveShape(int type, float t) /* Curve::EvaluateCurve (inc/Math/Curves.h:58-85) */
+	{
+		const float halfPi = 3.14159274f * 0.5f;
+		switch (type)
+		{
+		case 0: return 1.0f;
+		case 1: return t;
+		case 2: return std::sin(t * halfPi);
+		case 3: return 1.0f - std::cos(t * halfPi);
+		case 4: return t * t * (3 - 2 * t);
+		case 5: return std::log(1.0f + 0.41f * t) * (1.0f / std::log(1.41f));
+		case 6: return std::log(1.0f + 2.0f * t) * (1.0f / std::log(3.0f));
+		case 7: return (std::pow(1.41f, t) - 1.0f) * (1.0f / 0.41f);
+		case 8: return (std::pow(3.0f, t) - 1.0f) * 0.5f;
+		default: return t;
+		}
+	}
+	float orc_attenuation_curve(const float* pts, uint32_t k, float d) /* AttenuationCurve::Evaluate (:172-215); pts sorted, [k][3] = distance, value, type */
+	{
+		if (k == 0) return 1.0f;
+		if (d <= pts[0]) return pts[1];
+		if (d >= pts[3 * (k - 1)]) return pts[3 * (k - 1) + 1];
+		uint32_t i = 0;
+		while (i < k && !(d < pts[3 * i])) ++i;                 /* first point with d < Distance (std::upper_bound) */
+		const float* a = pts + 3 * (i - 1); const float* b = pts + 3 * i;
+		if (int(a[2]) == 0) return a[1];
+		float t = (d - a[0]) / (b[0] - a[0]);
+		t = t < 0.0f ? 0.0f : (1.0f < t ? 1.0f : t);
+		return a[1] + (b[1] - a[1]) * curveShape(int(a[2]), t);
+	}
+	/* JPL::log(simd) one lane, x > 0 (inc/Math/SIMDMath.h:191-226) */
+	static float logLane(float x)
+	{
+		uint32_t u; std::memcpy(&u, &x, 4);
+		if (u < 0x00800000u) u = 0x00800000u;
+		float e = float(int32_t(u >> 23) - 0x7f) + 1.0f;
+		u = (u & ~0x7f800000u) | 0x3f000000u; std::memcpy(&x, &u, 4);
+		const bool lo = x < 0.707106781186547524f;
+		if (lo) e -= 1.0f;
+		x += (lo ? x : 0.0f) - 1.0f;
+		float y = 7.0376836292e-2f;
+		const float c[8] = { -1.1514610310e-1f, 1.1676998740e-1f, -1.2420140846e-1f, 1.4249322787e-1f, -1.6668057665e-1f, 2.0000714765e-1f, -2.4999993993e-1f, 3.3333331174e-1f };
+		for (float ck : c) y = y * x + ck;
+		y *= x;
+		const float x2 = x * x;
+		y = (e * -2.12194440e-4f + y * x2) - x2 * 0.5f;
+		return e * 0.693359375f + (x + y);
+	}
+	float orc_speed_of_sound(float tC) { return 343.2f * std::sqrt((273.15f + tC) * (1.0f / (20.0f + 273.15f))); } /* inc/SpeedOfSound.h:38-47 */
+	/* AirAbsorption::CacheParameters (inc/AirAbsorption.h:179-210, 297-368); out [32] like ref_air_cache, knee [4] */
+	void orc_air_cache(const float* bands, float tC, float rh, float pa, float nyquist, float* out, uint32_t* knee)
+	{
+		const float pr = 101.325f, T = tC + 273.15f, T0 = 293.15f, T01 = 273.16f, tr = T / T0, prel = pa / pr;
+		const float psat = pr * ::pow(10.0f, -6.8346f * ::pow(T01 / T, 1.261f) + 4.6151f);
+		const float h = rh * (psat / pa);
+		const float frO = prel * (24.0f + 4.04e4f * h * ((0.02f + h) / (0.391f + h)));
+		const float frN = prel * ::pow(tr, -0.5f) * (9.0f + 280.0f * h * ::exp(-4.170f * (::pow(tr, -1.0f / 3.0f) - 1.0f)));
+		const float classical = 1.84e-11f * ::pow(prel, -1.0f) * ::sqrt(tr);
+		const float scale = ::pow(tr, -2.5f);
+		const float cO = 0.01275f * ::exp(-2239.1f / T), cN = 0.1068f * ::exp(-3352.0f / T);
+		const float iO = 1.0f / frO, iN = 1.0f / frN;
+		auto alpha = [&](float f) { const float f2 = f * f; return (8.68588963807f * f2) * (classical + scale * (cO / (f2 * iO + frO) + cN / (f2 * iN + frN))); };
+		const float f3 = bands[3] * bands[3] / nyquist, f2 = bands[2] * bands[2] / f3, f1 = bands[1] * bands[1] / f2;   /* FrequencyBands.h:52-62 */
+		const float lo[4] = { 20.0f, f1, f2, f3 }, hi[4] = { f1, f2, f3, 22050.0f };
+		for (int i = 0; i < 4; ++i)
+		{
+			const float third = lo[i] * expLane((1.0f / 6.0f) * logLane(hi[i] / lo[i]));   /* simd pow = exp(y * log x) (SIMDMath.h:372-379) */
+			const float ctr = alpha(bands[i]), low = alpha(third), wtd = alpha(bands[i] >= 1000.0f ? third : bands[i]);
+			const float rk = (bands[i] >= 1000.0f ? 14.0f : 6.0f) / ctr;
+			out[i] = bands[i]; out[4 + i] = third; out[8 + i] = ctr; out[12 + i] = low; out[16 + i] = wtd;
+			out[20 + i] = wtd * orc_speed_of_sound(tC); out[24 + i] = rk; out[28 + i] = rk * (ctr - low);
+			knee[i] = bands[i] > 400.0f;
+		}
+	}
+	/* AirAbsorption::ComputeForDistance (:212-234) + dBToGain(simd) of the negated loss; cache = orc_air_cache's out / knee */
+	void orc_air_for_distance(const float* cache, const uint32_t* knee, float d, float* db, float* gain)
+	{
+		for (int i = 0; i < 4; ++i)
+		{
+			const float lin = d * cache[12 + i] + cache[28 + i], ctr = d * cache[8 + i];
+			const float loss = (knee[i] && d >= cache[24 + i]) ? lin : ctr;
+			if (db) db[i] = loss;
+			if (gain) gain[i] = expLane((2.302585092994046f * 0.05f) * (0.0f - loss));
+		}
+	}
+	void orc_sanitize_source_dir(const float* d, float* out) /* Impl::SanitizeSourceDir (inc/Services/PanningService.h:480-495) */
+	{
+		/* fallbackDir is constant-initialised: 1 / SqrtConstevalFallback<float, 2>(1 + 0.05^2) (inc/Math/Math.h:213-262) */
+		const float x = 0.0f * 0.0f + 1.0f * 1.0f + -5e-2f * -5e-2f;
+		uint32_t u; std::memcpy(&u, &x, 4); u = 0x5f3759dfu - (u >> 1);
+		float y; std::memcpy(&y, &u, 4);
+		for (int i = 0; i < 2; ++i) y = y * (1.5f - (0.5f * x) * y * y);
+		float r = x * y; r = 0.5f * (r + x / r);
+		const float il = 1.0f / r;
+		const bool vertical = std::fabs(std::fabs(d[1]) - 1.0f) <= 1e-6f;
+		out[0] = vertical ? 0.0f * il : d[0];
+		out[1] = std::copysign(vertical ? 1.0f * il : d[1], d[1]);
+		out[2] = vertical ? -5e-2f * il : d[2];
+	}
+	float orc_spread_from_size(int flavour, float size, float distance) /* SpatialManager.h:617-623 / PannerBase.h:69-74 */
+	{
+		if (distance <= 0.0f) return 1.0f;
+		return flavour == 0 ? std::atan((0.5f * size) / distance) * 0.318309886f : atanf((size * 0.5f) / distance) * (0.318309886f * 2.0f);
 	}
 }

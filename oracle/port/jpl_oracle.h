@@ -82,6 +82,18 @@ uint32_t    orc_erbus_num_taps(const orc_erbus*);
 void        orc_erbus_set_taps(orc_erbus*, uint32_t n, const float* filter_gains, const float* delay_seconds, const uint32_t* ids, const float* gains);
 void        orc_erbus_process(orc_erbus*, const float* in, uint32_t n_in, float* out, uint32_t frames);          /* out accumulated into */
 
+/* ---- scene front-end (inc/SpatialManager.h:374-420 and the services / producers it calls); positions = location, up, forward */
+int   orc_mdap_oriented(const orc_panner*, uint32_t source_mask, const float* params /* [n][11] */, uint32_t n, float* out); /* PannerBase.h:501-515 */
+void  orc_direct_path(const float* source, const float* listener, float out[12]);        /* inc/Services/DirectPathService.h:280-338 */
+float orc_angle_attenuation(float azimuth_cos, float inner, float outer);                 /* :340-364 */
+float orc_attenuation_model(int model, float min_d, float max_d, float rolloff, float d); /* inc/DistanceAttenuation.h:66-119 */
+float orc_attenuation_curve(const float* points, uint32_t k, float d);                    /* :172-215 (points sorted) */
+float orc_speed_of_sound(float temperature_c);                                            /* inc/SpeedOfSound.h:38-47 */
+void  orc_air_cache(const float* bands, float t_c, float rh, float p_kpa, float nyquist, float out[32], uint32_t knee[4]); /* inc/AirAbsorption.h:179-210 */
+void  orc_air_for_distance(const float* cache, const uint32_t* knee, float d, float* db, float* gain); /* :212-234 + DecibelsAndGain.h:40-50 */
+void  orc_sanitize_source_dir(const float d[3], float out[3]);                            /* inc/Services/PanningService.h:480-495 */
+float orc_spread_from_size(int flavour, float size, float distance);                      /* inc/SpatialManager.h:617-623, inc/Panning/PannerBase.h:69-74 */
+
 #ifdef __cplusplus
 }
 #endif

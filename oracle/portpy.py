@@ -147,6 +147,70 @@ class Port:
             self._panners[key] = self.panner(target_mask)
         return self._panners[key].mdap(source_mask, params)
 
+    # ---- scene front-end
+    def direct_path(self, sources, listeners, listener_index=None):
+        s = _f(sources).reshape(-1, 9); l = _f(listeners).reshape(-1, 9)
+        out = np.empty((s.shape[0], 12), np.float32)
+        for i in range(s.shape[0]):
+            li = 0 if listener_index is None else int(listener_index[i])
+            self.lib.orc_direct_path(_vp(s[i].ctypes.data), _vp(l[li].ctypes.data), _vp(out[i].ctypes.data))
+        return out
+
+    def angle_attenuation(self, dots, cones):
+        self.lib.orc_angle_attenuation.restype = _f32; self.lib.orc_angle_attenuation.argtypes = [_f32, _f32, _f32]
+        c = _f(cones).reshape(-1, 2)
+        return np.array([self.lib.orc_angle_attenuation(float(d), float(a), float(b)) for d, (a, b) in zip(_f(dots), c)], np.float32)
+
+    def attenuation_model(self, model, mn, mx, rolloff, distance):
+        self.lib.orc_attenuation_model.restype = _f32; self.lib.orc_attenuation_model.argtypes = [C.c_int, _f32, _f32, _f32, _f32]
+        return np.array([self.lib.orc_attenuation_model(int(model), mn, mx, rolloff, float(d)) for d in _f(distance)], np.float32)
+
+    def attenuation_curve(self, points, distance):
+        """points are sorted by distance first (AttenuationCurve::SortPoints; distinct distances assumed here)"""
+        self.lib.orc_attenuation_curve.restype = _f32; self.lib.orc_attenuation_curve.argtypes = [_vp, _u32, _f32]
+        p = _f(points).reshape(-1, 3)
+        p = np.ascontiguousarray(p[np.argsort(p[:, 0], kind="stable")]) if p.shape[0] else p
+        return np.array([self.lib.orc_attenuation_curve(p.ctypes.data, p.shape[0], float(d)) for d in _f(distance)], np.float32)
+
+    def speed_of_sound(self, t):
+        self.lib.orc_speed_of_sound.restype = _f32; self.lib.orc_speed_of_sound.argtypes = [_f32]
+        return float(self.lib.orc_speed_of_sound(t))
+
+    def air_cache(self, bands, temp_c=20.0, humidity=50.0, pressure=101.325, nyquist=22050.0):
+        self.lib.orc_air_cache.argtypes = [_vp, _f32, _f32, _f32, _f32, _vp, _vp]
+        b = _f(bands); out = np.empty(32, np.float32); knee = np.empty(4, np.uint32)
+        self.lib.orc_air_cache(b.ctypes.data, temp_c, humidity, pressure, nyquist, out.ctypes.data, knee.ctypes.data)
+        return out, knee
+
+    def air_for_distance(self, cache, knee, distance):
+        self.lib.orc_air_for_distance.argtypes = [_vp, _vp, _f32, _vp, _vp]
+        d = _f(distance); db = np.empty((d.size, 4), np.float32); g = np.empty((d.size, 4), np.float32)
+        for i in range(d.size):
+            self.lib.orc_air_for_distance(cache.ctypes.data, knee.ctypes.data, float(d[i]), db[i].ctypes.data, g[i].ctypes.data)
+        return db, g
+
+    def sanitize_source_dir(self, dirs):
+        d = _f(dirs).reshape(-1, 3); out = np.empty_like(d)
+        for i in range(d.shape[0]):
+            self.lib.orc_sanitize_source_dir(_vp(d[i].ctypes.data), _vp(out[i].ctypes.data))
+        return out
+
+    def spread_from_size(self, flavour, size, distance):
+        self.lib.orc_spread_from_size.restype = _f32; self.lib.orc_spread_from_size.argtypes = [C.c_int, _f32, _f32]
+        return np.array([self.lib.orc_spread_from_size(int(flavour), float(s), float(d)) for s, d in zip(_f(size), _f(distance))], np.float32)
+
+    def mdap_oriented(self, target_mask, source_mask, params):
+        if target_mask not in self._panners:
+            self._panners[target_mask] = self.panner(target_mask)
+        pn = self._panners[target_mask]
+        p = _f(params).reshape(-1, 11)
+        info = pn.layout_info(source_mask)
+        ch = int(info["channels"]) if isinstance(info, dict) else int(info[0][0])
+        out = np.zeros((p.shape[0], ch, pn.L), np.float32)
+        self.lib.orc_mdap_oriented.argtypes = [_vp, _u32, _vp, _u32, _vp]
+        assert self.lib.orc_mdap_oriented(pn.h, source_mask, p.ctypes.data, p.shape[0], out.ctypes.data)
+        return out
+
     # ---- DSP
     def xover_coeffs(self, fs=48000.0, f1=176.0, f2=775.0, f3=3408.0):
         o = np.zeros(27, np.float32); self.lib.orc_xover_coeffs(fs, f1, f2, f3, o.ctypes.data); return o

@@ -15,19 +15,10 @@ import pytest
 
 import jplspatial_b200 as J
 from tests import util
+from tests.frontend_inputs import make_positions
 
 pytestmark = pytest.mark.gpu
 M = J.ChannelMask
-
-
-def make_positions(n, seed, spread_m=60.0):
-    """[n,9] location, up, forward: random locations, random orthonormal up / forward."""
-    loc = (util.white_noise((n, 3), seed) * np.float32(spread_m)).astype(np.float32)
-    fwd = util.unit_directions(n, seed + 1)
-    tmp = util.unit_directions(n, seed + 2)
-    up = np.cross(fwd.astype(np.float64), tmp.astype(np.float64))
-    up /= np.linalg.norm(up, axis=1, keepdims=True)
-    return np.ascontiguousarray(np.concatenate([loc, up.astype(np.float32), fwd], axis=1))
 
 
 def ulp_diff(a, b):
