@@ -253,6 +253,9 @@ JPLG_API jplg_status jplg_delay_bank_push(jplg_delay_bank b, const float* in, ui
 /* For each line: for k in [0,taps): tap.SetDelay(delays[line][k]); out[line][k] = tap.Process(line) (:53-67),
  * the tap's interpolator state carried across k (and across calls for Thiran). */
 JPLG_API jplg_status jplg_delay_bank_read(jplg_delay_bank b, const float* delays, uint32_t taps, int32_t interp, float* out, int32_t mem);
+/* DelayTapXFade x n (:73-122). For each line: for k in [0,taps): tap.SetCrossfade(alphas[line][k]); tap.SetDelay(delays[line][k]);
+ * out[line][k] = tap.Process(line); the tap's previous / target delay pair is carried across k and across calls (both start at 0). */
+JPLG_API jplg_status jplg_delay_bank_read_xfade(jplg_delay_bank b, const float* delays, const float* alphas, uint32_t taps, float* out, int32_t mem);
 
 /* ChannelMixing free functions (replaces inc/Auralization/ChannelMixing.h:32-136), batched over `n`
  * independent (dest, source) pairs laid out back to back. */

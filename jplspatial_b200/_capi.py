@@ -92,6 +92,7 @@ _sig("jplg_delay_bank_size", _u32, [_vp])
 _sig("jplg_delay_bank_clear", _i32, [_vp])
 _sig("jplg_delay_bank_push", _i32, [_vp, _fp, _u32, _i32])
 _sig("jplg_delay_bank_read", _i32, [_vp, _fp, _u32, _i32, _fp, _i32])
+_sig("jplg_delay_bank_read_xfade", _i32, [_vp, _fp, _fp, _u32, _fp, _i32])
 _sig("jplg_mix_add_and_apply_gain_ramp", _i32, [_vp, _fp, _fp, _u32, _u32, _u32, _u32, _u32, _u32, _fp, _fp, _i32])
 _sig("jplg_mix_apply_gain", _i32, [_vp, _fp, _u32, _u32, _fp, _i32])
 
@@ -660,6 +661,14 @@ class DelayBank:
         d = np.ascontiguousarray(delays, np.float32).reshape(self.n, -1)
         out = np.empty_like(d)
         self.ctx.check(lib.jplg_delay_bank_read(self.h, d.ctypes.data, d.shape[1], int(interp), out.ctypes.data, MEM_HOST))
+        return out
+
+    def ReadXFade(self, delays, alphas):
+        """DelayTapXFade (DelayLine.h:73-122): per tap SetCrossfade(alpha), SetDelay(delay), Process"""
+        d = np.ascontiguousarray(delays, np.float32).reshape(self.n, -1)
+        a = np.ascontiguousarray(alphas, np.float32).reshape(self.n, -1)
+        out = np.empty_like(d)
+        self.ctx.check(lib.jplg_delay_bank_read_xfade(self.h, d.ctypes.data, a.ctypes.data, d.shape[1], out.ctypes.data, MEM_HOST))
         return out
 
     def __del__(self):

@@ -898,13 +898,13 @@ jplg_status jplg_delay_bank_create(jplg_context ctx, uint32_t n, uint32_t min_si
 	uint32_t ring = 1; while (ring < min_size) ring <<= 1; // std::bit_ceil (inc/Utilities/AbstractIndex.h:235)
 	cudaSetDevice(ctx->device);
 	auto* b = new jplg_delay_bank_t{ ctx, n, ring, 0, nullptr, nullptr };
-	if (cudaMalloc(reinterpret_cast<void**>(&b->rings), size_t(n) * ring * 4) != cudaSuccess || cudaMalloc(reinterpret_cast<void**>(&b->y1), size_t(n) * 4) != cudaSuccess)
+	if (cudaMalloc(reinterpret_cast<void**>(&b->rings), size_t(n) * ring * 4) != cudaSuccess || cudaMalloc(reinterpret_cast<void**>(&b->y1), size_t(n) * 12) != cudaSuccess)   // y1 [n] | DelayTapXFade {last, new} delays [2][n]
 	{
 		cudaGetLastError(); if (b->rings) cudaFree(b->rings); delete b;
 		return Fail(ctx, JPLG_ERR_OUT_OF_MEMORY, "delay bank allocation failed");
 	}
 	cudaMemsetAsync(b->rings, 0, size_t(n) * ring * 4, ctx->stream);
-	cudaMemsetAsync(b->y1, 0, size_t(n) * 4, ctx->stream);
+	cudaMemsetAsync(b->y1, 0, size_t(n) * 12, ctx->stream);
 	*out = b;
 	return JPLG_OK;
 }
@@ -965,6 +965,35 @@ jplg_status jplg_delay_bank_read(jplg_delay_bank b, const float* delays, uint32_
 		dDelays = static_cast<float*>(a); dOut = static_cast<float*>(o);
 	}
 	JPLG_CUDA_TRY(ctx, LaunchDelayRead(b->rings, b->n, b->ringSize, b->pos, dDelays, taps, interp, b->y1, dOut, ctx->stream)); ctx->launches++;
+	if (mem == JPLG_MEM_HOST)
+	{
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(out, dOut, nt * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	}
+	return JPLG_OK;
+}
+
+jplg_status jplg_delay_bank_read_xfade(jplg_delay_bank b, const float* delays, const float* alphas, uint32_t taps, float* out, int32_t mem)
+{
+	if (!b || (taps && (!delays || !alphas || !out))) return JPLG_ERR_INVALID_ARGUMENT;
+	jplg_context ctx = b->ctx;
+	JPLG_NEED_DEVICE(ctx);
+	if (taps == 0) return JPLG_OK;
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	const size_t nt = size_t(b->n) * taps;
+	const float* dDelays = delays; const float* dAlphas = alphas; float* dOut = out;
+	if (mem == JPLG_MEM_HOST)
+	{
+		void *a, *c, *o;
+		jplg_status st = Scratch(ctx, 0, nt * 4, &a); if (st) return st;
+		st = Scratch(ctx, 1, nt * 4, &o); if (st) return st;
+		st = Scratch(ctx, 2, nt * 4, &c); if (st) return st;
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(a, delays, nt * 4, cudaMemcpyHostToDevice, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(c, alphas, nt * 4, cudaMemcpyHostToDevice, ctx->stream));
+		dDelays = static_cast<float*>(a); dAlphas = static_cast<float*>(c); dOut = static_cast<float*>(o);
+	}
+	JPLG_CUDA_TRY(ctx, LaunchDelayReadXFade(b->rings, b->n, b->ringSize, b->pos, dDelays, dAlphas, taps, reinterpret_cast<int32_t*>(b->y1 + b->n), dOut, ctx->stream)); ctx->launches++;
 	if (mem == JPLG_MEM_HOST)
 	{
 		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(out, dOut, nt * 4, cudaMemcpyDeviceToHost, ctx->stream));

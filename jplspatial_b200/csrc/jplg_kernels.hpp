@@ -95,6 +95,8 @@ namespace jplg
 	cudaError_t LaunchDelayPush(float* rings, uint32_t n, uint32_t ringSize, uint64_t pos, const float* in, uint32_t frames, cudaStream_t st);
 	cudaError_t LaunchDelayRead(const float* rings, uint32_t n, uint32_t ringSize, uint64_t pos, const float* delays, uint32_t taps,
 								int interp, float* thiranY1, float* out, cudaStream_t st);
+	cudaError_t LaunchDelayReadXFade(const float* rings, uint32_t n, uint32_t ringSize, uint64_t pos, const float* delays, const float* alphas,
+									 uint32_t taps, int32_t* lastNew, float* out, cudaStream_t st);
 	cudaError_t LaunchMixRamp(float* dest, const float* src, uint32_t n, uint32_t destCh, uint32_t srcCh, uint32_t nDest, uint32_t nSrc,
 							  uint32_t frames, const float* g0, const float* g1, cudaStream_t st);
 	cudaError_t LaunchApplyGain(float* dest, uint32_t n, uint32_t frames, const float* gains, cudaStream_t st);

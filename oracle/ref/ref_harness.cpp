@@ -444,6 +444,7 @@ extern "C"
 		Line line;
 		DelayTap<Thiran1stInterpolator> thiran;
 		DelayTap<LinearInterpolator> linear;
+		DelayTapXFade xfade;
 		explicit RefDelay(uint32 minSize) : line(minSize) {}
 	};
 	void* ref_delay_create(uint32_t minSize) { return new RefDelay(minSize); }
@@ -453,6 +454,8 @@ extern "C"
 	float ref_delay_read_int(void* h, uint32_t delay) { return static_cast<RefDelay*>(h)->line.GetReadWindow<1>(delay); }
 	float ref_delay_tap_thiran(void* h, float delay) { auto* d = static_cast<RefDelay*>(h); d->thiran.SetDelay(delay); return d->thiran.Process(d->line); }
 	float ref_delay_tap_linear(void* h, float delay) { auto* d = static_cast<RefDelay*>(h); d->linear.SetDelay(delay); return d->linear.Process(d->line); }
+
+	float ref_delay_tap_xfade(void* h, float delay, float alpha) { auto* d = static_cast<RefDelay*>(h); d->xfade.SetCrossfade(alpha); d->xfade.SetDelay(delay); return d->xfade.Process(d->line); }
 
 	// SmoothedValue exp smoothing (SmoothedValue.h:36-41,73-77)
 	float ref_smoother_alpha(uint32_t ticks) { return SmoothedValue<float>::GetExpAlpha(ticks); }

@@ -378,6 +378,10 @@ class RefDelay:
     def tap_linear(self, d):
         return float(self.lib.ref_delay_tap_linear(self.h, float(d)))
 
+    def tap_xfade(self, d, alpha):
+        self.lib.ref_delay_tap_xfade.restype = _f32; self.lib.ref_delay_tap_xfade.argtypes = [_vp, _f32, _f32]
+        return float(self.lib.ref_delay_tap_xfade(self.h, float(d), float(alpha)))
+
     def __del__(self):
         try:
             self.lib.ref_delay_destroy(self.h)

@@ -187,6 +187,17 @@ def test_delay_bank_vs_reference(gpu_ctx, ref):
     for i in range(n):
         r = np.array([rd[i].tap_thiran(float(v)) for v in delays[i]], np.float32)
         assert util.bits_equal(th[i], r)
+    # DelayTapXFade (DelayLine.h:73-122): cosine crossfade between the previous and the new integer delay, state carried across taps and calls.
+    # The gains go through libm's cosf in the reference: 1e-6 absolute on samples in [-1, 1), bit-exact where alpha is 0 or 1.
+    xd = (util.uniform01(n * 32, util.SEED + 54).reshape(n, 32) * 250.0).astype(np.float32)
+    xa = util.uniform01(n * 32, util.SEED + 55).reshape(n, 32).astype(np.float32)
+    xa[:, :4] = [0.0, 1.0, 0.5, 0.25]
+    for rep in range(2):
+        xf = bank.ReadXFade(xd, xa)
+        for i in range(n):
+            r = np.array([rd[i].tap_xfade(float(v), float(a)) for v, a in zip(xd[i], xa[i])], np.float32)
+            assert np.abs(xf[i] - r).max() <= 1e-6
+            assert util.bits_equal(xf[i, :2], r[:2])
     # wrap: push past the ring size and read across the seam
     big = util.white_noise((n, 1500), util.SEED + 53)
     bank.Push(big[:, :1000]); bank.Push(big[:, 1000:])
