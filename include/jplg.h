@@ -56,7 +56,12 @@ enum {
     JPLG_ERR_TRIANGULATION = 8
 };
 
-enum { JPLG_MEM_HOST = 0, JPLG_MEM_DEVICE = 1 };
+enum { JPLG_MEM_HOST = 0, JPLG_MEM_DEVICE = 1,
+       /* PINNED host memory, asynchronous: the call enqueues its copies and kernels and returns without waiting; the buffers must stay
+        * untouched until jplg_renderer_wait_block / jplg_context_synchronize. Accepted by jplg_panner_mdap(_oriented), jplg_renderer_update
+        * and jplg_renderer_process_block (whose input transfer then runs on a copy stream into one of two staging buffers, so the PCIe
+        * transfer of block k+1 overlaps the render of block k). */
+       JPLG_MEM_HOST_ASYNC = 2 };
 
 /* Arithmetic mode of the render kernels.
  *  JPLG_MODE_PARITY     every reference FMA(a,b,c) is a separately rounded mul + add, exactly like the
@@ -208,6 +213,9 @@ JPLG_API jplg_status jplg_renderer_update(jplg_renderer r, const float* band_gai
  * bus: [frames][L] interleaved, ACCUMULATED INTO like the reference's `output` span; all N sources add
  *      into the same bus (the host loop "for each effect: ProcessInterleaved(in_i, bus)"). */
 JPLG_API jplg_status jplg_renderer_process_block(jplg_renderer r, const float* in, float* bus, uint32_t frames, int32_t mem);
+/* JPLG_MEM_HOST_ASYNC blocks complete in submission order; this waits (on the host) for the oldest block not yet waited for: its `bus`
+ * is then valid. At most two blocks are in flight (a third submission first waits for the oldest). */
+JPLG_API jplg_status jplg_renderer_wait_block(jplg_renderer r);
 /* Same, but also writes every source's own contribution: per_source [N][frames][L] (overwritten). */
 JPLG_API jplg_status jplg_renderer_process_block_debug(jplg_renderer r, const float* in, float* bus, float* per_source,
                                                        uint32_t frames, int32_t mem);

@@ -16,7 +16,7 @@ There is NO CPU fallback: without the built library the import fails, without a 
 """
 from ._capi import (  # noqa: F401
     JplgError, lib, lib_path, device_count, version,
-    MEM_HOST, MEM_DEVICE, MODE_PARITY, MODE_THROUGHPUT,
+    MEM_HOST, MEM_DEVICE, MEM_HOST_ASYNC, MODE_PARITY, MODE_THROUGHPUT,
     EChannel, ChannelMask, ChannelMap,
     Context, VBAPanner, SourceLayout, DirectSoundBatch, CrossoverBank, DelayBank, ReverbBusBatch, ERBusBatch,
     add_and_apply_gain_ramp, apply_gain, normalize_weights, get_spread_from_source_size,

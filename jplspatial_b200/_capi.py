@@ -11,7 +11,7 @@ if not os.path.exists(lib_path):
         "(there is no CPU/PyTorch fallback for this package)")
 lib = C.CDLL(lib_path)
 
-MEM_HOST, MEM_DEVICE = 0, 1
+MEM_HOST, MEM_DEVICE, MEM_HOST_ASYNC = 0, 1, 2
 MODE_PARITY, MODE_THROUGHPUT = 0, 1
 STATE_FLOATS = 64
 _vp, _u32, _i32, _f32, _u64 = C.c_void_p, C.c_uint32, C.c_int32, C.c_float, C.c_uint64
@@ -76,6 +76,7 @@ _sig("jplg_renderer_destroy", None, [_vp])
 _sig("jplg_renderer_update", _i32, [_vp, _fp, _fp, _fp, _i32])
 _sig("jplg_renderer_process_block", _i32, [_vp, _fp, _fp, _u32, _i32])
 _sig("jplg_renderer_process_block_debug", _i32, [_vp, _fp, _fp, _fp, _u32, _i32])
+_sig("jplg_renderer_wait_block", _i32, [_vp])
 _sig("jplg_renderer_device_bus", _vp, [_vp])
 _sig("jplg_renderer_ring_size", _u32, [_vp])
 _sig("jplg_renderer_state_export", _i32, [_vp, _fp, _fp, C.POINTER(_u64)])
@@ -352,8 +353,9 @@ class VBAPanner:
         self.ctx.check(lib.jplg_panner_point_gains(self.h, d, n, o, mem))
         return out
 
-    def ProcessVBAPData(self, layout, params, out=None):
-        """params [n,5] = {dir.xyz, focus, spread} -> mix maps [n, channels, L]"""
+    def ProcessVBAPData(self, layout, params, out=None, async_host=False):
+        """params [n,5] = {dir.xyz, focus, spread} -> mix maps [n, channels, L]. async_host: params / out are PINNED host arrays and the call
+        returns without waiting (JPLG_MEM_HOST_ASYNC)."""
         p, mem, keep = _arg(params)
         n = keep.shape[0]
         L = self.GetNumChannels()
@@ -365,7 +367,7 @@ class VBAPanner:
                 out = np.empty((n, layout.num_channels, L), np.float32)
         o, omem, okeep = _arg(out)
         assert omem == mem
-        self.ctx.check(lib.jplg_panner_mdap(self.h, layout.h, p, n, o, mem))
+        self.ctx.check(lib.jplg_panner_mdap(self.h, layout.h, p, n, o, MEM_HOST_ASYNC if (async_host and mem == MEM_HOST) else mem))
         return out
 
     def ProcessVBAPDataOriented(self, layout, params, out=None):
@@ -434,19 +436,28 @@ class DirectSoundBatch:
         self.h = h
         self.ring_size = int(lib.jplg_renderer_ring_size(h))
 
-    def UpdateParameters(self, filter_gains=None, delay_seconds=None, mix_maps=None):
+    def UpdateParameters(self, filter_gains=None, delay_seconds=None, mix_maps=None, async_host=False):
         b, m1, kb = _arg(filter_gains)
         d, m2, kd = _arg(delay_seconds)
         m, m3, km = _arg(mix_maps)
         mems = {x for x in (m1, m2, m3) if x is not None}
         assert len(mems) <= 1, "all update arrays must live in the same memory space"
-        self.ctx.check(lib.jplg_renderer_update(self.h, b, d, m, mems.pop() if mems else MEM_HOST))
+        mem = mems.pop() if mems else MEM_HOST
+        self.ctx.check(lib.jplg_renderer_update(self.h, b, d, m, MEM_HOST_ASYNC if (async_host and mem == MEM_HOST) else mem))
 
-    def ProcessInterleaved(self, inp, bus, num_frames, per_source=None):
-        """inp [N, frames, C]; bus [frames, L] accumulated into; per_source optional [N, frames, L] (debug)."""
+    def WaitBlock(self):
+        """host-wait for the oldest asynchronous block (see ProcessInterleaved(async_host=True))"""
+        self.ctx.check(lib.jplg_renderer_wait_block(self.h))
+
+    def ProcessInterleaved(self, inp, bus, num_frames, per_source=None, async_host=False):
+        """inp [N, frames, C]; bus [frames, L] accumulated into; per_source optional [N, frames, L] (debug).
+        async_host: inp / bus are PINNED host arrays; the block is enqueued (its input transfer overlaps the previous block's render) and
+        `bus` is valid after WaitBlock()."""
         i, mem, ki = _arg(inp)
         o, omem, ko = _arg(bus)
         assert mem == omem
+        if async_host and mem == MEM_HOST:
+            mem = MEM_HOST_ASYNC
         if per_source is None:
             self.ctx.check(lib.jplg_renderer_process_block(self.h, i, o, int(num_frames), mem))
         else:

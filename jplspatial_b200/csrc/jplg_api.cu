@@ -421,7 +421,7 @@ static jplg_status MdapImpl(jplg_panner p, jplg_source_layout l, const float* pa
 	cudaSetDevice(ctx->device);
 	const size_t outFloats = size_t(n) * l->host.numChannels * p->host.numChannels;
 	const float* dParams = params; float* dOut = out;
-	if (mem == JPLG_MEM_HOST)
+	if (mem == JPLG_MEM_HOST || mem == JPLG_MEM_HOST_ASYNC)
 	{
 		void *a, *b;
 		jplg_status st = Scratch(ctx, 0, size_t(n) * stride * 4, &a); if (st) return st;
@@ -430,10 +430,10 @@ static jplg_status MdapImpl(jplg_panner p, jplg_source_layout l, const float* pa
 		dParams = static_cast<float*>(a); dOut = static_cast<float*>(b);
 	}
 	JPLG_LAUNCH(ctx, JPLG_K_MDAP, LaunchMdap(p->dev, l->lp, dParams, stride, n, dOut, ctx->numSMs, ctx->stream));
-	if (mem == JPLG_MEM_HOST)
+	if (mem == JPLG_MEM_HOST || mem == JPLG_MEM_HOST_ASYNC)
 	{
 		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(out, dOut, outFloats * 4, cudaMemcpyDeviceToHost, ctx->stream));
-		JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+		if (mem == JPLG_MEM_HOST) JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
 	}
 	return JPLG_OK;
 }
@@ -503,6 +503,12 @@ struct jplg_renderer_t
 	float *partial = nullptr, *deviceBus = nullptr, *stageIn = nullptr, *stageBus = nullptr, *stagePerSource = nullptr;
 	float *stageParams = nullptr; // update staging: band [N][4] | delay [N] | mix [N][C*L]
 	size_t stagePerSourceFloats = 0;
+	// JPLG_MEM_HOST_ASYNC: two input staging buffers (slot 0 = stageIn) fed by the copy stream, so the PCIe transfer of block k+1 overlaps the
+	// render of block k; evPushed[s] = k_push has consumed staging slot s, evDone[s] = the block's bus is back in host memory
+	float* stageIn2 = nullptr;
+	cudaEvent_t evCopiedA[2] = {}, evPushedA[2] = {}, evDoneA[2] = {};
+	bool asyncReady = false;
+	uint64_t asyncSubmitted = 0, asyncWaited = 0;
 };
 
 // targets in the reference's layouts -> SoA per source-channel (UpdateParameters, src/Auralization/DirectSound.cpp:231-239)
@@ -554,6 +560,13 @@ static void FreeRenderer(jplg_renderer r)
 {
 	float** ptrs[] = { &r->state, &r->curMix, &r->tgtDelay, &r->tgtBand, &r->tgtMix, &r->rings, &r->partial, &r->deviceBus, &r->stageIn, &r->stageBus, &r->stagePerSource, &r->stageParams };
 	for (float** p : ptrs) if (*p) { cudaFree(*p); *p = nullptr; }
+	if (r->asyncReady)
+	{
+		if (r->ctx->auxReady) cudaStreamSynchronize(r->ctx->aux[0]);
+		if (r->stageIn2) { cudaFree(r->stageIn2); r->stageIn2 = nullptr; }
+		for (int i = 0; i < 2; ++i) { cudaEventDestroy(r->evCopiedA[i]); cudaEventDestroy(r->evPushedA[i]); cudaEventDestroy(r->evDoneA[i]); }
+		r->asyncReady = false;
+	}
 }
 
 static jplg_status RendererUpdateLocked(jplg_renderer r, const float* band, const float* delay, const float* mix, int32_t mem)
@@ -561,7 +574,7 @@ static jplg_status RendererUpdateLocked(jplg_renderer r, const float* band, cons
 	jplg_context ctx = r->ctx;
 	const uint32_t N = r->cfg.num_sources, C = r->cfg.source_channels, L = r->cfg.output_channels;
 	const float *dBand = band, *dDelay = delay, *dMix = mix;
-	if (mem == JPLG_MEM_HOST)
+	if (mem == JPLG_MEM_HOST || mem == JPLG_MEM_HOST_ASYNC)
 	{
 		float* base = r->stageParams;
 		if (band) { JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(base, band, size_t(N) * 4 * 4, cudaMemcpyHostToDevice, ctx->stream)); dBand = base; }
@@ -669,6 +682,37 @@ static jplg_status ProcessBlock(jplg_renderer r, const float* in, float* bus, fl
 	const float* dIn = in; float* dBus = bus; float* dPer = perSource;
 	const size_t perFloats = size_t(N) * frames * L;
 	const bool pipelinedHost = mem == JPLG_MEM_HOST && ctx->hostPipeline > 0 && r->numCTAs >= 32 && !perSource;
+	int asyncSlot = -1;
+	if (mem == JPLG_MEM_HOST_ASYNC)
+	{
+		if (perSource) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "process_block_debug: JPLG_MEM_HOST_ASYNC is not supported");
+		jplg_status ast = EnsureAux(ctx); if (ast != JPLG_OK) return ast;
+		if (!r->asyncReady)
+		{
+			if (cudaMalloc(reinterpret_cast<void**>(&r->stageIn2), size_t(r->numSC) * r->maxFrames * 4) != cudaSuccess) { cudaGetLastError(); return Fail(ctx, JPLG_ERR_OUT_OF_MEMORY, "async staging allocation failed"); }
+			for (int i = 0; i < 2; ++i)
+			{
+				JPLG_CUDA_TRY(ctx, cudaEventCreateWithFlags(&r->evCopiedA[i], cudaEventDisableTiming));
+				JPLG_CUDA_TRY(ctx, cudaEventCreateWithFlags(&r->evPushedA[i], cudaEventDisableTiming));
+				JPLG_CUDA_TRY(ctx, cudaEventCreateWithFlags(&r->evDoneA[i], cudaEventDisableTiming));
+			}
+			r->asyncReady = true;
+		}
+		if (r->asyncSubmitted - r->asyncWaited >= 2)   // both slots in flight: wait for the older block (its host bus is then valid too)
+		{
+			JPLG_CUDA_TRY(ctx, cudaEventSynchronize(r->evDoneA[r->asyncWaited & 1]));
+			r->asyncWaited++;
+		}
+		asyncSlot = static_cast<int>(r->asyncSubmitted & 1);
+		float* stage = asyncSlot ? r->stageIn2 : r->stageIn;
+		cudaStream_t copy = ctx->aux[0];
+		if (r->asyncSubmitted >= 2) JPLG_CUDA_TRY(ctx, cudaStreamWaitEvent(copy, r->evPushedA[asyncSlot], 0));   // the push of block k-2 has read this slot
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(stage, in, size_t(N) * frames * C * 4, cudaMemcpyHostToDevice, copy));
+		JPLG_CUDA_TRY(ctx, cudaEventRecord(r->evCopiedA[asyncSlot], copy));
+		JPLG_CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, r->evCopiedA[asyncSlot], 0));
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(r->stageBus, bus, size_t(frames) * L * 4, cudaMemcpyHostToDevice, ctx->stream));
+		dIn = stage; dBus = r->stageBus;
+	}
 	if (mem == JPLG_MEM_HOST)
 	{
 		if (!pipelinedHost) JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(r->stageIn, in, size_t(N) * frames * C * 4, cudaMemcpyHostToDevice, ctx->stream));
@@ -734,6 +778,7 @@ static jplg_status ProcessBlock(jplg_renderer r, const float* in, float* bus, fl
 	else
 	{
 		JPLG_LAUNCH(ctx, JPLG_K_PUSH, LaunchPush(rp, 0, N, ctx->stream));
+		if (asyncSlot >= 0) JPLG_CUDA_TRY(ctx, cudaEventRecord(r->evPushedA[asyncSlot], ctx->stream));
 		JPLG_LAUNCH(ctx, JPLG_K_RENDER, LaunchRender(rp, r->cfg.mode, 0, r->numCTAs, ctx->stream));
 	}
 	JPLG_LAUNCH(ctx, JPLG_K_BUS_REDUCE, LaunchBusReduce(rp, r->deviceBus, dBus, ctx->stream));
@@ -744,6 +789,24 @@ static jplg_status ProcessBlock(jplg_renderer r, const float* in, float* bus, fl
 		if (perSource) JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(perSource, dPer, perFloats * 4, cudaMemcpyDeviceToHost, ctx->stream));
 		JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
 	}
+	if (asyncSlot >= 0)
+	{
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(bus, dBus, size_t(frames) * L * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaEventRecord(r->evDoneA[asyncSlot], ctx->stream));
+		r->asyncSubmitted++;
+	}
+	return JPLG_OK;
+}
+
+jplg_status jplg_renderer_wait_block(jplg_renderer r)
+{
+	if (!r) return JPLG_ERR_INVALID_ARGUMENT;
+	jplg_context ctx = r->ctx;
+	JPLG_NEED_DEVICE(ctx);
+	if (r->asyncWaited >= r->asyncSubmitted) return JPLG_OK;   // nothing in flight
+	cudaSetDevice(ctx->device);
+	JPLG_CUDA_TRY(ctx, cudaEventSynchronize(r->evDoneA[r->asyncWaited & 1]));
+	r->asyncWaited++;
 	return JPLG_OK;
 }
 

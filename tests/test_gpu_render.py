@@ -277,3 +277,52 @@ def test_pipelined_host_path_equals_device_path(C, pipeline):
         assert util.bits_equal(bus_n, want), f"block {b}: pageable host path differs"
     for r in (ra, rb, rc):
         r.close()
+
+
+def test_async_host_path_equals_sync_host_path():
+    """JPLG_MEM_HOST_ASYNC: MDAP -> update -> process_block enqueued without host waits, the input transfer of block k+1 on the copy stream
+    while block k renders (two staging slots, at most two blocks in flight). Every block's bus must equal the synchronous JPLG_MEM_HOST path
+    bit for bit; submitting a third block before waiting must not corrupt the first."""
+    import torch
+    ctx = J.Context(0)
+    N, C, L, blocks, frames = 4133, 1, 12, 7, 512
+    sc = make_scene(N, C, L, blocks, frames, util.SEED + 78)
+    pan = J.VBAPanner(ctx); assert pan.Initialize(J.ChannelMask.Surround_7_1_4)
+    lay = pan.InitializeSourceLayout(J.ChannelMask.Mono)
+    params = [util.pan_params(N, util.SEED + 500 + b) for b in range(blocks)]
+
+    def make():
+        return J.DirectSoundBatch(ctx, FS, N, C, L, sc["band"][0], sc["delay"][0], sc["mix"][0], ring_size=4096, max_block_frames=512, mode=J.MODE_PARITY)
+
+    def pin(a):
+        t = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+        return t, t.numpy()
+
+    rs, ra = make(), make()
+    want = []
+    for b in range(blocks):
+        mix = pan.ProcessVBAPData(lay, params[b])
+        rs.UpdateParameters(sc["band"][b + 1], sc["delay"][b + 1], mix)
+        bus = np.zeros((frames, L), np.float32)
+        rs.ProcessInterleaved(sc["audio"][b], bus, frames)
+        want.append(bus)
+    keep = [pin(x) for b in range(blocks) for x in (params[b], sc["band"][b + 1], sc["delay"][b + 1], sc["audio"][b])]
+    h = [k[1] for k in keep]
+    kmix, hmix = pin(np.zeros((N, 1, L), np.float32))
+    buses = [pin(np.zeros((frames, L), np.float32)) for _ in range(blocks)]
+    for b in range(blocks):
+        p, band, delay, audio = h[4 * b:4 * b + 4]
+        pan.ProcessVBAPData(lay, p, out=hmix, async_host=True)
+        ra.UpdateParameters(band, delay, hmix, async_host=True)
+        ra.ProcessInterleaved(audio, buses[b][1], frames, async_host=True)
+        if b in (1, 2, 5):          # sometimes two blocks in flight, sometimes the library has to wait itself (third submission)
+            ra.WaitBlock()
+    for _ in range(blocks):
+        ra.WaitBlock()              # waiting with nothing in flight is a no-op
+    ctx.synchronize()
+    for b in range(blocks):
+        assert np.abs(want[b]).max() > 0
+        assert util.bits_equal(buses[b][1], want[b]), f"block {b}: asynchronous host path differs from the synchronous one"
+    rs.close(); ra.close()
+    del pan, lay
+    ctx.close()
