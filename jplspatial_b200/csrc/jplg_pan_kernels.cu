@@ -72,6 +72,7 @@ namespace jplg
 	// G lanes per source (G = 16 when the target has <= 16 channels: two sources share a warp, which halves the cost of the
 	// speaker-ordered accumulation and wastes fewer lanes on the 72 = 4.5 x 16 virtual sources of mono -> 7.1.4; else G = 32).
 	// Shared memory per group: ring sin/cos (2*24 floats) + one 16-B entry per virtual source + mixBuffer.
+	constexpr uint32_t kMdapRows = 32;   // virtual sources per accumulation batch (rows of the per-group gain matrix)
 	template<int G>
 	__global__ void __launch_bounds__(JPLG_MDAP_WARPS * 32)
 	k_mdap_3d(const uint4* __restrict__ lut, const uint32_t* __restrict__ rsqTable, MdapLayoutParams lp,
@@ -84,12 +85,14 @@ namespace jplg
 		float* sGroupBase = sAzCos + 32;
 		constexpr uint32_t kGroups = JPLG_MDAP_WARPS * 32 / G;
 		const uint32_t grp = threadIdx.x / G, gl = threadIdx.x % G;
-		// per group: ring sin/cos [24+24] | one 16-B entry per virtual source { spk0 | spk1<<8 | spk2<<16, v0, v1, v2 } | mixBuffer [32]
-		float* sRingS = sGroupBase + grp * (48 + 4 * lp.numVS + kMaxChannelsDev);
+		// per group: ring sin/cos [24+24] | gain matrix [kMdapRows][G] (row = virtual source of the current batch, column = speaker; all zero
+		// between batches) | mixBuffer [32]
+		float* sRingS = sGroupBase + grp * (48 + kMdapRows * G + kMaxChannelsDev);
 		float* sRingC = sRingS + 24;
-		uint4* sEnt = reinterpret_cast<uint4*>(sRingC + 24);
-		float* sMix = reinterpret_cast<float*>(sEnt + lp.numVS);                      // [32] mixBuffer
+		float* sMat = sRingC + 24;
+		float* sMix = sMat + kMdapRows * G;                                           // [32] mixBuffer
 
+		for (uint32_t i = threadIdx.x; i < kGroups * kMdapRows * G; i += blockDim.x) sGroupBase[(i / (kMdapRows * G)) * (48 + kMdapRows * G + kMaxChannelsDev) + 48 + i % (kMdapRows * G)] = 0.0f;
 		for (uint32_t i = threadIdx.x; i < 2048; i += blockDim.x) sRsq[i] = rsqTable[i];
 		if (threadIdx.x < 32) { sAzSin[threadIdx.x] = lp.azSin[threadIdx.x]; sAzCos[threadIdx.x] = lp.azCos[threadIdx.x]; }
 		__syncthreads();
@@ -128,41 +131,78 @@ namespace jplg
 				const Q4 qc{ lp.quats[ch][0], lp.quats[ch][1], lp.quats[ch][2], lp.quats[ch][3] };
 				const B3 basis = quat_to_basis(quat_mul(m.qPan, qc)); // PannerBase.h:593-601
 
-				for (uint32_t v = gl; v < lp.numVS; v += G)
+				// outGains[speakers[s]] += gains[s] in entry order (PannerBase.h:846-849), per speaker == lane. A batch of kMdapRows virtual sources
+				// scatters its (vsWeight * g) * g values into the zeroed gain matrix (the three speakers of a cell are distinct: a triangle, the dummy
+				// replaced by an index not in it, VBAPLUT3D.h:803-815), then lane s adds column s row after row: the entries of other speakers
+				// contribute +0.0f, which leaves a non-negative running sum unchanged bit for bit, so the additions that matter happen in the
+				// reference's order. 2 instructions per entry instead of a 14-instruction compare / select scan (ncu r01d: that scan was 33 % of
+				// the kernel's issued instructions).
+				float acc = 0.0f;
+				for (uint32_t vb = 0; vb < lp.numVS; vb += kMdapRows)
 				{
-					const uint32_t pack = v >> 2, l4 = v & 3u;
-					uint32_t sci, azi; bool mirror = false;
-					if (pack < packsHalf) { sci = pack / H; azi = pack - sci * H; }
-					else if (pack < 2 * packsHalf) { const uint32_t p2 = pack - packsHalf; sci = p2 / H; azi = p2 - sci * H; mirror = true; }
-					else { sci = pack - 2 * packsHalf; azi = H; }
-					const float sinPhi = sRingS[sci], cosPhi = sRingC[sci];
-					F3 d;
-					d.x = sinPhi * sAzCos[azi * 4 + l4];
-					d.y = sinPhi * sAzSin[azi * 4 + l4];
-					if (mirror) d.y = 0.0f - d.y;
-					d.z = cosPhi;
-					d = basis_transform_simd(basis, d);                 // RotateChannelCap (:895-901)
-					d = slerp_simd(sRsq, d, m.target, m.tSlerp);        // SlerpChannelCap (:904-919)
-					const uint32_t code = oct_encode_simd(d.x, d.y, d.z);
-					const uint4 cell = __ldg(&lut[code]);
-					// (vsWeight * g) * g (PannerBase.h:836-839); entry order = pack*12 + lane*3 + k = v*3 + k (:846-849)
-					const float g0 = u2f(cell.x), g1 = u2f(cell.y), g2 = u2f(cell.z);
-					sEnt[v] = make_uint4(cell.w & 0xffffffu, f2u((lp.vsWeight * g0) * g0), f2u((lp.vsWeight * g1) * g1), f2u((lp.vsWeight * g2) * g2));
+					uint32_t mine[kMdapRows / G];      // matrix offsets this lane wrote (to clear them afterwards), 3 x 10 bits each
+					#pragma unroll
+					for (uint32_t it = 0; it < kMdapRows / G; ++it)
+					{
+						const uint32_t row = it * G + gl, v = vb + row;
+						mine[it] = 0xffffffffu;
+						if (v < lp.numVS)
+						{
+							const uint32_t pack = v >> 2, l4 = v & 3u;
+							uint32_t sci, azi; bool mirror = false;
+							if (pack < packsHalf) { sci = pack / H; azi = pack - sci * H; }
+							else if (pack < 2 * packsHalf) { const uint32_t p2 = pack - packsHalf; sci = p2 / H; azi = p2 - sci * H; mirror = true; }
+							else { sci = pack - 2 * packsHalf; azi = H; }
+							const float sinPhi = sRingS[sci], cosPhi = sRingC[sci];
+							F3 d;
+							d.x = sinPhi * sAzCos[azi * 4 + l4];
+							d.y = sinPhi * sAzSin[azi * 4 + l4];
+							if (mirror) d.y = 0.0f - d.y;
+							d.z = cosPhi;
+							d = basis_transform_simd(basis, d);                 // RotateChannelCap (:895-901)
+							d = slerp_simd(sRsq, d, m.target, m.tSlerp);        // SlerpChannelCap (:904-919)
+							const uint32_t code = oct_encode_simd(d.x, d.y, d.z);
+							const uint4 cell = __ldg(&lut[code]);
+							// (vsWeight * g) * g (PannerBase.h:836-839)
+							const float g0 = u2f(cell.x), g1 = u2f(cell.y), g2 = u2f(cell.z);
+							const uint32_t s0 = cell.w & 0xffu, s1 = (cell.w >> 8) & 0xffu, s2 = (cell.w >> 16) & 0xffu;
+							float* mrow = sMat + row * G;
+							if (s0 < G) mrow[s0] = (lp.vsWeight * g0) * g0;
+							if (s1 < G) mrow[s1] = (lp.vsWeight * g1) * g1;
+							if (s2 < G) mrow[s2] = (lp.vsWeight * g2) * g2;
+							mine[it] = cell.w & 0xffffffu;
+						}
+					}
+					__syncwarp();
+					if (gl < L)
+					{
+						const uint32_t rows = min(kMdapRows, lp.numVS - vb);
+						const float* col = sMat + gl;
+						if (rows == kMdapRows)
+						{
+							#pragma unroll
+							for (uint32_t e = 0; e < kMdapRows; ++e) acc += col[e * G];
+						}
+						else
+							for (uint32_t e = 0; e < rows; ++e) acc += col[e * G];
+					}
+					__syncwarp();
+					#pragma unroll
+					for (uint32_t it = 0; it < kMdapRows / G; ++it)
+					{
+						if (mine[it] != 0xffffffffu)
+						{
+							float* mrow = sMat + (it * G + gl) * G;
+							const uint32_t s0 = mine[it] & 0xffu, s1 = (mine[it] >> 8) & 0xffu, s2 = (mine[it] >> 16) & 0xffu;
+							if (s0 < G) mrow[s0] = 0.0f;
+							if (s1 < G) mrow[s1] = 0.0f;
+							if (s2 < G) mrow[s2] = 0.0f;
+						}
+					}
+					// the next batch's writes of a lane only touch rows it owns, which it has just cleared; readers of this batch are behind the barrier above
 				}
-				__syncwarp();
-				// outGains[speakers[s]] += gains[s], in entry order, per speaker == lane. The three speakers of a cell are distinct
-				// (a triangle, the dummy replaced by an index not in it: VBAPLUT3D.h:803-815), so at most one of a cell's entries hits a lane.
 				if (gl < L)
 				{
-					float acc = 0.0f;
-					const uint32_t laneRep = gl * 0x010101u;
-					#pragma unroll 4
-					for (uint32_t e = 0; e < lp.numVS; ++e)
-					{
-						const uint4 en = sEnt[e];
-						const uint32_t mm = __vcmpeq4(en.x, laneRep);         // byte k = 0xff where speaker k == lane (top byte: 0 == 0, ignored)
-						if (mm & 0x00ffffffu) acc += u2f((mm & 0xffu) ? en.y : ((mm & 0xff00u) ? en.z : en.w));
-					}
 					if (valid) outSrc[ch * L + gl] = acc; // pre-normalisation value; rescaled below
 					sMix[gl] += acc;                       // mixBuffer[i] += gains[i] (:683-686)
 				}
@@ -306,7 +346,7 @@ namespace jplg
 	size_t MdapSmemBytes(const PannerDev& p, const MdapLayoutParams& lp)
 	{
 		const uint32_t groups = JPLG_MDAP_WARPS * 32 / MdapLanesPerSource(p);
-		if (p.is3D) return (2048 + 64) * 4 + size_t(groups) * (48 + 4 * lp.numVS + kMaxChannelsDev) * 4;
+		if (p.is3D) return (2048 + 64) * 4 + size_t(groups) * (48 + kMdapRows * MdapLanesPerSource(p) + kMaxChannelsDev) * 4;
 		return (2048 + JPLG_MDAP_WARPS * 32) * 4;
 	}
 
