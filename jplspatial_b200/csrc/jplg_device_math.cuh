@@ -106,31 +106,40 @@ __device__ __forceinline__ F3 slerp_simd(const uint32_t* __restrict__ rsq, F3 v0
 	const bool isParallel = dot > oneMinusEps;
 	const bool isOpposite = dot < minusOnePlusEps;
 
-	// opposite case
-	const float dAxisX = v0.x * 1.0f + v0.y * 0.0f + v0.z * 0.0f;
-	const bool isClose = absbits(dAxisX) > oneMinusEps;
-	const F3 axis{ isClose ? 0.0f : 1.0f, isClose ? 1.0f : 0.0f, 0.0f };
-	const float dAxis = dot3(v0, axis);
-	F3 proj{ axis.x - v0.x * dAxis, axis.y - v0.y * dAxis, axis.z - v0.z * dAxis };
+	// The reference evaluates all three cases in every SIMD lane and selects; a lane's result only depends on the case it selects, so the
+	// unselected ones are skipped here (bit-identical, and the parallel / opposite cases are rare)
+	F3 mulA = v0, addC;
+	float mulB;
+	if (isParallel)
 	{
-		const float il = invsqrt_fast(rsq, dot3(proj, proj));
-		proj.x *= il; proj.y *= il; proj.z *= il;
+		mulA = F3{ v1.x - v0.x, v1.y - v0.y, v1.z - v0.z };
+		mulB = t;
+		addC = v0;
 	}
-	float sinA, cosA;
-	sincos_simd(t * 3.14159265358979323846f, sinA, cosA);
-	const F3 oppB{ proj.x * sinA, proj.y * sinA, proj.z * sinA };
-
-	// general case
-	const float invSinTheta = invsqrt_fast(rsq, 1.0f - dot * dot);
-	const float theta = acos_simd(dot);
-	float sinT, cosT;
-	sincos_simd(t * theta, sinT, cosT);
-	const float w1 = sinT * invSinTheta;
-	const float w0 = cosT - dot * w1;
-
-	const F3 mulA = isParallel ? F3{ v1.x - v0.x, v1.y - v0.y, v1.z - v0.z } : v0;
-	const float mulB = isParallel ? t : (isOpposite ? cosA : w0);
-	const F3 addC = isParallel ? v0 : (isOpposite ? oppB : F3{ v1.x * w1, v1.y * w1, v1.z * w1 });
+	else if (isOpposite)
+	{
+		const float dAxisX = v0.x * 1.0f + v0.y * 0.0f + v0.z * 0.0f;
+		const bool isClose = absbits(dAxisX) > oneMinusEps;
+		const F3 axis{ isClose ? 0.0f : 1.0f, isClose ? 1.0f : 0.0f, 0.0f };
+		const float dAxis = dot3(v0, axis);
+		F3 proj{ axis.x - v0.x * dAxis, axis.y - v0.y * dAxis, axis.z - v0.z * dAxis };
+		const float ilp = invsqrt_fast(rsq, dot3(proj, proj));
+		proj.x *= ilp; proj.y *= ilp; proj.z *= ilp;
+		float sinA, cosA;
+		sincos_simd(t * 3.14159265358979323846f, sinA, cosA);
+		mulB = cosA;
+		addC = F3{ proj.x * sinA, proj.y * sinA, proj.z * sinA };
+	}
+	else
+	{
+		const float invSinTheta = invsqrt_fast(rsq, 1.0f - dot * dot);
+		const float theta = acos_simd(dot);
+		float sinT, cosT;
+		sincos_simd(t * theta, sinT, cosT);
+		const float w1 = sinT * invSinTheta;
+		mulB = cosT - dot * w1;
+		addC = F3{ v1.x * w1, v1.y * w1, v1.z * w1 };
+	}
 	F3 r{ mulA.x * mulB + addC.x, mulA.y * mulB + addC.y, mulA.z * mulB + addC.z };
 	const float il = invsqrt_fast(rsq, dot3(r, r));
 	r.x *= il; r.y *= il; r.z *= il;
