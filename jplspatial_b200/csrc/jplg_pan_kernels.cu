@@ -95,10 +95,22 @@ namespace jplg
 		for (uint32_t i = threadIdx.x; i < kGroups * kMdapRows * G; i += blockDim.x) sGroupBase[(i / (kMdapRows * G)) * (48 + kMdapRows * G + kMaxChannelsDev) + 48 + i % (kMdapRows * G)] = 0.0f;
 		for (uint32_t i = threadIdx.x; i < 2048; i += blockDim.x) sRsq[i] = rsqTable[i];
 		if (threadIdx.x < 32) { sAzSin[threadIdx.x] = lp.azSin[threadIdx.x]; sAzCos[threadIdx.x] = lp.azCos[threadIdx.x]; }
-		__syncthreads();
-
 		const uint32_t R = lp.numRings, H = lp.halfSamples;
 		const uint32_t packsHalf = R * H;
+		// virtual source -> (ring, azimuth slot, mirrored) of GenerateSpreadCap's pack order (VBAPanning3D.h:449-518): the same for every source,
+		// so the two integer divisions per virtual source are done once per CTA. Entry = ring | azimuth float index << 8 | mirror << 16.
+		uint32_t* sVsIdx = reinterpret_cast<uint32_t*>(sGroupBase + kGroups * (48 + kMdapRows * G + kMaxChannelsDev));
+		for (uint32_t v = threadIdx.x; v < lp.numVS; v += blockDim.x)
+		{
+			const uint32_t pack = v >> 2, l4 = v & 3u;
+			uint32_t sci, azi, mirror = 0;
+			if (pack < packsHalf) { sci = pack / H; azi = pack - sci * H; }
+			else if (pack < 2 * packsHalf) { const uint32_t p2 = pack - packsHalf; sci = p2 / H; azi = p2 - sci * H; mirror = 1; }
+			else { sci = pack - 2 * packsHalf; azi = H; }
+			sVsIdx[v] = sci | ((azi * 4 + l4) << 8) | (mirror << 16);
+		}
+		__syncthreads();
+
 		const float nChF = static_cast<float>(lp.numChannels);
 
 		for (uint32_t srcBase = blockIdx.x * kGroups; srcBase < n; srcBase += gridDim.x * kGroups)
@@ -148,16 +160,12 @@ namespace jplg
 						mine[it] = 0xffffffffu;
 						if (v < lp.numVS)
 						{
-							const uint32_t pack = v >> 2, l4 = v & 3u;
-							uint32_t sci, azi; bool mirror = false;
-							if (pack < packsHalf) { sci = pack / H; azi = pack - sci * H; }
-							else if (pack < 2 * packsHalf) { const uint32_t p2 = pack - packsHalf; sci = p2 / H; azi = p2 - sci * H; mirror = true; }
-							else { sci = pack - 2 * packsHalf; azi = H; }
+							const uint32_t vi = sVsIdx[v], sci = vi & 0xffu, az = (vi >> 8) & 0xffu;
 							const float sinPhi = sRingS[sci], cosPhi = sRingC[sci];
 							F3 d;
-							d.x = sinPhi * sAzCos[azi * 4 + l4];
-							d.y = sinPhi * sAzSin[azi * 4 + l4];
-							if (mirror) d.y = 0.0f - d.y;
+							d.x = sinPhi * sAzCos[az];
+							d.y = sinPhi * sAzSin[az];
+							if (vi >> 16) d.y = 0.0f - d.y;
 							d.z = cosPhi;
 							d = basis_transform_simd(basis, d);                 // RotateChannelCap (:895-901)
 							d = slerp_simd(sRsq, d, m.target, m.tSlerp);        // SlerpChannelCap (:904-919)
@@ -346,7 +354,7 @@ namespace jplg
 	size_t MdapSmemBytes(const PannerDev& p, const MdapLayoutParams& lp)
 	{
 		const uint32_t groups = JPLG_MDAP_WARPS * 32 / MdapLanesPerSource(p);
-		if (p.is3D) return (2048 + 64) * 4 + size_t(groups) * (48 + kMdapRows * MdapLanesPerSource(p) + kMaxChannelsDev) * 4;
+		if (p.is3D) return (2048 + 64) * 4 + size_t(groups) * (48 + kMdapRows * MdapLanesPerSource(p) + kMaxChannelsDev) * 4 + size_t(lp.numVS) * 4;
 		return (2048 + JPLG_MDAP_WARPS * 32) * 4;
 	}
 
