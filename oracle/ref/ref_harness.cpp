@@ -744,4 +744,45 @@ extern "C"
 			p->p3.ProcessVBAPData(l->l3, u, std::span<float>(out + size_t(i) * row, row));
 		}
 	}
+	//==========================================================================
+	// 3D panners with the other LUT storage variants (inc/Panning/VBAPLUT3D.h:93-104): kind 0 KB_983, 1 KB_851, 2 KB_786, 3 KB_655, 4 KB_65.
+	// One-shot: builds the panner + source layout, runs ProcessVBAPData for n rows and GetSpeakerGains for m directions.
+	} // extern "C" (templates need C++ linkage)
+	template<VBAP::ELUTSize K>
+	static int RunLutVariant(uint32_t targetMask, uint32_t sourceMask, const float* params, uint32_t n, float* outMix, const float* dirs, uint32_t m, float* outPoint)
+	{
+		using P = VBAPanner3D<VBAPStandardTraits, K>;
+		auto p = std::make_unique<P>();
+		if (!p->Initialize(ChannelMap::FromChannelMask(targetMask))) return 0;
+		typename P::SourceLayoutType lay;
+		if (!p->InitializeSourceLayout(ChannelMap::FromChannelMask(sourceMask), lay)) return 0;
+		const uint32 L = p->GetNumChannels();
+		const size_t stride = lay.ChannelGroups.size() * L;
+		for (uint32_t i = 0; i < n; ++i)
+		{
+			const float* q = params + 5 * size_t(i);
+			typename P::PanUpdateData d{ .SourceDirection = MinimalVec3(q[0], q[1], q[2]), .Focus = q[3], .Spread = q[4] };
+			p->ProcessVBAPData(lay, d, std::span<float>(outMix + stride * i, stride));
+		}
+		for (uint32_t i = 0; i < m; ++i)
+		{
+			float* o = outPoint + size_t(i) * L;
+			for (uint32 c = 0; c < L; ++c) o[c] = 0.0f;
+			p->GetSpeakerGains(MinimalVec3(dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2]), std::span<float>(o, L));
+		}
+		return static_cast<int>(stride);
+	}
+	extern "C" {
+	int ref_lut_variant(int kind, uint32_t targetMask, uint32_t sourceMask, const float* params, uint32_t n, float* outMix, const float* dirs, uint32_t m, float* outPoint)
+	{
+		switch (kind)
+		{
+		case 0: return RunLutVariant<VBAP::ELUTSize::KB_983>(targetMask, sourceMask, params, n, outMix, dirs, m, outPoint);
+		case 1: return RunLutVariant<VBAP::ELUTSize::KB_851>(targetMask, sourceMask, params, n, outMix, dirs, m, outPoint);
+		case 2: return RunLutVariant<VBAP::ELUTSize::KB_786>(targetMask, sourceMask, params, n, outMix, dirs, m, outPoint);
+		case 3: return RunLutVariant<VBAP::ELUTSize::KB_655>(targetMask, sourceMask, params, n, outMix, dirs, m, outPoint);
+		case 4: return RunLutVariant<VBAP::ELUTSize::KB_65>(targetMask, sourceMask, params, n, outMix, dirs, m, outPoint);
+		default: return 0;
+		}
+	}
 } // extern "C"
