@@ -381,7 +381,7 @@ typedef struct jplg_frontend_io {
     float           focus, spread;
     const uint32_t* function_index;  /* [n] attenuation function per source, NULL = function 0 */
     uint32_t        pan_stride;      /* 5: PanUpdateData rows, 11: PanUpdateDataWithOrientation rows */
-    float* direct;        /* [n][4] Distance, DirectionDot, InvDirectionDot, cone factor (ProcessAngleAttenuationImpl(InvDirectionDot, cone)) */
+    float* direct;        /* (16-byte aligned) [n][4] Distance, DirectionDot, InvDirectionDot, cone factor (ProcessAngleAttenuationImpl(InvDirectionDot, cone)) */
     float* relative;      /* [n][9] DirectPathResult::Position */
     float* pan_params;    /* [n][pan_stride]: what jplg_panner_mdap / jplg_panner_mdap_oriented consume */
     float* distance_attenuation; /* [n] AttenuationFunction::Evaluate(Distance) */

@@ -338,6 +338,7 @@ jplg_status jplg_panner_set_lut(jplg_panner p, const float* gains, const uint8_t
 
 jplg_status jplg_panner_point_gains(jplg_panner p, const float* dirs, uint32_t n, float* out, int32_t mem)
 {
+	if (mem != JPLG_MEM_HOST && mem != JPLG_MEM_DEVICE) return JPLG_ERR_INVALID_ARGUMENT;   // JPLG_MEM_HOST_ASYNC: mdap / update / process_block only
 	if (!p || (n && (!dirs || !out))) return JPLG_ERR_INVALID_ARGUMENT;
 	jplg_context ctx = p->ctx;
 	JPLG_NEED_DEVICE(ctx);
@@ -448,6 +449,7 @@ jplg_status jplg_panner_mdap_oriented(jplg_panner p, jplg_source_layout l, const
 
 jplg_status jplg_panner_process_virtual_sources(jplg_panner p, const float* vs, uint32_t n, uint32_t batches, float* out, int32_t mem)
 {
+	if (mem != JPLG_MEM_HOST && mem != JPLG_MEM_DEVICE) return JPLG_ERR_INVALID_ARGUMENT;   // JPLG_MEM_HOST_ASYNC: mdap / update / process_block only
 	if (!p || (batches && (!out || (n && !vs)))) return JPLG_ERR_INVALID_ARGUMENT;
 	jplg_context ctx = p->ctx;
 	JPLG_NEED_DEVICE(ctx);
@@ -898,6 +900,7 @@ void jplg_crossover_bank_coeffs(jplg_crossover_bank b, float out[27]) { if (b &&
 
 jplg_status jplg_crossover_bank_process_ramp(jplg_crossover_bank b, const float* in, const float* start_gains, const float* end_gains, float* out, uint32_t frames, int32_t mem)
 {
+	if (mem != JPLG_MEM_HOST && mem != JPLG_MEM_DEVICE) return JPLG_ERR_INVALID_ARGUMENT;   // JPLG_MEM_HOST_ASYNC: mdap / update / process_block only
 	if (!b || !in || !start_gains || !end_gains || !out) return JPLG_ERR_INVALID_ARGUMENT;
 	jplg_context ctx = b->ctx;
 	JPLG_NEED_DEVICE(ctx);
@@ -928,6 +931,7 @@ jplg_status jplg_crossover_bank_process_ramp(jplg_crossover_bank b, const float*
 
 jplg_status jplg_crossover_bank_split(jplg_crossover_bank b, const float* in, float* out_bands, uint32_t frames, int32_t mem)
 {
+	if (mem != JPLG_MEM_HOST && mem != JPLG_MEM_DEVICE) return JPLG_ERR_INVALID_ARGUMENT;   // JPLG_MEM_HOST_ASYNC: mdap / update / process_block only
 	if (!b || !in || !out_bands) return JPLG_ERR_INVALID_ARGUMENT;
 	jplg_context ctx = b->ctx;
 	JPLG_NEED_DEVICE(ctx);
@@ -990,6 +994,7 @@ jplg_status jplg_delay_bank_clear(jplg_delay_bank b)
 }
 jplg_status jplg_delay_bank_push(jplg_delay_bank b, const float* in, uint32_t frames, int32_t mem)
 {
+	if (mem != JPLG_MEM_HOST && mem != JPLG_MEM_DEVICE) return JPLG_ERR_INVALID_ARGUMENT;   // JPLG_MEM_HOST_ASYNC: mdap / update / process_block only
 	if (!b || (frames && !in)) return JPLG_ERR_INVALID_ARGUMENT;
 	jplg_context ctx = b->ctx;
 	JPLG_NEED_DEVICE(ctx);
@@ -1011,6 +1016,7 @@ jplg_status jplg_delay_bank_push(jplg_delay_bank b, const float* in, uint32_t fr
 }
 jplg_status jplg_delay_bank_read(jplg_delay_bank b, const float* delays, uint32_t taps, int32_t interp, float* out, int32_t mem)
 {
+	if (mem != JPLG_MEM_HOST && mem != JPLG_MEM_DEVICE) return JPLG_ERR_INVALID_ARGUMENT;   // JPLG_MEM_HOST_ASYNC: mdap / update / process_block only
 	if (!b || (taps && (!delays || !out)) || interp < 0 || interp > 2) return JPLG_ERR_INVALID_ARGUMENT;
 	jplg_context ctx = b->ctx;
 	JPLG_NEED_DEVICE(ctx);
@@ -1038,6 +1044,7 @@ jplg_status jplg_delay_bank_read(jplg_delay_bank b, const float* delays, uint32_
 
 jplg_status jplg_delay_bank_read_xfade(jplg_delay_bank b, const float* delays, const float* alphas, uint32_t taps, float* out, int32_t mem)
 {
+	if (mem != JPLG_MEM_HOST && mem != JPLG_MEM_DEVICE) return JPLG_ERR_INVALID_ARGUMENT;   // JPLG_MEM_HOST_ASYNC: mdap / update / process_block only
 	if (!b || (taps && (!delays || !alphas || !out))) return JPLG_ERR_INVALID_ARGUMENT;
 	jplg_context ctx = b->ctx;
 	JPLG_NEED_DEVICE(ctx);
@@ -1068,6 +1075,7 @@ jplg_status jplg_delay_bank_read_xfade(jplg_delay_bank b, const float* delays, c
 jplg_status jplg_mix_add_and_apply_gain_ramp(jplg_context ctx, float* dest, const float* source, uint32_t n, uint32_t dest_channel, uint32_t source_channel,
 											 uint32_t dest_num_channels, uint32_t source_num_channels, uint32_t frames, const float* gain_start, const float* gain_end, int32_t mem)
 {
+	if (mem != JPLG_MEM_HOST && mem != JPLG_MEM_DEVICE) return JPLG_ERR_INVALID_ARGUMENT;   // JPLG_MEM_HOST_ASYNC: mdap / update / process_block only
 	if (!ctx || !dest || !source || !gain_start || !gain_end || dest_channel >= dest_num_channels || source_channel >= source_num_channels) return JPLG_ERR_INVALID_ARGUMENT;
 	JPLG_NEED_DEVICE(ctx);
 	if (n == 0 || frames == 0) return JPLG_OK;
@@ -1098,6 +1106,7 @@ jplg_status jplg_mix_add_and_apply_gain_ramp(jplg_context ctx, float* dest, cons
 
 jplg_status jplg_mix_apply_gain(jplg_context ctx, float* dest, uint32_t n, uint32_t frames, const float* gains, int32_t mem)
 {
+	if (mem != JPLG_MEM_HOST && mem != JPLG_MEM_DEVICE) return JPLG_ERR_INVALID_ARGUMENT;   // JPLG_MEM_HOST_ASYNC: mdap / update / process_block only
 	if (!ctx || !dest || !gains) return JPLG_ERR_INVALID_ARGUMENT;
 	JPLG_NEED_DEVICE(ctx);
 	if (n == 0 || frames == 0) return JPLG_OK;
@@ -1183,6 +1192,7 @@ __global__ void k_reverb_set_slope(const float* __restrict__ v, size_t count, in
 }
 static jplg_status ReverbSet(jplg_reverb_bank b, const float* v, int rt60, int32_t mem)
 {
+	if (mem != JPLG_MEM_HOST && mem != JPLG_MEM_DEVICE) return JPLG_ERR_INVALID_ARGUMENT;   // JPLG_MEM_HOST_ASYNC: mdap / update / process_block only
 	if (!b || !v) return JPLG_ERR_INVALID_ARGUMENT;
 	jplg_context ctx = b->ctx;
 	JPLG_NEED_DEVICE(ctx);
@@ -1231,6 +1241,7 @@ jplg_status jplg_reverb_bank_decay_gains(jplg_reverb_bank b, float* out /* host 
 }
 jplg_status jplg_reverb_bank_process(jplg_reverb_bank b, const float* in, uint32_t in_channels, float* out, uint32_t frames, int32_t mem)
 {
+	if (mem != JPLG_MEM_HOST && mem != JPLG_MEM_DEVICE) return JPLG_ERR_INVALID_ARGUMENT;   // JPLG_MEM_HOST_ASYNC: mdap / update / process_block only
 	if (!b || (frames && (!in || !out))) return JPLG_ERR_INVALID_ARGUMENT;
 	jplg_context ctx = b->ctx;
 	JPLG_NEED_DEVICE(ctx);
@@ -1418,6 +1429,7 @@ __global__ void k_accumulate(float* __restrict__ dst, const float* __restrict__ 
 
 static jplg_status ErProcess(jplg_erbus_bank b, const float* in, uint32_t in_channels, float* out, float* perTap, uint32_t frames, int32_t mem)
 {
+	if (mem != JPLG_MEM_HOST && mem != JPLG_MEM_DEVICE) return JPLG_ERR_INVALID_ARGUMENT;   // JPLG_MEM_HOST_ASYNC: mdap / update / process_block only
 	if (!b || (frames && (!in || !out)) || in_channels == 0) return JPLG_ERR_INVALID_ARGUMENT;
 	jplg_context ctx = b->ctx;
 	JPLG_NEED_DEVICE(ctx);
@@ -1502,10 +1514,12 @@ static jplg_status ErProcess(jplg_erbus_bank b, const float* in, uint32_t in_cha
 }
 jplg_status jplg_erbus_bank_process(jplg_erbus_bank b, const float* in, uint32_t in_channels, float* out, uint32_t frames, int32_t mem)
 {
+	if (mem != JPLG_MEM_HOST && mem != JPLG_MEM_DEVICE) return JPLG_ERR_INVALID_ARGUMENT;   // JPLG_MEM_HOST_ASYNC: mdap / update / process_block only
 	return ErProcess(b, in, in_channels, out, nullptr, frames, mem);
 }
 jplg_status jplg_erbus_bank_process_debug(jplg_erbus_bank b, const float* in, uint32_t in_channels, float* out, float* per_tap, uint32_t frames, int32_t mem)
 {
+	if (mem != JPLG_MEM_HOST && mem != JPLG_MEM_DEVICE) return JPLG_ERR_INVALID_ARGUMENT;   // JPLG_MEM_HOST_ASYNC: mdap / update / process_block only
 	if (!per_tap) return JPLG_ERR_INVALID_ARGUMENT;
 	return ErProcess(b, in, in_channels, out, per_tap, frames, mem);
 }

@@ -110,6 +110,7 @@ void jplg_frontend_destroy(jplg_frontend f)
 
 jplg_status jplg_frontend_process(jplg_frontend f, const jplg_frontend_io* io, int32_t mem)
 {
+	if (mem != JPLG_MEM_HOST && mem != JPLG_MEM_DEVICE) return JPLG_ERR_INVALID_ARGUMENT;   // JPLG_MEM_HOST_ASYNC: mdap / update / process_block only
 	if (!f || !io) return JPLG_ERR_INVALID_ARGUMENT;
 	jplg_context ctx = f->ctx;
 	JPLG_NEED_DEVICE(ctx);

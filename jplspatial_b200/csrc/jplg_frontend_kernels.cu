@@ -120,7 +120,7 @@ namespace jplg
 		using namespace fe;
 		for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < fa.n; i += gridDim.x * blockDim.x)
 		{
-			float distance, invDirectionDot;
+			float distance, invDirectionDot, directionDot = 0.0f;
 			F3 dir{ 0.0f, 0.0f, -1.0f };
 			if (fa.sources)
 			{
@@ -139,11 +139,10 @@ namespace jplg
 				}
 				distance = sqrtf(p.x * p.x + p.y * p.y + p.z * p.z);
 				dir = { p.x / distance, p.y / distance, p.z / distance };
-				const float directionDot = dir.x * 0.0f + dir.y * 0.0f + dir.z * -1.0f;
+				directionDot = dir.x * 0.0f + dir.y * 0.0f + dir.z * -1.0f;
 				const F3 nd{ -dir.x, -dir.y, -dir.z };
 				const F3 l2s{ dot3(nd, lb.X), dot3(nd, lb.Y), dot3(nd, lb.Z) };
 				invDirectionDot = dot3(sFwd, l2s);
-				if (fa.direct) { float* o = fa.direct + size_t(i) * 4; o[0] = distance; o[1] = directionDot; o[2] = invDirectionDot; }
 				if (fa.rel || fa.panStride == 11)
 				{
 					// source orientation in the listener's frame: listenerBasis.InverseTransform(source basis) (:307)
@@ -169,7 +168,13 @@ namespace jplg
 			}
 
 			// ---- EvaluateDirection: cone factor of the source's cone towards the listener (SpatialManager.h:404)
-			if (fa.cones && fa.direct) fa.direct[size_t(i) * 4 + 3] = angle_attenuation(invDirectionDot, fa.cones[2 * size_t(i)], fa.cones[2 * size_t(i) + 1]);
+			if (fa.direct)
+			{
+				// one 16-byte store per source (the rows are 16-byte aligned: cudaMalloc / pinned staging); without a cone the last column keeps 0
+				float cone = 0.0f;
+				if (fa.cones) { const float2 c = reinterpret_cast<const float2*>(fa.cones)[i]; cone = angle_attenuation(invDirectionDot, c.x, c.y); }
+				reinterpret_cast<float4*>(fa.direct)[i] = make_float4(fa.sources ? distance : 0.0f, directionDot, fa.sources ? invDirectionDot : 0.0f, cone);
+			}
 
 			// ---- EvaluateDistance (SpatialManager.h:401)
 			if (fa.distAtt)
@@ -210,15 +215,17 @@ namespace jplg
 			// ---- air absorption -> band gains (AirAbsorption.h:212-234); SSE2 build: Math::FMA = multiply, then add
 			if (fa.airDb || fa.bandGains)
 			{
+				float loss[4], gain[4];
 				#pragma unroll
 				for (int b = 0; b < 4; ++b)
 				{
 					const float lin = distance * fa.air.lowerThirdDb[b] + fa.air.linFactor[b];
 					const float centre = distance * fa.air.centerDb[b];
-					const float loss = (fa.air.hasKnee[b] && distance >= fa.air.distanceToKnee[b]) ? lin : centre;
-					if (fa.airDb) fa.airDb[size_t(i) * 4 + b] = loss;
-					if (fa.bandGains) fa.bandGains[size_t(i) * 4 + b] = exp_simd_lane((2.302585092994046f * 0.05f) * (0.0f - loss));
+					loss[b] = (fa.air.hasKnee[b] && distance >= fa.air.distanceToKnee[b]) ? lin : centre;
+					gain[b] = exp_simd_lane((2.302585092994046f * 0.05f) * (0.0f - loss[b]));
 				}
+				if (fa.airDb) reinterpret_cast<float4*>(fa.airDb)[i] = make_float4(loss[0], loss[1], loss[2], loss[3]);
+				if (fa.bandGains) reinterpret_cast<float4*>(fa.bandGains)[i] = make_float4(gain[0], gain[1], gain[2], gain[3]);
 			}
 			if (fa.delay) fa.delay[i] = distance * fa.invSpeedOfSound;
 		}

@@ -43,7 +43,7 @@ for n in (16384, 262144, 2097152):
         for _ in range(20):
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             with torch.cuda.stream(stream):
-                flush.zero_()                      # L2 flush between timed iterations (256 MB > 126 MB L2)
+                sink = flush.sum()                 # L2 flush between timed iterations: READ 256 MB (> 126 MB L2) so no dirty lines are written back under the timed kernel
                 e0.record(stream); tick(chain); e1.record(stream)
             torch.cuda.synchronize(); times.append(e0.elapsed_time(e1))
         ms = float(np.median(times))
