@@ -119,7 +119,7 @@ def run_reference_arm(args, rank, world):
     from oracle import refpy
     kind = "reference"
     if not refpy.available("sse2"):
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libjplref_sse2.so not present (reference tree absent at build time)"}))
+        _emit(({"impl": "reference", "unavailable": "oracle/_ref/libjplref_sse2.so not present (reference tree absent at build time)"}))
         return
     cores = os.cpu_count() or 1
     n = args.ref_sources
@@ -155,7 +155,7 @@ def run_reference_arm(args, rank, world):
                          "sample": f"{n} mono sources x {args.steps} blocks of 512 frames, {cores} std::threads, reference SSE2 build (-O2)"},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
-    print(json.dumps(line))
+    _emit(line)
 
 
 def cpu_baseline_sample(log_fn):
@@ -194,7 +194,26 @@ def cpu_baseline_sample(log_fn):
 
 
 # ------------------------------------------------------------------------------------------------
+_JSON_OUT = None
+
+
+def _claim_stdout():
+    """The driver reads ONE JSON line from stdout: keep a private handle to the real stdout for it and point fd 1 at stderr for everything else
+    (NCCL prints its version banner to stdout on the rank that initialises first)."""
+    global _JSON_OUT
+    if _JSON_OUT is None:
+        sys.stdout.flush()
+        _JSON_OUT = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+
+
+def _emit(line):
+    _JSON_OUT.write(json.dumps(line) + "\n")
+    _JSON_OUT.flush()
+
+
 def main():
+    _claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=200)
@@ -207,6 +226,9 @@ def main():
     ap.add_argument("--ref-sources", type=int, default=2048)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--bus", choices=["peer", "nccl"], default="peer",
+                    help="multi-GPU combine of the partial buses: peer = jplg_bus_exchange (stores into the root GPU's memory over NVLink, rank-ordered sum), "
+                         "nccl = torch.distributed reduce, double-buffered")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
@@ -251,22 +273,38 @@ def main():
         d_mix = torch.empty((N, 1, L_OUT), dtype=torch.float32, device=dev)
     ctx.synchronize()
 
-    from jplspatial_b200.sharding import PipelinedBusReduce
-    # two bus buffers: the NCCL reduce of block k overlaps the render of block k+1 (the only collective of the path)
+    from jplspatial_b200.sharding import PipelinedBusReduce, make_peer_bus_exchange
+    # the only exchange of the path: the sum of the per-GPU partial buses ([512][12] floats per rank and block)
+    use_peer = dist is not None and args.bus == "peer"
+    # nccl mode: two bus buffers, the NCCL reduce of block k overlaps the render of block k+1
     reducer = PipelinedBusReduce(FRAMES, L_OUT, dev, depth=2, dst=0)
+    exchange = make_peer_bus_exchange(ctx, FRAMES * L_OUT) if use_peer else None
+    with torch.cuda.stream(stream):
+        local_bus = torch.zeros((FRAMES, L_OUT), dtype=torch.float32, device=dev)
+        final_bus = torch.zeros((FRAMES, L_OUT), dtype=torch.float32, device=dev)
+    seq = [0]
 
     def step_device(k):
         j = k % args.pool
         with torch.cuda.stream(stream):
             pan.ProcessVBAPData(lay, d_params[j], out=d_mix)
             rend.UpdateParameters(d_band[j], d_delay[j], d_mix)
-            bus = reducer.begin(k)
-            rend.ProcessInterleaved(d_audio[j], bus, FRAMES)
-            reducer.submit(k)
+            if use_peer:
+                # every rank's k_bus_reduce result goes straight into the root GPU's gather buffer (peer stores over NVLink); the root adds the
+                # slots in rank order. No collective library on the data path.
+                rend.ProcessInterleaved(d_audio[j], local_bus, FRAMES)
+                exchange.submit(rend.device_bus_ptr(), FRAMES * L_OUT, seq[0], out=final_bus if rank == 0 else None)
+                seq[0] += 1
+            else:
+                bus = reducer.begin(k)
+                rend.ProcessInterleaved(d_audio[j], bus, FRAMES)
+                reducer.submit(k)
 
     def barrier():
         with torch.cuda.stream(stream):
             reducer.drain()
+            if exchange is not None:
+                exchange.wait()
         if dist is not None:
             dist.barrier()
         torch.cuda.synchronize()
@@ -291,6 +329,8 @@ def main():
         step_device(args.warmup + k)
     with torch.cuda.stream(stream):
         reducer.drain()              # the last blocks' reduces are inside the timed region
+        if exchange is not None:
+            exchange.wait()          # ... and so is the peer-memory combine of the last blocks
         ev1.record(stream)
     barrier()
     ms_total = ev0.elapsed_time(ev1)
@@ -375,6 +415,8 @@ def main():
                "path": "C ABI with pinned HOST buffers, JPLG_MEM_HOST_ASYNC: block k+1's input transfer overlaps block k's render (2 blocks in flight)"}
 
     clocks = sampler.stop()
+    if exchange is not None and exchange.error() != 0:
+        raise SystemExit(f"bench.py: bus exchange reported a device-side wait timeout (error {exchange.error()}) on rank {rank}")
     if rank != 0:
         if dist is not None:
             dist.destroy_process_group()
@@ -418,10 +460,11 @@ def main():
                                "(MDAP gains + update + push + fused delay/LR4/mix + bus reduce per block)",
                    "sources_per_gpu": N, "total_sources": N * world, "mode": args.mode, "ring_size": rend.ring_size,
                    "l2_policy": f"inputs larger than L2: {args.pool} distinct 33.5 MB input blocks cycled, {N * rend.ring_size * 4 / 2**30:.1f} GiB of rings",
-                   "parallelism": f"sources sharded over {world} GPU(s); NCCL reduce of the [512x12] bus, double-buffered (block k reduce overlaps block k+1 render)" if world > 1 else "single GPU"},
+                   "parallelism": (f"sources sharded over {world} GPU(s); partial [512x12] buses stored into the root GPU's gather buffer over NVLink peer memory and summed in rank order (jplg_bus_exchange, no collective library on the data path)"
+                                   if use_peer else f"sources sharded over {world} GPU(s); NCCL reduce of the [512x12] bus, double-buffered (block k reduce overlaps block k+1 render)") if world > 1 else "single GPU"},
         "clocks": clocks, "gpu_launches": launches, "e2e": e2e, "roofline": roofline, "cpu_baseline": cpu,
     }
-    print(json.dumps(line))
+    _emit(line)
     if dist is not None:
         dist.destroy_process_group()
 

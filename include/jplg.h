@@ -80,6 +80,7 @@ typedef struct jplg_delay_bank_t*    jplg_delay_bank;
 typedef struct jplg_reverb_bank_t*   jplg_reverb_bank;
 typedef struct jplg_erbus_bank_t*    jplg_erbus_bank;
 typedef struct jplg_frontend_t*      jplg_frontend;
+typedef struct jplg_bus_exchange_t*  jplg_bus_exchange;
 
 /* replaces: JPL::SpatialTrace (inc/ErrorReporting.h:44-47) */
 typedef void (*jplg_trace_fn)(const char* message);
@@ -108,7 +109,7 @@ JPLG_API uint64_t    jplg_context_launch_count(jplg_context ctx);
  * so the events do not perturb the others). `which`: one of JPLG_K_*. kernel_time synchronises the stream and returns the accumulated
  * milliseconds and launch count since the last reset. */
 enum { JPLG_K_PUSH = 0, JPLG_K_RENDER = 1, JPLG_K_BUS_REDUCE = 2, JPLG_K_MDAP = 3, JPLG_K_POINT_GAINS = 4,
-       JPLG_K_UPDATE = 5, JPLG_K_OTHER = 6, JPLG_K_FDN = 7, JPLG_K_ER_PUSH = 8, JPLG_K_FRONTEND = 9, JPLG_K_COUNT = 10 };
+       JPLG_K_UPDATE = 5, JPLG_K_OTHER = 6, JPLG_K_FDN = 7, JPLG_K_ER_PUSH = 8, JPLG_K_FRONTEND = 9, JPLG_K_EXCHANGE = 10, JPLG_K_COUNT = 11 };
 JPLG_API void        jplg_context_set_kernel_timing(jplg_context ctx, int32_t enabled);
 JPLG_API void        jplg_context_reset_kernel_timing(jplg_context ctx);
 JPLG_API jplg_status jplg_context_kernel_time(jplg_context ctx, int32_t which, double* total_ms, uint64_t* launches);
@@ -397,6 +398,34 @@ JPLG_API void        jplg_frontend_destroy(jplg_frontend f);
 JPLG_API jplg_status jplg_frontend_process(jplg_frontend f, const jplg_frontend_io* io, int32_t mem);
 /* the fallback direction SanitizeSourceDir substitutes for straight-up / straight-down sources */
 JPLG_API void        jplg_sanitize_fallback_dir(float out[3]);
+
+/* ---------------------------------------------------------------------------------------------- */
+/* Multi-GPU: peer-memory combine of the per-GPU partial buses (no counterpart in the reference,   */
+/* which is a single process). One process per GPU; the ROOT rank (0) owns a gather  */
+/* buffer, every other rank maps it through CUDA IPC and stores its bus into its slot over NVLink; */
+/* the root sums the slots in rank order (deterministic). Nothing but the 64-byte handle has to    */
+/* travel through the host application (e.g. torch.distributed broadcast).                          */
+
+#define JPLG_IPC_HANDLE_BYTES 64
+/* rank 0: allocates the gather buffer for `world` ranks x two blocks in flight x max_floats, returns the IPC handle to distribute */
+JPLG_API jplg_status jplg_bus_exchange_create_root(jplg_context ctx, uint32_t world, uint32_t max_floats, jplg_bus_exchange* out,
+                                                   uint8_t handle_out[JPLG_IPC_HANDLE_BYTES]);
+/* rank != 0: maps the root's buffer (the root's GPU must be peer-accessible from this context's GPU) */
+JPLG_API jplg_status jplg_bus_exchange_open_peer(jplg_context ctx, uint32_t world, uint32_t rank, uint32_t max_floats,
+                                                 const uint8_t handle[JPLG_IPC_HANDLE_BYTES], jplg_bus_exchange* out);
+JPLG_API void        jplg_bus_exchange_destroy(jplg_bus_exchange x);
+/* Once per block and rank with the same `seq` (0, 1, 2, ...) on every rank. `device_bus`: this rank's partial
+ * bus (n floats, 16-byte aligned, e.g. jplg_renderer_device_bus). Rank != 0: waits (on the device) until the root has consumed block seq-2,
+ * stores the bus into the root's slot and publishes it. Rank 0: waits for every rank's block `seq`, then device_out[i] (+)= own[i] + sum over
+ * ranks in rank order (`accumulate` != 0 adds into device_out like the renderer's bus), and acknowledges.
+ * The call copies `device_bus` into a private staging slot on the context stream and runs the peer traffic on a side stream, so the context
+ * stream continues with the next block while the root waits for the other ranks; device_out is complete after jplg_bus_exchange_wait. */
+JPLG_API jplg_status jplg_bus_exchange_submit(jplg_bus_exchange x, const float* device_bus, uint32_t n, uint64_t seq, float* device_out,
+                                              int32_t accumulate);
+/* makes the context stream wait (on the device, not the host) for every block submitted so far */
+JPLG_API jplg_status jplg_bus_exchange_wait(jplg_bus_exchange x);
+/* 0 = healthy; != 0 after a device-side wait timed out (~2 s: a rank died or stalled): results of that block are undefined, nothing hangs */
+JPLG_API int32_t     jplg_bus_exchange_error(jplg_bus_exchange x);
 
 #ifdef __cplusplus
 }

@@ -212,7 +212,7 @@ class Context:
     def launch_count(self):
         return int(lib.jplg_context_launch_count(self.h))
 
-    KERNELS = {"push": 0, "render": 1, "bus_reduce": 2, "mdap": 3, "point_gains": 4, "update": 5, "other": 6, "fdn": 7, "er_push": 8, "frontend": 9}
+    KERNELS = {"push": 0, "render": 1, "bus_reduce": 2, "mdap": 3, "point_gains": 4, "update": 5, "other": 6, "fdn": 7, "er_push": 8, "frontend": 9, "exchange": 10}
 
     def set_kernel_timing(self, enabled, only=None):
         """only: iterable of kernel names (see kernel_time) to bracket with events; default every kernel"""
@@ -842,5 +842,65 @@ class DirectPathBatch:
             if self.h:
                 lib.jplg_frontend_destroy(self.h)
                 self.h = None
+        except Exception:
+            pass
+
+
+# ------------------------------------------------------------------------------------------------
+# Multi-GPU: peer-memory combine of the per-GPU partial buses (include/jplg.h "Multi-GPU")
+_sig("jplg_bus_exchange_create_root", _i32, [_vp, _u32, _u32, C.POINTER(_vp), _vp])
+_sig("jplg_bus_exchange_open_peer", _i32, [_vp, _u32, _u32, _u32, _vp, C.POINTER(_vp)])
+_sig("jplg_bus_exchange_destroy", None, [_vp])
+_sig("jplg_bus_exchange_submit", _i32, [_vp, _fp, _u32, _u64, _fp, _i32])
+_sig("jplg_bus_exchange_error", _i32, [_vp])
+_sig("jplg_bus_exchange_wait", _i32, [_vp])
+DECLARED_SYMBOLS = [n for n in dir(lib) if n.startswith("jplg_")]
+IPC_HANDLE_BYTES = 64
+
+
+class BusExchange:
+    """One per rank. Rank 0: BusExchange.create_root(ctx, world, max_floats) -> (exchange, handle bytes to distribute);
+    other ranks: BusExchange.open_peer(ctx, world, rank, max_floats, handle)."""
+
+    def __init__(self, ctx, h, world, rank):
+        self.ctx, self.h, self.world, self.rank = ctx, h, world, rank
+
+    @staticmethod
+    def create_root(ctx, world, max_floats):
+        h = _vp()
+        handle = np.zeros(IPC_HANDLE_BYTES, np.uint8)
+        ctx.check(lib.jplg_bus_exchange_create_root(ctx.h, int(world), int(max_floats), C.byref(h), handle.ctypes.data))
+        return BusExchange(ctx, h, int(world), 0), handle
+
+    @staticmethod
+    def open_peer(ctx, world, rank, max_floats, handle):
+        h = _vp()
+        hb = np.ascontiguousarray(handle, np.uint8)
+        ctx.check(lib.jplg_bus_exchange_open_peer(ctx.h, int(world), int(rank), int(max_floats), hb.ctypes.data, C.byref(h)))
+        return BusExchange(ctx, h, int(world), int(rank))
+
+    def submit(self, device_bus_ptr, n, seq, out=None, accumulate=False):
+        """device_bus_ptr: raw device address of this rank's partial bus (e.g. DirectSoundBatch.device_bus_ptr()); out: CUDA tensor on rank 0"""
+        o = None
+        if out is not None:
+            o, mem, _ = _arg(out)
+            assert mem == MEM_DEVICE
+        self.ctx.check(lib.jplg_bus_exchange_submit(self.h, device_bus_ptr, int(n), int(seq), o, 1 if accumulate else 0))
+
+    def wait(self):
+        """the context stream waits (on the device) for every block submitted so far; on rank 0 `out` is then complete"""
+        self.ctx.check(lib.jplg_bus_exchange_wait(self.h))
+
+    def error(self):
+        return int(lib.jplg_bus_exchange_error(self.h))
+
+    def close(self):
+        if self.h:
+            lib.jplg_bus_exchange_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
         except Exception:
             pass

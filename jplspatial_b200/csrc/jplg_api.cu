@@ -6,6 +6,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstddef>
 #include <cstdlib>
 #include <cstdio>
 #include <cstring>
@@ -1532,5 +1533,6 @@ int32_t jplg_erbus_bank_tap_slot(jplg_erbus_bank b, uint32_t bus, uint32_t id)
 }
 
 #include "jplg_api_frontend.inl"
+#include "jplg_api_exchange.inl"
 
 } // extern "C"

@@ -169,4 +169,18 @@ namespace jplg
 		float* delay;      // [n] seconds
 	};
 	cudaError_t LaunchFrontend(const FrontendArgs& fa, int numSMs, cudaStream_t st);
+	//======================================================================
+	// Peer-memory bus exchange (jplg_exchange_kernels.cu)
+	constexpr uint32_t kMaxWorld = 16;
+	struct ExchangeHeader
+	{
+		unsigned long long ack;                 // blocks consumed by the root
+		uint32_t done, error;
+		unsigned long long flags[2][kMaxWorld]; // (seq + 1) last published by a rank into that slot
+	};
+	constexpr size_t kExchangeDataOffset = 512;   // bytes: header padded so the slot data is 256-byte aligned
+	static_assert(sizeof(ExchangeHeader) <= kExchangeDataOffset, "exchange header too large");
+	cudaError_t LaunchBusSend(ExchangeHeader* hdr, float* slotData, const float* bus, uint32_t n, uint32_t rank, uint64_t seq, cudaStream_t st);
+	cudaError_t LaunchBusGather(ExchangeHeader* hdr, const float* data, uint32_t world, uint32_t maxFloats, const float* own, uint32_t n, uint64_t seq,
+								float* out, int accumulate, cudaStream_t st);
 }

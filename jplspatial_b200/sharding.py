@@ -109,3 +109,28 @@ class PipelinedBusReduce:
             if w is not None:
                 w.wait()
                 self.pending[j] = None
+
+
+def make_peer_bus_exchange(ctx, max_floats: int, group=None):
+    """Sets up the peer-memory bus combine (include/jplg.h "Multi-GPU") across the ranks of `group`: rank 0 allocates the gather buffer, its 64-byte
+    CUDA IPC handle is broadcast with torch.distributed (a CUDA uint8 tensor with NCCL, a CPU tensor with gloo), every other rank maps it.
+    Returns a jplspatial_b200.BusExchange; the per-block data path then never touches torch.distributed / NCCL."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from . import BusExchange
+    from ._capi import IPC_HANDLE_BYTES
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    backend = dist.get_backend(group)
+    dev = torch.device("cuda", ctx.device) if backend == "nccl" else torch.device("cpu")
+    if rank == 0:
+        x, handle = BusExchange.create_root(ctx, world, max_floats)
+        t = torch.from_numpy(handle.copy()).to(dev)
+    else:
+        x = None
+        t = torch.zeros(IPC_HANDLE_BYTES, dtype=torch.uint8, device=dev)
+    dist.broadcast(t, src=0, group=group)
+    if rank != 0:
+        x = BusExchange.open_peer(ctx, world, rank, max_floats, t.cpu().numpy())
+    dist.barrier(group)
+    return x
