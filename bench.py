@@ -72,6 +72,9 @@ class ClockSampler:
         except Exception:
             self.proc = None
 
+    def count(self):
+        return len(self.lines)
+
     def stop(self):
         if self.proc is not None:
             time.sleep(0.15)
@@ -414,6 +417,13 @@ def main():
                "ms_per_step": dt * 1e3, "steps": e2e_steps,
                "path": "C ABI with pinned HOST buffers, JPLG_MEM_HOST_ASYNC: block k+1's input transfer overlaps block k's render (2 blocks in flight)"}
 
+    # a short run (--no-e2e, few steps) can end before nvidia-smi has delivered its first line: keep the GPU under the same load until it has
+    extra, t_end = 0, time.time() + 3.0
+    while sampler.proc is not None and sampler.count() == 0 and time.time() < t_end:
+        for k in range(64):
+            step_device(extra + k)
+        extra += 64
+        barrier()
     clocks = sampler.stop()
     if exchange is not None and exchange.error() != 0:
         raise SystemExit(f"bench.py: bus exchange reported a device-side wait timeout (error {exchange.error()}) on rank {rank}")
