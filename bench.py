@@ -418,8 +418,16 @@ def main():
                "path": "C ABI with pinned HOST buffers, JPLG_MEM_HOST_ASYNC: block k+1's input transfer overlaps block k's render (2 blocks in flight)"}
 
     # a short run (--no-e2e, few steps) can end before nvidia-smi has delivered its first line: keep the GPU under the same load until it has
+    # (every rank takes the same decision: the steps contain the bus exchange)
     extra, t_end = 0, time.time() + 3.0
-    while sampler.proc is not None and sampler.count() == 0 and time.time() < t_end:
+    while True:
+        need = 1 if (sampler.proc is not None and sampler.count() == 0 and time.time() < t_end) else 0
+        if dist is not None:
+            tn = torch.tensor([need], dtype=torch.int32, device=dev)
+            dist.all_reduce(tn, op=dist.ReduceOp.MAX)
+            need = int(tn.item())
+        if not need:
+            break
         for k in range(64):
             step_device(extra + k)
         extra += 64
