@@ -229,6 +229,8 @@ def main():
     ap.add_argument("--ref-sources", type=int, default=2048)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-push-ahead", action="store_true",
+                    help="issue every block's ring pushes inside process_block instead of one block ahead on a side stream (jplg_renderer_push_ahead)")
     ap.add_argument("--bus", choices=["peer", "nccl"], default="peer",
                     help="multi-GPU combine of the partial buses: peer = jplg_bus_exchange (stores into the root GPU's memory over NVLink, rank-ordered sum), "
                          "nccl = torch.distributed reduce, double-buffered")
@@ -287,12 +289,29 @@ def main():
         final_bus = torch.zeros((FRAMES, L_OUT), dtype=torch.float32, device=dev)
     seq = [0]
 
-    def step_device(k):
+    push_ahead = not args.no_push_ahead
+    gk = [0]
+
+    def step_device(_k):
+        k = gk[0]          # consecutive block numbers whatever the caller's phase, so the block pushed ahead is always the next one rendered
+        gk[0] += 1
         j = k % args.pool
         with torch.cuda.stream(stream):
             pan.ProcessVBAPData(lay, d_params[j], out=d_mix)
             rend.UpdateParameters(d_band[j], d_delay[j], d_mix)
-            if use_peer:
+            if push_ahead:
+                # throughput rendering: block k+1's input is resident, so its ring pushes (an HBM-bound copy) are issued right after block k's render
+                # has been enqueued and run beside it on the SMs the render leaves free; block k only waits for the pushes issued one step earlier
+                if use_peer:
+                    rend.ProcessInterleaved(d_audio[j], local_bus, FRAMES)
+                    exchange.submit(rend.device_bus_ptr(), FRAMES * L_OUT, seq[0], out=final_bus if rank == 0 else None)
+                    seq[0] += 1
+                else:
+                    bus = reducer.begin(k)
+                    rend.ProcessInterleaved(d_audio[j], bus, FRAMES)
+                    reducer.submit(k)
+                rend.PushAhead(d_audio[(k + 1) % args.pool], FRAMES)
+            elif use_peer:
                 # every rank's k_bus_reduce result goes straight into the root GPU's gather buffer (peer stores over NVLink); the root adds the
                 # slots in rank order. No collective library on the data path.
                 rend.ProcessInterleaved(d_audio[j], local_bus, FRAMES)

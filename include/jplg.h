@@ -214,6 +214,14 @@ JPLG_API jplg_status jplg_renderer_update(jplg_renderer r, const float* band_gai
  * bus: [frames][L] interleaved, ACCUMULATED INTO like the reference's `output` span; all N sources add
  *      into the same bus (the host loop "for each effect: ProcessInterleaved(in_i, bus)"). */
 JPLG_API jplg_status jplg_renderer_process_block(jplg_renderer r, const float* in, float* bus, uint32_t frames, int32_t mem);
+/* Offline / throughput rendering: issues the ring pushes of the NEXT block (device pointer `in`, already resident) on a side stream, so that
+ * they overlap the render of the block enqueued before this call: the copy is HBM-bound and runs on the SMs the render leaves free. The two
+ * touch disjoint ring slots as long as the ring holds the longest delay in use plus four blocks, which the caller guarantees (true for the
+ * reference ring size bit_ceil(2 fs) with delays up to 1.9 s). The next jplg_renderer_process_block must get the same `in` / `frames`
+ * (JPLG_MEM_DEVICE); it waits for these pushes instead of issuing its own (any other block simply overwrites them: the ring position only advances
+ * in process_block). A real-time engine, whose next block does not exist yet, does not
+ * need this call. */
+JPLG_API jplg_status jplg_renderer_push_ahead(jplg_renderer r, const float* in, uint32_t frames);
 /* JPLG_MEM_HOST_ASYNC blocks complete in submission order; this waits (on the host) for the oldest block not yet waited for: its `bus`
  * is then valid. At most two blocks are in flight (a third submission first waits for the oldest). */
 JPLG_API jplg_status jplg_renderer_wait_block(jplg_renderer r);

@@ -77,6 +77,7 @@ _sig("jplg_renderer_update", _i32, [_vp, _fp, _fp, _fp, _i32])
 _sig("jplg_renderer_process_block", _i32, [_vp, _fp, _fp, _u32, _i32])
 _sig("jplg_renderer_process_block_debug", _i32, [_vp, _fp, _fp, _fp, _u32, _i32])
 _sig("jplg_renderer_wait_block", _i32, [_vp])
+_sig("jplg_renderer_push_ahead", _i32, [_vp, _fp, _u32])
 _sig("jplg_renderer_device_bus", _vp, [_vp])
 _sig("jplg_renderer_ring_size", _u32, [_vp])
 _sig("jplg_renderer_state_export", _i32, [_vp, _fp, _fp, C.POINTER(_u64)])
@@ -444,6 +445,13 @@ class DirectSoundBatch:
         assert len(mems) <= 1, "all update arrays must live in the same memory space"
         mem = mems.pop() if mems else MEM_HOST
         self.ctx.check(lib.jplg_renderer_update(self.h, b, d, m, MEM_HOST_ASYNC if (async_host and mem == MEM_HOST) else mem))
+
+    def PushAhead(self, inp, num_frames):
+        """issue the NEXT block's ring pushes now, on a side stream (jplg_renderer_push_ahead); `inp` is a CUDA tensor that the next
+        ProcessInterleaved call must be given again"""
+        i, mem, ki = _arg(inp)
+        assert mem == MEM_DEVICE
+        self.ctx.check(lib.jplg_renderer_push_ahead(self.h, i, int(num_frames)))
 
     def WaitBlock(self):
         """host-wait for the oldest asynchronous block (see ProcessInterleaved(async_host=True))"""

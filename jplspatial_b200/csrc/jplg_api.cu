@@ -512,6 +512,10 @@ struct jplg_renderer_t
 	cudaEvent_t evCopiedA[2] = {}, evPushedA[2] = {}, evDoneA[2] = {};
 	bool asyncReady = false;
 	uint64_t asyncSubmitted = 0, asyncWaited = 0;
+	// jplg_renderer_push_ahead: the next block's ring pushes, issued early on a side stream
+	const float* aheadIn = nullptr;
+	uint32_t aheadFrames = 0;
+	cudaEvent_t evAhead = nullptr;
 };
 
 // targets in the reference's layouts -> SoA per source-channel (UpdateParameters, src/Auralization/DirectSound.cpp:231-239)
@@ -570,6 +574,7 @@ static void FreeRenderer(jplg_renderer r)
 		for (int i = 0; i < 2; ++i) { cudaEventDestroy(r->evCopiedA[i]); cudaEventDestroy(r->evPushedA[i]); cudaEventDestroy(r->evDoneA[i]); }
 		r->asyncReady = false;
 	}
+	if (r->evAhead) { if (r->ctx->auxReady) cudaStreamSynchronize(r->ctx->aux[1]); cudaEventDestroy(r->evAhead); r->evAhead = nullptr; }
 }
 
 static jplg_status RendererUpdateLocked(jplg_renderer r, const float* band, const float* delay, const float* mix, int32_t mem)
@@ -684,6 +689,13 @@ static jplg_status ProcessBlock(jplg_renderer r, const float* in, float* bus, fl
 	const uint32_t N = r->cfg.num_sources, C = r->cfg.source_channels, L = r->cfg.output_channels;
 	const float* dIn = in; float* dBus = bus; float* dPer = perSource;
 	const size_t perFloats = size_t(N) * frames * L;
+	if (r->aheadIn && !(mem == JPLG_MEM_DEVICE && r->aheadIn == in && r->aheadFrames == frames && !perSource))
+	{
+		// a different block than the one pushed ahead: its pushes went to the slots this block is about to write (the ring position only
+		// advances in process_block), so let them land first and push this block over them
+		JPLG_CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, r->evAhead, 0));
+		r->aheadIn = nullptr;
+	}
 	const bool pipelinedHost = mem == JPLG_MEM_HOST && ctx->hostPipeline > 0 && r->numCTAs >= 32 && !perSource;
 	int asyncSlot = -1;
 	if (mem == JPLG_MEM_HOST_ASYNC)
@@ -778,6 +790,13 @@ static jplg_status ProcessBlock(jplg_renderer r, const float* in, float* bus, fl
 			JPLG_CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, ctx->evDone[a], 0));
 		}
 	}
+	else if (mem == JPLG_MEM_DEVICE && r->aheadIn == in && r->aheadFrames == frames && !perSource)
+	{
+		// this block's pushes were issued ahead of time (jplg_renderer_push_ahead): only wait for them
+		JPLG_CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, r->evAhead, 0));
+		r->aheadIn = nullptr;
+		JPLG_LAUNCH(ctx, JPLG_K_RENDER, LaunchRender(rp, r->cfg.mode, 0, r->numCTAs, ctx->stream));
+	}
 	else
 	{
 		JPLG_LAUNCH(ctx, JPLG_K_PUSH, LaunchPush(rp, 0, N, ctx->stream));
@@ -798,6 +817,28 @@ static jplg_status ProcessBlock(jplg_renderer r, const float* in, float* bus, fl
 		JPLG_CUDA_TRY(ctx, cudaEventRecord(r->evDoneA[asyncSlot], ctx->stream));
 		r->asyncSubmitted++;
 	}
+	return JPLG_OK;
+}
+
+jplg_status jplg_renderer_push_ahead(jplg_renderer r, const float* in, uint32_t frames)
+{
+	if (!r || !in || frames == 0) return JPLG_ERR_INVALID_ARGUMENT;
+	jplg_context ctx = r->ctx;
+	JPLG_NEED_DEVICE(ctx);
+	if (frames > r->maxFrames) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "push_ahead: frames exceeds max_block_frames");
+	if (r->aheadIn) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "push_ahead: a block is already pushed ahead");
+	if (r->ringSize < 4u * TotalPushes(frames)) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "push_ahead: ring too small to hold a block ahead");
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	jplg_status ast = EnsureAux(ctx); if (ast != JPLG_OK) return ast;
+	if (!r->evAhead) JPLG_CUDA_TRY(ctx, cudaEventCreateWithFlags(&r->evAhead, cudaEventDisableTiming));
+	RenderParams rp{};
+	rp.numSC = r->numSC; rp.srcChannels = r->cfg.source_channels; rp.L = r->cfg.output_channels; rp.ringSize = r->ringSize; rp.ringMask = r->ringSize - 1;
+	rp.pos = r->pos; rp.frames = frames; rp.rings = r->rings; rp.in = in;
+	cudaStream_t side = ctx->aux[1];
+	JPLG_LAUNCH_ON(ctx, JPLG_K_PUSH, side, LaunchPush(rp, 0, r->cfg.num_sources, side));
+	JPLG_CUDA_TRY(ctx, cudaEventRecord(r->evAhead, side));
+	r->aheadIn = in; r->aheadFrames = frames;
 	return JPLG_OK;
 }
 

@@ -326,3 +326,49 @@ def test_async_host_path_equals_sync_host_path():
     rs.close(); ra.close()
     del pan, lay
     ctx.close()
+
+
+def test_push_ahead_equals_plain_path():
+    """jplg_renderer_push_ahead: block k+1's ring pushes on a side stream while block k renders. Same buses, bit for bit, as pushing inside
+    process_block; a process_block with a different block overwrites the stale pushes."""
+    import torch
+    ctx = J.Context(0)
+    N, C, L, blocks, frames = 2085, 1, 12, 6, 512
+    sc = make_scene(N, C, L, blocks, frames, util.SEED + 79)
+    dev = torch.device("cuda", 0)
+    stream = ctx.torch_stream()
+
+    def make():
+        return J.DirectSoundBatch(ctx, FS, N, C, L, sc["band"][0], sc["delay"][0], sc["mix"][0], ring_size=0, max_block_frames=512, mode=J.MODE_PARITY)   # reference ring (131,072): holds the longest delay of the scene (42 k samples) + blocks ahead
+
+    ra, rb = make(), make()
+    with torch.cuda.stream(stream):
+        d_audio = [torch.from_numpy(sc["audio"][b]).to(dev) for b in range(blocks)]
+        bus_a = [torch.zeros((frames, L), dtype=torch.float32, device=dev) for _ in range(blocks)]
+        bus_b = [torch.zeros((frames, L), dtype=torch.float32, device=dev) for _ in range(blocks)]
+    ctx.synchronize()
+    for b in range(blocks):
+        ra.UpdateParameters(sc["band"][b + 1], sc["delay"][b + 1], sc["mix"][b + 1])
+        ra.ProcessInterleaved(d_audio[b], bus_a[b], frames)
+    for b in range(blocks):
+        rb.UpdateParameters(sc["band"][b + 1], sc["delay"][b + 1], sc["mix"][b + 1])
+        rb.ProcessInterleaved(d_audio[b], bus_b[b], frames)          # block 0 pushes itself, the others were pushed ahead
+        if b + 1 < blocks:
+            rb.PushAhead(d_audio[b + 1], frames)
+            if b == 2:
+                with pytest.raises(J.JplgError):
+                    rb.PushAhead(d_audio[b + 1], frames)            # only one block ahead
+    ctx.synchronize()
+    for b in range(blocks):
+        assert np.abs(bus_a[b].cpu().numpy()).max() > 0
+        assert util.bits_equal(bus_b[b].cpu().numpy(), bus_a[b].cpu().numpy()), f"block {b}: push-ahead path differs"
+    # a different block than the one pushed ahead: same result as without the stale pushes
+    with torch.cuda.stream(stream):
+        xa = torch.zeros((frames, L), dtype=torch.float32, device=dev); xb = torch.zeros((frames, L), dtype=torch.float32, device=dev)
+    rb.PushAhead(d_audio[0], frames)
+    rb.ProcessInterleaved(d_audio[1], xb, frames)
+    ra.ProcessInterleaved(d_audio[1], xa, frames)
+    ctx.synchronize()
+    assert util.bits_equal(xa.cpu().numpy(), xb.cpu().numpy())
+    ra.close(); rb.close()
+    ctx.close()
