@@ -231,6 +231,9 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-push-ahead", action="store_true",
                     help="issue every block's ring pushes inside process_block instead of one block ahead on a side stream (jplg_renderer_push_ahead)")
+    ap.add_argument("--no-pan-overlap", action="store_true",
+                    help="compute the panning data on the rendering context's stream instead of a background context (jplg_context_create_ex) "
+                         "that works one block ahead on the SMs the render leaves free")
     ap.add_argument("--bus", choices=["peer", "nccl"], default="peer",
                     help="multi-GPU combine of the partial buses: peer = jplg_bus_exchange (stores into the root GPU's memory over NVLink, rank-ordered sum), "
                          "nccl = torch.distributed reduce, double-buffered")
@@ -291,14 +294,50 @@ def main():
 
     push_ahead = not args.no_push_ahead
     gk = [0]
+    # game-thread / audio-thread split of the reference (SpatialManager::AdvanceSimulation beside the audio callback): block k+1's panning data is
+    # computed by a background context while block k renders; its stream has the lower priority, so k_render's 128 CTAs are placed first and
+    # k_mdap_3d fills the remaining SMs. Two mix-map buffers; events order the two streams.
+    pan_overlap = not args.no_pan_overlap
+    if pan_overlap:
+        ctx_pan = J.Context(local_rank, background=True)
+        stream_pan = ctx_pan.torch_stream()
+        pan_bg = J.VBAPanner(ctx_pan)
+        assert pan_bg.Initialize(J.ChannelMask.Surround_7_1_4)
+        lay_bg = pan_bg.InitializeSourceLayout(J.ChannelMask.Mono)
+        with torch.cuda.stream(stream):
+            d_mix_bg = [torch.empty((N, 1, L_OUT), dtype=torch.float32, device=dev) for _ in range(2)]
+        ctx.synchronize()
+        ev_mdap = [torch.cuda.Event() for _ in range(2)]
+        ev_upd = torch.cuda.Event()
+        mdap_issued = [-1]
+
+        def issue_mdap(k, after_update):
+            with torch.cuda.stream(stream_pan):
+                if after_update:
+                    stream_pan.wait_event(ev_upd)      # the buffer's previous reader (update k-1) is older than this event
+                    rend.WaitRenderStarted(ctx_pan)    # ... and only once block k-1's render is resident: k_mdap_3d takes the SMs it leaves free
+                pan_bg.ProcessVBAPData(lay_bg, d_params[k % args.pool], out=d_mix_bg[k & 1])
+                ev_mdap[k & 1].record(stream_pan)
+            mdap_issued[0] = k
+
+        def join_pan():
+            if mdap_issued[0] >= 0:
+                stream.wait_event(ev_mdap[mdap_issued[0] & 1])
 
     def step_device(_k):
         k = gk[0]          # consecutive block numbers whatever the caller's phase, so the block pushed ahead is always the next one rendered
         gk[0] += 1
         j = k % args.pool
+        if pan_overlap and mdap_issued[0] != k:
+            issue_mdap(k, False)
         with torch.cuda.stream(stream):
-            pan.ProcessVBAPData(lay, d_params[j], out=d_mix)
-            rend.UpdateParameters(d_band[j], d_delay[j], d_mix)
+            if pan_overlap:
+                stream.wait_event(ev_mdap[k & 1])
+                rend.UpdateParameters(d_band[j], d_delay[j], d_mix_bg[k & 1])
+                ev_upd.record(stream)
+            else:
+                pan.ProcessVBAPData(lay, d_params[j], out=d_mix)
+                rend.UpdateParameters(d_band[j], d_delay[j], d_mix)
             if push_ahead:
                 # throughput rendering: block k+1's input is resident, so its ring pushes (an HBM-bound copy) are issued right after block k's render
                 # has been enqueued and run beside it on the SMs the render leaves free; block k only waits for the pushes issued one step earlier
@@ -310,6 +349,8 @@ def main():
                     bus = reducer.begin(k)
                     rend.ProcessInterleaved(d_audio[j], bus, FRAMES)
                     reducer.submit(k)
+                if pan_overlap:
+                    issue_mdap(k + 1, True)
                 rend.PushAhead(d_audio[(k + 1) % args.pool], FRAMES)
             elif use_peer:
                 # every rank's k_bus_reduce result goes straight into the root GPU's gather buffer (peer stores over NVLink); the root adds the
@@ -321,9 +362,13 @@ def main():
                 bus = reducer.begin(k)
                 rend.ProcessInterleaved(d_audio[j], bus, FRAMES)
                 reducer.submit(k)
+            if pan_overlap and not push_ahead:
+                issue_mdap(k + 1, True)
 
     def barrier():
         with torch.cuda.stream(stream):
+            if pan_overlap:
+                join_pan()
             reducer.drain()
             if exchange is not None:
                 exchange.wait()
@@ -341,7 +386,7 @@ def main():
     # breakdown of the other kernels is taken in a separate short pass afterwards so its events do not stretch the timed steps
     ctx.set_kernel_timing(True, only=("render",))
     ctx.reset_kernel_timing()
-    launches0 = ctx.launch_count
+    launches0 = ctx.launch_count + (ctx_pan.launch_count if pan_overlap else 0)
     ev0 = torch.cuda.Event(enable_timing=True)
     ev1 = torch.cuda.Event(enable_timing=True)
     barrier()
@@ -350,23 +395,36 @@ def main():
     for k in range(args.steps):
         step_device(args.warmup + k)
     with torch.cuda.stream(stream):
+        if pan_overlap:
+            join_pan()               # the panning data computed one block ahead by the last step is inside the timed region too
         reducer.drain()              # the last blocks' reduces are inside the timed region
         if exchange is not None:
             exchange.wait()          # ... and so is the peer-memory combine of the last blocks
         ev1.record(stream)
     barrier()
     ms_total = ev0.elapsed_time(ev1)
-    launches = ctx.launch_count - launches0  # our kernels only (torch's bus zero-fill and NCCL are not counted)
+    # fingerprint of the last timed block's (combined) bus: the same for every pipelining option at equal --warmup / --steps / --pool / --gpus
+    import zlib
+    last_bus = final_bus if use_peer else reducer.result(gk[0] - 1)
+    bus_crc = zlib.crc32(last_bus.cpu().numpy().tobytes()) if rank == 0 else 0
+    launches = ctx.launch_count + (ctx_pan.launch_count if pan_overlap else 0) - launches0  # our kernels only (torch's bus zero-fill and NCCL are not counted)
     ktimes = {"render": ctx.kernel_time("render")}
     ctx.set_kernel_timing(False)
     bsteps = max(10, min(args.steps, 40))
     ctx.set_kernel_timing(True)
     ctx.reset_kernel_timing()
+    if pan_overlap:
+        ctx_pan.set_kernel_timing(True)
+        ctx_pan.reset_kernel_timing()
     for k in range(bsteps):
         step_device(args.warmup + args.steps + k)
     barrier()
     breakdown = {name: ctx.kernel_time(name) for name in ("mdap", "update", "push", "render", "bus_reduce")}
     ctx.set_kernel_timing(False)
+    if pan_overlap:
+        # measured while sharing the device with k_render (and the pushes): a duration under overlap, not the kernel's own cost
+        breakdown["mdap"] = ctx_pan.kernel_time("mdap")
+        ctx_pan.set_kernel_timing(False)
     t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -496,10 +554,13 @@ def main():
         "config": {"workload": "BASELINE config 3: full block render, 16,384 mono sources per GPU -> 7.1.4, 48 kHz / 512 frames "
                                "(MDAP gains + update + push + fused delay/LR4/mix + bus reduce per block)",
                    "sources_per_gpu": N, "total_sources": N * world, "mode": args.mode, "ring_size": rend.ring_size,
+                   "pipelining": {"push_ahead": push_ahead, "pan_overlap": pan_overlap,
+                                  "note": "every step runs all five kernels once; with push_ahead / pan_overlap block k+1's ring pushes / panning data "
+                                          "are produced on lower-priority streams while block k renders"},
                    "l2_policy": f"inputs larger than L2: {args.pool} distinct 33.5 MB input blocks cycled, {N * rend.ring_size * 4 / 2**30:.1f} GiB of rings",
                    "parallelism": (f"sources sharded over {world} GPU(s); partial [512x12] buses stored into the root GPU's gather buffer over NVLink peer memory and summed in rank order (jplg_bus_exchange, no collective library on the data path)"
                                    if use_peer else f"sources sharded over {world} GPU(s); NCCL reduce of the [512x12] bus, double-buffered (block k reduce overlaps block k+1 render)") if world > 1 else "single GPU"},
-        "clocks": clocks, "gpu_launches": launches, "e2e": e2e, "roofline": roofline, "cpu_baseline": cpu,
+        "bus_crc32": f"{bus_crc:08x}", "clocks": clocks, "gpu_launches": launches, "e2e": e2e, "roofline": roofline, "cpu_baseline": cpu,
     }
     _emit(line)
     if dist is not None:

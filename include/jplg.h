@@ -94,6 +94,12 @@ JPLG_API int32_t jplg_device_count(void);
 /* context: device, stream, constant tables                                                        */
 
 JPLG_API jplg_status jplg_context_create(int32_t device, jplg_context* out);
+/* The reference runs SpatialManager::AdvanceSimulation (panning data, scene front-end) on the game thread beside the audio thread that renders
+ * (SURVEY.md 3); the device analogue is a second context whose stream has a LOWER priority than the rendering context's: with both eligible, the
+ * renderer's CTAs are dispatched first and the background context's kernels fill the SMs the renderer leaves free. Order work between the two
+ * contexts with events on jplg_context_stream(). flags = 0 is jplg_context_create. */
+enum { JPLG_CONTEXT_BACKGROUND = 1 };
+JPLG_API jplg_status jplg_context_create_ex(int32_t device, uint32_t flags, jplg_context* out);
 JPLG_API void        jplg_context_destroy(jplg_context ctx);
 JPLG_API const char* jplg_last_error(jplg_context ctx);
 /* cudaStream_t of the context, as void*; all work of this context is enqueued on it. */
@@ -222,6 +228,10 @@ JPLG_API jplg_status jplg_renderer_process_block(jplg_renderer r, const float* i
  * in process_block). A real-time engine, whose next block does not exist yet, does not
  * need this call. */
 JPLG_API jplg_status jplg_renderer_push_ahead(jplg_renderer r, const float* in, uint32_t frames);
+/* Makes `waiting`'s stream (a JPLG_CONTEXT_BACKGROUND context on the same device) wait until every CTA of the k_render launch enqueued last by
+ * jplg_renderer_process_block is resident on the device. Work enqueued on `waiting` afterwards (the next block's jplg_panner_mdap, the scene
+ * front-end) runs beside that render on the SMs it leaves free instead of occupying SMs its CTAs need. No-op before the first block. */
+JPLG_API jplg_status jplg_renderer_wait_render_started(jplg_renderer r, jplg_context waiting);
 /* JPLG_MEM_HOST_ASYNC blocks complete in submission order; this waits (on the host) for the oldest block not yet waited for: its `bus`
  * is then valid. At most two blocks are in flight (a third submission first waits for the oldest). */
 JPLG_API jplg_status jplg_renderer_wait_block(jplg_renderer r);

@@ -35,6 +35,7 @@ _sig("jplg_set_trace_callback", None, [_TRACE])
 _sig("jplg_version", C.c_char_p, [])
 _sig("jplg_device_count", _i32, [])
 _sig("jplg_context_create", _i32, [_i32, C.POINTER(_vp)])
+_sig("jplg_context_create_ex", _i32, [_i32, _u32, C.POINTER(_vp)])
 _sig("jplg_context_destroy", None, [_vp])
 _sig("jplg_last_error", C.c_char_p, [_vp])
 _sig("jplg_context_stream", _vp, [_vp])
@@ -78,6 +79,7 @@ _sig("jplg_renderer_process_block", _i32, [_vp, _fp, _fp, _u32, _i32])
 _sig("jplg_renderer_process_block_debug", _i32, [_vp, _fp, _fp, _fp, _u32, _i32])
 _sig("jplg_renderer_wait_block", _i32, [_vp])
 _sig("jplg_renderer_push_ahead", _i32, [_vp, _fp, _u32])
+_sig("jplg_renderer_wait_render_started", _i32, [_vp, _vp])
 _sig("jplg_renderer_device_bus", _vp, [_vp])
 _sig("jplg_renderer_ring_size", _u32, [_vp])
 _sig("jplg_renderer_state_export", _i32, [_vp, _fp, _fp, C.POINTER(_u64)])
@@ -178,13 +180,22 @@ def _arg(x, dtype=np.float32):
     return a.ctypes.data, MEM_HOST, a
 
 
+def _ctx_alive(obj):
+    ctx = getattr(obj, "ctx", None)
+    if ctx is None:
+        owner = getattr(obj, "panner", None)
+        ctx = getattr(owner, "ctx", None)
+    return ctx is None or ctx.h is not None
+
+
 class Context:
     """Device + stream + constant tables. device=-1 gives a host-only context: the builders (LUTs, layouts,
     filter coefficients) work, every data-path call raises JplgError(JPLG_ERR_NO_DEVICE)."""
 
-    def __init__(self, device=0):
+    def __init__(self, device=0, background=False):
+        """background=True: the context's stream has a lower priority than a rendering context's (jplg_context_create_ex)."""
         h = _vp()
-        st = lib.jplg_context_create(int(device), C.byref(h))
+        st = lib.jplg_context_create_ex(int(device), 1 if background else 0, C.byref(h))
         if st != 0:
             raise JplgError(st, "jplg_context_create failed (no CUDA device? this library has no CPU fallback)")
         self.h = h
@@ -271,7 +282,7 @@ class SourceLayout:
 
     def __del__(self):
         try:
-            if self.h:
+            if self.h and _ctx_alive(self):   # a closed context's children are gone with it
                 lib.jplg_source_layout_destroy(self.h)
                 self.h = None
         except Exception:
@@ -401,7 +412,7 @@ class VBAPanner:
 
     def __del__(self):
         try:
-            if self.h:
+            if self.h and _ctx_alive(self):   # a closed context's children are gone with it
                 lib.jplg_panner_destroy(self.h)
                 self.h = None
         except Exception:
@@ -445,6 +456,10 @@ class DirectSoundBatch:
         assert len(mems) <= 1, "all update arrays must live in the same memory space"
         mem = mems.pop() if mems else MEM_HOST
         self.ctx.check(lib.jplg_renderer_update(self.h, b, d, m, MEM_HOST_ASYNC if (async_host and mem == MEM_HOST) else mem))
+
+    def WaitRenderStarted(self, waiting_ctx):
+        """`waiting_ctx`'s stream waits until the k_render enqueued last is fully resident (jplg_renderer_wait_render_started)."""
+        self.ctx.check(lib.jplg_renderer_wait_render_started(self.h, waiting_ctx.h))
 
     def PushAhead(self, inp, num_frames):
         """issue the NEXT block's ring pushes now, on a side stream (jplg_renderer_push_ahead); `inp` is a CUDA tensor that the next
@@ -490,7 +505,7 @@ class DirectSoundBatch:
         self.ctx.check(lib.jplg_renderer_state_import(self.h, st.ctypes.data, None if rg is None else rg.ctypes.data, int(pos)))
 
     def close(self):
-        if self.h:
+        if self.h and _ctx_alive(self):   # a closed context's children are gone with it
             lib.jplg_renderer_destroy(self.h)
             self.h = None
 
@@ -545,7 +560,7 @@ class ReverbBusBatch:
 
     def __del__(self):
         try:
-            if self.h:
+            if self.h and _ctx_alive(self):   # a closed context's children are gone with it
                 lib.jplg_reverb_bank_destroy(self.h)
                 self.h = None
         except Exception:
@@ -609,7 +624,7 @@ class ERBusBatch:
 
     def __del__(self):
         try:
-            if self.h:
+            if self.h and _ctx_alive(self):   # a closed context's children are gone with it
                 lib.jplg_erbus_bank_destroy(self.h)
                 self.h = None
         except Exception:
@@ -649,7 +664,7 @@ class CrossoverBank:
 
     def __del__(self):
         try:
-            if self.h:
+            if self.h and _ctx_alive(self):   # a closed context's children are gone with it
                 lib.jplg_crossover_bank_destroy(self.h)
                 self.h = None
         except Exception:
@@ -692,7 +707,7 @@ class DelayBank:
 
     def __del__(self):
         try:
-            if self.h:
+            if self.h and _ctx_alive(self):   # a closed context's children are gone with it
                 lib.jplg_delay_bank_destroy(self.h)
                 self.h = None
         except Exception:
@@ -847,7 +862,7 @@ class DirectPathBatch:
 
     def __del__(self):
         try:
-            if self.h:
+            if self.h and _ctx_alive(self):   # a closed context's children are gone with it
                 lib.jplg_frontend_destroy(self.h)
                 self.h = None
         except Exception:
@@ -903,7 +918,7 @@ class BusExchange:
         return int(lib.jplg_bus_exchange_error(self.h))
 
     def close(self):
-        if self.h:
+        if self.h and _ctx_alive(self):   # a closed context's children are gone with it
             lib.jplg_bus_exchange_destroy(self.h)
             self.h = None
 

@@ -129,9 +129,11 @@ int32_t jplg_device_count(void)
 }
 
 //==================================================================================================
-jplg_status jplg_context_create(int32_t device, jplg_context* out)
+jplg_status jplg_context_create(int32_t device, jplg_context* out) { return jplg_context_create_ex(device, 0u, out); }
+
+jplg_status jplg_context_create_ex(int32_t device, uint32_t flags, jplg_context* out)
 {
-	if (!out) return JPLG_ERR_INVALID_ARGUMENT;
+	if (!out || (flags & ~uint32_t(JPLG_CONTEXT_BACKGROUND))) return JPLG_ERR_INVALID_ARGUMENT;
 	*out = nullptr;
 	auto* ctx = new jplg_context_t();
 	static uint32_t sTable[2048];
@@ -147,7 +149,10 @@ jplg_status jplg_context_create(int32_t device, jplg_context* out)
 	if (device >= jplg_device_count()) { delete ctx; if (gTrace) gTrace("jplg_context_create: no such CUDA device"); return JPLG_ERR_NO_DEVICE; }
 	ctx->device = device;
 	cudaError_t e = cudaSetDevice(device);
-	if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+	int prioLeast = 0, prioGreatest = 0;
+	if (e == cudaSuccess) e = cudaDeviceGetStreamPriorityRange(&prioLeast, &prioGreatest);
+	// audio-rate contexts dispatch ahead of background ones (and of the library's own copy / push-ahead side streams, which stay at the default)
+	if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&ctx->stream, cudaStreamNonBlocking, (flags & JPLG_CONTEXT_BACKGROUND) ? prioLeast : prioGreatest);
 	if (e == cudaSuccess) e = cudaDeviceGetAttribute(&ctx->numSMs, cudaDevAttrMultiProcessorCount, device);
 	if (e == cudaSuccess) e = cudaMalloc(&ctx->dRsq, sizeof(sTable));
 	if (e == cudaSuccess) e = cudaMemcpy(ctx->dRsq, sTable, sizeof(sTable), cudaMemcpyHostToDevice);
@@ -516,6 +521,8 @@ struct jplg_renderer_t
 	const float* aheadIn = nullptr;
 	uint32_t aheadFrames = 0;
 	cudaEvent_t evAhead = nullptr;
+	cudaEvent_t evStarted = nullptr;   // launch-completion event of the last whole-grid k_render: fires when all its CTAs are resident
+	bool startedRecorded = false;
 };
 
 // targets in the reference's layouts -> SoA per source-channel (UpdateParameters, src/Auralization/DirectSound.cpp:231-239)
@@ -574,6 +581,7 @@ static void FreeRenderer(jplg_renderer r)
 		for (int i = 0; i < 2; ++i) { cudaEventDestroy(r->evCopiedA[i]); cudaEventDestroy(r->evPushedA[i]); cudaEventDestroy(r->evDoneA[i]); }
 		r->asyncReady = false;
 	}
+	if (r->evStarted) { cudaEventDestroy(r->evStarted); r->evStarted = nullptr; }
 	if (r->evAhead) { if (r->ctx->auxReady) cudaStreamSynchronize(r->ctx->aux[1]); cudaEventDestroy(r->evAhead); r->evAhead = nullptr; }
 }
 
@@ -795,13 +803,17 @@ static jplg_status ProcessBlock(jplg_renderer r, const float* in, float* bus, fl
 		// this block's pushes were issued ahead of time (jplg_renderer_push_ahead): only wait for them
 		JPLG_CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, r->evAhead, 0));
 		r->aheadIn = nullptr;
-		JPLG_LAUNCH(ctx, JPLG_K_RENDER, LaunchRender(rp, r->cfg.mode, 0, r->numCTAs, ctx->stream));
+		if (!r->evStarted) JPLG_CUDA_TRY(ctx, cudaEventCreateWithFlags(&r->evStarted, cudaEventDisableTiming));
+		JPLG_LAUNCH(ctx, JPLG_K_RENDER, LaunchRender(rp, r->cfg.mode, 0, r->numCTAs, ctx->stream, r->evStarted));
+		r->startedRecorded = true;
 	}
 	else
 	{
 		JPLG_LAUNCH(ctx, JPLG_K_PUSH, LaunchPush(rp, 0, N, ctx->stream));
 		if (asyncSlot >= 0) JPLG_CUDA_TRY(ctx, cudaEventRecord(r->evPushedA[asyncSlot], ctx->stream));
-		JPLG_LAUNCH(ctx, JPLG_K_RENDER, LaunchRender(rp, r->cfg.mode, 0, r->numCTAs, ctx->stream));
+		if (!r->evStarted) JPLG_CUDA_TRY(ctx, cudaEventCreateWithFlags(&r->evStarted, cudaEventDisableTiming));
+		JPLG_LAUNCH(ctx, JPLG_K_RENDER, LaunchRender(rp, r->cfg.mode, 0, r->numCTAs, ctx->stream, r->evStarted));
+		r->startedRecorded = true;
 	}
 	JPLG_LAUNCH(ctx, JPLG_K_BUS_REDUCE, LaunchBusReduce(rp, r->deviceBus, dBus, ctx->stream));
 	r->pos += TotalPushes(frames);
@@ -836,9 +848,24 @@ jplg_status jplg_renderer_push_ahead(jplg_renderer r, const float* in, uint32_t 
 	rp.numSC = r->numSC; rp.srcChannels = r->cfg.source_channels; rp.L = r->cfg.output_channels; rp.ringSize = r->ringSize; rp.ringMask = r->ringSize - 1;
 	rp.pos = r->pos; rp.frames = frames; rp.rings = r->rings; rp.in = in;
 	cudaStream_t side = ctx->aux[1];
+	// not before the render enqueued last has all its CTAs resident: the pushes then only take SMs that grid leaves free
+	if (r->startedRecorded) JPLG_CUDA_TRY(ctx, cudaStreamWaitEvent(side, r->evStarted, 0));
 	JPLG_LAUNCH_ON(ctx, JPLG_K_PUSH, side, LaunchPush(rp, 0, r->cfg.num_sources, side));
 	JPLG_CUDA_TRY(ctx, cudaEventRecord(r->evAhead, side));
 	r->aheadIn = in; r->aheadFrames = frames;
+	return JPLG_OK;
+}
+
+jplg_status jplg_renderer_wait_render_started(jplg_renderer r, jplg_context waiting)
+{
+	if (!r || !waiting) return JPLG_ERR_INVALID_ARGUMENT;
+	jplg_context ctx = r->ctx;
+	JPLG_NEED_DEVICE(ctx);
+	JPLG_NEED_DEVICE(waiting);
+	if (waiting->device != ctx->device) return Fail(waiting, JPLG_ERR_INVALID_ARGUMENT, "wait_render_started: contexts on different devices");
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	if (r->startedRecorded) JPLG_CUDA_TRY(waiting, cudaStreamWaitEvent(waiting->stream, r->evStarted, 0));
 	return JPLG_OK;
 }
 

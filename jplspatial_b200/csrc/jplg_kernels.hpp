@@ -83,7 +83,7 @@ namespace jplg
 	uint32_t TotalPushes(uint32_t frames); // ring pushes one block of `frames` causes (reference quirk, see k_push)
 	uint32_t RenderSourcesPerCTA(uint32_t srcChannels);
 	cudaError_t LaunchPush(const RenderParams& rp, uint32_t srcBegin, uint32_t srcCount, cudaStream_t st);
-	cudaError_t LaunchRender(const RenderParams& rp, int mode, uint32_t ctaBegin, uint32_t ctaCount, cudaStream_t st);
+	cudaError_t LaunchRender(const RenderParams& rp, int mode, uint32_t ctaBegin, uint32_t ctaCount, cudaStream_t st, cudaEvent_t started = nullptr);
 	// bus[frames][L] (+)= sum over CTAs of partial; also writes the plain sum to `deviceBus`
 	cudaError_t LaunchBusReduce(const RenderParams& rp, float* deviceBus, float* busAccumulate, cudaStream_t st);
 	cudaError_t LaunchStateTranspose(const float* in, float* out, uint32_t rows, uint32_t cols, cudaStream_t st);

@@ -372,3 +372,75 @@ def test_push_ahead_equals_plain_path():
     assert util.bits_equal(xa.cpu().numpy(), xb.cpu().numpy())
     ra.close(); rb.close()
     ctx.close()
+
+
+@pytest.mark.gpu
+def test_background_context_panning_one_block_ahead_equals_serial():
+    """jplg_context_create_ex(JPLG_CONTEXT_BACKGROUND): the panning data of block k+1 computed by a second, lower-priority context while block k
+    renders (the reference's game thread beside its audio thread), ordered with events, gives the buses of the serial order bit for bit."""
+    import torch
+    ctx = J.Context(0)
+    bg = J.Context(0, background=True)
+    N, C, L, blocks, frames = 2085, 1, 12, 6, 512
+    sc = make_scene(N, C, L, blocks, frames, util.SEED + 83)
+    params = np.stack([util.pan_params(N, util.SEED + 90 + b, edge=True) for b in range(blocks)])
+    dev = torch.device("cuda", 0)
+    stream, stream_bg = ctx.torch_stream(), bg.torch_stream()
+    pans = []
+    for c in (ctx, bg):
+        p = J.VBAPanner(c)
+        assert p.Initialize(J.ChannelMask.Surround_7_1_4)
+        pans.append((p, p.InitializeSourceLayout(J.ChannelMask.Mono)))
+    mix0 = pans[0][0].ProcessVBAPData(pans[0][1], params[0]).reshape(N, C, L)
+    assert util.bits_equal(pans[1][0].ProcessVBAPData(pans[1][1], params[0]).reshape(N, C, L), mix0)
+
+    def make():
+        return J.DirectSoundBatch(ctx, FS, N, C, L, sc["band"][0], sc["delay"][0], mix0, ring_size=0, max_block_frames=512, mode=J.MODE_PARITY)
+
+    ra, rb = make(), make()
+    with torch.cuda.stream(stream):
+        d_audio = [torch.from_numpy(sc["audio"][b]).to(dev) for b in range(blocks)]
+        d_params = torch.from_numpy(params).to(dev)
+        d_band = torch.from_numpy(sc["band"]).to(dev)
+        d_delay = torch.from_numpy(sc["delay"]).to(dev)
+        d_mix = torch.empty((N, C, L), dtype=torch.float32, device=dev)
+        d_mix2 = [torch.empty((N, C, L), dtype=torch.float32, device=dev) for _ in range(2)]
+        bus_a = [torch.zeros((frames, L), dtype=torch.float32, device=dev) for _ in range(blocks)]
+        bus_b = [torch.zeros((frames, L), dtype=torch.float32, device=dev) for _ in range(blocks)]
+    ctx.synchronize()
+    # serial: everything on the rendering context
+    for b in range(blocks):
+        pans[0][0].ProcessVBAPData(pans[0][1], d_params[b], out=d_mix)
+        ra.UpdateParameters(d_band[b + 1], d_delay[b + 1], d_mix)
+        ra.ProcessInterleaved(d_audio[b], bus_a[b], frames)
+    ctx.synchronize()
+    # pipelined: the background context works one block ahead into two mix-map buffers
+    ev_mdap = [torch.cuda.Event() for _ in range(2)]
+    ev_upd = torch.cuda.Event()
+
+    def issue(b, after_update):
+        with torch.cuda.stream(stream_bg):
+            if after_update:
+                stream_bg.wait_event(ev_upd)
+                rb.WaitRenderStarted(bg)
+            pans[1][0].ProcessVBAPData(pans[1][1], d_params[b], out=d_mix2[b & 1])
+            ev_mdap[b & 1].record(stream_bg)
+
+    issue(0, False)
+    for b in range(blocks):
+        with torch.cuda.stream(stream):
+            stream.wait_event(ev_mdap[b & 1])
+            rb.UpdateParameters(d_band[b + 1], d_delay[b + 1], d_mix2[b & 1])
+            ev_upd.record(stream)
+            rb.ProcessInterleaved(d_audio[b], bus_b[b], frames)
+        if b + 1 < blocks:
+            issue(b + 1, True)
+            rb.PushAhead(d_audio[b + 1], frames)
+    ctx.synchronize(); bg.synchronize()
+    for b in range(blocks):
+        assert np.abs(bus_a[b].cpu().numpy()).max() > 0
+        assert util.bits_equal(bus_b[b].cpu().numpy(), bus_a[b].cpu().numpy()), f"block {b}: pipelined panning differs"
+    del d_audio, d_params, d_band, d_delay, d_mix, d_mix2, bus_a, bus_b
+    ra.close(); rb.close()
+    del pans, p
+    bg.close(); ctx.close()
