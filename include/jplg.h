@@ -60,7 +60,10 @@ enum { JPLG_MEM_HOST = 0, JPLG_MEM_DEVICE = 1,
        /* PINNED host memory, asynchronous: the call enqueues its copies and kernels and returns without waiting; the buffers must stay
         * untouched until jplg_renderer_wait_block / jplg_context_synchronize. Accepted by jplg_panner_mdap(_oriented), jplg_renderer_update
         * and jplg_renderer_process_block (whose input transfer then runs on a copy stream into one of two staging buffers, so the PCIe
-        * transfer of block k+1 overlaps the render of block k). */
+        * transfer of block k+1 overlaps the render of block k). Page-locked buffers (cudaHostAlloc / cudaHostRegister) have a device alias
+        * under unified addressing: the small per-block arrays (pan parameters, band gains, delays, mix maps) and the bus are then read /
+        * accumulated by the kernels directly over PCIe, so they never queue behind the audio transfer on the copy engine. Pageable
+        * buffers are accepted and take staged copies (the driver then blocks the caller for their duration). */
        JPLG_MEM_HOST_ASYNC = 2 };
 
 /* Arithmetic mode of the render kernels.

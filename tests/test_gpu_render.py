@@ -298,18 +298,20 @@ def test_async_host_path_equals_sync_host_path():
         t = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
         return t, t.numpy()
 
-    rs, ra = make(), make()
+    rs, ra, rp = make(), make(), make()
     want = []
+    base_bus = (util.uniform01(frames * L, util.SEED + 501).reshape(frames, L) - 0.5).astype(np.float32)   # the bus is accumulated into, not overwritten
     for b in range(blocks):
         mix = pan.ProcessVBAPData(lay, params[b])
         rs.UpdateParameters(sc["band"][b + 1], sc["delay"][b + 1], mix)
-        bus = np.zeros((frames, L), np.float32)
+        bus = base_bus.copy()
         rs.ProcessInterleaved(sc["audio"][b], bus, frames)
         want.append(bus)
+    # page-locked buffers: the small arrays and the bus are read / written by the kernels through their device alias, only the audio is copied
     keep = [pin(x) for b in range(blocks) for x in (params[b], sc["band"][b + 1], sc["delay"][b + 1], sc["audio"][b])]
     h = [k[1] for k in keep]
     kmix, hmix = pin(np.zeros((N, 1, L), np.float32))
-    buses = [pin(np.zeros((frames, L), np.float32)) for _ in range(blocks)]
+    buses = [pin(base_bus.copy()) for _ in range(blocks)]
     for b in range(blocks):
         p, band, delay, audio = h[4 * b:4 * b + 4]
         pan.ProcessVBAPData(lay, p, out=hmix, async_host=True)
@@ -323,7 +325,18 @@ def test_async_host_path_equals_sync_host_path():
     for b in range(blocks):
         assert np.abs(want[b]).max() > 0
         assert util.bits_equal(buses[b][1], want[b]), f"block {b}: asynchronous host path differs from the synchronous one"
-    rs.close(); ra.close()
+    # pageable buffers: same call, staged copies instead of the alias
+    pmix = np.zeros((N, 1, L), np.float32)
+    pbuses = [base_bus.copy() for _ in range(blocks)]
+    for b in range(blocks):
+        pan.ProcessVBAPData(lay, params[b], out=pmix, async_host=True)
+        rp.UpdateParameters(sc["band"][b + 1], sc["delay"][b + 1], pmix, async_host=True)
+        rp.ProcessInterleaved(sc["audio"][b], pbuses[b], frames, async_host=True)
+        rp.WaitBlock()
+    ctx.synchronize()
+    for b in range(blocks):
+        assert util.bits_equal(pbuses[b], want[b]), f"block {b}: asynchronous path with pageable buffers differs"
+    rs.close(); ra.close(); rp.close()
     del pan, lay
     ctx.close()
 
