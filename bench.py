@@ -234,7 +234,7 @@ def main():
     ap.add_argument("--no-pan-overlap", action="store_true",
                     help="compute the panning data on the rendering context's stream instead of a background context (jplg_context_create_ex) "
                          "that works one block ahead on the SMs the render leaves free")
-    ap.add_argument("--bus", choices=["peer", "nccl"], default="peer",
+    ap.add_argument("--bus", choices=["peer", "nccl", "none"], default="peer",
                     help="multi-GPU combine of the partial buses: peer = jplg_bus_exchange (stores into the root GPU's memory over NVLink, rank-ordered sum), "
                          "nccl = torch.distributed reduce, double-buffered")
     args = ap.parse_args()
@@ -286,6 +286,8 @@ def main():
     use_peer = dist is not None and args.bus == "peer"
     # nccl mode: two bus buffers, the NCCL reduce of block k overlaps the render of block k+1
     reducer = PipelinedBusReduce(FRAMES, L_OUT, dev, depth=2, dst=0)
+    if args.bus == "none":
+        reducer.submit = lambda k: None     # diagnostic only: N independent replicas, no combine (the line's `config.parallelism` says so)
     exchange = make_peer_bus_exchange(ctx, FRAMES * L_OUT) if use_peer else None
     with torch.cuda.stream(stream):
         local_bus = torch.zeros((FRAMES, L_OUT), dtype=torch.float32, device=dev)
@@ -312,58 +314,56 @@ def main():
         mdap_issued = [-1]
 
         def issue_mdap(k, after_update):
-            with torch.cuda.stream(stream_pan):
-                if after_update:
-                    stream_pan.wait_event(ev_upd)      # the buffer's previous reader (update k-1) is older than this event
-                    rend.WaitRenderStarted(ctx_pan)    # ... and only once block k-1's render is resident: k_mdap_3d takes the SMs it leaves free
-                pan_bg.ProcessVBAPData(lay_bg, d_params[k % args.pool], out=d_mix_bg[k & 1])
-                ev_mdap[k & 1].record(stream_pan)
+            # (the library enqueues on its contexts' own streams whatever torch's current stream is: no stream context managers in the step)
+            if after_update:
+                stream_pan.wait_event(ev_upd)      # the buffer's previous reader (update k-1) is older than this event
+                rend.WaitRenderStarted(ctx_pan)    # ... and only once block k-1's render is resident: k_mdap_3d takes the SMs it leaves free
+            pan_bg.ProcessVBAPData(lay_bg, v_params[k % args.pool], out=d_mix_bg[k & 1])
+            ev_mdap[k & 1].record(stream_pan)
             mdap_issued[0] = k
 
         def join_pan():
             if mdap_issued[0] >= 0:
                 stream.wait_event(ev_mdap[mdap_issued[0] & 1])
 
+    # per-block views made once: the step itself is host-side plumbing and has to stay well under the 0.14 ms the device needs per block
+    v_params = [d_params[j] for j in range(args.pool)]
+    v_band = [d_band[j] for j in range(args.pool)]
+    v_delay = [d_delay[j] for j in range(args.pool)]
+    v_audio = [d_audio[j] for j in range(args.pool)]
+    bus_ptr, bus_floats = rend.device_bus_ptr(), FRAMES * L_OUT
+    peer_out = final_bus if rank == 0 else None
+
     def step_device(_k):
         k = gk[0]          # consecutive block numbers whatever the caller's phase, so the block pushed ahead is always the next one rendered
         gk[0] += 1
         j = k % args.pool
-        if pan_overlap and mdap_issued[0] != k:
-            issue_mdap(k, False)
-        with torch.cuda.stream(stream):
-            if pan_overlap:
-                stream.wait_event(ev_mdap[k & 1])
-                rend.UpdateParameters(d_band[j], d_delay[j], d_mix_bg[k & 1])
-                ev_upd.record(stream)
-            else:
-                pan.ProcessVBAPData(lay, d_params[j], out=d_mix)
-                rend.UpdateParameters(d_band[j], d_delay[j], d_mix)
-            if push_ahead:
-                # throughput rendering: block k+1's input is resident, so its ring pushes (an HBM-bound copy) are issued right after block k's render
-                # has been enqueued and run beside it on the SMs the render leaves free; block k only waits for the pushes issued one step earlier
-                if use_peer:
-                    rend.ProcessInterleaved(d_audio[j], local_bus, FRAMES)
-                    exchange.submit(rend.device_bus_ptr(), FRAMES * L_OUT, seq[0], out=final_bus if rank == 0 else None)
-                    seq[0] += 1
-                else:
-                    bus = reducer.begin(k)
-                    rend.ProcessInterleaved(d_audio[j], bus, FRAMES)
-                    reducer.submit(k)
-                if pan_overlap:
-                    issue_mdap(k + 1, True)
-                rend.PushAhead(d_audio[(k + 1) % args.pool], FRAMES)
-            elif use_peer:
-                # every rank's k_bus_reduce result goes straight into the root GPU's gather buffer (peer stores over NVLink); the root adds the
-                # slots in rank order. No collective library on the data path.
-                rend.ProcessInterleaved(d_audio[j], local_bus, FRAMES)
-                exchange.submit(rend.device_bus_ptr(), FRAMES * L_OUT, seq[0], out=final_bus if rank == 0 else None)
-                seq[0] += 1
-            else:
+        if pan_overlap:
+            if mdap_issued[0] != k:
+                issue_mdap(k, False)
+            stream.wait_event(ev_mdap[k & 1])
+            rend.UpdateParameters(v_band[j], v_delay[j], d_mix_bg[k & 1])
+            ev_upd.record(stream)
+        else:
+            pan.ProcessVBAPData(lay, v_params[j], out=d_mix)
+            rend.UpdateParameters(v_band[j], v_delay[j], d_mix)
+        if use_peer:
+            # every rank's k_bus_reduce result goes straight into the root GPU's gather buffer (peer stores over NVLink); the root adds the
+            # slots in rank order. No collective library on the data path.
+            rend.ProcessInterleaved(v_audio[j], local_bus, FRAMES)
+            exchange.submit(bus_ptr, bus_floats, seq[0], out=peer_out)
+            seq[0] += 1
+        else:
+            with torch.cuda.stream(stream):       # torch ops (the bus zero-fill, NCCL's stream ordering) follow torch's current stream
                 bus = reducer.begin(k)
-                rend.ProcessInterleaved(d_audio[j], bus, FRAMES)
+                rend.ProcessInterleaved(v_audio[j], bus, FRAMES)
                 reducer.submit(k)
-            if pan_overlap and not push_ahead:
-                issue_mdap(k + 1, True)
+        if pan_overlap:
+            issue_mdap(k + 1, True)
+        if push_ahead:
+            # throughput rendering: block k+1's input is resident, so its ring pushes (an HBM-bound copy) are issued right after block k's render
+            # has been enqueued and run beside it on the SMs the render leaves free; block k only waits for the pushes issued one step earlier
+            rend.PushAhead(v_audio[(k + 1) % args.pool], FRAMES)
 
     def barrier():
         with torch.cuda.stream(stream):
@@ -392,8 +392,10 @@ def main():
     barrier()
     with torch.cuda.stream(stream):
         ev0.record(stream)
+    t_host0 = time.perf_counter()
     for k in range(args.steps):
         step_device(args.warmup + k)
+    host_ms_step = (time.perf_counter() - t_host0) * 1e3 / args.steps     # host time to enqueue a step: must stay below the device's step time
     with torch.cuda.stream(stream):
         if pan_overlap:
             join_pan()               # the panning data computed one block ahead by the last step is inside the timed region too
@@ -426,7 +428,11 @@ def main():
         breakdown["mdap"] = ctx_pan.kernel_time("mdap")
         ctx_pan.set_kernel_timing(False)
     t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    per_rank_ms = [ms_total / args.steps]
     if dist is not None:
+        allt = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(allt, t)
+        per_rank_ms = [float(x.item()) / args.steps for x in allt]
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_step = float(t.item()) / args.steps
     value = N * world * BLOCK_S / (ms_step * 1e-3)
@@ -562,8 +568,8 @@ def main():
                                           "are produced on lower-priority streams while block k renders"},
                    "l2_policy": f"inputs larger than L2: {args.pool} distinct 33.5 MB input blocks cycled, {N * rend.ring_size * 4 / 2**30:.1f} GiB of rings",
                    "parallelism": (f"sources sharded over {world} GPU(s); partial [512x12] buses stored into the root GPU's gather buffer over NVLink peer memory and summed in rank order (jplg_bus_exchange, no collective library on the data path)"
-                                   if use_peer else f"sources sharded over {world} GPU(s); NCCL reduce of the [512x12] bus, double-buffered (block k reduce overlaps block k+1 render)") if world > 1 else "single GPU"},
-        "bus_crc32": f"{bus_crc:08x}", "clocks": clocks, "gpu_launches": launches, "e2e": e2e, "roofline": roofline, "cpu_baseline": cpu,
+                                   if use_peer else "DIAGNOSTIC: independent replicas, buses NOT combined" if args.bus == "none" else f"sources sharded over {world} GPU(s); NCCL reduce of the [512x12] bus, double-buffered (block k reduce overlaps block k+1 render)") if world > 1 else "single GPU"},
+        "per_rank_ms_per_step": [round(x, 5) for x in per_rank_ms], "host_enqueue_ms_per_step": round(host_ms_step, 5), "bus_crc32": f"{bus_crc:08x}", "clocks": clocks, "gpu_launches": launches, "e2e": e2e, "roofline": roofline, "cpu_baseline": cpu,
     }
     _emit(line)
     if dist is not None:

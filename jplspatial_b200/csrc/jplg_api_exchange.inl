@@ -17,7 +17,12 @@ struct jplg_bus_exchange_t
 static jplg_status ExchangeSideInit(jplg_bus_exchange x)
 {
 	jplg_context ctx = x->ctx;
-	JPLG_CUDA_TRY(ctx, cudaStreamCreateWithFlags(&x->side, cudaStreamNonBlocking));
+	{
+		// highest priority: the exchange kernels are tiny and latency-bound, they should take the first free slot
+		int prioLeast = 0, prioGreatest = 0;
+		JPLG_CUDA_TRY(ctx, cudaDeviceGetStreamPriorityRange(&prioLeast, &prioGreatest));
+		JPLG_CUDA_TRY(ctx, cudaStreamCreateWithPriority(&x->side, cudaStreamNonBlocking, prioGreatest));
+	}
 	JPLG_CUDA_TRY(ctx, cudaMalloc(reinterpret_cast<void**>(&x->staging), size_t(2) * x->maxFloats * sizeof(float)));
 	for (int i = 0; i < 2; ++i)
 	{

@@ -28,8 +28,10 @@ namespace jplg
 	}
 	constexpr long long kSpinLimitCycles = 4000000000ll;   // ~2 s at 1.965 GHz
 
-	// non-root rank: one CTA. Wait until the root has consumed block seq-2 (the previous user of this slot), store the bus, publish.
-	__global__ void __launch_bounds__(1024) k_bus_send(ExchangeHeader* __restrict__ hdr, float* __restrict__ slotData, const float* __restrict__ bus,
+	// non-root rank: one small CTA (128 threads x 32 registers: it has to fit beside the CTAs of the next block's panning / push kernels, which fill
+	// whatever the render grid leaves free — a 1,024-thread CTA needed half an SM's register file and waited a whole block for it at 8 GPUs).
+	// Wait until the root has consumed block seq-2 (the previous user of this slot), store the bus, publish.
+	__global__ void __launch_bounds__(128) k_bus_send(ExchangeHeader* __restrict__ hdr, float* __restrict__ slotData, const float* __restrict__ bus,
 													   uint32_t n, uint32_t rank, unsigned long long seq)
 	{
 		__shared__ int ok;
@@ -52,7 +54,7 @@ namespace jplg
 	}
 
 	// root: wait for every peer's block `seq`, out (+)= own + slots in rank order, then acknowledge (last CTA).
-	__global__ void __launch_bounds__(256) k_bus_gather(ExchangeHeader* __restrict__ hdr, const float* __restrict__ data, uint32_t world, uint32_t maxFloats,
+	__global__ void __launch_bounds__(128) k_bus_gather(ExchangeHeader* __restrict__ hdr, const float* __restrict__ data, uint32_t world, uint32_t maxFloats,
 														const float* __restrict__ own, uint32_t n, unsigned long long seq, float* __restrict__ out, int accumulate)
 	{
 		if (threadIdx.x > 0 && threadIdx.x < world)
@@ -63,10 +65,28 @@ namespace jplg
 		}
 		__syncthreads();
 		const float* slots = data + size_t(seq & 1ull) * world * maxFloats;
-		for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
+		// All of a thread's slot loads are issued before the first add: they bypass the caches (written by peer GPUs), and as a load-add-load-add
+		// chain their latencies added up to a gather as long as the block itself at 8 GPUs (7 x 8 dependent loads per thread, ~3 us each beside a
+		// running render), which made the root the slowest rank. The sum itself stays in rank order.
+		const uint32_t n4 = ((reinterpret_cast<uintptr_t>(own) | reinterpret_cast<uintptr_t>(out) | reinterpret_cast<uintptr_t>(slots)) & 15u) == 0 && (maxFloats & 3u) == 0 ? n / 4 : 0;
+		for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += gridDim.x * blockDim.x)
+		{
+			float4 v[kMaxWorld];
+			#pragma unroll
+			for (uint32_t r = 1; r < kMaxWorld; ++r)
+				if (r < world) v[r] = __ldcv(reinterpret_cast<const float4*>(slots + size_t(r) * maxFloats) + i);
+			float4 acc = reinterpret_cast<const float4*>(own)[i];
+			#pragma unroll
+			for (uint32_t r = 1; r < kMaxWorld; ++r)
+				if (r < world) { acc.x += v[r].x; acc.y += v[r].y; acc.z += v[r].z; acc.w += v[r].w; }
+			float4* o4 = reinterpret_cast<float4*>(out) + i;
+			if (accumulate) { const float4 o = *o4; acc.x = o.x + acc.x; acc.y = o.y + acc.y; acc.z = o.z + acc.z; acc.w = o.w + acc.w; }
+			*o4 = acc;
+		}
+		for (uint32_t i = n4 * 4 + blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x)
 		{
 			float acc = own[i];
-			for (uint32_t r = 1; r < world; ++r) acc += __ldcv(slots + size_t(r) * maxFloats + i);   // written by a peer GPU: bypass stale lines
+			for (uint32_t r = 1; r < world; ++r) acc += __ldcv(slots + size_t(r) * maxFloats + i);
 			out[i] = accumulate ? out[i] + acc : acc;
 		}
 		__threadfence();
@@ -84,14 +104,14 @@ namespace jplg
 
 	cudaError_t LaunchBusSend(ExchangeHeader* hdr, float* slotData, const float* bus, uint32_t n, uint32_t rank, uint64_t seq, cudaStream_t st)
 	{
-		k_bus_send<<<1, 1024, 0, st>>>(hdr, slotData, bus, n, rank, seq);
+		k_bus_send<<<1, 128, 0, st>>>(hdr, slotData, bus, n, rank, seq);
 		return cudaGetLastError();
 	}
 	cudaError_t LaunchBusGather(ExchangeHeader* hdr, const float* data, uint32_t world, uint32_t maxFloats, const float* own, uint32_t n, uint64_t seq,
 								float* out, int accumulate, cudaStream_t st)
 	{
-		const uint32_t grid = (n + 1023) / 1024 ? (n + 1023) / 1024 : 1;
-		k_bus_gather<<<grid, 256, 0, st>>>(hdr, data, world, maxFloats, own, n, seq, out, accumulate);
+		const uint32_t grid = (n + 511) / 512 ? (n + 511) / 512 : 1;      // one float4 per thread
+		k_bus_gather<<<grid, 128, 0, st>>>(hdr, data, world, maxFloats, own, n, seq, out, accumulate);
 		return cudaGetLastError();
 	}
 }
