@@ -200,6 +200,32 @@ def cpu_baseline_sample(log_fn):
 _JSON_OUT = None
 
 
+def bind_to_gpu_numa_node(torch, local_rank):
+    """Run this rank (and first-touch its pinned buffers) on the NUMA node its GPU hangs off: with one rank per GPU on a two-socket box the host side of
+    eight concurrent 33.5 MB-per-block input streams otherwise crosses the socket interconnect. Returns the node, or None when the box does not expose one."""
+    try:
+        pr = torch.cuda.get_device_properties(local_rank)
+        bdf = f"{pr.pci_domain_id:04x}:{pr.pci_bus_id:02x}:{pr.pci_device_id:02x}.0"
+        node = int(open(f"/sys/bus/pci/devices/{bdf}/numa_node").read().strip())
+        if node < 0:
+            return None
+        cpus = set()
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            if "-" in part:
+                a, b = part.split("-")
+                cpus |= set(range(int(a), int(b) + 1))
+            elif part:
+                cpus.add(int(part))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return node
+    except Exception as e:          # purely an optimisation
+        log(f"[bench] NUMA binding skipped: {e}")
+        return None
+
+
 def _claim_stdout():
     """The driver reads ONE JSON line from stdout: keep a private handle to the real stdout for it and point fd 1 at stderr for everything else
     (NCCL prints its version banner to stdout on the rank that initialises first)."""
@@ -255,6 +281,7 @@ def main():
     if not torch.cuda.is_available() or J.device_count() == 0:
         raise SystemExit("bench.py: no CUDA device — this framework has no CPU fallback (use --impl reference for the CPU reference arm)")
     torch.cuda.set_device(local_rank)
+    numa_node = bind_to_gpu_numa_node(torch, local_rank)
     dist = None
     if world > 1:
         import torch.distributed as dist_mod
@@ -456,6 +483,16 @@ def main():
         # stream while block k-1 renders) and then block k-1 is collected; every step still moves its own inputs H2D and its own bus D2H
         tb, h_bus2 = pinned(np.zeros((FRAMES, L_OUT), np.float32)); keep.append(tb)
         h_buses = (h_bus, h_bus2)
+        if use_peer:
+            with torch.cuda.stream(stream):
+                d_final2 = [torch.zeros((FRAMES, L_OUT), dtype=torch.float32, device=dev) for _ in range(2)]
+            t_final, h_final = [], []
+            for _ in range(2):
+                tt, nn = pinned(np.zeros((FRAMES, L_OUT), np.float32)); t_final.append(tt); h_final.append(nn)
+            ev_final = [torch.cuda.Event() for _ in range(2)]
+            ev_read = [torch.cuda.Event() for _ in range(2)]
+            rd_stream = torch.cuda.Stream(device=dev)
+            ctx.synchronize()
 
         def submit_host(k):
             j = k % args.pool
@@ -464,11 +501,29 @@ def main():
             rend.UpdateParameters(h_band[j], h_delay[j], h_mix, async_host=True)        # H2D
             hb[:] = 0.0
             rend.ProcessInterleaved(h_audio[j], hb, FRAMES, async_host=True)            # H2D audio (copy stream) + bus, D2H bus
+            if use_peer:
+                # N > 1: the partial buses are combined on the device (peer-memory exchange, as in the device-resident pass) and the root reads the
+                # combined bus back; the other ranks' own partial buses still travel D2H with their blocks
+                exchange.submit(bus_ptr, bus_floats, seq[0], out=d_final2[k & 1] if rank == 0 else None)
+                seq[0] += 1
+                if rank == 0:
+                    exchange.wait()
+                    ev_final[k & 1].record(stream)
+                    # read-back on a torch-owned stream (torch's pinned-memory allocator remembers the streams a pinned block was used on, and the
+                    # library's stream dies with its context)
+                    rd_stream.wait_event(ev_final[k & 1])
+                    with torch.cuda.stream(rd_stream):
+                        t_final[k & 1].copy_(d_final2[k & 1], non_blocking=True)
+                        ev_read[k & 1].record(rd_stream)
 
         def collect_host(k):
             rend.WaitBlock()
             hb = h_buses[k & 1]
-            if dist is not None:
+            if use_peer:
+                if rank == 0:
+                    ev_read[k & 1].synchronize()
+                    return float(h_final[k & 1][0, 0])
+            elif dist is not None:
                 d_partial.copy_(torch.from_numpy(hb))
                 dist.reduce(d_partial, dst=0)
                 if rank == 0:
@@ -498,10 +553,11 @@ def main():
             dist.all_reduce(tt2, op=dist.ReduceOp.MAX)
         dt = float(tt2.item())
         h2d = N * FRAMES * 4 + N * 20 + N * 16 + N * 4 + N * L_OUT * 4 + FRAMES * L_OUT * 4
-        d2h = N * L_OUT * 4 + FRAMES * L_OUT * 4
+        d2h = N * L_OUT * 4 + FRAMES * L_OUT * 4 + (FRAMES * L_OUT * 4 if use_peer else 0)     # per rank; the last term is the root's combined bus
         e2e = {"value": N * world * BLOCK_S / dt, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                "ms_per_step": dt * 1e3, "steps": e2e_steps,
-               "path": "C ABI with pinned HOST buffers, JPLG_MEM_HOST_ASYNC: block k+1's input transfer overlaps block k's render (2 blocks in flight); the audio goes through the copy engine, the small arrays and the bus are read / written by the kernels through the buffers' device alias (same bytes over PCIe)"}
+               "path": "C ABI with pinned HOST buffers, JPLG_MEM_HOST_ASYNC: block k+1's input transfer overlaps block k's render (2 blocks in flight); the audio goes through the copy engine, the small arrays and the bus are read / written by the kernels through the buffers' device alias (same bytes over PCIe)"
+                       + ("; N > 1: partial buses combined on the device by the peer-memory exchange, the root reads the combined bus back" if use_peer else "")}
 
     # a short run (--no-e2e, few steps) can end before nvidia-smi has delivered its first line: keep the GPU under the same load until it has
     # (every rank takes the same decision: the steps contain the bus exchange)
@@ -563,6 +619,7 @@ def main():
         "config": {"workload": "BASELINE config 3: full block render, 16,384 mono sources per GPU -> 7.1.4, 48 kHz / 512 frames "
                                "(MDAP gains + update + push + fused delay/LR4/mix + bus reduce per block)",
                    "sources_per_gpu": N, "total_sources": N * world, "mode": args.mode, "ring_size": rend.ring_size,
+                   "host_numa_node": numa_node,
                    "pipelining": {"push_ahead": push_ahead, "pan_overlap": pan_overlap,
                                   "note": "every step runs all five kernels once; with push_ahead / pan_overlap block k+1's ring pushes / panning data "
                                           "are produced on lower-priority streams while block k renders"},
