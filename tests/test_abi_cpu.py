@@ -54,6 +54,31 @@ def test_library_is_sm100a_and_has_no_cpu_fallback(J, host_ctx):
         pan.ProcessVBAPData(lay, np.float32([[0, 0, -1, 0.5, 0.5]]))
 
 
+def test_background_context_flag(J):
+    """jplg_context_create_ex: flags = 0 is jplg_context_create, JPLG_CONTEXT_BACKGROUND is accepted (host-only contexts have no stream to
+    prioritise), anything else is rejected; jplg_renderer_wait_render_started checks its arguments."""
+    lib = C.CDLL(J.lib_path)
+    lib.jplg_context_create_ex.restype = C.c_int32
+    lib.jplg_context_create_ex.argtypes = [C.c_int32, C.c_uint32, C.POINTER(C.c_void_p)]
+    for flags, want in ((0, 0), (1, 0), (2, 1), (0x80000001, 1)):
+        h = C.c_void_p()
+        st = lib.jplg_context_create_ex(-1, flags, C.byref(h))
+        assert st == want, (flags, st)                       # 1 = JPLG_ERR_INVALID_ARGUMENT
+        if st == 0:
+            lib.jplg_context_destroy.argtypes = [C.c_void_p]
+            lib.jplg_context_destroy(h)
+        else:
+            assert not h.value
+    bg = J.Context(-1, background=True)
+    pan = J.VBAPanner(bg)
+    assert pan.Initialize(J.ChannelMask.Quad)                # host builders work on a background context too
+    lib.jplg_renderer_wait_render_started.restype = C.c_int32
+    lib.jplg_renderer_wait_render_started.argtypes = [C.c_void_p, C.c_void_p]
+    assert lib.jplg_renderer_wait_render_started(None, bg.h) == 1
+    del pan
+    bg.close()
+
+
 def test_channel_map_helpers(J):
     """inc/ChannelMap.h:153-249"""
     M, E = J.ChannelMask, J.EChannel
