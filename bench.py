@@ -260,6 +260,8 @@ def main():
     ap.add_argument("--no-pan-overlap", action="store_true",
                     help="compute the panning data on the rendering context's stream instead of a background context (jplg_context_create_ex) "
                          "that works one block ahead on the SMs the render leaves free")
+    ap.add_argument("--no-fused-update", action="store_true",
+                    help="jplg_panner_mdap + jplg_renderer_update as two launches with the mix maps in between, instead of jplg_renderer_update_panned")
     ap.add_argument("--bus", choices=["peer", "nccl", "none"], default="peer",
                     help="multi-GPU combine of the partial buses: peer = jplg_bus_exchange (stores into the root GPU's memory over NVLink, rank-ordered sum), "
                          "nccl = torch.distributed reduce, double-buffered")
@@ -327,6 +329,7 @@ def main():
     # computed by a background context while block k renders; its stream has the lower priority, so k_render's 128 CTAs are placed first and
     # k_mdap_3d fills the remaining SMs. Two mix-map buffers; events order the two streams.
     pan_overlap = not args.no_pan_overlap
+    fused_update = not args.no_fused_update       # panning kernel writes the renderer's next target set itself (jplg_renderer_update_panned)
     if pan_overlap:
         ctx_pan = J.Context(local_rank, background=True)
         stream_pan = ctx_pan.torch_stream()
@@ -342,10 +345,15 @@ def main():
 
         def issue_mdap(k, after_update):
             # (the library enqueues on its contexts' own streams whatever torch's current stream is: no stream context managers in the step)
+            j = k % args.pool
             if after_update:
-                stream_pan.wait_event(ev_upd)      # the buffer's previous reader (update k-1) is older than this event
-                rend.WaitRenderStarted(ctx_pan)    # ... and only once block k-1's render is resident: k_mdap_3d takes the SMs it leaves free
-            pan_bg.ProcessVBAPData(lay_bg, v_params[k % args.pool], out=d_mix_bg[k & 1])
+                if not fused_update:
+                    stream_pan.wait_event(ev_upd)  # the buffer's previous reader (update k-1) is older than this event
+                rend.WaitRenderStarted(ctx_pan)    # only once block k-1's render is resident: k_mdap_3d takes the SMs it leaves free
+            if fused_update:
+                rend.UpdatePanned(pan_bg, lay_bg, v_params[j], v_band[j], v_delay[j])      # the library orders it against the renders itself
+            else:
+                pan_bg.ProcessVBAPData(lay_bg, v_params[j], out=d_mix_bg[k & 1])
             ev_mdap[k & 1].record(stream_pan)
             mdap_issued[0] = k
 
@@ -368,9 +376,12 @@ def main():
         if pan_overlap:
             if mdap_issued[0] != k:
                 issue_mdap(k, False)
-            stream.wait_event(ev_mdap[k & 1])
-            rend.UpdateParameters(v_band[j], v_delay[j], d_mix_bg[k & 1])
-            ev_upd.record(stream)
+            if not fused_update:
+                stream.wait_event(ev_mdap[k & 1])
+                rend.UpdateParameters(v_band[j], v_delay[j], d_mix_bg[k & 1])
+                ev_upd.record(stream)
+        elif fused_update:
+            rend.UpdatePanned(pan, lay, v_params[j], v_band[j], v_delay[j])
         else:
             pan.ProcessVBAPData(lay, v_params[j], out=d_mix)
             rend.UpdateParameters(v_band[j], v_delay[j], d_mix)
@@ -385,12 +396,12 @@ def main():
                 bus = reducer.begin(k)
                 rend.ProcessInterleaved(v_audio[j], bus, FRAMES)
                 reducer.submit(k)
-        if pan_overlap:
-            issue_mdap(k + 1, True)
         if push_ahead:
             # throughput rendering: block k+1's input is resident, so its ring pushes (an HBM-bound copy) are issued right after block k's render
             # has been enqueued and run beside it on the SMs the render leaves free; block k only waits for the pushes issued one step earlier
             rend.PushAhead(v_audio[(k + 1) % args.pool], FRAMES)
+        if pan_overlap:
+            issue_mdap(k + 1, True)
 
     def barrier():
         with torch.cuda.stream(stream):
@@ -620,7 +631,7 @@ def main():
                                "(MDAP gains + update + push + fused delay/LR4/mix + bus reduce per block)",
                    "sources_per_gpu": N, "total_sources": N * world, "mode": args.mode, "ring_size": rend.ring_size,
                    "host_numa_node": numa_node,
-                   "pipelining": {"push_ahead": push_ahead, "pan_overlap": pan_overlap,
+                   "pipelining": {"push_ahead": push_ahead, "pan_overlap": pan_overlap, "fused_update": fused_update,
                                   "note": "every step runs all five kernels once; with push_ahead / pan_overlap block k+1's ring pushes / panning data "
                                           "are produced on lower-priority streams while block k renders"},
                    "l2_policy": f"inputs larger than L2: {args.pool} distinct 33.5 MB input blocks cycled, {N * rend.ring_size * 4 / 2**30:.1f} GiB of rings",

@@ -222,6 +222,15 @@ JPLG_API jplg_status jplg_renderer_update(jplg_renderer r, const float* band_gai
  * in : [N][frames][C] (each source's block is interleaved exactly as the reference's `input` span)
  * bus: [frames][L] interleaved, ACCUMULATED INTO like the reference's `output` span; all N sources add
  *      into the same bus (the host loop "for each effect: ProcessInterleaved(in_i, bus)"). */
+/* jplg_panner_mdap + jplg_renderer_update in one launch, for sources whose pan parameters change every block (replaces the pair
+ * VBAPanner::ProcessVBAPData, inc/Panning/PannerBase.h:315 -> DirectSoundEffect::UpdateParameters, src/Auralization/DirectSound.cpp:231-239, per
+ * source): pan_params [N][5], band_gains [N][4], delay_seconds [N], all JPLG_MEM_DEVICE. The mix maps never leave the device: the panning kernel
+ * writes them, the band gains and the delays straight into the renderer's NEXT set of targets, which the next jplg_renderer_process_block adopts
+ * (it waits for them on the device). The work is enqueued on the PANNER's context stream — with a JPLG_CONTEXT_BACKGROUND panner context it runs
+ * while the renderer's context still renders the previous block, which keeps reading the current targets. Same values, bit for bit, as the two
+ * separate calls. 3D panners; the layout's channel count must be the renderer's source_channels and the panner's channel count its output_channels. */
+JPLG_API jplg_status jplg_renderer_update_panned(jplg_renderer r, jplg_panner p, jplg_source_layout l, const float* pan_params,
+                                                 const float* band_gains, const float* delay_seconds, int32_t mem);
 JPLG_API jplg_status jplg_renderer_process_block(jplg_renderer r, const float* in, float* bus, uint32_t frames, int32_t mem);
 /* Offline / throughput rendering: issues the ring pushes of the NEXT block (device pointer `in`, already resident) on a side stream, so that
  * they overlap the render of the block enqueued before this call: the copy is HBM-bound and runs on the SMs the render leaves free. The two

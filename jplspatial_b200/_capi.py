@@ -78,6 +78,7 @@ _sig("jplg_renderer_update", _i32, [_vp, _fp, _fp, _fp, _i32])
 _sig("jplg_renderer_process_block", _i32, [_vp, _fp, _fp, _u32, _i32])
 _sig("jplg_renderer_process_block_debug", _i32, [_vp, _fp, _fp, _fp, _u32, _i32])
 _sig("jplg_renderer_wait_block", _i32, [_vp])
+_sig("jplg_renderer_update_panned", _i32, [_vp, _vp, _vp, _vp, _vp, _vp, _i32])
 _sig("jplg_renderer_push_ahead", _i32, [_vp, _fp, _u32])
 _sig("jplg_renderer_wait_render_started", _i32, [_vp, _vp])
 _sig("jplg_renderer_device_bus", _vp, [_vp])
@@ -456,6 +457,13 @@ class DirectSoundBatch:
         assert len(mems) <= 1, "all update arrays must live in the same memory space"
         mem = mems.pop() if mems else MEM_HOST
         self.ctx.check(lib.jplg_renderer_update(self.h, b, d, m, MEM_HOST_ASYNC if (async_host and mem == MEM_HOST) else mem))
+
+    def UpdatePanned(self, panner, layout, pan_params, band_gains, delay_seconds):
+        """ProcessVBAPData + UpdateParameters fused on the device (jplg_renderer_update_panned): CUDA tensors; enqueued on the panner's context stream,
+        adopted by the next ProcessInterleaved."""
+        pp, m0, _ = _arg(pan_params); bb, m1, _ = _arg(band_gains); dd, m2, _ = _arg(delay_seconds)
+        assert m0 == m1 == m2 == MEM_DEVICE
+        panner.ctx.check(lib.jplg_renderer_update_panned(self.h, panner.h, layout.h, pp, bb, dd, MEM_DEVICE))
 
     def WaitRenderStarted(self, waiting_ctx):
         """`waiting_ctx`'s stream waits until the k_render enqueued last is fully resident (jplg_renderer_wait_render_started)."""

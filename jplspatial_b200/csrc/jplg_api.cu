@@ -543,6 +543,12 @@ struct jplg_renderer_t
 	cudaEvent_t evAhead = nullptr;
 	cudaEvent_t evStarted = nullptr;   // launch-completion event of the last whole-grid k_render: fires when all its CTAs are resident
 	bool startedRecorded = false;
+	// jplg_renderer_update_panned: a second set of target arrays, written (possibly by another context's stream) while the render of the
+	// current block still reads the active set; the next process_block swaps the sets. evSetFree[id] = the last render that read set id is done.
+	float *tgt2Delay = nullptr, *tgt2Band = nullptr, *tgt2Mix = nullptr;
+	int activeSet = 0;
+	bool pendingPanned = false, setFreeRecorded[2] = { false, false };
+	cudaEvent_t evUpdated = nullptr, evSetFree[2] = {};
 };
 
 // targets in the reference's layouts -> SoA per source-channel (UpdateParameters, src/Auralization/DirectSound.cpp:231-239)
@@ -602,6 +608,9 @@ static void FreeRenderer(jplg_renderer r)
 		r->asyncReady = false;
 	}
 	if (r->evStarted) { cudaEventDestroy(r->evStarted); r->evStarted = nullptr; }
+	if (r->evUpdated) { cudaEventDestroy(r->evUpdated); r->evUpdated = nullptr; }
+	for (auto& e : r->evSetFree) if (e) { cudaEventDestroy(e); e = nullptr; }
+	for (float** q : { &r->tgt2Delay, &r->tgt2Band, &r->tgt2Mix }) if (*q) { cudaFree(*q); *q = nullptr; }
 	if (r->evAhead) { if (r->ctx->auxReady) cudaStreamSynchronize(r->ctx->aux[1]); cudaEventDestroy(r->evAhead); r->evAhead = nullptr; }
 }
 
@@ -619,8 +628,15 @@ static jplg_status RendererUpdateLocked(jplg_renderer r, const float* band, cons
 		if (delay) { if (tryAlias && (al = MappedHostAlias(delay))) dDelay = al; else { JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(base + size_t(N) * 4, delay, size_t(N) * 4, cudaMemcpyHostToDevice, ctx->stream)); dDelay = base + size_t(N) * 4; } }
 		if (mix) { if (tryAlias && (al = MappedHostAlias(mix))) dMix = al; else { JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(base + size_t(N) * 5, mix, size_t(N) * C * L * 4, cudaMemcpyHostToDevice, ctx->stream)); dMix = base + size_t(N) * 5; } }
 	}
+	float *wBand = r->tgtBand, *wDelay = r->tgtDelay, *wMix = r->tgtMix;
+	if (r->pendingPanned)
+	{
+		// the next block will use the set jplg_renderer_update_panned has written: this update refines that one, after it
+		JPLG_CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, r->evUpdated, 0));
+		wBand = r->tgt2Band; wDelay = r->tgt2Delay; wMix = r->tgt2Mix;
+	}
 	TimeBegin(ctx, JPLG_K_UPDATE);
-	k_update_targets<<<(r->numSC + 127) / 128, 128, 0, ctx->stream>>>(dBand, dDelay, dMix, r->numSC, C, L, r->cfg.sample_rate, r->tgtBand, r->tgtDelay, r->tgtMix);
+	k_update_targets<<<(r->numSC + 127) / 128, 128, 0, ctx->stream>>>(dBand, dDelay, dMix, r->numSC, C, L, r->cfg.sample_rate, wBand, wDelay, wMix);
 	TimeEnd(ctx);
 	JPLG_CUDA_TRY(ctx, cudaGetLastError()); ctx->launches++;
 	if (mem == JPLG_MEM_HOST) JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream)); // host buffers are caller-owned: safe to reuse on return
@@ -696,10 +712,55 @@ jplg_status jplg_renderer_update(jplg_renderer r, const float* band_gains, const
 	return RendererUpdateLocked(r, band_gains, delay_seconds, mix_maps, mem);
 }
 
+jplg_status jplg_renderer_update_panned(jplg_renderer r, jplg_panner p, jplg_source_layout l, const float* pan_params, const float* band_gains,
+										const float* delay_seconds, int32_t mem)
+{
+	if (!r || !p || !l || l->panner != p || !pan_params || !band_gains || !delay_seconds) return JPLG_ERR_INVALID_ARGUMENT;
+	if (mem != JPLG_MEM_DEVICE) return JPLG_ERR_INVALID_ARGUMENT;       // a device-side fusion: host callers use jplg_panner_mdap + jplg_renderer_update
+	jplg_context rc = r->ctx, ctx = p->ctx;                             // the work runs on the PANNER's context stream
+	JPLG_NEED_DEVICE(rc);
+	JPLG_NEED_DEVICE(ctx);
+	if (rc->device != ctx->device) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "update_panned: panner and renderer on different devices");
+	if (!p->host.is3D) return Fail(ctx, JPLG_ERR_UNSUPPORTED, "update_panned: 3D panners only (use jplg_panner_mdap + jplg_renderer_update)");
+	if (l->host.numChannels != r->cfg.source_channels || p->host.numChannels != r->cfg.output_channels)
+		return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "update_panned: source layout / panner channel counts do not match the renderer");
+	std::unique_lock<std::mutex> lkA(rc->mtx, std::defer_lock), lkB(ctx->mtx, std::defer_lock);
+	if (rc == ctx) lkA.lock(); else std::lock(lkA, lkB);
+	cudaSetDevice(ctx->device);
+	const uint32_t N = r->cfg.num_sources, L = r->cfg.output_channels;
+	const size_t nsc = r->numSC;
+	if (!r->tgt2Mix)
+	{
+		if (cudaMalloc(reinterpret_cast<void**>(&r->tgt2Delay), nsc * 4) != cudaSuccess || cudaMalloc(reinterpret_cast<void**>(&r->tgt2Band), nsc * 16) != cudaSuccess
+			|| cudaMalloc(reinterpret_cast<void**>(&r->tgt2Mix), nsc * L * 4) != cudaSuccess)
+		{ cudaGetLastError(); return Fail(ctx, JPLG_ERR_OUT_OF_MEMORY, "update_panned: target set allocation failed"); }
+		JPLG_CUDA_TRY(ctx, cudaEventCreateWithFlags(&r->evUpdated, cudaEventDisableTiming));
+		for (auto& e : r->evSetFree) JPLG_CUDA_TRY(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+	}
+	const int w = r->activeSet ^ 1;
+	// the render that last read the set about to be overwritten (two blocks back) has to be done; the one reading the active set may still run
+	if (r->setFreeRecorded[w]) JPLG_CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, r->evSetFree[w], 0));
+	void* scratch = nullptr;
+	jplg_status st = Scratch(ctx, 1, size_t(N) * l->host.numChannels * L * 4, &scratch); if (st) return st;
+	MdapFuse fz;
+	fz.tgtMix = r->tgt2Mix; fz.tgtBand = r->tgt2Band; fz.tgtDelay = r->tgt2Delay;
+	fz.band = band_gains; fz.delaySec = delay_seconds; fz.sampleRate = r->cfg.sample_rate; fz.numSC = r->numSC;
+	JPLG_LAUNCH(ctx, JPLG_K_MDAP, LaunchMdap(p->dev, l->lp, pan_params, 5, N, static_cast<float*>(scratch), ctx->numSMs, ctx->stream, &fz));
+	JPLG_CUDA_TRY(ctx, cudaEventRecord(r->evUpdated, ctx->stream));
+	r->pendingPanned = true;
+	return JPLG_OK;
+}
+
 static jplg_status EnsureAux(jplg_context ctx)
 {
 	if (ctx->auxReady) return JPLG_OK;
-	for (auto& a : ctx->aux) JPLG_CUDA_TRY(ctx, cudaStreamCreateWithFlags(&a, cudaStreamNonBlocking));
+	// The side streams rank between a rendering context's stream (greatest priority) and a background context's (least): the next block's ring pushes
+	// (aux[1]) then take the SMs a render leaves free BEFORE the background panning kernels do and are over in a third of the render's duration;
+	// spread over all of it, sharing those SMs, their ring writes slow the render's ring reads down by 9 % (measured).
+	int prioLeast = 0, prioGreatest = 0;
+	JPLG_CUDA_TRY(ctx, cudaDeviceGetStreamPriorityRange(&prioLeast, &prioGreatest));
+	const int prioSide = prioLeast - 1 >= prioGreatest ? prioLeast - 1 : prioLeast;
+	for (auto& a : ctx->aux) JPLG_CUDA_TRY(ctx, cudaStreamCreateWithPriority(&a, cudaStreamNonBlocking, prioSide));
 	JPLG_CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->evStart, cudaEventDisableTiming));
 	for (auto& e : ctx->evCopied) JPLG_CUDA_TRY(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
 	for (auto& e : ctx->evDone) JPLG_CUDA_TRY(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -778,6 +839,14 @@ static jplg_status ProcessBlock(jplg_renderer r, const float* in, float* bus, fl
 			dPer = r->stagePerSource;
 		}
 	}
+	if (r->pendingPanned)
+	{
+		// targets written by jplg_renderer_update_panned (maybe on another context's stream): they become the active set once they are complete
+		JPLG_CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, r->evUpdated, 0));
+		std::swap(r->tgtDelay, r->tgt2Delay); std::swap(r->tgtBand, r->tgt2Band); std::swap(r->tgtMix, r->tgt2Mix);
+		r->activeSet ^= 1;
+		r->pendingPanned = false;
+	}
 	RenderParams rp{};
 	rp.numSC = r->numSC; rp.srcChannels = C; rp.L = L; rp.ringSize = r->ringSize; rp.ringMask = r->ringSize - 1; rp.pos = r->pos; rp.frames = frames;
 	rp.alpha = r->alpha; std::memcpy(rp.coef, r->coef, sizeof(rp.coef));
@@ -839,6 +908,7 @@ static jplg_status ProcessBlock(jplg_renderer r, const float* in, float* bus, fl
 		JPLG_LAUNCH(ctx, JPLG_K_RENDER, LaunchRender(rp, r->cfg.mode, 0, r->numCTAs, ctx->stream, r->evStarted));
 		r->startedRecorded = true;
 	}
+	if (r->evSetFree[r->activeSet]) { JPLG_CUDA_TRY(ctx, cudaEventRecord(r->evSetFree[r->activeSet], ctx->stream)); r->setFreeRecorded[r->activeSet] = true; }
 	JPLG_LAUNCH(ctx, JPLG_K_BUS_REDUCE, LaunchBusReduce(rp, r->deviceBus, dBus, ctx->stream));
 	r->pos += TotalPushes(frames);
 	if (mem == JPLG_MEM_HOST)

@@ -32,7 +32,17 @@ namespace jplg
 	};
 
 	cudaError_t LaunchPointGains(const PannerDev& p, const float* dirs, uint32_t n, float* out, cudaStream_t st);
-	cudaError_t LaunchMdap(const PannerDev& p, const MdapLayoutParams& lp, const float* params, uint32_t paramStride, uint32_t n, float* out, int numSMs, cudaStream_t st);
+	// Optional fused epilogue of k_mdap_3d (jplg_renderer_update_panned): the normalised mix maps go straight into a renderer's target arrays
+	// (SoA [L][numSC]; the layout's channel count is the renderer's source channel count) together with the band gains and the delay in samples,
+	// i.e. what k_update_targets would make of them. tgtMix == nullptr: plain MDAP.
+	struct MdapFuse
+	{
+		float* tgtMix = nullptr; float* tgtBand = nullptr; float* tgtDelay = nullptr;
+		const float* band = nullptr; const float* delaySec = nullptr;
+		float sampleRate = 0.0f; uint32_t numSC = 0;
+	};
+	cudaError_t LaunchMdap(const PannerDev& p, const MdapLayoutParams& lp, const float* params, uint32_t paramStride, uint32_t n, float* out, int numSMs, cudaStream_t st,
+						   const MdapFuse* fuse = nullptr);
 	cudaError_t LaunchProcessVS(const PannerDev& p, const float* vs, uint32_t n, uint32_t batches, float* out, cudaStream_t st);
 
 	//======================================================================

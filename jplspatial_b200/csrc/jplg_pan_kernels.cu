@@ -76,7 +76,7 @@ namespace jplg
 	template<int G>
 	__global__ void __launch_bounds__(JPLG_MDAP_WARPS * 32)
 	k_mdap_3d(const uint4* __restrict__ lut, const uint32_t* __restrict__ rsqTable, MdapLayoutParams lp,
-			  const float* __restrict__ params, uint32_t n, uint32_t L, float* __restrict__ out)
+			  const float* __restrict__ params, uint32_t n, uint32_t L, float* __restrict__ out, const MdapFuse fz)
 	{
 		extern __shared__ __align__(16) unsigned char smemRaw[];
 		uint32_t* sRsq = reinterpret_cast<uint32_t*>(smemRaw);                       // 2048
@@ -222,7 +222,26 @@ namespace jplg
 			{
 				const float g = sMix[gl];
 				const float norm = g > 0.0f ? invsqrt_exact(g * nChF) : 0.0f;
-				for (uint32_t ch = 0; ch < lp.numChannels; ++ch) outSrc[ch * L + gl] *= norm;
+				for (uint32_t ch = 0; ch < lp.numChannels; ++ch)
+				{
+					const float v = outSrc[ch * L + gl] * norm;
+					outSrc[ch * L + gl] = v;
+					if (fz.tgtMix) fz.tgtMix[size_t(gl) * fz.numSC + size_t(src) * lp.numChannels + ch] = v;   // k_update_targets' transpose
+				}
+			}
+			if (fz.tgtMix && valid)
+			{
+				// UpdateParameters (src/Auralization/DirectSound.cpp:231-239) for this source's channels: band gains, delay in samples
+				if (gl < 4)
+				{
+					const float b = fz.band[size_t(src) * 4 + gl];
+					for (uint32_t ch = 0; ch < lp.numChannels; ++ch) fz.tgtBand[size_t(gl) * fz.numSC + size_t(src) * lp.numChannels + ch] = b;
+				}
+				if (gl == 4)
+				{
+					const float d = fz.delaySec[src] * fz.sampleRate;
+					for (uint32_t ch = 0; ch < lp.numChannels; ++ch) fz.tgtDelay[size_t(src) * lp.numChannels + ch] = d;
+				}
 			}
 			__syncwarp();
 		}
@@ -358,8 +377,11 @@ namespace jplg
 		return (2048 + JPLG_MDAP_WARPS * 32) * 4;
 	}
 
-	cudaError_t LaunchMdap(const PannerDev& p, const MdapLayoutParams& lpIn, const float* params, uint32_t paramStride, uint32_t n, float* out, int numSMs, cudaStream_t st)
+	cudaError_t LaunchMdap(const PannerDev& p, const MdapLayoutParams& lpIn, const float* params, uint32_t paramStride, uint32_t n, float* out, int numSMs, cudaStream_t st,
+						   const MdapFuse* fuse)
 	{
+		const MdapFuse fz = fuse ? *fuse : MdapFuse{};
+		if (fz.tgtMix && !p.is3D) return cudaErrorNotSupported;
 		MdapLayoutParams lp = lpIn;
 		lp.paramStride = paramStride;
 		if (n == 0) return cudaSuccess;
@@ -372,7 +394,7 @@ namespace jplg
 		{
 			auto kernel = groups == JPLG_MDAP_WARPS ? k_mdap_3d<32> : k_mdap_3d<16>;
 			cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
-			kernel<<<grid, JPLG_MDAP_WARPS * 32, smem, st>>>(p.lut3d, p.rsqTable, lp, params, n, p.numChannels, out);
+			kernel<<<grid, JPLG_MDAP_WARPS * 32, smem, st>>>(p.lut3d, p.rsqTable, lp, params, n, p.numChannels, out, fz);
 		}
 		else
 		{

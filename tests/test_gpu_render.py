@@ -457,3 +457,81 @@ def test_background_context_panning_one_block_ahead_equals_serial():
     ra.close(); rb.close()
     del pans, p
     bg.close(); ctx.close()
+
+
+@pytest.mark.gpu
+def test_update_panned_equals_mdap_then_update():
+    """jplg_renderer_update_panned (panning kernel with the UpdateParameters epilogue, double-buffered targets) against jplg_panner_mdap +
+    jplg_renderer_update: same buses bit for bit, (a) on the renderer's own context, (b) from a background context one block ahead, (c) with a
+    classic partial update refining a pending panned update. Mono and stereo sources."""
+    import torch
+    for C, mask in ((1, J.ChannelMask.Mono), (2, J.ChannelMask.Stereo)):
+        ctx = J.Context(0)
+        bg = J.Context(0, background=True)
+        N, L, blocks, frames = 1031, 12, 5, 512
+        sc = make_scene(N, C, L, blocks, frames, util.SEED + 87 + C)
+        params = np.stack([util.pan_params(N, util.SEED + 120 + b, edge=True) for b in range(blocks)])
+        dev = torch.device("cuda", 0)
+        stream, stream_bg = ctx.torch_stream(), bg.torch_stream()
+        pans = []
+        for c in (ctx, bg):
+            p = J.VBAPanner(c)
+            assert p.Initialize(J.ChannelMask.Surround_7_1_4)
+            pans.append((p, p.InitializeSourceLayout(mask)))
+        mix0 = pans[0][0].ProcessVBAPData(pans[0][1], params[0]).reshape(N, C, L)
+
+        def make():
+            return J.DirectSoundBatch(ctx, FS, N, C, L, sc["band"][0], sc["delay"][0], mix0, ring_size=0, max_block_frames=512, mode=J.MODE_PARITY)
+
+        ra, rb, rc_, rd = make(), make(), make(), make()
+        with torch.cuda.stream(stream):
+            d_audio = [torch.from_numpy(sc["audio"][b]).to(dev) for b in range(blocks)]
+            d_params = torch.from_numpy(params).to(dev)
+            d_band = torch.from_numpy(sc["band"]).to(dev)
+            d_delay = torch.from_numpy(sc["delay"]).to(dev)
+            d_mix = torch.empty((N, C, L), dtype=torch.float32, device=dev)
+            buses = {k: [torch.zeros((frames, L), dtype=torch.float32, device=dev) for _ in range(blocks)] for k in "abcd"}
+        ctx.synchronize()
+        for b in range(blocks):                      # reference order: two calls
+            pans[0][0].ProcessVBAPData(pans[0][1], d_params[b], out=d_mix)
+            ra.UpdateParameters(d_band[b + 1], d_delay[b + 1], d_mix)
+            ra.ProcessInterleaved(d_audio[b], buses["a"][b], frames)
+        for b in range(blocks):                      # (a) fused, same context
+            rb.UpdatePanned(pans[0][0], pans[0][1], d_params[b], d_band[b + 1], d_delay[b + 1])
+            rb.ProcessInterleaved(d_audio[b], buses["b"][b], frames)
+        ctx.synchronize()
+        # (b) fused on the background context, issued one block ahead (the library orders the two streams itself)
+        rc_.UpdatePanned(pans[1][0], pans[1][1], d_params[0], d_band[1], d_delay[1])
+        for b in range(blocks):
+            rc_.ProcessInterleaved(d_audio[b], buses["c"][b], frames)
+            if b + 1 < blocks:
+                rc_.WaitRenderStarted(bg)
+                rc_.UpdatePanned(pans[1][0], pans[1][1], d_params[b + 1], d_band[b + 2], d_delay[b + 2])
+        ctx.synchronize(); bg.synchronize()
+        # (c) a pending panned update refined by a classic one (other band gains), against the same in two calls
+        with torch.cuda.stream(stream):
+            xa = torch.zeros((frames, L), dtype=torch.float32, device=dev)
+        pans[0][0].ProcessVBAPData(pans[0][1], d_params[1], out=d_mix)
+        ra.UpdateParameters(d_band[3], d_delay[2], d_mix)
+        ra.ProcessInterleaved(d_audio[0], xa, frames)
+        rd_in = buses["d"][0]
+        for b in range(blocks):                      # bring rd to ra's state first
+            rd.UpdatePanned(pans[0][0], pans[0][1], d_params[b], d_band[b + 1], d_delay[b + 1])
+            rd.ProcessInterleaved(d_audio[b], buses["d"][b], frames)
+        with torch.cuda.stream(stream):
+            xd = torch.zeros((frames, L), dtype=torch.float32, device=dev)
+        rd.UpdatePanned(pans[0][0], pans[0][1], d_params[1], d_band[2], d_delay[2])
+        rd.UpdateParameters(d_band[3], None, None)
+        rd.ProcessInterleaved(d_audio[0], xd, frames)
+        ctx.synchronize()
+        for b in range(blocks):
+            want = buses["a"][b].cpu().numpy()
+            assert np.abs(want).max() > 0
+            for k in "bcd":
+                assert util.bits_equal(buses[k][b].cpu().numpy(), want), f"C={C} block {b}: fused path {k} differs"
+        assert util.bits_equal(xd.cpu().numpy(), xa.cpu().numpy()), f"C={C}: classic update on top of a pending panned update differs"
+        del d_audio, d_params, d_band, d_delay, d_mix, buses, xa, xd, rd_in
+        for r_ in (ra, rb, rc_, rd):
+            r_.close()
+        del pans, p
+        bg.close(); ctx.close()
