@@ -75,6 +75,9 @@ def test_background_context_flag(J):
     lib.jplg_renderer_wait_render_started.restype = C.c_int32
     lib.jplg_renderer_wait_render_started.argtypes = [C.c_void_p, C.c_void_p]
     assert lib.jplg_renderer_wait_render_started(None, bg.h) == 1
+    lib.jplg_renderer_update_panned.restype = C.c_int32
+    lib.jplg_renderer_update_panned.argtypes = [C.c_void_p] * 6 + [C.c_int32]
+    assert lib.jplg_renderer_update_panned(None, None, None, None, None, None, 1) == 1      # no renderer / panner: invalid argument, nothing touched
     del pan
     bg.close()
 
