@@ -237,8 +237,9 @@ JPLG_API jplg_status jplg_renderer_process_block(jplg_renderer r, const float* i
  * touch disjoint ring slots as long as the ring holds the longest delay in use plus four blocks, which the caller guarantees (true for the
  * reference ring size bit_ceil(2 fs) with delays up to 1.9 s). The next jplg_renderer_process_block must get the same `in` / `frames`
  * (JPLG_MEM_DEVICE); it waits for these pushes instead of issuing its own (any other block simply overwrites them: the ring position only advances
- * in process_block). A real-time engine, whose next block does not exist yet, does not
- * need this call. */
+ * in process_block). The side stream starts them once the render enqueued last is fully resident, and ranks above JPLG_CONTEXT_BACKGROUND
+ * contexts, so they neither delay that render's placement nor trail behind background panning work. A real-time engine, whose next block does
+ * not exist yet, does not need this call. */
 JPLG_API jplg_status jplg_renderer_push_ahead(jplg_renderer r, const float* in, uint32_t frames);
 /* Makes `waiting`'s stream (a JPLG_CONTEXT_BACKGROUND context on the same device) wait until every CTA of the k_render launch enqueued last by
  * jplg_renderer_process_block is resident on the device. Work enqueued on `waiting` afterwards (the next block's jplg_panner_mdap, the scene
