@@ -455,8 +455,17 @@ JPLG_API jplg_status jplg_bus_exchange_submit(jplg_bus_exchange x, const float* 
                                               int32_t accumulate);
 /* makes the context stream wait (on the device, not the host) for every block submitted so far */
 JPLG_API jplg_status jplg_bus_exchange_wait(jplg_bus_exchange x);
-/* 0 = healthy; != 0 after a device-side wait timed out (~2 s: a rank died or stalled): results of that block are undefined, nothing hangs */
+/* 0 = healthy; != 0 after a device-side wait timed out (a rank died or stalled for longer than the time-out): nothing hangs and nothing stale is
+ * summed — a sender that timed out stores / publishes nothing, a gather that timed out (or runs after an error) leaves device_out untouched and only
+ * acknowledges. The state is sticky until jplg_bus_exchange_clear_error. This call may read the root's header (a blocking 4-byte copy);
+ * jplg_bus_exchange_poll_error only reads this rank's own host-mapped error word (cheap enough to call after every block). */
 JPLG_API int32_t     jplg_bus_exchange_error(jplg_bus_exchange x);
+JPLG_API int32_t     jplg_bus_exchange_poll_error(jplg_bus_exchange x);
+/* device-side wait time-out of this rank's exchange kernels, default 2,000 ms; set it before the first submit or between blocks */
+JPLG_API jplg_status jplg_bus_exchange_set_timeout_ms(jplg_bus_exchange x, uint32_t milliseconds);
+/* collective recovery: every rank drains its streams and clears its error word, the root also zeroes the header (flags, acknowledgement); call it on
+ * every rank between two host-side barriers, then restart `seq` at 0 */
+JPLG_API jplg_status jplg_bus_exchange_clear_error(jplg_bus_exchange x);
 
 #ifdef __cplusplus
 }

@@ -4,7 +4,7 @@ import os
 import numpy as np
 
 _here = os.path.dirname(os.path.abspath(__file__))
-lib_path = os.path.join(_here, "libjplg.so")
+lib_path = os.environ.get("JPLG_LIB_PATH") or os.path.join(_here, "libjplg.so")   # JPLG_LIB_PATH: experiment builds (scratch/), A/B runs only
 if not os.path.exists(lib_path):
     raise ImportError(
         f"{lib_path} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
@@ -885,6 +885,9 @@ _sig("jplg_bus_exchange_destroy", None, [_vp])
 _sig("jplg_bus_exchange_submit", _i32, [_vp, _fp, _u32, _u64, _fp, _i32])
 _sig("jplg_bus_exchange_error", _i32, [_vp])
 _sig("jplg_bus_exchange_wait", _i32, [_vp])
+_sig("jplg_bus_exchange_poll_error", _i32, [_vp])
+_sig("jplg_bus_exchange_set_timeout_ms", _i32, [_vp, _u32])
+_sig("jplg_bus_exchange_clear_error", _i32, [_vp])
 DECLARED_SYMBOLS = [n for n in dir(lib) if n.startswith("jplg_")]
 IPC_HANDLE_BYTES = 64
 
@@ -924,6 +927,17 @@ class BusExchange:
 
     def error(self):
         return int(lib.jplg_bus_exchange_error(self.h))
+
+    def poll_error(self):
+        """this rank's own host-mapped error word: no device access, cheap enough to call after every block"""
+        return int(lib.jplg_bus_exchange_poll_error(self.h))
+
+    def set_timeout_ms(self, ms):
+        self.ctx.check(lib.jplg_bus_exchange_set_timeout_ms(self.h, int(ms)))
+
+    def clear_error(self):
+        """collective: call on every rank between two host-side barriers, then restart seq at 0"""
+        self.ctx.check(lib.jplg_bus_exchange_clear_error(self.h))
 
     def close(self):
         if self.h and _ctx_alive(self):   # a closed context's children are gone with it

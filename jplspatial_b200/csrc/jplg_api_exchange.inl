@@ -12,6 +12,10 @@ struct jplg_bus_exchange_t
 	float* staging = nullptr;        // [2][maxFloats]
 	cudaEvent_t evReady[2] = {}, evDone[2] = {};
 	uint64_t submitted = 0;
+	long long spinLimitCycles = 0;   // device-side wait time-out (jplg_bus_exchange_set_timeout_ms; default 2 s)
+	uint32_t* errHost = nullptr;     // page-locked, device-mapped word the kernels raise on a time-out: readable without touching the device
+	uint32_t* errDev = nullptr;      // its device alias
+	int clockKHz = 0;
 };
 
 static jplg_status ExchangeSideInit(jplg_bus_exchange x)
@@ -24,6 +28,11 @@ static jplg_status ExchangeSideInit(jplg_bus_exchange x)
 		JPLG_CUDA_TRY(ctx, cudaStreamCreateWithPriority(&x->side, cudaStreamNonBlocking, prioGreatest));
 	}
 	JPLG_CUDA_TRY(ctx, cudaMalloc(reinterpret_cast<void**>(&x->staging), size_t(2) * x->maxFloats * sizeof(float)));
+	JPLG_CUDA_TRY(ctx, cudaHostAlloc(reinterpret_cast<void**>(&x->errHost), sizeof(uint32_t), cudaHostAllocMapped));
+	*x->errHost = 0;
+	JPLG_CUDA_TRY(ctx, cudaHostGetDevicePointer(reinterpret_cast<void**>(&x->errDev), x->errHost, 0));
+	JPLG_CUDA_TRY(ctx, cudaDeviceGetAttribute(&x->clockKHz, cudaDevAttrClockRate, ctx->device));
+	if (x->spinLimitCycles == 0) x->spinLimitCycles = 2000ll * x->clockKHz;   // 2 s
 	for (int i = 0; i < 2; ++i)
 	{
 		JPLG_CUDA_TRY(ctx, cudaEventCreateWithFlags(&x->evReady[i], cudaEventDisableTiming));
@@ -90,6 +99,7 @@ void jplg_bus_exchange_destroy(jplg_bus_exchange x)
 			cudaStreamSynchronize(x->side);
 			cudaStreamDestroy(x->side);
 			if (x->staging) cudaFree(x->staging);
+			if (x->errHost) cudaFreeHost(x->errHost);
 			for (int i = 0; i < 2; ++i) { cudaEventDestroy(x->evReady[i]); cudaEventDestroy(x->evDone[i]); }
 		}
 		if (x->base) { if (x->root) cudaFree(x->base); else cudaIpcCloseMemHandle(x->base); }
@@ -115,9 +125,9 @@ jplg_status jplg_bus_exchange_submit(jplg_bus_exchange x, const float* device_bu
 	JPLG_CUDA_TRY(ctx, cudaEventRecord(x->evReady[slot], ctx->stream));
 	JPLG_CUDA_TRY(ctx, cudaStreamWaitEvent(x->side, x->evReady[slot], 0));
 	if (x->root)
-		JPLG_LAUNCH_ON(ctx, JPLG_K_EXCHANGE, x->side, LaunchBusGather(hdr, data, x->world, x->maxFloats, stage, n, seq, device_out, accumulate ? 1 : 0, x->side));
+		JPLG_LAUNCH_ON(ctx, JPLG_K_EXCHANGE, x->side, LaunchBusGather(hdr, data, x->world, x->maxFloats, stage, n, seq, device_out, accumulate ? 1 : 0, x->spinLimitCycles, x->errDev, x->side));
 	else
-		JPLG_LAUNCH_ON(ctx, JPLG_K_EXCHANGE, x->side, LaunchBusSend(hdr, data + (size_t(slot) * x->world + x->rank) * x->maxFloats, stage, n, x->rank, seq, x->side));
+		JPLG_LAUNCH_ON(ctx, JPLG_K_EXCHANGE, x->side, LaunchBusSend(hdr, data + (size_t(slot) * x->world + x->rank) * x->maxFloats, stage, n, x->rank, seq, x->spinLimitCycles, x->errDev, x->side));
 	JPLG_CUDA_TRY(ctx, cudaEventRecord(x->evDone[slot], x->side));
 	x->submitted++;
 	return JPLG_OK;
@@ -136,9 +146,48 @@ jplg_status jplg_bus_exchange_wait(jplg_bus_exchange x)
 	return JPLG_OK;
 }
 
+jplg_status jplg_bus_exchange_set_timeout_ms(jplg_bus_exchange x, uint32_t milliseconds)
+{
+	if (!x || milliseconds == 0) return JPLG_ERR_INVALID_ARGUMENT;
+	jplg_context ctx = x->ctx;
+	JPLG_NEED_DEVICE(ctx);
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	int khz = 0;
+	JPLG_CUDA_TRY(ctx, cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, ctx->device));
+	x->spinLimitCycles = static_cast<long long>(milliseconds) * khz;
+	return JPLG_OK;
+}
+
+int32_t jplg_bus_exchange_poll_error(jplg_bus_exchange x)
+{
+	if (!x) return -1;
+	return x->errHost ? static_cast<int32_t>(*reinterpret_cast<volatile uint32_t*>(x->errHost)) : 0;
+}
+
+jplg_status jplg_bus_exchange_clear_error(jplg_bus_exchange x)
+{
+	if (!x) return JPLG_ERR_INVALID_ARGUMENT;
+	jplg_context ctx = x->ctx;
+	JPLG_NEED_DEVICE(ctx);
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	if (x->side) JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(x->side));
+	if (x->errHost) *x->errHost = 0;
+	if (x->root)
+	{
+		// the root owns the header: sequence flags and the acknowledgement restart from zero, every rank restarts its sequence numbers at 0
+		JPLG_CUDA_TRY(ctx, cudaMemset(x->base, 0, kExchangeDataOffset));
+	}
+	x->submitted = 0;
+	return JPLG_OK;
+}
+
 int32_t jplg_bus_exchange_error(jplg_bus_exchange x)
 {
 	if (!x || !x->base || x->ctx->device < 0) return -1;
+	if (x->errHost && *reinterpret_cast<volatile uint32_t*>(x->errHost) != 0) return static_cast<int32_t>(*reinterpret_cast<volatile uint32_t*>(x->errHost));
 	cudaSetDevice(x->ctx->device);
 	uint32_t e = 0;
 	if (cudaMemcpy(&e, x->base + offsetof(ExchangeHeader, error), 4, cudaMemcpyDeviceToHost) != cudaSuccess) { cudaGetLastError(); return -1; }

@@ -190,7 +190,9 @@ namespace jplg
 	};
 	constexpr size_t kExchangeDataOffset = 512;   // bytes: header padded so the slot data is 256-byte aligned
 	static_assert(sizeof(ExchangeHeader) <= kExchangeDataOffset, "exchange header too large");
-	cudaError_t LaunchBusSend(ExchangeHeader* hdr, float* slotData, const float* bus, uint32_t n, uint32_t rank, uint64_t seq, cudaStream_t st);
+	// spinLimitCycles: device-side wait time-out (SM clock cycles); localError: this rank's host-mapped error word
+	cudaError_t LaunchBusSend(ExchangeHeader* hdr, float* slotData, const float* bus, uint32_t n, uint32_t rank, uint64_t seq, long long spinLimitCycles,
+							  uint32_t* localError, cudaStream_t st);
 	cudaError_t LaunchBusGather(ExchangeHeader* hdr, const float* data, uint32_t world, uint32_t maxFloats, const float* own, uint32_t n, uint64_t seq,
-								float* out, int accumulate, cudaStream_t st);
+								float* out, int accumulate, long long spinLimitCycles, uint32_t* localError, cudaStream_t st);
 }
