@@ -2,19 +2,28 @@
 """bench.py — headline benchmark of the B200-native many-source spatial renderer.
 
 Metric (BASELINE.json): real-time sources @ 48 kHz / 512-frame blocks -> 7.1.4.
-Workload at every N: BASELINE config 3 per GPU — 16,384 mono sources, full block render
-(MDAP gains -> Doppler fractional delay -> LR4 4-band filter -> gain-ramped mix to 7.1.4), weak scaling
-(each rank owns 16,384 sources; the only collective is the reduce of the [512 x 12] speaker bus to rank 0).
 
-One "step" = one 512-frame audio block for all sources of the job:
-    (1) jplg_panner_mdap        new pan parameters for every source   -> mix maps
-    (2) jplg_renderer_update    band gains, delays, mix maps
-    (3) jplg_renderer_process_block   push + fused render + bus reduce
-    (4) N > 1: torch.distributed.reduce(bus) over NCCL
-value = sources * (block duration / step time) = how many sources this job renders in real time.
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--config 1..5] [--mode parity|throughput] [--schedule realtime|packed]
+  python bench.py --impl reference ...     times the reference's own CPU code (oracle/_ref, upstream -O3 builds) on the host cores
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--mode parity|throughput] [--sources S]
-  python bench.py --impl reference ...     times the reference's own CPU code (oracle/_ref) on the host cores
+--config selects the BASELINE.json configuration (default 3, the one the metric is quoted on):
+  1  HelloJPLSpatial: 360-direction VBAP gain table, quad layout (gains only)
+  2  MDAP spread/focus gain evaluation, 65,536 sources -> 7.1.4 (gains only)
+  3  full block render, 16,384 mono sources per GPU -> 7.1.4 (MDAP -> delay/Doppler -> LR4 -> mix), the contract line
+  4  multichannel sources {mono, stereo, quad, 5.1} -> 9.1.6, 32,768 per GPU (= 262,144 on 8 GPUs), cost-weighted source sharding
+  5  4,096 x (16th-order FDN late reverb + 16-tap early-reflection bus), mono in -> 7.1.4
+
+Config 3, one "step" = one 512-frame audio block for all sources of the job:
+    (1) jplg_renderer_update_panned   new pan parameters for every source -> MDAP gains -> the renderer's next targets (fused), computed one
+                                      block ahead on a background context (the reference's game thread beside its audio thread)
+    (2) jplg_renderer_process_block   ring push + fused delay / LR4 / mix render + bus reduce
+    (3) N > 1: peer-memory combine of the [512 x 12] speaker bus on rank 0 (jplg_bus_exchange_*; --bus nccl: torch.distributed reduce)
+Schedules: `realtime` (default) pushes a block's input into the rings when the block is processed, as a real-time engine must;
+`packed` issues block k+1's pushes beside block k's render (jplg_renderer_push_ahead, offline rendering only).
+
+`ms_per_step` = the K timed steps of that workload. `value` (real-time sources) = the largest source count actually RENDERED inside the
+10.667 ms block period by the capacity pass (same per-source pipeline, real-time schedule, reference ring size), not an extrapolation;
+`config.capacity` lists what was measured, the compute-limited figure and the memory-limited one.
 """
 import argparse
 import json
@@ -23,6 +32,7 @@ import subprocess
 import sys
 import threading
 import time
+import zlib
 
 import numpy as np
 
@@ -41,6 +51,23 @@ UNIT = "sources"
 RENDER_BYTES_PER_SOURCE = (FRAMES + 2) * 4 + 68 + 2 * 128 + 2 * 48
 # whole step (all kernels): + input read 2048 + ring write 2176 (544 pushes, reference chunk quirk) + MDAP in/out 68
 STEP_BYTES_PER_SOURCE = RENDER_BYTES_PER_SOURCE + FRAMES * 4 + 544 * 4 + 68
+# algorithmic FP32 operations of the reference's arithmetic per source-sample (each multiply / add / divide counted once; the SSE2 parity
+# semantic has no fused operations): 12 SVF sections x 10 (CrossoverFilter.h:64-76), LR4 high-pass recombination 4, 4 all-pass sums x 3,
+# band gains 4 mul + 3 add + 4 ramp adds, smoothing + tap set-up + Thiran 12 (FractionalDelay.h:105-124), mix L x (mul + add + ramp add)
+RENDER_FLOPS_PER_SOURCE_SAMPLE = 12 * 10 + 4 + 12 + 11 + 12 + 3 * L_OUT
+
+
+def _load_masks():
+    """ChannelMask constants from jplspatial_b200/_masks.py, loaded by file path: importing the package would map libjplg.so into the CPU arm"""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("_jplg_masks_only", os.path.join(ROOT, "jplspatial_b200", "_masks.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod.ChannelMask
+
+
+_CM = _load_masks()
+MASK_MONO, MASK_QUAD, MASK_7_1_4 = _CM.Mono, _CM.Quad, _CM.Surround_7_1_4
 
 
 def log(*a):
@@ -96,7 +123,7 @@ class ClockSampler:
             except Exception:
                 pass
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons), "samples": len(sm),
-                "window": "warm-up + timed region + e2e region (100 ms period)"}
+                "window": "warm-up + timed region + capacity / e2e passes (100 ms period)"}
 
 
 def make_inputs(n_sources, pool, seed):
@@ -114,86 +141,108 @@ def make_inputs(n_sources, pool, seed):
 
 
 # ------------------------------------------------------------------------------------------------
-def run_reference_arm(args, rank, world):
-    """Times the reference's own CPU implementation of the path (oracle/_ref: the unmodified reference compiled from
-    /root/reference) on the host cores, all hardware threads, on a bounded sample of the same workload."""
-    if rank != 0:
-        return
+# CPU arm: the unmodified reference (oracle/_ref), upstream Release flags, persistent worker pool
+def _reference_variants():
+    """timing builds, fastest expected first; the -O2 SSE2 parity build only if the -O3 ones did not travel"""
     from oracle import refpy
-    kind = "reference"
-    if not refpy.available("sse2"):
-        _emit(({"impl": "reference", "unavailable": "oracle/_ref/libjplref_sse2.so not present (reference tree absent at build time)"}))
-        return
-    cores = os.cpu_count() or 1
-    n = args.ref_sources
-    ref = refpy.Ref("sse2")
-    M = __import__("jplspatial_b200").ChannelMask
-    audio, params, band, delay = make_inputs(n, 4, 0x5EED)
-    rp = ref.panner(M.Surround_7_1_4)
-    rl = rp.layout(M.Mono)
+    return [v for v in ("o3_avx2fma", "o3_sse2", "sse2") if refpy.available(v)]
+
+
+def _time_reference_c3(ref, n, blocks, threads, seed=0x5EED, warm=1):
+    """`blocks` timed blocks of config 3's per-block work (MDAP for every source, UpdateParameters, ProcessInterleaved) for n mono sources -> 7.1.4"""
+    audio, params, band, delay = make_inputs(n, 4, seed)
+    rp = ref.panner(MASK_7_1_4)
+    rl = rp.layout(MASK_MONO)
     mix0 = rp.mdap(rl, params[0]).reshape(n, L_OUT)
     fx = [ref.dse(FS, 1, L_OUT, band[0, i], float(delay[0, i]), mix0[i]) for i in range(n)]
+    handles = ref.dse_handles(fx)
     bus = np.zeros((FRAMES, L_OUT), np.float32)
+    flat = [np.ascontiguousarray(audio[j].reshape(n, -1)) for j in range(audio.shape[0])]
 
     def step(k):
         j = k % audio.shape[0]
-        mix = rp.mdap(rl, params[j], threads=cores).reshape(n, L_OUT)
-        ref.dse_batch_update(fx, band[j], delay[j], mix)
+        mix = rp.mdap(rl, params[j], threads=threads).reshape(n, L_OUT)
+        ref.dse_batch_update(handles, band[j], delay[j], mix, threads=threads)
         bus[:] = 0
-        ref.dse_batch_process(fx, audio[j].reshape(n, -1), FRAMES, bus.reshape(-1), threads=cores)
+        ref.dse_batch_process(handles, flat[j], FRAMES, bus.reshape(-1), threads=threads)
 
-    for k in range(args.warmup):
+    for k in range(warm):
         step(k)
     t0 = time.perf_counter()
-    for k in range(args.steps):
-        step(args.warmup + k)
-    dt = (time.perf_counter() - t0) / args.steps
+    for k in range(blocks):
+        step(warm + k)
+    dt = (time.perf_counter() - t0) / blocks
+    del fx
+    return dt
+
+
+def best_reference(n, blocks, log_fn=None):
+    """times every available reference build on all host threads and on one, returns the fastest all-thread figure with its description"""
+    from oracle import refpy
+    cores = os.cpu_count() or 1
+    results = []
+    for v in _reference_variants():
+        ref = refpy.Ref(v)
+        dt_all = _time_reference_c3(ref, n, blocks, cores)
+        dt_one = _time_reference_c3(ref, min(n, 256), max(2, blocks // 4), 1)
+        results.append({"variant": v, "flags": ref.build_info(), "ms_per_block_all_threads": dt_all * 1e3, "sources": n,
+                        "us_per_source_block_1_thread": dt_one / min(n, 256) * 1e6})
+        if log_fn:
+            log_fn(f"reference {v} ({ref.build_info()}): {dt_all * 1e3:.2f} ms per {n}-source block on {cores} threads; "
+                   f"1 thread {dt_one / min(n, 256) * 1e6:.1f} us per source-block")
+    if not results:
+        return None
+    best = min(results, key=lambda r: r["ms_per_block_all_threads"])
+    return {"best": best, "all": results, "cores": cores}
+
+
+def run_reference_arm(args, rank, world):
+    """Times the reference's own CPU implementation of the path (oracle/_ref: the unmodified reference compiled from /root/reference with the
+    upstream Release flags, SSE2 and AVX2+FMA variants, the faster one reported) on the host cores, all hardware threads through a persistent
+    worker pool, on a bounded sample of the same workload. Loads nothing of the product."""
+    if rank != 0:
+        return
+    if not _reference_variants():
+        _emit(({"impl": "reference", "unavailable": "oracle/_ref/libjplref_*.so not present (reference tree absent at build time)"}))
+        return
+    from oracle import refpy
+    cores = os.cpu_count() or 1
+    n = args.ref_sources
+    # pick the faster build on a short probe, then time --steps blocks of it
+    probe = best_reference(min(n, 1024), 3)
+    variant = probe["best"]["variant"]
+    ref = refpy.Ref(variant)
+    dt = _time_reference_c3(ref, n, args.steps, cores, warm=max(1, min(args.warmup, 5)))
     value = n * BLOCK_S / dt
+    one = probe["best"]["us_per_source_block_1_thread"]
+    sample = (f"{n} mono sources x {args.steps} blocks of 512 frames (MDAP + UpdateParameters + ProcessInterleaved per block), {cores} threads "
+              f"(persistent pool), unmodified reference, {ref.build_info()} [fastest of: "
+              + "; ".join(f"{r['variant']} {r['ms_per_block_all_threads']:.2f} ms per {r['sources']}-source block" for r in probe["all"])
+              + f"]; 1 thread: {one:.1f} us per source-block")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": "BASELINE config 3: full block render, mono sources -> 7.1.4, 48 kHz / 512 frames (MDAP gains + update + render per block)",
-                   "sources_per_step": n, "note": "bounded sample of the 16,384-source workload; value = sample sources x block duration / step time"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
-                         "sample": f"{n} mono sources x {args.steps} blocks of 512 frames, {cores} std::threads, reference SSE2 build (-O2)"},
+                   "sources_per_step": n, "note": "bounded sample of the 16,384-source workload; value = sample sources x block duration / step time "
+                                                    "(the CPU path is linear in the number of sources)"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "reference", "sample": sample, "variant": variant,
+                         "one_thread_us_per_source_block": one},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     _emit(line)
 
 
 def cpu_baseline_sample(log_fn):
-    """Bounded CPU sample for the `cpu_baseline` object of the GPU arm (rank 0, N = 1)."""
-    from oracle import refpy
-    cores = os.cpu_count() or 1
-    if refpy.available("sse2"):
-        ref = refpy.Ref("sse2")
-        kind = "reference"
-    else:
+    """Bounded CPU sample for the `cpu_baseline` object of the GPU arm (rank 0, N = 1): every reference build, all threads and one thread."""
+    if not _reference_variants():
         return None
-    import jplspatial_b200 as J
-    n, blocks = 1024, 24
-    audio, params, band, delay = make_inputs(n, 4, 0xC0FFEE)
-    rp = ref.panner(J.ChannelMask.Surround_7_1_4)
-    rl = rp.layout(J.ChannelMask.Mono)
-    mix0 = rp.mdap(rl, params[0]).reshape(n, L_OUT)
-    fx = [ref.dse(FS, 1, L_OUT, band[0, i], float(delay[0, i]), mix0[i]) for i in range(n)]
-    bus = np.zeros((FRAMES, L_OUT), np.float32)
-    t0 = time.perf_counter()
-    for k in range(blocks):
-        j = k % 4
-        mix = rp.mdap(rl, params[j], threads=cores).reshape(n, L_OUT)
-        ref.dse_batch_update(fx, band[j], delay[j], mix)
-        ref.dse_batch_process(fx, audio[j].reshape(n, -1), FRAMES, bus.reshape(-1), threads=cores)
-    dt = (time.perf_counter() - t0) / blocks
-    # single-thread figure for context
-    t1 = time.perf_counter()
-    for k in range(4):
-        ref.dse_batch_process(fx[:256], audio[k % 4, :256].reshape(256, -1), FRAMES, bus.reshape(-1), threads=1)
-    us1 = (time.perf_counter() - t1) / (4 * 256) * 1e6
-    log_fn(f"cpu baseline: {dt * 1e3:.2f} ms per {n}-source block on {cores} threads; single-thread DirectSoundEffect {us1:.1f} us/source-block")
-    return {"value": n * BLOCK_S / dt, "unit": UNIT, "cores": cores, "kind": kind,
-            "sample": f"{n} mono sources x {blocks} blocks of 512 frames (MDAP + update + render), {cores} std::threads, reference SSE2 build; "
-                      f"1-thread DirectSoundEffect = {us1:.1f} us per source-block"}
+    r = best_reference(2048, 10, log_fn)
+    b = r["best"]
+    return {"value": b["sources"] * BLOCK_S / (b["ms_per_block_all_threads"] * 1e-3), "unit": UNIT, "cores": r["cores"], "kind": "reference",
+            "variant": b["variant"],
+            "sample": f"{b['sources']} mono sources x 10 blocks of 512 frames (MDAP + update + render), {r['cores']} threads (persistent pool), unmodified "
+                      f"reference, {b['flags']}; 1 thread: {b['us_per_source_block_1_thread']:.1f} us per source-block; all builds: "
+                      + "; ".join(f"{x['variant']} {x['ms_per_block_all_threads']:.2f} ms" for x in r["all"])}
 
 
 # ------------------------------------------------------------------------------------------------
@@ -241,6 +290,886 @@ def _emit(line):
     _JSON_OUT.flush()
 
 
+def hbm_peak():
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        return float(json.load(open(peaks_path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class Env:
+    """rank / device / torch.distributed plumbing shared by the configurations"""
+
+    def __init__(self, args):
+        import torch
+        import jplspatial_b200 as J
+        self.torch, self.J = torch, J
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available() or J.device_count() == 0:
+            raise SystemExit("bench.py: no CUDA device — this framework has no CPU fallback (use --impl reference for the CPU reference arm)")
+        torch.cuda.set_device(self.local)
+        self.numa = bind_to_gpu_numa_node(torch, self.local)
+        self.dist = None
+        if self.world > 1:
+            import torch.distributed as dist_mod
+            self.dist = dist_mod
+            self.dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+        self.dev = torch.device("cuda", self.local)
+        self.mode = J.MODE_PARITY if args.mode == "parity" else J.MODE_THROUGHPUT
+
+    def max_over_ranks(self, x):
+        t = self.torch.tensor([x], dtype=self.torch.float64, device=self.dev)
+        if self.dist is not None:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def gather_floats(self, x):
+        if self.dist is None:
+            return [x]
+        t = self.torch.tensor([x], dtype=self.torch.float64, device=self.dev)
+        allt = [self.torch.zeros_like(t) for _ in range(self.world)]
+        self.dist.all_gather(allt, t)
+        return [float(v.item()) for v in allt]
+
+    def finish(self):
+        if self.dist is not None:
+            self.dist.destroy_process_group()
+
+
+class _DeviceFloats:
+    """CUDA array interface over a raw device pointer of the library (read-only view for the checks)"""
+
+    def __init__(self, ptr, n):
+        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": "<f4", "data": (int(ptr), True), "version": 2}
+
+
+class Config3Pipeline:
+    """Config 3's per-block pipeline for `N` mono sources -> 7.1.4 on one rank (see the module docstring for the step), built once and stepped."""
+
+    def __init__(self, env, args, N, ring, pool_arrays, schedule, use_exchange=True):
+        torch, J = env.torch, env.J
+        self.env, self.args, self.N = env, args, N
+        self.schedule = schedule
+        self.push_ahead = schedule == "packed" and not args.no_push_ahead
+        self.pan_overlap = not args.no_pan_overlap
+        self.fused_update = not args.no_fused_update
+        dev = env.dev
+        self.ctx = J.Context(env.local)
+        self.stream = self.ctx.torch_stream()
+        audio, params, band, delay = pool_arrays          # device tensors [pool][N]...
+        self.pool = audio.shape[0]
+        self.pan = J.VBAPanner(self.ctx)
+        assert self.pan.Initialize(J.ChannelMask.Surround_7_1_4)
+        self.lay = self.pan.InitializeSourceLayout(J.ChannelMask.Mono)
+        h_params0 = params[0].cpu().numpy()
+        mix0 = self.pan.ProcessVBAPData(self.lay, h_params0).reshape(N, L_OUT)
+        self.rend = J.DirectSoundBatch(self.ctx, FS, N, 1, L_OUT, band[0].cpu().numpy(), delay[0].cpu().numpy(), mix0, ring_size=ring,
+                                       max_block_frames=FRAMES, mode=env.mode)
+        with torch.cuda.stream(self.stream):
+            self.d_mix = torch.empty((N, 1, L_OUT), dtype=torch.float32, device=dev)
+            self.local_bus = torch.zeros((FRAMES, L_OUT), dtype=torch.float32, device=dev)
+            self.final_bus = torch.zeros((FRAMES, L_OUT), dtype=torch.float32, device=dev)
+        self.ctx.synchronize()
+        from jplspatial_b200.sharding import PipelinedBusReduce, make_peer_bus_exchange
+        self.use_peer = env.dist is not None and args.bus == "peer" and use_exchange
+        # nccl mode: two bus buffers, the NCCL reduce of block k overlaps the render of block k+1
+        self.reducer = PipelinedBusReduce(FRAMES, L_OUT, dev, depth=2, dst=0)
+        if args.bus == "none" or not use_exchange:
+            self.reducer.submit = lambda k: None     # N independent replicas, no combine (the line's `config.parallelism` says so)
+        self.exchange = make_peer_bus_exchange(self.ctx, FRAMES * L_OUT) if self.use_peer else None
+        self.seq = 0
+        self.gk = 0
+        self.v_params = [params[j] for j in range(self.pool)]
+        self.v_band = [band[j] for j in range(self.pool)]
+        self.v_delay = [delay[j] for j in range(self.pool)]
+        self.v_audio = [audio[j] for j in range(self.pool)]
+        self.bus_ptr, self.bus_floats = self.rend.device_bus_ptr(), FRAMES * L_OUT
+        self.peer_out = self.final_bus if env.rank == 0 else None
+        # game-thread / audio-thread split of the reference (SpatialManager::AdvanceSimulation beside the audio callback): block k+1's panning data is
+        # computed by a background context while block k renders; its stream has the lower priority, so k_render's CTAs are placed first and
+        # k_mdap_3d fills the remaining SMs. Events order the two streams.
+        if self.pan_overlap:
+            self.ctx_pan = J.Context(env.local, background=True)
+            self.stream_pan = self.ctx_pan.torch_stream()
+            self.pan_bg = J.VBAPanner(self.ctx_pan)
+            assert self.pan_bg.Initialize(J.ChannelMask.Surround_7_1_4)
+            self.lay_bg = self.pan_bg.InitializeSourceLayout(J.ChannelMask.Mono)
+            with torch.cuda.stream(self.stream):
+                self.d_mix_bg = [torch.empty((N, 1, L_OUT), dtype=torch.float32, device=dev) for _ in range(2)]
+            self.ctx.synchronize()
+            self.ev_mdap = [torch.cuda.Event() for _ in range(2)]
+            self.ev_upd = torch.cuda.Event()
+            self.mdap_issued = -1
+
+    # (the library enqueues on its contexts' own streams whatever torch's current stream is: no stream context managers in the step)
+    def _issue_mdap(self, k, after_update):
+        j = k % self.pool
+        if after_update:
+            if not self.fused_update:
+                self.stream_pan.wait_event(self.ev_upd)  # the buffer's previous reader (update k-1) is older than this event
+            self.rend.WaitRenderStarted(self.ctx_pan)    # only once block k-1's render is resident: k_mdap_3d takes the SMs it leaves free
+        if self.fused_update:
+            self.rend.UpdatePanned(self.pan_bg, self.lay_bg, self.v_params[j], self.v_band[j], self.v_delay[j])   # the library orders it against the renders
+        else:
+            self.pan_bg.ProcessVBAPData(self.lay_bg, self.v_params[j], out=self.d_mix_bg[k & 1])
+        self.ev_mdap[k & 1].record(self.stream_pan)
+        self.mdap_issued = k
+
+    def join_pan(self):
+        if self.pan_overlap and self.mdap_issued >= 0:
+            self.stream.wait_event(self.ev_mdap[self.mdap_issued & 1])
+
+    def step(self, _k=None):
+        torch = self.env.torch
+        k = self.gk          # consecutive block numbers whatever the caller's phase, so a block pushed ahead is always the next one rendered
+        self.gk += 1
+        j = k % self.pool
+        if self.pan_overlap:
+            if self.mdap_issued != k:
+                self._issue_mdap(k, False)
+            if not self.fused_update:
+                self.stream.wait_event(self.ev_mdap[k & 1])
+                self.rend.UpdateParameters(self.v_band[j], self.v_delay[j], self.d_mix_bg[k & 1])
+                self.ev_upd.record(self.stream)
+        elif self.fused_update:
+            self.rend.UpdatePanned(self.pan, self.lay, self.v_params[j], self.v_band[j], self.v_delay[j])
+        else:
+            self.pan.ProcessVBAPData(self.lay, self.v_params[j], out=self.d_mix)
+            self.rend.UpdateParameters(self.v_band[j], self.v_delay[j], self.d_mix)
+        if self.use_peer:
+            # every rank's k_bus_reduce result goes straight into the root GPU's gather buffer (peer stores over NVLink); the root adds the
+            # slots in rank order. No collective library on the data path.
+            self.rend.ProcessInterleaved(self.v_audio[j], self.local_bus, FRAMES)
+            self.exchange.submit(self.bus_ptr, self.bus_floats, self.seq, out=self.peer_out)
+            self.seq += 1
+        else:
+            with torch.cuda.stream(self.stream):       # torch ops (the bus zero-fill, NCCL's stream ordering) follow torch's current stream
+                bus = self.reducer.begin(k)
+                self.rend.ProcessInterleaved(self.v_audio[j], bus, FRAMES)
+                self.reducer.submit(k)
+        if self.push_ahead:
+            # offline rendering: block k+1's input is resident, so its ring pushes (an HBM-bound copy) are issued right after block k's render
+            # has been enqueued and run beside it on the SMs the render leaves free; block k only waits for the pushes issued one step earlier
+            self.rend.PushAhead(self.v_audio[(k + 1) % self.pool], FRAMES)
+        if self.pan_overlap:
+            self._issue_mdap(k + 1, True)
+
+    def barrier(self):
+        torch = self.env.torch
+        with torch.cuda.stream(self.stream):
+            self.join_pan()
+            self.reducer.drain()
+            if self.exchange is not None:
+                self.exchange.wait()
+        if self.env.dist is not None:
+            self.env.dist.barrier()
+        torch.cuda.synchronize()
+
+    def join_tail(self):
+        """everything the timed steps started (panning data one block ahead, reduces, the peer combine) joins the context stream"""
+        torch = self.env.torch
+        with torch.cuda.stream(self.stream):
+            self.join_pan()
+            self.reducer.drain()
+            if self.exchange is not None:
+                self.exchange.wait()
+
+    def launches(self):
+        return self.ctx.launch_count + (self.ctx_pan.launch_count if self.pan_overlap else 0)
+
+    def last_bus(self):
+        return self.final_bus if self.use_peer else self.reducer.result(self.gk - 1)
+
+    def timed(self, steps):
+        """K steps bracketed by events on the context stream, everything they started joined before the stop event; returns ms in total"""
+        torch = self.env.torch
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        self.barrier()
+        with torch.cuda.stream(self.stream):
+            ev0.record(self.stream)
+        t_host0 = time.perf_counter()
+        for _ in range(steps):
+            self.step()
+        self.host_ms_step = (time.perf_counter() - t_host0) * 1e3 / steps     # host time to enqueue a step: must stay below the device's step time
+        self.join_tail()
+        with torch.cuda.stream(self.stream):
+            ev1.record(self.stream)
+        self.barrier()
+        return ev0.elapsed_time(ev1)
+
+    def check_bus(self):
+        """N > 1: one more block; the combined bus on rank 0 must equal the RANK-ORDERED float sum of the per-rank partial buses bit for bit
+        (peer combine) / within the fp32 summation bound (NCCL). Returns (label, ok)."""
+        env, torch = self.env, self.env.torch
+        if env.dist is None:
+            return "single GPU (no combine)", True
+        self.barrier()
+        self.step()
+        self.barrier()
+        # the renderer's device bus holds exactly this rank's partial sum of the last block (everything has been synchronised by the barrier)
+        part = torch.as_tensor(_DeviceFloats(self.bus_ptr, FRAMES * L_OUT), device=env.dev).clone().reshape(FRAMES, L_OUT)
+        torch.cuda.synchronize()
+        parts = [torch.zeros_like(part) for _ in range(env.world)]
+        env.dist.all_gather(parts, part)
+        ok, label = True, ""
+        if env.rank == 0:
+            want = parts[0].clone()
+            for r in range(1, env.world):
+                want = want + parts[r]                  # rank order, float32
+            if self.use_peer:
+                got = self.final_bus
+                ok = bool(torch.equal(got.view(torch.int32), want.view(torch.int32))) and bool(want.abs().max().item() > 0)
+                label = "bit-equal" if ok else f"MISMATCH max abs {float((got - want).abs().max().item()):.3e}"
+            elif self.args.bus == "nccl":
+                got = self.reducer.result(self.gk - 1)
+                bound = 4.0 * float(np.finfo(np.float32).eps) * sum(p.abs().double() for p in parts) + 1e-12
+                ok = bool(((got.double() - sum(p.double() for p in parts)).abs() <= bound).all().item())
+                label = "within fp32 summation bound (NCCL reduce order)" if ok else "MISMATCH"
+            else:
+                label = "not combined (--bus none)"
+        flag = torch.tensor([0 if ok else 1], device=env.dev)
+        env.dist.all_reduce(flag)
+        return label, int(flag.item()) == 0
+
+    def close(self):
+        for o in (getattr(self, "exchange", None), self.rend):
+            if o is not None:
+                o.close()
+        if self.pan_overlap:
+            self.ctx_pan.synchronize()
+            self.ctx_pan.close()
+        self.ctx.synchronize()
+        self.ctx.close()
+
+
+def tile_pool(torch, arrays, reps, pool):
+    """capacity inputs: the 16,384-source pool tiled `reps` times along the source axis, a different pool block per tile (resident in HBM)"""
+    audio, params, band, delay = arrays
+    P = audio.shape[0]
+    out = []
+    for a in (audio, params, band, delay):
+        out.append(torch.stack([torch.cat([a[(j + i) % P] for i in range(reps)], dim=0) for j in range(pool)]))
+    return out
+
+
+def run_config3(args):
+    env = Env(args)
+    torch, J = env.torch, env.J
+    rank, world, dev = env.rank, env.world, env.dev
+    N = args.sources
+    audio, params, band, delay = make_inputs(N, args.pool, 0xB200 + rank)
+    d_arrays = [torch.from_numpy(a).to(dev) for a in (audio, params, band, delay)]
+    torch.cuda.synchronize()
+    pipe = Config3Pipeline(env, args, N, args.ring, d_arrays, args.schedule)
+    ctx = pipe.ctx
+
+    # ---- device-resident timing of the K steps (`ms_per_step`)
+    sampler = ClockSampler(env.local)
+    sampler.start()
+    for _ in range(args.warmup):
+        pipe.step()
+    pipe.barrier()
+    # only the dominant kernel is bracketed by events inside the timed region (two event records per step); the per-kernel
+    # breakdown of the other kernels is taken in a separate short pass afterwards so its events do not stretch the timed steps
+    ctx.set_kernel_timing(True, only=("render",))
+    ctx.reset_kernel_timing()
+    launches0 = pipe.launches()
+    ms_total = pipe.timed(args.steps)
+    host_ms_step = pipe.host_ms_step
+    # fingerprint of the last timed block's (combined) bus: the same for every pipelining option at equal --warmup / --steps / --pool / --gpus
+    bus_crc = zlib.crc32(pipe.last_bus().cpu().numpy().tobytes()) if rank == 0 else 0
+    launches = pipe.launches() - launches0  # our kernels only (torch's bus zero-fill and NCCL are not counted)
+    ktimes = {"render": ctx.kernel_time("render")}
+    ctx.set_kernel_timing(False)
+    bsteps = max(10, min(args.steps, 40))
+    ctx.set_kernel_timing(True)
+    ctx.reset_kernel_timing()
+    if pipe.pan_overlap:
+        pipe.ctx_pan.set_kernel_timing(True)
+        pipe.ctx_pan.reset_kernel_timing()
+    for _ in range(bsteps):
+        pipe.step()
+    pipe.barrier()
+    breakdown = {name: ctx.kernel_time(name) for name in ("mdap", "update", "push", "render", "bus_reduce")}
+    ctx.set_kernel_timing(False)
+    if pipe.pan_overlap:
+        # measured while sharing the device with k_render (and the pushes): a duration under overlap, not the kernel's own cost
+        breakdown["mdap"] = pipe.ctx_pan.kernel_time("mdap")
+        pipe.ctx_pan.set_kernel_timing(False)
+    per_rank_ms = [x / args.steps for x in env.gather_floats(ms_total)]
+    ms_step = env.max_over_ranks(ms_total) / args.steps
+    value_c3 = N * world * BLOCK_S / (ms_step * 1e-3)
+
+    # ---- N > 1: the combined bus against the rank-ordered sum of the partial buses
+    bus_check, bus_ok = pipe.check_bus()
+
+    # ---- offline (packed) schedule for comparison: block k+1's pushes beside block k's render
+    offline = None
+    if args.schedule == "realtime" and not args.no_offline:
+        pipe.push_ahead = not args.no_push_ahead
+        for _ in range(max(3, args.warmup // 2)):
+            pipe.step()
+        osteps = max(20, min(args.steps, 100))
+        ms_off = env.max_over_ranks(pipe.timed(osteps)) / osteps
+        offline = {"ms_per_step": ms_off, "value": N * world * BLOCK_S / (ms_off * 1e-3), "steps": osteps,
+                   "note": "packed schedule: block k+1's ring pushes issued beside block k's render (jplg_renderer_push_ahead); needs the next block's "
+                           "input one block early, so offline rendering only; value = sources x block duration / step time (linear extrapolation from "
+                           f"{N} sources per GPU, not a capacity measurement)"}
+        pipe.push_ahead = False
+        pipe.barrier()
+
+    # ---- end to end through the C-ABI with HOST (pinned) buffers: H2D of the step's inputs and D2H of the bus inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        e2e = run_e2e(env, args, pipe, (audio, params, band, delay))
+
+    # FP32 lane rate of this GPU (the ceiling the fused render is bound by), measured live
+    fp32 = None
+    try:
+        fp32 = ctx.probe_fp32_lane_rate()
+    except Exception as e:
+        log("fp32 probe failed:", e)
+    ring_used = pipe.rend.ring_size
+    pipe.close()
+    del pipe, d_arrays
+    torch.cuda.empty_cache()
+
+    # ---- capacity: the largest source count actually rendered inside the block period (real-time schedule)
+    capacity = None
+    if not args.no_capacity:
+        capacity = run_capacity(env, args, (audio, params, band, delay))
+
+    # a short run (--no-e2e, few steps) can end before nvidia-smi has delivered its first line: wait for one (bounded)
+    t_end = time.time() + 3.0
+    while sampler.proc is not None and sampler.count() == 0 and time.time() < t_end:
+        time.sleep(0.05)
+    clocks = sampler.stop()
+    if rank != 0:
+        env.finish()
+        if not bus_ok:
+            raise SystemExit(3)
+        return
+
+    # ---- roofline of the dominant kernel (k_render), measured live with CUDA events on the launching stream
+    peak, peak_src = hbm_peak()
+    r_ms, r_n = ktimes["render"]
+    r_avg_ms = r_ms / max(r_n, 1)
+    achieved_gbs = RENDER_BYTES_PER_SOURCE * N / (r_avg_ms * 1e-3) / 1e9
+    ncu_traffic = None
+    tpath = os.path.join(ROOT, "profiles", "render_traffic.json")
+    if os.path.exists(tpath):
+        try:
+            ncu_traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
+        except Exception:
+            pass
+    flops = RENDER_FLOPS_PER_SOURCE_SAMPLE * N * FRAMES
+    achieved_tf = flops / (r_avg_ms * 1e-3) / 1e12
+    fp32_peak_tf = (fp32["lane_ops_per_s"] / 1e12) if fp32 else 148 * 128 * 1.965e9 / 1e12
+    roofline = {"bound": "fp32", "kernel": "k_render", "achieved": achieved_tf, "peak": fp32_peak_tf, "unit": "TFLOP/s", "frac": achieved_tf / fp32_peak_tf,
+                "traffic": ncu_traffic, "avg_launch_ms": r_avg_ms,
+                "peak_source": ("measured live: jplg_context_probe_fp32 (packed FMUL2 / FFMA2 stream on every SM, one multiply or add per lane and issue — "
+                                "the parity arithmetic has no fused operations)" if fp32 else "nominal 148 SMs x 128 lanes x 1.965 GHz"),
+                "algorithmic_flops_per_launch": flops,
+                "flops_note": f"{RENDER_FLOPS_PER_SOURCE_SAMPLE} FP32 operations of the reference's arithmetic per source-sample (bench.py RENDER_FLOPS_PER_SOURCE_SAMPLE, DESIGN.md §5)",
+                "hbm": {"bound": "hbm", "achieved": achieved_gbs, "peak": peak, "unit": "GB/s", "frac": achieved_gbs / peak, "traffic": ncu_traffic,
+                        "peak_source": peak_src, "algorithmic_bytes_per_launch": RENDER_BYTES_PER_SOURCE * N,
+                        "whole_step_gbs": STEP_BYTES_PER_SOURCE * N / (ms_step * 1e-3) / 1e9,
+                        "note": "the fused render moves 2.5 KB and executes ~100 K FP32 operations per source-block (~40 op/B, the B200 FP32:HBM ridge is ~5.7): "
+                                "its HBM fraction is small by construction, see DESIGN.md §5"},
+                "kernel_ms_per_step": {k: v[0] / max(bsteps, 1) for k, v in breakdown.items()},
+                "kernel_ms_per_step_note": f"separate pass of {bsteps} steps with every kernel bracketed by events (not part of the timed region)"}
+
+    cpu = None
+    if not args.no_cpu_baseline and world == 1:
+        try:
+            cpu = cpu_baseline_sample(log)
+        except Exception as e:  # the checker is optional at bench time
+            log("cpu baseline failed:", e)
+
+    if capacity is not None:
+        value = capacity["value"]
+        value_src = capacity["value_source"]
+    else:
+        value = value_c3
+        value_src = f"sources x block duration / step time at {N} sources per GPU (linear extrapolation; run without --no-capacity for the measured capacity)"
+    use_peer = world > 1 and args.bus == "peer"
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "BASELINE config 3: full block render, 16,384 mono sources per GPU -> 7.1.4, 48 kHz / 512 frames "
+                               "(MDAP gains + update + push + fused delay/LR4/mix + bus reduce per block)",
+                   "sources_per_gpu": N, "total_sources": N * world, "mode": args.mode, "ring_size": ring_used,
+                   "schedule": args.schedule, "value_source": value_src,
+                   "value_at_workload_size": value_c3,
+                   "capacity": capacity, "offline_schedule": offline,
+                   "host_numa_node": env.numa,
+                   "pipelining": {"push_ahead": args.schedule == "packed" and not args.no_push_ahead, "pan_overlap": not args.no_pan_overlap, "fused_update": not args.no_fused_update,
+                                  "note": "every step runs every kernel of the block once; the panning data of block k+1 is produced on a lower-priority "
+                                          "stream while block k renders (game thread beside audio thread)"},
+                   "l2_policy": f"inputs larger than L2: {args.pool} distinct 33.5 MB input blocks cycled, {N * ring_used * 4 / 2**30:.1f} GiB of rings",
+                   "parallelism": (f"sources sharded over {world} GPU(s); partial [512x12] buses stored into the root GPU's gather buffer over NVLink peer memory and summed in rank order (jplg_bus_exchange, no collective library on the data path)"
+                                   if use_peer else "DIAGNOSTIC: independent replicas, buses NOT combined" if args.bus == "none" else f"sources sharded over {world} GPU(s); NCCL reduce of the [512x12] bus, double-buffered (block k reduce overlaps block k+1 render)") if world > 1 else "single GPU"},
+        "per_rank_ms_per_step": [round(x, 5) for x in per_rank_ms], "host_enqueue_ms_per_step": round(host_ms_step, 5), "bus_crc32": f"{bus_crc:08x}",
+        "bus_check": bus_check, "clocks": clocks, "gpu_launches": launches, "e2e": e2e, "roofline": roofline, "cpu_baseline": cpu,
+    }
+    _emit(line)
+    env.finish()
+    if not bus_ok:
+        raise SystemExit(f"bench.py: combined bus check failed: {bus_check}")
+
+
+def run_e2e(env, args, pipe, host_arrays):
+    """the same step through the C ABI with pinned HOST buffers (JPLG_MEM_HOST_ASYNC), host<->device copies inside the timed region"""
+    torch = env.torch
+    rank, world, dev = env.rank, env.world, env.dev
+    audio, params, band, delay = host_arrays
+    N = pipe.N
+    rend, pan, lay, stream, ctx = pipe.rend, pipe.pan, pipe.lay, pipe.stream, pipe.ctx
+    use_peer, exchange = pipe.use_peer, pipe.exchange
+    dist = env.dist
+
+    def pinned(a):
+        t_ = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
+        return t_, t_.numpy()
+    keep = []
+    h_audio, h_params, h_band, h_delay = [], [], [], []
+    for j in range(args.pool):
+        for src, dst in ((audio[j], h_audio), (params[j], h_params), (band[j], h_band), (delay[j], h_delay)):
+            tt, nn = pinned(src); keep.append(tt); dst.append(nn)
+    tt, h_mix = pinned(np.zeros((N, 1, L_OUT), np.float32)); keep.append(tt)
+    tt, h_bus = pinned(np.zeros((FRAMES, L_OUT), np.float32)); keep.append(tt)
+    d_partial = torch.zeros((FRAMES, L_OUT), dtype=torch.float32, device=dev)
+
+    # two bus slots: block k is submitted (JPLG_MEM_HOST_ASYNC: nothing waits on the host, the 33.5 MB input transfer runs on the library's copy
+    # stream while block k-1 renders) and then block k-1 is collected; every step still moves its own inputs H2D and its own bus D2H
+    tb, h_bus2 = pinned(np.zeros((FRAMES, L_OUT), np.float32)); keep.append(tb)
+    h_buses = (h_bus, h_bus2)
+    if use_peer:
+        with torch.cuda.stream(stream):
+            d_final2 = [torch.zeros((FRAMES, L_OUT), dtype=torch.float32, device=dev) for _ in range(2)]
+        t_final, h_final = [], []
+        for _ in range(2):
+            tt, nn = pinned(np.zeros((FRAMES, L_OUT), np.float32)); t_final.append(tt); h_final.append(nn)
+        ev_final = [torch.cuda.Event() for _ in range(2)]
+        ev_read = [torch.cuda.Event() for _ in range(2)]
+        rd_stream = torch.cuda.Stream(device=dev)
+        ctx.synchronize()
+
+    def submit_host(k):
+        j = k % args.pool
+        hb = h_buses[k & 1]
+        pan.ProcessVBAPData(lay, h_params[j], out=h_mix, async_host=True)          # H2D params, D2H mix maps (enqueued)
+        rend.UpdateParameters(h_band[j], h_delay[j], h_mix, async_host=True)        # H2D
+        hb[:] = 0.0
+        rend.ProcessInterleaved(h_audio[j], hb, FRAMES, async_host=True)            # H2D audio (copy stream) + bus, D2H bus
+        if use_peer:
+            # N > 1: the partial buses are combined on the device (peer-memory exchange, as in the device-resident pass) and the root reads the
+            # combined bus back; the other ranks' own partial buses still travel D2H with their blocks
+            exchange.submit(pipe.bus_ptr, pipe.bus_floats, pipe.seq, out=d_final2[k & 1] if rank == 0 else None)
+            pipe.seq += 1
+            if rank == 0:
+                exchange.wait()
+                ev_final[k & 1].record(stream)
+                # read-back on a torch-owned stream (torch's pinned-memory allocator remembers the streams a pinned block was used on, and the
+                # library's stream dies with its context)
+                rd_stream.wait_event(ev_final[k & 1])
+                with torch.cuda.stream(rd_stream):
+                    t_final[k & 1].copy_(d_final2[k & 1], non_blocking=True)
+                    ev_read[k & 1].record(rd_stream)
+
+    def collect_host(k):
+        rend.WaitBlock()
+        hb = h_buses[k & 1]
+        if use_peer:
+            if rank == 0:
+                ev_read[k & 1].synchronize()
+                return float(h_final[k & 1][0, 0])
+        elif dist is not None and args.bus != "none":
+            d_partial.copy_(torch.from_numpy(hb))
+            dist.reduce(d_partial, dst=0)
+            if rank == 0:
+                hb[:] = d_partial.cpu().numpy()
+        return float(hb[0, 0])
+
+    e2e_steps = max(10, min(args.steps, 100))
+    # warm-up: the device-resident pass above left the PCIe link idle for ~a second and the first tens of transfers after that run at a fraction
+    # of the link's rate (measured on these boxes: 16-40 GB/s for the first copies, 50-55 GB/s once it has ramped up)
+    e2e_warm = max(args.warmup, 30)
+    pipe.barrier()          # every rank has pinned its buffers before anybody enters the exchange (ranks pin ~270 MB each at different speeds)
+    for k in range(e2e_warm):
+        submit_host(k)
+        if k:
+            collect_host(k - 1)
+    collect_host(e2e_warm - 1)
+    pipe.barrier()
+    t0 = time.perf_counter()
+    for k in range(e2e_steps):
+        submit_host(e2e_warm + k)
+        if k:
+            collect_host(e2e_warm + k - 1)
+    collect_host(e2e_warm + e2e_steps - 1)
+    pipe.barrier()
+    dt = env.max_over_ranks((time.perf_counter() - t0) / e2e_steps)
+    if exchange is not None and exchange.error() != 0:
+        raise SystemExit(f"bench.py: bus exchange reported a device-side wait timeout (error {exchange.error()}) on rank {rank}")
+    h2d = N * FRAMES * 4 + N * 20 + N * 16 + N * 4 + N * L_OUT * 4 + FRAMES * L_OUT * 4
+    d2h = N * L_OUT * 4 + FRAMES * L_OUT * 4 + (FRAMES * L_OUT * 4 if use_peer else 0)     # per rank; the last term is the root's combined bus
+    return {"value": N * world * BLOCK_S / dt, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+            "ms_per_step": dt * 1e3, "steps": e2e_steps,
+            "path": "C ABI with pinned HOST buffers, JPLG_MEM_HOST_ASYNC: block k+1's input transfer overlaps block k's render (2 blocks in flight); the audio goes through the copy engine, the small arrays and the bus are read / written by the kernels through the buffers' device alias (same bytes over PCIe)"
+                    + ("; N > 1: partial buses combined on the device by the peer-memory exchange, the root reads the combined bus back" if use_peer else ""),
+            "note": "value = sources x block duration / step time at 16,384 sources per GPU: the step is the PCIe transfer of the block's 33.5 MB of input audio, "
+                    "which is linear in the number of sources"}
+
+
+def run_capacity(env, args, host_arrays):
+    """Renders N_cap sources per GPU per block in the real-time schedule and reports the measured ms per block: `value` is the largest N_cap that
+    stayed inside the 10.667 ms block period (the metric's definition), at the REFERENCE ring size (bit_ceil(2 fs) samples per
+    source, DirectSound.cpp:79). A second pass with rings sized for this scene's longest delay shows the compute-limited side."""
+    torch = env.torch
+    dev, world = env.dev, env.world
+    audio, params, band, delay = host_arrays
+    base_n = audio.shape[1]
+    free_b, total_b = torch.cuda.mem_get_info()
+    passes = []
+    plan = []
+    ref_ring = 131072
+    scene_ring = 65536            # longest delay of the synthetic scene: 300 m + 8 blocks x 30 m/s ~ 0.88 s = 42 k samples
+    for ring, label in ((ref_ring, "reference ring: bit_ceil(2 x 48000) = 131,072 samples (2.7 s) per source"),
+                        (scene_ring, "ring sized for the scene's longest delay: 65,536 samples (1.37 s, 468 m) per source")):
+        per_source = ring * 4 + 2 * FRAMES * 4 + 1024            # ring + two input pool blocks + state / targets / mix maps
+        reps = int((free_b - (6 << 30)) // (per_source * base_n))
+        if args.capacity_sources:
+            reps = min(reps, max(1, args.capacity_sources // base_n))
+        if reps >= 1:
+            plan.append((ring, label, reps))
+    d_base = [torch.from_numpy(a).to(dev) for a in (audio, params, band, delay)]
+    for ring, label, reps in plan:
+        n_cap = reps * base_n
+        try:
+            arrays = tile_pool(torch, d_base, reps, 2)
+            torch.cuda.synchronize()
+            pipe = Config3Pipeline(env, args, n_cap, ring, arrays, "realtime", use_exchange=False)
+            for _ in range(3):
+                pipe.step()
+            steps = 12
+            ms = env.max_over_ranks(pipe.timed(steps)) / steps
+            passes.append({"ring_size": ring, "ring": label, "sources_per_gpu": n_cap, "total_sources": n_cap * world, "ms_per_block": ms, "steps": steps,
+                           "inside_block_period": ms <= BLOCK_S * 1e3, "real_time_multiple": BLOCK_S * 1e3 / ms,
+                           "ring_gib_per_gpu": n_cap * ring * 4 / 2**30,
+                           "compute_limited_sources": n_cap * world * BLOCK_S * 1e3 / ms})
+            pipe.close()
+            del pipe, arrays
+        except Exception as e:
+            passes.append({"ring_size": ring, "ring": label, "sources_per_gpu": n_cap, "error": str(e)[:200]})
+        torch.cuda.empty_cache()
+    del d_base
+    torch.cuda.empty_cache()
+    ok = [p for p in passes if p.get("inside_block_period")]
+    if not ok:
+        return None
+    head = ok[0]              # the reference ring size is the headline; the scene-sized ring is reported beside it
+    return {"value": head["total_sources"],
+            "value_source": (f"capacity pass: {head['sources_per_gpu']} sources per GPU x {world} GPU(s) rendered per 512-frame block in {head['ms_per_block']:.3f} ms "
+                             f"(< 10.667 ms) in the real-time schedule at the {head['ring']}; memory-limited ({head['ring_gib_per_gpu']:.0f} GiB of rings per GPU), "
+                             f"the arithmetic would allow {head['compute_limited_sources']:.0f}"),
+            "schedule": "realtime (no push-ahead; panning data one block ahead on the background context)",
+            "inputs": f"the {base_n}-source pool tiled along the source axis (a different pool block per tile), 2 input blocks cycled (> L2), N > 1: independent ranks (the bus combine is timed in the K steps)",
+            "memory_limited_sources": head["total_sources"], "compute_limited_sources": head["compute_limited_sources"],
+            "passes": passes}
+
+
+# ------------------------------------------------------------------------------------------------
+# the other BASELINE configurations: short device-resident passes with their own JSON line (same contract keys)
+def _simple_line(args, env, metric, unit, value, ms_step, workload, extra, launches, clocks, dtype="f32"):
+    return {"metric": metric, "value": value, "unit": unit, "n_gpus": env.world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": dtype, "data": "synthetic",
+            "config": dict({"workload": workload, "mode": args.mode}, **extra), "clocks": clocks, "gpu_launches": launches}
+
+
+def run_gains_config(args):
+    """configs 1 and 2: gains only"""
+    env = Env(args)
+    torch, J = env.torch, env.J
+    from tests import util
+    ctx = J.Context(env.local)
+    stream = ctx.torch_stream()
+    M = J.ChannelMask
+    sampler = ClockSampler(env.local); sampler.start()
+    pan = J.VBAPanner(ctx)
+    if args.config == 1:
+        assert pan.Initialize(M.Quad)
+        n = 360
+        ang = np.deg2rad(np.arange(n, dtype=np.float32))
+        dirs = np.stack([np.sin(ang), np.zeros(n, np.float32), -np.cos(ang)], 1).astype(np.float32)
+        with torch.cuda.stream(stream):
+            d_in = torch.from_numpy(dirs).to(env.dev); d_out = torch.empty((n, 4), dtype=torch.float32, device=env.dev)
+        call = lambda: pan.GetSpeakerGains(d_in, out=d_out)
+        workload = "BASELINE config 1: HelloJPLSpatial, 360 directions around a quad layout (VBAP point gains)"
+        unit_n, metric, unit = n, "VBAP gain evaluations per second (point sources)", "gains/s"
+        bytes_per_unit = 12 + 16
+    else:
+        assert pan.Initialize(M.Surround_7_1_4)
+        lay = pan.InitializeSourceLayout(M.Mono)
+        n = 65536
+        pools = [util.pan_params(n, 0xC2 + k + 100 * env.rank, edge=False) for k in range(4)]
+        with torch.cuda.stream(stream):
+            d_pool = [torch.from_numpy(p).to(env.dev) for p in pools]; d_out = torch.empty((n, 1, L_OUT), dtype=torch.float32, device=env.dev)
+        it = [0]
+
+        def call():
+            pan.ProcessVBAPData(lay, d_pool[it[0] & 3], out=d_out); it[0] += 1
+        workload = "BASELINE config 2: MDAP spread/focus gain evaluation, 65,536 mono sources per GPU -> 7.1.4 (72 virtual sources each, gains only)"
+        unit_n, metric, unit = n, "MDAP source evaluations per second (65,536 sources -> 7.1.4)", "sources/s"
+        bytes_per_unit = 20 + 48
+    ctx.synchronize()
+    for _ in range(args.warmup):
+        call()
+    ctx.synchronize()
+    l0 = ctx.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if env.dist is not None:
+        env.dist.barrier()
+    torch.cuda.synchronize()
+    with torch.cuda.stream(stream):
+        e0.record(stream)
+    for _ in range(args.steps):
+        call()
+    with torch.cuda.stream(stream):
+        e1.record(stream)
+    torch.cuda.synchronize()
+    ms = env.max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    launches = ctx.launch_count - l0
+    clocks = sampler.stop()
+    if env.rank == 0:
+        peak, peak_src = hbm_peak()
+        gbs = bytes_per_unit * unit_n / (ms * 1e-3) / 1e9
+        line = _simple_line(args, env, metric, unit, unit_n * env.world / (ms * 1e-3), ms, workload,
+                            {"units_per_gpu": unit_n, "parallelism": "independent sources, no exchange" if env.world > 1 else "single GPU",
+                             "l2_policy": "inputs are 1.3 MB (L2 resident by nature): the kernel is issue-bound, not memory-bound"}, launches, clocks)
+        line["roofline"] = {"bound": "hbm", "kernel": "k_mdap_3d" if args.config == 2 else "k_point_gains_2d", "achieved": gbs, "peak": peak, "unit": "GB/s",
+                            "frac": gbs / peak, "traffic": None, "peak_source": peak_src,
+                            "note": "68 B of traffic per source against ~4,500 FP32 instructions: issue-bound (DESIGN.md §4)"}
+        _emit(line)
+    ctx.close()
+    env.finish()
+
+
+C4_LAYOUTS = (("Mono", 1, 288), ("Stereo", 2, 288), ("Quad", 4, 240), ("Surround_5_1", 6, 240))   # name, rendered channels, virtual sources per source -> 9.1.6
+# per-source cost model of the weighted sharding (measured, DESIGN.md §7): 6.3 ns per rendered source-channel-block + 0.027 ns per virtual source
+C4_COST = lambda ch, vs: 6.3 * ch + 0.027 * vs
+
+
+def run_config4(args):
+    """BASELINE config 4: multichannel sources -> 9.1.6. Global source list = four equal segments (mono, stereo, quad, 5.1) of 8,192 x world sources;
+    contiguous cost-weighted shards (sharding.shard_range); every rank builds one renderer per layout piece it owns; the [512][16] buses of a rank's
+    renderers are added in layout order, the ranks' buses are combined by the peer exchange (bit-checked against the rank-ordered sum)."""
+    env = Env(args)
+    torch, J = env.torch, env.J
+    from tests import util
+    from jplspatial_b200.sharding import shard_range, make_peer_bus_exchange
+    M = J.ChannelMask
+    rank, world, dev = env.rank, env.world, env.dev
+    L = 16
+    per_layout = args.c4_per_layout * world
+    total = 4 * per_layout
+    weights = []
+    for _, ch, vs in C4_LAYOUTS:
+        weights += [C4_COST(ch, vs)] * per_layout
+    begin, end = shard_range(total, world, rank, weights)
+    ctx = J.Context(env.local)
+    stream = ctx.torch_stream()
+    ctx_pan = J.Context(env.local, background=True)
+    sampler = ClockSampler(env.local); sampler.start()
+    units = []
+    for li, (name, C, _vs) in enumerate(C4_LAYOUTS):
+        lo, hi = max(begin, li * per_layout), min(end, (li + 1) * per_layout)
+        if hi <= lo:
+            continue
+        n = hi - lo
+        uctx = J.Context(env.local)                     # one context (= one stream) per layout: the renderers' grids overlap instead of leaving tails
+        pan = J.VBAPanner(ctx_pan); assert pan.Initialize(M.Surround_9_1_6)
+        lay = pan.InitializeSourceLayout(getattr(M, name))
+        seed = 0xC4 + 7919 * li + lo
+        params = np.stack([util.pan_params(n, seed + 10 * b, edge=False) for b in range(2)])
+        band = (0.1 + 0.9 * util.uniform01(2 * n * 4, seed + 1)).reshape(2, n, 4).astype(np.float32)
+        delay = ((1.0 + 299.0 * util.uniform01(2 * n, seed + 2)) / 343.2).reshape(2, n).astype(np.float32)
+        audio = util.white_noise((2, n, FRAMES, C), seed + 3)
+        rend = J.DirectSoundBatch(uctx, FS, n, C, L, band[0], delay[0], np.zeros((n, C * L), np.float32), ring_size=args.ring, max_block_frames=FRAMES, mode=env.mode)
+        ust = uctx.torch_stream()
+        with torch.cuda.stream(ust):
+            u = dict(name=name, C=C, n=n, ctx=uctx, stream=ust, pan=pan, lay=lay, rend=rend,
+                     bus=torch.zeros((FRAMES, L), dtype=torch.float32, device=dev), done=torch.cuda.Event(),
+                     params=torch.from_numpy(params).to(dev), band=torch.from_numpy(band).to(dev), delay=torch.from_numpy(delay).to(dev),
+                     audio=torch.from_numpy(audio).to(dev))
+        uctx.synchronize()
+        units.append(u)
+    with torch.cuda.stream(stream):
+        bus = torch.zeros((FRAMES, L), dtype=torch.float32, device=dev)
+        final = torch.zeros((FRAMES, L), dtype=torch.float32, device=dev)
+    exchange = make_peer_bus_exchange(ctx, FRAMES * L) if world > 1 else None
+    seq = [0]
+    pan_stream = ctx_pan.torch_stream()
+    ctx.synchronize()
+    kcount = [0]
+
+    def issue_pan(k):
+        j = k & 1
+        # no jplg_renderer_wait_render_started here: with 800+ CTAs queued on 148 SMs the last layout's grid is only fully resident near the end of the
+        # block, which would push the panning kernels behind the renders they are meant to run beside (the low stream priority orders them instead)
+        for u in units:
+            u["rend"].UpdatePanned(u["pan"], u["lay"], u["params"][j], u["band"][j], u["delay"][j])
+
+    def step():
+        k = kcount[0]; kcount[0] += 1
+        j = k & 1
+        if k == 0:
+            issue_pan(0)
+        with torch.cuda.stream(stream):
+            start = torch.cuda.Event(); start.record(stream)
+        for u in units:
+            st = u["stream"]
+            st.wait_event(start)        # the previous block's sum has read this unit's bus
+            with torch.cuda.stream(st):
+                u["bus"].zero_()
+            u["rend"].ProcessInterleaved(u["audio"][j], u["bus"], FRAMES)
+            u["done"].record(st)
+        issue_pan(k + 1)                # the next block's panning data, on the background context beside the renders
+        with torch.cuda.stream(stream):
+            for u in units:
+                stream.wait_event(u["done"])
+            bus.zero_()
+            for u in units:
+                bus.add_(u["bus"])      # fixed (layout) order
+        if exchange is not None:
+            exchange.submit(bus.data_ptr(), FRAMES * L, seq[0], out=final if rank == 0 else None)
+            seq[0] += 1
+
+    def barrier():
+        with torch.cuda.stream(stream):
+            stream.wait_stream(pan_stream)
+            if exchange is not None:
+                exchange.wait()
+        if env.dist is not None:
+            env.dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    l0 = sum(u["ctx"].launch_count for u in units) + ctx.launch_count + ctx_pan.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(stream):
+        e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    with torch.cuda.stream(stream):
+        stream.wait_stream(pan_stream)
+        if exchange is not None:
+            exchange.wait()
+        e1.record(stream)
+    barrier()
+    ms_rank = e0.elapsed_time(e1) / args.steps
+    ms = env.max_over_ranks(ms_rank)
+    per_rank = env.gather_floats(ms_rank)
+    launches = sum(u["ctx"].launch_count for u in units) + ctx.launch_count + ctx_pan.launch_count - l0
+    # combined bus of the last block against the rank-ordered float sum of the ranks' buses
+    bus_check, ok = "single GPU (no combine)", True
+    if env.dist is not None:
+        parts = [torch.zeros_like(bus) for _ in range(world)]
+        env.dist.all_gather(parts, bus)
+        if rank == 0:
+            want = parts[0].clone()
+            for r in range(1, world):
+                want = want + parts[r]
+            ok = bool(torch.equal(final.view(torch.int32), want.view(torch.int32))) and bool(want.abs().max().item() > 0)
+            bus_check = "bit-equal" if ok else f"MISMATCH max abs {float((final - want).abs().max().item()):.3e}"
+        flag = torch.tensor([0 if ok else 1], device=dev)
+        env.dist.all_reduce(flag)
+        ok = int(flag.item()) == 0
+        if exchange.error() != 0:
+            ok = False
+    shards = None
+    if env.dist is not None:
+        mine = [begin, end, sum(u["n"] * u["C"] for u in units)]
+        allm = [None] * world
+        env.dist.all_gather_object(allm, mine)
+        shards = allm
+    clocks = sampler.stop()
+    if rank == 0:
+        line = _simple_line(args, env, "real-time multichannel sources @48kHz/512-frame->9.1.6 (full block render)", UNIT, total * BLOCK_S / (ms * 1e-3), ms,
+                            f"BASELINE config 4: {total} multichannel sources ({per_layout} each of mono / stereo / quad / 5.1) -> 9.1.6 over {world} GPU(s), "
+                            "MDAP gains + fused update + push + render + bus reduce per block, real-time schedule",
+                            {"total_sources": total, "sources_this_rank": end - begin, "ring_size": units[0]["rend"].ring_size,
+                             "real_time_multiple": BLOCK_S * 1e3 / ms,
+                             "sharding": "contiguous cost-weighted ranges (sharding.shard_range, cost = 6.3 ns x channels + 0.027 ns x virtual sources per source)",
+                             "shards_begin_end_sourcechannels": shards,
+                             "parallelism": f"sources sharded over {world} GPU(s), peer-memory combine of the [512x16] bus" if world > 1 else "single GPU"},
+                            launches, clocks)
+        line["per_rank_ms_per_step"] = [round(x, 5) for x in per_rank]
+        line["bus_check"] = bus_check
+        _emit(line)
+    for u in units:
+        u["rend"].close()
+    env.finish()
+    if not ok:
+        raise SystemExit(f"bench.py --config 4: combined bus check failed: {bus_check}")
+
+
+def run_config5(args):
+    """BASELINE config 5: 4,096 x (ReverbBus FDN16 + ERBus with 16 taps), mono in -> 7.1.4"""
+    env = Env(args)
+    torch, J = env.torch, env.J
+    from tests import util
+    N, L, TAPS = 4096, L_OUT, 16
+    ctx = J.Context(env.local); stream = ctx.torch_stream(); dev = env.dev
+    sampler = ClockSampler(env.local); sampler.start()
+    x = util.white_noise((4, N, FRAMES), 5 + env.rank) * np.float32(0.5)
+    rt = (0.3 + 2.7 * util.uniform01(N * 4, 6)).reshape(N, 4).astype(np.float32)
+    rev = J.ReverbBusBatch(ctx, N, FS, L, mode=env.mode); rev.SetRT60(rt)
+    er = J.ERBusBatch(ctx, N, TAPS, FS, L, mode=env.mode)
+    u = util.uniform01(N * TAPS * (6 + L), 7).reshape(N, TAPS, 6 + L)
+    for i in range(N):
+        er.SetTaps(i, 0.1 + 0.9 * u[i, :, :4], 0.002 + 0.078 * u[i, :, 4], np.arange(1, TAPS + 1), u[i, :, 6:])
+    with torch.cuda.stream(stream):
+        d_x = torch.from_numpy(x).to(dev)
+        d_rev = torch.zeros((N, FRAMES, L), dtype=torch.float32, device=dev)
+        d_er = torch.zeros((N, FRAMES, L), dtype=torch.float32, device=dev)
+    ctx.synchronize()
+    it = [0]
+
+    def step():
+        k = it[0]; it[0] += 1
+        rev.ProcessInterleaved(d_x[k % 4], d_rev, FRAMES)
+        er.ProcessInterleaved(d_x[k % 4].reshape(N, FRAMES, 1), d_er, FRAMES)
+    for _ in range(args.warmup):
+        step()
+    ctx.synchronize()
+    if env.dist is not None:
+        env.dist.barrier()
+    l0 = ctx.launch_count
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.cuda.stream(stream):
+        e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    with torch.cuda.stream(stream):
+        e1.record(stream)
+    torch.cuda.synchronize()
+    ms = env.max_over_ranks(e0.elapsed_time(e1)) / args.steps
+    launches = ctx.launch_count - l0
+    clocks = sampler.stop()
+    if env.rank == 0:
+        line = _simple_line(args, env, "real-time reverb instances @48kHz/512-frame->7.1.4 (FDN16 + 16-tap ER bus)", "instances", N * env.world * BLOCK_S / (ms * 1e-3), ms,
+                            "BASELINE config 5: 4,096 x (16th-order FDN late reverb + early-reflection bus with 16 taps) per GPU, mono in -> 7.1.4, 48 kHz / 512 frames",
+                            {"instances_per_gpu": N, "parallelism": "independent instances, no exchange" if env.world > 1 else "single GPU"}, launches, clocks)
+        _emit(line)
+    ctx.close()
+    env.finish()
+
+
 def main():
     _claim_stdout()
     ap = argparse.ArgumentParser()
@@ -248,15 +1177,21 @@ def main():
     ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--config", type=int, default=3, choices=[1, 2, 3, 4, 5], help="BASELINE.json configuration (default 3: the contract line)")
     ap.add_argument("--mode", default="parity", choices=["parity", "throughput"])
+    ap.add_argument("--schedule", default="realtime", choices=["realtime", "packed"],
+                    help="realtime: a block's ring pushes are issued when the block is processed; packed: one block ahead beside the previous render (offline)")
     ap.add_argument("--sources", type=int, default=SOURCES_PER_GPU, help="sources per GPU")
     ap.add_argument("--ring", type=int, default=0, help="ring size per source (0 = reference value bit_ceil(2*fs) = 131072)")
     ap.add_argument("--pool", type=int, default=8, help="distinct input blocks cycled through (pool x 33.5 MB > L2)")
-    ap.add_argument("--ref-sources", type=int, default=2048)
+    ap.add_argument("--ref-sources", type=int, default=4096)
+    ap.add_argument("--capacity-sources", type=int, default=0, help="cap of the capacity pass's sources per GPU (0 = what fits in HBM)")
+    ap.add_argument("--c4-per-layout", type=int, default=8192, help="config 4: sources per layout and GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--no-push-ahead", action="store_true",
-                    help="issue every block's ring pushes inside process_block instead of one block ahead on a side stream (jplg_renderer_push_ahead)")
+    ap.add_argument("--no-capacity", action="store_true", help="skip the capacity pass (value then falls back to the linear figure at --sources)")
+    ap.add_argument("--no-offline", action="store_true", help="skip the comparison pass with the packed schedule")
+    ap.add_argument("--no-push-ahead", action="store_true", help="packed schedule without jplg_renderer_push_ahead (diagnostic)")
     ap.add_argument("--no-pan-overlap", action="store_true",
                     help="compute the panning data on the rendering context's stream instead of a background context (jplg_context_create_ex) "
                          "that works one block ahead on the SMs the render leaves free")
@@ -271,377 +1206,17 @@ def main():
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
-    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
-
     if args.impl == "reference":
         run_reference_arm(args, rank, world)
         return
-
-    import torch
-    import jplspatial_b200 as J
-
-    if not torch.cuda.is_available() or J.device_count() == 0:
-        raise SystemExit("bench.py: no CUDA device — this framework has no CPU fallback (use --impl reference for the CPU reference arm)")
-    torch.cuda.set_device(local_rank)
-    numa_node = bind_to_gpu_numa_node(torch, local_rank)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist_mod
-        dist = dist_mod
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-
-    N = args.sources
-    mode = J.MODE_PARITY if args.mode == "parity" else J.MODE_THROUGHPUT
-    ctx = J.Context(local_rank)
-    stream = ctx.torch_stream()
-    audio, params, band, delay = make_inputs(N, args.pool, 0xB200 + rank)
-    pan = J.VBAPanner(ctx)
-    assert pan.Initialize(J.ChannelMask.Surround_7_1_4)
-    lay = pan.InitializeSourceLayout(J.ChannelMask.Mono)
-    mix0 = pan.ProcessVBAPData(lay, params[0]).reshape(N, L_OUT)
-    rend = J.DirectSoundBatch(ctx, FS, N, 1, L_OUT, band[0], delay[0], mix0, ring_size=args.ring, max_block_frames=FRAMES, mode=mode)
-    dev = torch.device("cuda", local_rank)
-
-    with torch.cuda.stream(stream):
-        d_audio = torch.from_numpy(audio).to(dev)
-        d_params = torch.from_numpy(params).to(dev)
-        d_band = torch.from_numpy(band).to(dev)
-        d_delay = torch.from_numpy(delay).to(dev)
-        d_mix = torch.empty((N, 1, L_OUT), dtype=torch.float32, device=dev)
-    ctx.synchronize()
-
-    from jplspatial_b200.sharding import PipelinedBusReduce, make_peer_bus_exchange
-    # the only exchange of the path: the sum of the per-GPU partial buses ([512][12] floats per rank and block)
-    use_peer = dist is not None and args.bus == "peer"
-    # nccl mode: two bus buffers, the NCCL reduce of block k overlaps the render of block k+1
-    reducer = PipelinedBusReduce(FRAMES, L_OUT, dev, depth=2, dst=0)
-    if args.bus == "none":
-        reducer.submit = lambda k: None     # diagnostic only: N independent replicas, no combine (the line's `config.parallelism` says so)
-    exchange = make_peer_bus_exchange(ctx, FRAMES * L_OUT) if use_peer else None
-    with torch.cuda.stream(stream):
-        local_bus = torch.zeros((FRAMES, L_OUT), dtype=torch.float32, device=dev)
-        final_bus = torch.zeros((FRAMES, L_OUT), dtype=torch.float32, device=dev)
-    seq = [0]
-
-    push_ahead = not args.no_push_ahead
-    gk = [0]
-    # game-thread / audio-thread split of the reference (SpatialManager::AdvanceSimulation beside the audio callback): block k+1's panning data is
-    # computed by a background context while block k renders; its stream has the lower priority, so k_render's 128 CTAs are placed first and
-    # k_mdap_3d fills the remaining SMs. Two mix-map buffers; events order the two streams.
-    pan_overlap = not args.no_pan_overlap
-    fused_update = not args.no_fused_update       # panning kernel writes the renderer's next target set itself (jplg_renderer_update_panned)
-    if pan_overlap:
-        ctx_pan = J.Context(local_rank, background=True)
-        stream_pan = ctx_pan.torch_stream()
-        pan_bg = J.VBAPanner(ctx_pan)
-        assert pan_bg.Initialize(J.ChannelMask.Surround_7_1_4)
-        lay_bg = pan_bg.InitializeSourceLayout(J.ChannelMask.Mono)
-        with torch.cuda.stream(stream):
-            d_mix_bg = [torch.empty((N, 1, L_OUT), dtype=torch.float32, device=dev) for _ in range(2)]
-        ctx.synchronize()
-        ev_mdap = [torch.cuda.Event() for _ in range(2)]
-        ev_upd = torch.cuda.Event()
-        mdap_issued = [-1]
-
-        def issue_mdap(k, after_update):
-            # (the library enqueues on its contexts' own streams whatever torch's current stream is: no stream context managers in the step)
-            j = k % args.pool
-            if after_update:
-                if not fused_update:
-                    stream_pan.wait_event(ev_upd)  # the buffer's previous reader (update k-1) is older than this event
-                rend.WaitRenderStarted(ctx_pan)    # only once block k-1's render is resident: k_mdap_3d takes the SMs it leaves free
-            if fused_update:
-                rend.UpdatePanned(pan_bg, lay_bg, v_params[j], v_band[j], v_delay[j])      # the library orders it against the renders itself
-            else:
-                pan_bg.ProcessVBAPData(lay_bg, v_params[j], out=d_mix_bg[k & 1])
-            ev_mdap[k & 1].record(stream_pan)
-            mdap_issued[0] = k
-
-        def join_pan():
-            if mdap_issued[0] >= 0:
-                stream.wait_event(ev_mdap[mdap_issued[0] & 1])
-
-    # per-block views made once: the step itself is host-side plumbing and has to stay well under the 0.14 ms the device needs per block
-    v_params = [d_params[j] for j in range(args.pool)]
-    v_band = [d_band[j] for j in range(args.pool)]
-    v_delay = [d_delay[j] for j in range(args.pool)]
-    v_audio = [d_audio[j] for j in range(args.pool)]
-    bus_ptr, bus_floats = rend.device_bus_ptr(), FRAMES * L_OUT
-    peer_out = final_bus if rank == 0 else None
-
-    def step_device(_k):
-        k = gk[0]          # consecutive block numbers whatever the caller's phase, so the block pushed ahead is always the next one rendered
-        gk[0] += 1
-        j = k % args.pool
-        if pan_overlap:
-            if mdap_issued[0] != k:
-                issue_mdap(k, False)
-            if not fused_update:
-                stream.wait_event(ev_mdap[k & 1])
-                rend.UpdateParameters(v_band[j], v_delay[j], d_mix_bg[k & 1])
-                ev_upd.record(stream)
-        elif fused_update:
-            rend.UpdatePanned(pan, lay, v_params[j], v_band[j], v_delay[j])
-        else:
-            pan.ProcessVBAPData(lay, v_params[j], out=d_mix)
-            rend.UpdateParameters(v_band[j], v_delay[j], d_mix)
-        if use_peer:
-            # every rank's k_bus_reduce result goes straight into the root GPU's gather buffer (peer stores over NVLink); the root adds the
-            # slots in rank order. No collective library on the data path.
-            rend.ProcessInterleaved(v_audio[j], local_bus, FRAMES)
-            exchange.submit(bus_ptr, bus_floats, seq[0], out=peer_out)
-            seq[0] += 1
-        else:
-            with torch.cuda.stream(stream):       # torch ops (the bus zero-fill, NCCL's stream ordering) follow torch's current stream
-                bus = reducer.begin(k)
-                rend.ProcessInterleaved(v_audio[j], bus, FRAMES)
-                reducer.submit(k)
-        if push_ahead:
-            # throughput rendering: block k+1's input is resident, so its ring pushes (an HBM-bound copy) are issued right after block k's render
-            # has been enqueued and run beside it on the SMs the render leaves free; block k only waits for the pushes issued one step earlier
-            rend.PushAhead(v_audio[(k + 1) % args.pool], FRAMES)
-        if pan_overlap:
-            issue_mdap(k + 1, True)
-
-    def barrier():
-        with torch.cuda.stream(stream):
-            if pan_overlap:
-                join_pan()
-            reducer.drain()
-            if exchange is not None:
-                exchange.wait()
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    # ---- device-resident timing (`value`)
-    sampler = ClockSampler(local_rank)
-    sampler.start()
-    for k in range(args.warmup):
-        step_device(k)
-    barrier()
-    # only the dominant kernel is bracketed by events inside the timed region (two event records per step); the per-kernel
-    # breakdown of the other kernels is taken in a separate short pass afterwards so its events do not stretch the timed steps
-    ctx.set_kernel_timing(True, only=("render",))
-    ctx.reset_kernel_timing()
-    launches0 = ctx.launch_count + (ctx_pan.launch_count if pan_overlap else 0)
-    ev0 = torch.cuda.Event(enable_timing=True)
-    ev1 = torch.cuda.Event(enable_timing=True)
-    barrier()
-    with torch.cuda.stream(stream):
-        ev0.record(stream)
-    t_host0 = time.perf_counter()
-    for k in range(args.steps):
-        step_device(args.warmup + k)
-    host_ms_step = (time.perf_counter() - t_host0) * 1e3 / args.steps     # host time to enqueue a step: must stay below the device's step time
-    with torch.cuda.stream(stream):
-        if pan_overlap:
-            join_pan()               # the panning data computed one block ahead by the last step is inside the timed region too
-        reducer.drain()              # the last blocks' reduces are inside the timed region
-        if exchange is not None:
-            exchange.wait()          # ... and so is the peer-memory combine of the last blocks
-        ev1.record(stream)
-    barrier()
-    ms_total = ev0.elapsed_time(ev1)
-    # fingerprint of the last timed block's (combined) bus: the same for every pipelining option at equal --warmup / --steps / --pool / --gpus
-    import zlib
-    last_bus = final_bus if use_peer else reducer.result(gk[0] - 1)
-    bus_crc = zlib.crc32(last_bus.cpu().numpy().tobytes()) if rank == 0 else 0
-    launches = ctx.launch_count + (ctx_pan.launch_count if pan_overlap else 0) - launches0  # our kernels only (torch's bus zero-fill and NCCL are not counted)
-    ktimes = {"render": ctx.kernel_time("render")}
-    ctx.set_kernel_timing(False)
-    bsteps = max(10, min(args.steps, 40))
-    ctx.set_kernel_timing(True)
-    ctx.reset_kernel_timing()
-    if pan_overlap:
-        ctx_pan.set_kernel_timing(True)
-        ctx_pan.reset_kernel_timing()
-    for k in range(bsteps):
-        step_device(args.warmup + args.steps + k)
-    barrier()
-    breakdown = {name: ctx.kernel_time(name) for name in ("mdap", "update", "push", "render", "bus_reduce")}
-    ctx.set_kernel_timing(False)
-    if pan_overlap:
-        # measured while sharing the device with k_render (and the pushes): a duration under overlap, not the kernel's own cost
-        breakdown["mdap"] = ctx_pan.kernel_time("mdap")
-        ctx_pan.set_kernel_timing(False)
-    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
-    per_rank_ms = [ms_total / args.steps]
-    if dist is not None:
-        allt = [torch.zeros_like(t) for _ in range(world)]
-        dist.all_gather(allt, t)
-        per_rank_ms = [float(x.item()) / args.steps for x in allt]
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_step = float(t.item()) / args.steps
-    value = N * world * BLOCK_S / (ms_step * 1e-3)
-
-    # ---- end to end through the C-ABI with HOST (pinned) buffers: H2D of the step's inputs and D2H of the bus inside the timed region
-    e2e = None
-    if not args.no_e2e:
-        def pinned(a):
-            t_ = torch.from_numpy(np.ascontiguousarray(a)).pin_memory()
-            return t_, t_.numpy()
-        keep = []
-        h_audio, h_params, h_band, h_delay = [], [], [], []
-        for j in range(args.pool):
-            for src, dst in ((audio[j], h_audio), (params[j], h_params), (band[j], h_band), (delay[j], h_delay)):
-                tt, nn = pinned(src); keep.append(tt); dst.append(nn)
-        tt, h_mix = pinned(np.zeros((N, 1, L_OUT), np.float32)); keep.append(tt)
-        tt, h_bus = pinned(np.zeros((FRAMES, L_OUT), np.float32)); keep.append(tt)
-        d_partial = torch.zeros((FRAMES, L_OUT), dtype=torch.float32, device=dev)
-
-        # two bus slots: block k is submitted (JPLG_MEM_HOST_ASYNC: nothing waits on the host, the 33.5 MB input transfer runs on the library's copy
-        # stream while block k-1 renders) and then block k-1 is collected; every step still moves its own inputs H2D and its own bus D2H
-        tb, h_bus2 = pinned(np.zeros((FRAMES, L_OUT), np.float32)); keep.append(tb)
-        h_buses = (h_bus, h_bus2)
-        if use_peer:
-            with torch.cuda.stream(stream):
-                d_final2 = [torch.zeros((FRAMES, L_OUT), dtype=torch.float32, device=dev) for _ in range(2)]
-            t_final, h_final = [], []
-            for _ in range(2):
-                tt, nn = pinned(np.zeros((FRAMES, L_OUT), np.float32)); t_final.append(tt); h_final.append(nn)
-            ev_final = [torch.cuda.Event() for _ in range(2)]
-            ev_read = [torch.cuda.Event() for _ in range(2)]
-            rd_stream = torch.cuda.Stream(device=dev)
-            ctx.synchronize()
-
-        def submit_host(k):
-            j = k % args.pool
-            hb = h_buses[k & 1]
-            pan.ProcessVBAPData(lay, h_params[j], out=h_mix, async_host=True)          # H2D params, D2H mix maps (enqueued)
-            rend.UpdateParameters(h_band[j], h_delay[j], h_mix, async_host=True)        # H2D
-            hb[:] = 0.0
-            rend.ProcessInterleaved(h_audio[j], hb, FRAMES, async_host=True)            # H2D audio (copy stream) + bus, D2H bus
-            if use_peer:
-                # N > 1: the partial buses are combined on the device (peer-memory exchange, as in the device-resident pass) and the root reads the
-                # combined bus back; the other ranks' own partial buses still travel D2H with their blocks
-                exchange.submit(bus_ptr, bus_floats, seq[0], out=d_final2[k & 1] if rank == 0 else None)
-                seq[0] += 1
-                if rank == 0:
-                    exchange.wait()
-                    ev_final[k & 1].record(stream)
-                    # read-back on a torch-owned stream (torch's pinned-memory allocator remembers the streams a pinned block was used on, and the
-                    # library's stream dies with its context)
-                    rd_stream.wait_event(ev_final[k & 1])
-                    with torch.cuda.stream(rd_stream):
-                        t_final[k & 1].copy_(d_final2[k & 1], non_blocking=True)
-                        ev_read[k & 1].record(rd_stream)
-
-        def collect_host(k):
-            rend.WaitBlock()
-            hb = h_buses[k & 1]
-            if use_peer:
-                if rank == 0:
-                    ev_read[k & 1].synchronize()
-                    return float(h_final[k & 1][0, 0])
-            elif dist is not None:
-                d_partial.copy_(torch.from_numpy(hb))
-                dist.reduce(d_partial, dst=0)
-                if rank == 0:
-                    hb[:] = d_partial.cpu().numpy()
-            return float(hb[0, 0])
-
-        e2e_steps = max(10, min(args.steps, 100))
-        # warm-up: the device-resident pass above left the PCIe link idle for ~a second and the first tens of transfers after that run at a fraction
-        # of the link's rate (measured on these boxes: 16-40 GB/s for the first copies, 50-55 GB/s once it has ramped up)
-        e2e_warm = max(args.warmup, 30)
-        for k in range(e2e_warm):
-            submit_host(k)
-            if k:
-                collect_host(k - 1)
-        collect_host(e2e_warm - 1)
-        barrier()
-        t0 = time.perf_counter()
-        for k in range(e2e_steps):
-            submit_host(e2e_warm + k)
-            if k:
-                collect_host(e2e_warm + k - 1)
-        collect_host(e2e_warm + e2e_steps - 1)
-        barrier()
-        dt = (time.perf_counter() - t0) / e2e_steps
-        tt2 = torch.tensor([dt], dtype=torch.float64, device=dev)
-        if dist is not None:
-            dist.all_reduce(tt2, op=dist.ReduceOp.MAX)
-        dt = float(tt2.item())
-        h2d = N * FRAMES * 4 + N * 20 + N * 16 + N * 4 + N * L_OUT * 4 + FRAMES * L_OUT * 4
-        d2h = N * L_OUT * 4 + FRAMES * L_OUT * 4 + (FRAMES * L_OUT * 4 if use_peer else 0)     # per rank; the last term is the root's combined bus
-        e2e = {"value": N * world * BLOCK_S / dt, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-               "ms_per_step": dt * 1e3, "steps": e2e_steps,
-               "path": "C ABI with pinned HOST buffers, JPLG_MEM_HOST_ASYNC: block k+1's input transfer overlaps block k's render (2 blocks in flight); the audio goes through the copy engine, the small arrays and the bus are read / written by the kernels through the buffers' device alias (same bytes over PCIe)"
-                       + ("; N > 1: partial buses combined on the device by the peer-memory exchange, the root reads the combined bus back" if use_peer else "")}
-
-    # a short run (--no-e2e, few steps) can end before nvidia-smi has delivered its first line: keep the GPU under the same load until it has
-    # (every rank takes the same decision: the steps contain the bus exchange)
-    extra, t_end = 0, time.time() + 3.0
-    while True:
-        need = 1 if (sampler.proc is not None and sampler.count() == 0 and time.time() < t_end) else 0
-        if dist is not None:
-            tn = torch.tensor([need], dtype=torch.int32, device=dev)
-            dist.all_reduce(tn, op=dist.ReduceOp.MAX)
-            need = int(tn.item())
-        if not need:
-            break
-        for k in range(64):
-            step_device(extra + k)
-        extra += 64
-        barrier()
-    clocks = sampler.stop()
-    if exchange is not None and exchange.error() != 0:
-        raise SystemExit(f"bench.py: bus exchange reported a device-side wait timeout (error {exchange.error()}) on rank {rank}")
-    if rank != 0:
-        if dist is not None:
-            dist.destroy_process_group()
-        return
-
-    # ---- roofline of the dominant kernel (k_render), measured live with CUDA events on the launching stream
-    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    if os.path.exists(peaks_path):
-        peak = float(json.load(open(peaks_path))["hbm_gbs"]); peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)"
+    if args.config == 3:
+        run_config3(args)
+    elif args.config in (1, 2):
+        run_gains_config(args)
+    elif args.config == 4:
+        run_config4(args)
     else:
-        peak = 6650.0; peak_src = "fallback (B200_PROFILING.md)"
-    r_ms, r_n = ktimes["render"]
-    r_avg_ms = r_ms / max(r_n, 1)
-    achieved = RENDER_BYTES_PER_SOURCE * N / (r_avg_ms * 1e-3) / 1e9
-    ncu_traffic = None
-    tpath = os.path.join(ROOT, "profiles", "render_traffic.json")
-    if os.path.exists(tpath):
-        try:
-            ncu_traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
-        except Exception:
-            pass
-    roofline = {"bound": "hbm", "kernel": "k_render", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": ncu_traffic, "peak_source": peak_src, "avg_launch_ms": r_avg_ms,
-                "algorithmic_bytes_per_launch": RENDER_BYTES_PER_SOURCE * N,
-                "whole_step_gbs": STEP_BYTES_PER_SOURCE * N / (ms_step * 1e-3) / 1e9,
-                "note": "fused render is FP32-issue bound (~200 FP32 ops/sample in parity mode), not HBM bound: see DESIGN.md §5",
-                "kernel_ms_per_step": {k: v[0] / max(bsteps, 1) for k, v in breakdown.items()},
-                "kernel_ms_per_step_note": f"separate pass of {bsteps} steps with every kernel bracketed by events (not part of the timed region)"}
-
-    cpu = None
-    if not args.no_cpu_baseline and world == 1:
-        try:
-            cpu = cpu_baseline_sample(log)
-        except Exception as e:  # the checker is optional at bench time
-            log("cpu baseline failed:", e)
-
-    line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "BASELINE config 3: full block render, 16,384 mono sources per GPU -> 7.1.4, 48 kHz / 512 frames "
-                               "(MDAP gains + update + push + fused delay/LR4/mix + bus reduce per block)",
-                   "sources_per_gpu": N, "total_sources": N * world, "mode": args.mode, "ring_size": rend.ring_size,
-                   "host_numa_node": numa_node,
-                   "pipelining": {"push_ahead": push_ahead, "pan_overlap": pan_overlap, "fused_update": fused_update,
-                                  "note": "every step runs all five kernels once; with push_ahead / pan_overlap block k+1's ring pushes / panning data "
-                                          "are produced on lower-priority streams while block k renders"},
-                   "l2_policy": f"inputs larger than L2: {args.pool} distinct 33.5 MB input blocks cycled, {N * rend.ring_size * 4 / 2**30:.1f} GiB of rings",
-                   "parallelism": (f"sources sharded over {world} GPU(s); partial [512x12] buses stored into the root GPU's gather buffer over NVLink peer memory and summed in rank order (jplg_bus_exchange, no collective library on the data path)"
-                                   if use_peer else "DIAGNOSTIC: independent replicas, buses NOT combined" if args.bus == "none" else f"sources sharded over {world} GPU(s); NCCL reduce of the [512x12] bus, double-buffered (block k reduce overlaps block k+1 render)") if world > 1 else "single GPU"},
-        "per_rank_ms_per_step": [round(x, 5) for x in per_rank_ms], "host_enqueue_ms_per_step": round(host_ms_step, 5), "bus_crc32": f"{bus_crc:08x}", "clocks": clocks, "gpu_launches": launches, "e2e": e2e, "roofline": roofline, "cpu_baseline": cpu,
-    }
-    _emit(line)
-    if dist is not None:
-        dist.destroy_process_group()
+        run_config5(args)
 
 
 if __name__ == "__main__":

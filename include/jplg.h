@@ -122,6 +122,10 @@ enum { JPLG_K_PUSH = 0, JPLG_K_RENDER = 1, JPLG_K_BUS_REDUCE = 2, JPLG_K_MDAP = 
 JPLG_API void        jplg_context_set_kernel_timing(jplg_context ctx, int32_t enabled);
 JPLG_API void        jplg_context_reset_kernel_timing(jplg_context ctx);
 JPLG_API jplg_status jplg_context_kernel_time(jplg_context ctx, int32_t which, double* total_ms, uint64_t* launches);
+/* Measurement aid: the FP32 CUDA-core ceiling of this device for the instruction mix the parity arithmetic is made of (packed FP32x2 multiplies
+ * and adds, one rounded operation per lane and issue slot, no fused operations), in lane operations per second; a short blocking probe kernel on
+ * every SM (about 2 ms). bench.py uses it as the denominator of the fused render's roofline fraction. */
+JPLG_API jplg_status jplg_context_probe_fp32(jplg_context ctx, double* lane_ops_per_second, double* kernel_ms);
 
 /* ---------------------------------------------------------------------------------------------- */
 /* ChannelMap helpers  (replaces: inc/ChannelMap.h:153-249; masks are EChannel bit masks :38-79)    */
@@ -228,7 +232,10 @@ JPLG_API jplg_status jplg_renderer_update(jplg_renderer r, const float* band_gai
  * writes them, the band gains and the delays straight into the renderer's NEXT set of targets, which the next jplg_renderer_process_block adopts
  * (it waits for them on the device). The work is enqueued on the PANNER's context stream — with a JPLG_CONTEXT_BACKGROUND panner context it runs
  * while the renderer's context still renders the previous block, which keeps reading the current targets. Same values, bit for bit, as the two
- * separate calls. 3D panners; the layout's channel count must be the renderer's source_channels and the panner's channel count its output_channels. */
+ * separate calls. 3D panners; the panner's channel count must be the renderer's output_channels, and the renderer's source_channels either the
+ * layout's panned channel count or the channel count of the layout's source map: in that case (a 5.1 source rendered with all six channels) every
+ * panned channel group lands on the row of its channel in ascending EChannel order and the rows the panner skips (LFE, PannerBase.h:937) get zero
+ * gains, which is the mix map an engine assembles from the reference's per-channel gains. */
 JPLG_API jplg_status jplg_renderer_update_panned(jplg_renderer r, jplg_panner p, jplg_source_layout l, const float* pan_params,
                                                  const float* band_gains, const float* delay_seconds, int32_t mem);
 JPLG_API jplg_status jplg_renderer_process_block(jplg_renderer r, const float* in, float* bus, uint32_t frames, int32_t mem);

@@ -45,6 +45,7 @@ _sig("jplg_context_launch_count", _u64, [_vp])
 _sig("jplg_context_set_kernel_timing", None, [_vp, _i32])
 _sig("jplg_context_reset_kernel_timing", None, [_vp])
 _sig("jplg_context_kernel_time", _i32, [_vp, _i32, C.POINTER(C.c_double), C.POINTER(_u64)])
+_sig("jplg_context_probe_fp32", _i32, [_vp, C.POINTER(C.c_double), C.POINTER(C.c_double)])
 _sig("jplg_channel_map_num_channels", _u32, [_u32])
 _sig("jplg_channel_map_has_lfe", _i32, [_u32])
 _sig("jplg_channel_map_has_top_channels", _i32, [_u32])
@@ -239,6 +240,12 @@ class Context:
 
     def reset_kernel_timing(self):
         lib.jplg_context_reset_kernel_timing(self.h)
+
+    def probe_fp32_lane_rate(self):
+        """FP32 ceiling of this device for unfused packed multiplies / adds (jplg_context_probe_fp32)"""
+        rate, ms = C.c_double(), C.c_double()
+        self.check(lib.jplg_context_probe_fp32(self.h, C.byref(rate), C.byref(ms)))
+        return {"lane_ops_per_s": float(rate.value), "probe_ms": float(ms.value)}
 
     def kernel_time(self, name):
         """-> (total milliseconds, launches) of one of KERNELS since the last reset (CUDA events on the context stream)"""

@@ -222,6 +222,34 @@ jplg_status jplg_context_kernel_time(jplg_context ctx, int32_t which, double* to
 	return JPLG_OK;
 }
 
+jplg_status jplg_context_probe_fp32(jplg_context ctx, double* lane_ops_per_second, double* kernel_ms)
+{
+	if (!ctx || !lane_ops_per_second) return JPLG_ERR_INVALID_ARGUMENT;
+	JPLG_NEED_DEVICE(ctx);
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	void* sink = nullptr;
+	jplg_status st = Scratch(ctx, 0, 256, &sink); if (st) return st;
+	cudaEvent_t a, b;
+	JPLG_CUDA_TRY(ctx, cudaEventCreate(&a)); JPLG_CUDA_TRY(ctx, cudaEventCreate(&b));
+	const uint32_t grid = static_cast<uint32_t>(ctx->numSMs), iters = 20000;
+	double best = 1e30;
+	for (int rep = 0; rep < 4; ++rep)     // first launch warms up; best of the following three
+	{
+		JPLG_CUDA_TRY(ctx, cudaEventRecord(a, ctx->stream));
+		JPLG_CUDA_TRY(ctx, LaunchFp32Probe(static_cast<float*>(sink), grid, iters, ctx->stream)); ctx->launches++;
+		JPLG_CUDA_TRY(ctx, cudaEventRecord(b, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaEventSynchronize(b));
+		float ms = 0.0f; JPLG_CUDA_TRY(ctx, cudaEventElapsedTime(&ms, a, b));
+		if (rep > 0 && ms < best) best = ms;
+	}
+	cudaEventDestroy(a); cudaEventDestroy(b);
+	const double laneOps = double(grid) * 512.0 * double(iters) * 16.0 * 2.0;
+	*lane_ops_per_second = laneOps / (best * 1e-3);
+	if (kernel_ms) *kernel_ms = best;
+	return JPLG_OK;
+}
+
 //==================================================================================================
 uint32_t jplg_channel_map_num_channels(uint32_t mask) { return NumChannels(mask); }
 int32_t jplg_channel_map_has_lfe(uint32_t mask) { return HasLFE(mask) ? 1 : 0; }
@@ -722,8 +750,29 @@ jplg_status jplg_renderer_update_panned(jplg_renderer r, jplg_panner p, jplg_sou
 	JPLG_NEED_DEVICE(ctx);
 	if (rc->device != ctx->device) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "update_panned: panner and renderer on different devices");
 	if (!p->host.is3D) return Fail(ctx, JPLG_ERR_UNSUPPORTED, "update_panned: 3D panners only (use jplg_panner_mdap + jplg_renderer_update)");
-	if (l->host.numChannels != r->cfg.source_channels || p->host.numChannels != r->cfg.output_channels)
-		return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "update_panned: source layout / panner channel counts do not match the renderer");
+	// the renderer's channels per source: the layout's panned channels, or every channel of the layout's source map (a 5.1 source rendered with its
+	// LFE: the panner skips it, PannerBase.h:937, and its mix row stays zero)
+	uint8_t rows[kMaxSourceChannelsDev] = {};
+	{
+		const uint32_t C = r->cfg.source_channels;
+		uint32_t full = 0; for (uint32_t v = l->host.sourceMask; v; v &= v - 1) ++full;
+		bool okRows = p->host.numChannels == r->cfg.output_channels;
+		if (l->host.numChannels == C) for (uint32_t k = 0; k < C; ++k) rows[k] = static_cast<uint8_t>(k);
+		else if (full == C && C <= kMaxSourceChannelsDev)
+		{
+			uint32_t idx = 0, k = 0;
+			for (uint32_t v = l->host.sourceMask; v; v &= v - 1, ++idx)
+			{
+				const uint32_t bit = v & (0u - v);
+				if (bit == 0x8u /* LFE */ || bit >= (1u << 13) /* top channels are not panned as source channels */) continue;
+				if (k < kMaxSourceChannelsDev) rows[k] = static_cast<uint8_t>(idx);
+				++k;
+			}
+			okRows = okRows && k == l->host.numChannels;
+		}
+		else okRows = false;
+		if (!okRows) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "update_panned: source layout / panner channel counts do not match the renderer");
+	}
 	std::unique_lock<std::mutex> lkA(rc->mtx, std::defer_lock), lkB(ctx->mtx, std::defer_lock);
 	if (rc == ctx) lkA.lock(); else std::lock(lkA, lkB);
 	cudaSetDevice(ctx->device);
@@ -745,6 +794,9 @@ jplg_status jplg_renderer_update_panned(jplg_renderer r, jplg_panner p, jplg_sou
 	MdapFuse fz;
 	fz.tgtMix = r->tgt2Mix; fz.tgtBand = r->tgt2Band; fz.tgtDelay = r->tgt2Delay;
 	fz.band = band_gains; fz.delaySec = delay_seconds; fz.sampleRate = r->cfg.sample_rate; fz.numSC = r->numSC;
+	fz.rendC = r->cfg.source_channels; std::memcpy(fz.rows, rows, sizeof(rows));
+	fz.unpannedRows = (1u << fz.rendC) - 1u;
+	for (uint32_t k = 0; k < l->host.numChannels; ++k) fz.unpannedRows &= ~(1u << rows[k]);
 	JPLG_LAUNCH(ctx, JPLG_K_MDAP, LaunchMdap(p->dev, l->lp, pan_params, 5, N, static_cast<float*>(scratch), ctx->numSMs, ctx->stream, &fz));
 	JPLG_CUDA_TRY(ctx, cudaEventRecord(r->evUpdated, ctx->stream));
 	r->pendingPanned = true;
@@ -902,11 +954,18 @@ static jplg_status ProcessBlock(jplg_renderer r, const float* in, float* bus, fl
 	}
 	else
 	{
-		JPLG_LAUNCH(ctx, JPLG_K_PUSH, LaunchPush(rp, 0, N, ctx->stream));
-		if (asyncSlot >= 0) JPLG_CUDA_TRY(ctx, cudaEventRecord(r->evPushedA[asyncSlot], ctx->stream));
+		// real-time order: this block's input enters the rings now. Mono renderers let k_render's own push role do it (no separate kernel, the copy
+		// overlaps the start of the filters); everything else launches the push kernel first.
+		rp.fusedPush = RenderCanFusePush(rp) ? 1u : 0u;
+		if (!rp.fusedPush)
+		{
+			JPLG_LAUNCH(ctx, JPLG_K_PUSH, LaunchPush(rp, 0, N, ctx->stream));
+			if (asyncSlot >= 0) JPLG_CUDA_TRY(ctx, cudaEventRecord(r->evPushedA[asyncSlot], ctx->stream));
+		}
 		if (!r->evStarted) JPLG_CUDA_TRY(ctx, cudaEventCreateWithFlags(&r->evStarted, cudaEventDisableTiming));
 		JPLG_LAUNCH(ctx, JPLG_K_RENDER, LaunchRender(rp, r->cfg.mode, 0, r->numCTAs, ctx->stream, r->evStarted));
 		r->startedRecorded = true;
+		if (rp.fusedPush && asyncSlot >= 0) JPLG_CUDA_TRY(ctx, cudaEventRecord(r->evPushedA[asyncSlot], ctx->stream));   // the staging slot was read by the render
 	}
 	if (r->evSetFree[r->activeSet]) { JPLG_CUDA_TRY(ctx, cudaEventRecord(r->evSetFree[r->activeSet], ctx->stream)); r->setFreeRecorded[r->activeSet] = true; }
 	JPLG_LAUNCH(ctx, JPLG_K_BUS_REDUCE, LaunchBusReduce(rp, r->deviceBus, dBus, ctx->stream));

@@ -40,6 +40,10 @@ namespace jplg
 		float* tgtMix = nullptr; float* tgtBand = nullptr; float* tgtDelay = nullptr;
 		const float* band = nullptr; const float* delaySec = nullptr;
 		float sampleRate = 0.0f; uint32_t numSC = 0;
+		// renderer channels per source (>= the layout's panned channels) and the renderer row of every panned channel group: a 5.1 source is
+		// rendered with 6 channels, its LFE (skipped by the panner, PannerBase.h:937) keeps the all-zero mix row it was created with
+		uint32_t rendC = 0; uint8_t rows[kMaxSourceChannelsDev] = {};
+		uint32_t unpannedRows = 0;   // bit k: renderer row k has no panned channel group; its targets are written as zeros
 	};
 	cudaError_t LaunchMdap(const PannerDev& p, const MdapLayoutParams& lp, const float* params, uint32_t paramStride, uint32_t n, float* out, int numSMs, cudaStream_t st,
 						   const MdapFuse* fuse = nullptr);
@@ -86,16 +90,19 @@ namespace jplg
 		uint32_t plainPush;    // 1: a chunk pushes only its own frames (ERBus, EarlyReflectionsBus.cpp:119-122); 0: DirectSoundEffect's quirk
 		uint32_t groupsPerCTA; // mix groups per CTA (ER: buses per CTA = 128 / taps per bus), each with its own partial bus; 0 or 1 = one
 		uint32_t numGroups;    // total number of partial buses (groups) when groupsPerCTA > 1
+		uint32_t fusedPush;    // 1: k_render's push role writes this block's input into the rings itself (mono sources; set by LaunchRender's caller via RenderCanFusePush)
 		const uint8_t* flags;  // per source-channel: bit 0 = live, bit 1 = fading out (rendered for the first chunk of the block only); null = all live
 	};
 
 	uint32_t RenderNumCTAs(uint32_t numSC, uint32_t srcChannels);
 	uint32_t TotalPushes(uint32_t frames); // ring pushes one block of `frames` causes (reference quirk, see k_push)
 	uint32_t RenderSourcesPerCTA(uint32_t srcChannels);
+	bool RenderCanFusePush(const RenderParams& rp);   // conditions of k_render's push role (mono, 4-aligned block / ring position, input 16-byte aligned)
 	cudaError_t LaunchPush(const RenderParams& rp, uint32_t srcBegin, uint32_t srcCount, cudaStream_t st);
 	cudaError_t LaunchRender(const RenderParams& rp, int mode, uint32_t ctaBegin, uint32_t ctaCount, cudaStream_t st, cudaEvent_t started = nullptr);
 	// bus[frames][L] (+)= sum over CTAs of partial; also writes the plain sum to `deviceBus`
 	cudaError_t LaunchBusReduce(const RenderParams& rp, float* deviceBus, float* busAccumulate, cudaStream_t st);
+	cudaError_t LaunchFp32Probe(float* sink, uint32_t grid, uint32_t iters, cudaStream_t st);
 	cudaError_t LaunchStateTranspose(const float* in, float* out, uint32_t rows, uint32_t cols, cudaStream_t st);
 
 	// components

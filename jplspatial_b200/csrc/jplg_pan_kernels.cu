@@ -226,21 +226,24 @@ namespace jplg
 				{
 					const float v = outSrc[ch * L + gl] * norm;
 					outSrc[ch * L + gl] = v;
-					if (fz.tgtMix) fz.tgtMix[size_t(gl) * fz.numSC + size_t(src) * lp.numChannels + ch] = v;   // k_update_targets' transpose
+					if (fz.tgtMix) fz.tgtMix[size_t(gl) * fz.numSC + size_t(src) * fz.rendC + fz.rows[ch]] = v;   // k_update_targets' transpose
 				}
 			}
 			if (fz.tgtMix && valid)
 			{
+				if (fz.unpannedRows && gl < L)
+					for (uint32_t ch = 0; ch < fz.rendC; ++ch)
+						if ((fz.unpannedRows >> ch) & 1u) fz.tgtMix[size_t(gl) * fz.numSC + size_t(src) * fz.rendC + ch] = 0.0f;
 				// UpdateParameters (src/Auralization/DirectSound.cpp:231-239) for this source's channels: band gains, delay in samples
 				if (gl < 4)
 				{
 					const float b = fz.band[size_t(src) * 4 + gl];
-					for (uint32_t ch = 0; ch < lp.numChannels; ++ch) fz.tgtBand[size_t(gl) * fz.numSC + size_t(src) * lp.numChannels + ch] = b;
+					for (uint32_t ch = 0; ch < fz.rendC; ++ch) fz.tgtBand[size_t(gl) * fz.numSC + size_t(src) * fz.rendC + ch] = b;
 				}
 				if (gl == 4)
 				{
 					const float d = fz.delaySec[src] * fz.sampleRate;
-					for (uint32_t ch = 0; ch < lp.numChannels; ++ch) fz.tgtDelay[size_t(src) * lp.numChannels + ch] = d;
+					for (uint32_t ch = 0; ch < fz.rendC; ++ch) fz.tgtDelay[size_t(src) * fz.rendC + ch] = d;
 				}
 			}
 			__syncwarp();

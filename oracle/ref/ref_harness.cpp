@@ -41,6 +41,10 @@
 #include <cstring>
 #include <memory>
 #include <thread>
+#include <mutex>
+#include <condition_variable>
+#include <functional>
+#include <atomic>
 #include <vector>
 
 using namespace JPL;
@@ -73,6 +77,79 @@ namespace
 		std::unique_ptr<DirectSoundEffect> fx;
 		uint32 nSrc = 0, nOut = 0;
 	};
+}
+
+
+//==========================================================================
+// Persistent worker pool for the TIMED batch helpers (bench.py's CPU arm): threads are created once per thread count and parked on a
+// condition variable, so a timed call pays a wake-up, not std::thread creation + join.
+namespace
+{
+	class WorkerPool
+	{
+	public:
+		explicit WorkerPool(int n) : mN(n)
+		{
+			for (int t = 1; t < n; ++t) mThreads.emplace_back([this, t] { Loop(t); });
+		}
+		~WorkerPool()
+		{
+			{ std::lock_guard<std::mutex> lk(mMtx); mStop = true; ++mEpoch; }
+			mWake.notify_all();
+			for (auto& th : mThreads) th.join();
+		}
+		// runs fn(0..n-1), fn(0) on the calling thread; returns when all are done
+		void Run(const std::function<void(int)>& fn)
+		{
+			if (mN == 1) { fn(0); return; }
+			{ std::lock_guard<std::mutex> lk(mMtx); mFn = &fn; mPending = mN - 1; ++mEpoch; }
+			mWake.notify_all();
+			fn(0);
+			std::unique_lock<std::mutex> lk(mMtx);
+			mDone.wait(lk, [this] { return mPending == 0; });
+			mFn = nullptr;
+		}
+	private:
+		void Loop(int t)
+		{
+			uint64_t seen = 0;
+			for (;;)
+			{
+				const std::function<void(int)>* fn = nullptr;
+				{
+					std::unique_lock<std::mutex> lk(mMtx);
+					mWake.wait(lk, [&] { return mEpoch != seen; });
+					seen = mEpoch;
+					if (mStop) return;
+					fn = mFn;
+				}
+				(*fn)(t);
+				{ std::lock_guard<std::mutex> lk(mMtx); if (--mPending == 0) mDone.notify_one(); }
+			}
+		}
+		int mN;
+		std::vector<std::thread> mThreads;
+		std::mutex mMtx;
+		std::condition_variable mWake, mDone;
+		const std::function<void(int)>* mFn = nullptr;
+		int mPending = 0;
+		uint64_t mEpoch = 0;
+		bool mStop = false;
+	};
+	void RunParallel(int threads, const std::function<void(int)>& fn)
+	{
+		static std::mutex sMtx;
+		static std::vector<std::unique_ptr<WorkerPool>> sPools;   // one pool per thread count, kept for the life of the process
+		static std::vector<int> sCounts;
+		if (threads < 1) threads = 1;
+		WorkerPool* pool = nullptr;
+		{
+			std::lock_guard<std::mutex> lk(sMtx);
+			for (size_t i = 0; i < sCounts.size(); ++i) if (sCounts[i] == threads) pool = sPools[i].get();
+			if (!pool) { sPools.emplace_back(new WorkerPool(threads)); sCounts.push_back(threads); pool = sPools.back().get(); }
+		}
+		pool->Run(fn);
+	}
 }
 
 extern "C"
@@ -294,13 +371,11 @@ extern "C"
 		const size_t nCh = static_cast<RefPanner*>(hPanner)->is3D ? l->l3.ChannelGroups.size() : l->l2.ChannelGroups.size();
 		const size_t stride = nCh * L;
 		const auto t0 = std::chrono::steady_clock::now();
-		std::vector<std::thread> pool;
-		for (int t = 0; t < threads; ++t)
+		RunParallel(threads, [&](int t)
 		{
 			const uint32_t b = uint32_t(uint64_t(n) * t / threads), e = uint32_t(uint64_t(n) * (t + 1) / threads);
-			pool.emplace_back([=] { ref_mdap(hPanner, hLayout, params + 5 * size_t(b), e - b, out + stride * b); });
-		}
-		for (auto& th : pool) th.join();
+			([=] { ref_mdap(hPanner, hLayout, params + 5 * size_t(b), e - b, out + stride * b); })();
+		});
 		return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 	}
 
@@ -510,14 +585,12 @@ extern "C"
 			for (uint32_t i = 0; i < n; ++i) ref_dse_process(effects[i], in + inStride * i, bus, frames);
 			return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 		}
-		std::vector<std::thread> pool;
-		for (int t = 0; t < threads; ++t)
+		RunParallel(threads, [&](int t)
 		{
 			partial[t].assign(busSize, 0.0f);
 			const uint32_t b = uint32_t(uint64_t(n) * t / threads), e = uint32_t(uint64_t(n) * (t + 1) / threads);
-			pool.emplace_back([=, &partial] { for (uint32_t i = b; i < e; ++i) ref_dse_process(effects[i], in + inStride * i, partial[t].data(), frames); });
-		}
-		for (auto& th : pool) th.join();
+			([=, &partial] { for (uint32_t i = b; i < e; ++i) ref_dse_process(effects[i], in + inStride * i, partial[t].data(), frames); })();
+		});
 		for (int t = 0; t < threads; ++t) for (size_t i = 0; i < busSize; ++i) bus[i] += partial[t][i];
 		return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 	}
@@ -527,6 +600,34 @@ extern "C"
 		auto* d0 = static_cast<RefDSE*>(effects[0]);
 		const size_t mm = size_t(d0->nSrc) * d0->nOut;
 		for (uint32_t i = 0; i < n; ++i) ref_dse_update(effects[i], bandGains + 4 * size_t(i), delaySeconds[i], mixMaps + mm * i);
+	}
+	// UpdateParameters for every effect, sources partitioned over the pool's threads (each effect has its own RealtimeObject: no sharing)
+	void ref_dse_update_batch_mt(void** effects, uint32_t n, const float* bandGains, const float* delaySeconds, const float* mixMaps, int threads)
+	{
+		if (n == 0) return;
+		auto* d0 = static_cast<RefDSE*>(effects[0]);
+		const size_t mm = size_t(d0->nSrc) * d0->nOut;
+		RunParallel(threads, [&](int t)
+		{
+			const uint32_t b = uint32_t(uint64_t(n) * t / threads), e = uint32_t(uint64_t(n) * (t + 1) / threads);
+			for (uint32_t i = b; i < e; ++i) ref_dse_update(effects[i], bandGains + 4 * size_t(i), delaySeconds[i], mixMaps + mm * i);
+		});
+	}
+	// build flags of this library (bench.py reports them with the CPU baseline)
+	const char* ref_build_info()
+	{
+		return
+#if defined(JPL_USE_AVX2)
+			"AVX2+FMA (-mavx2 -mfma, JPL_USE_AVX2=1 JPL_USE_FMADD=1)"
+#else
+			"SSE2 baseline (JPL_SIMD_CONFIGURED=1)"
+#endif
+#if defined(__OPTIMIZE__) && defined(JPLREF_O3)
+			", -O3 -DNDEBUG"
+#else
+			", -O2 -DNDEBUG"
+#endif
+			;
 	}
 	//==========================================================================
 	// ReverbBus (LateReverb.h:84-108)
@@ -551,13 +652,11 @@ extern "C"
 	{
 		if (threads < 1) threads = 1;
 		const auto t0 = std::chrono::steady_clock::now();
-		std::vector<std::thread> pool;
-		for (int t = 0; t < threads; ++t)
+		RunParallel(threads, [&](int t)
 		{
 			const uint32_t b = uint32_t(uint64_t(n) * t / threads), e = uint32_t(uint64_t(n) * (t + 1) / threads);
-			pool.emplace_back([=] { for (uint32_t i = b; i < e; ++i) ref_reverb_process(buses[i], in + size_t(i) * frames, 1, out + size_t(i) * frames * nOut, nOut, frames); });
-		}
-		for (auto& th : pool) th.join();
+			([=] { for (uint32_t i = b; i < e; ++i) ref_reverb_process(buses[i], in + size_t(i) * frames, 1, out + size_t(i) * frames * nOut, nOut, frames); })();
+		});
 		return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 	}
 
@@ -591,13 +690,11 @@ extern "C"
 	{
 		if (threads < 1) threads = 1;
 		const auto t0 = std::chrono::steady_clock::now();
-		std::vector<std::thread> pool;
-		for (int t = 0; t < threads; ++t)
+		RunParallel(threads, [&](int t)
 		{
 			const uint32_t b = uint32_t(uint64_t(n) * t / threads), e = uint32_t(uint64_t(n) * (t + 1) / threads);
-			pool.emplace_back([=] { for (uint32_t i = b; i < e; ++i) { const uint32 L = static_cast<ERBus*>(buses[i])->GetNumChannels(); ref_erbus_process(buses[i], in + size_t(i) * frames, 1, out + size_t(i) * frames * L, frames); } });
-		}
-		for (auto& th : pool) th.join();
+			([=] { for (uint32_t i = b; i < e; ++i) { const uint32 L = static_cast<ERBus*>(buses[i])->GetNumChannels(); ref_erbus_process(buses[i], in + size_t(i) * frames, 1, out + size_t(i) * frames * L, frames); } })();
+		});
 		return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 	}
 	//==========================================================================
@@ -704,11 +801,10 @@ extern "C"
 		const AirAbsorptionCache& c = cDefaultAirAbsCache;
 		AttenuationBaseModel m; m.Model = static_cast<AttenuationModel>(int(model[0])); m.Parameters = { model[1], model[2], model[3] };
 		const auto t0 = std::chrono::steady_clock::now();
-		std::vector<std::thread> pool;
-		for (int t = 0; t < threads; ++t)
+		RunParallel(threads, [&](int t)
 		{
 			const uint32_t b = uint32_t(uint64_t(n) * t / threads), e = uint32_t(uint64_t(n) * (t + 1) / threads);
-			pool.emplace_back([=, &c, &m] {
+			([=, &c, &m] {
 				const Position<MinimalVec3> lis = ToPos(listeners);
 				for (uint32_t i = b; i < e; ++i)
 				{
@@ -722,9 +818,8 @@ extern "C"
 					dBToGain(simd(0.0f) - AirAbsorption::ComputeForDistance(r.Distance, c)).store(outBand + size_t(i) * 4);
 					outDelay[i] = r.Distance * SpeedOfSound::cInvReference;
 				}
-			});
-		}
-		for (auto& th : pool) th.join();
+			})();
+		});
 		return std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 	}
 

@@ -241,16 +241,30 @@ class Ref:
     def dse(self, fs, n_src, n_out, band_gains, delay_seconds, mix_map):
         return RefDSE(self, fs, n_src, n_out, band_gains, delay_seconds, mix_map)
 
-    def dse_batch_process(self, effects, inp, frames, bus, threads=1):
-        """effects: list of RefDSE; inp [N][frames*C]; bus [frames*L] accumulated. Returns seconds."""
-        arr = (_vp * len(effects))(*[e.h for e in effects])
-        x = self._f(inp)
-        return float(self.lib.ref_dse_process_batch(arr, _u32(len(effects)), _vp(x.ctypes.data), _u32(frames), _vp(bus.ctypes.data), C.c_int(threads)))
+    def dse_handles(self, effects):
+        """ctypes handle array of a list of RefDSE, built once (timed loops pass it instead of the list)"""
+        return (_vp * len(effects))(*[e.h for e in effects])
 
-    def dse_batch_update(self, effects, band, delay, mix):
-        arr = (_vp * len(effects))(*[e.h for e in effects])
+    def dse_batch_process(self, effects, inp, frames, bus, threads=1):
+        """effects: list of RefDSE or dse_handles(list); inp [N][frames*C]; bus [frames*L] accumulated. Returns seconds.
+        threads > 1: sources partitioned over a persistent worker pool, per-thread buses summed in thread order."""
+        arr = effects if isinstance(effects, C.Array) else self.dse_handles(effects)
+        x = self._f(inp)
+        return float(self.lib.ref_dse_process_batch(arr, _u32(len(arr)), _vp(x.ctypes.data), _u32(frames), _vp(bus.ctypes.data), C.c_int(threads)))
+
+    def dse_batch_update(self, effects, band, delay, mix, threads=1):
+        arr = effects if isinstance(effects, C.Array) else self.dse_handles(effects)
         b = self._f(band); d = self._f(delay); m = self._f(mix)
-        self.lib.ref_dse_update_batch(arr, _u32(len(effects)), _vp(b.ctypes.data), _vp(d.ctypes.data), _vp(m.ctypes.data))
+        if threads > 1 and hasattr(self.lib, "ref_dse_update_batch_mt"):
+            self.lib.ref_dse_update_batch_mt(arr, _u32(len(arr)), _vp(b.ctypes.data), _vp(d.ctypes.data), _vp(m.ctypes.data), C.c_int(threads))
+        else:
+            self.lib.ref_dse_update_batch(arr, _u32(len(arr)), _vp(b.ctypes.data), _vp(d.ctypes.data), _vp(m.ctypes.data))
+
+    def build_info(self):
+        if not hasattr(self.lib, "ref_build_info"):
+            return "unknown"
+        self.lib.ref_build_info.restype = C.c_char_p
+        return self.lib.ref_build_info().decode()
 
 
 class RefPanner:

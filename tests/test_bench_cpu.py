@@ -47,3 +47,16 @@ def test_gpu_arm_fails_loudly_without_a_device():
     assert r.returncode != 0
     assert "no CUDA device" in (r.stderr + r.stdout)
     assert not [ln for ln in r.stdout.splitlines() if ln.startswith("{")]      # no metric line from a CPU fallback
+
+
+def test_reference_arm_never_maps_the_product_library():
+    """the CPU arm must time the reference alone: nothing of jplspatial_b200 (libjplg.so) may be loaded into its process"""
+    from oracle import refpy
+    if not refpy.available("sse2"):
+        pytest.skip("oracle/_ref not built")
+    code = ("import sys, os; sys.path.insert(0, %r); import bench; r = bench.best_reference(64, 1); assert r and r['best']['ms_per_block_all_threads'] > 0; "
+            "maps = open('/proc/self/maps').read(); assert 'libjplg' not in maps, 'libjplg.so mapped'; assert 'jplspatial_b200' not in sys.modules; "
+            "assert 'libjplref' in maps; print('clean', r['best']['variant'])") % ROOT
+    r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, cwd=ROOT, timeout=300)
+    assert r.returncode == 0, r.stderr[-2000:]
+    assert "clean" in r.stdout
