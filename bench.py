@@ -342,7 +342,7 @@ class _DeviceFloats:
     """CUDA array interface over a raw device pointer of the library (read-only view for the checks)"""
 
     def __init__(self, ptr, n):
-        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": "<f4", "data": (int(ptr), True), "version": 2}
+        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": "<f4", "data": (int(ptr), False), "version": 2}
 
 
 class Config3Pipeline:
@@ -958,8 +958,10 @@ def run_gains_config(args):
 
 
 C4_LAYOUTS = (("Mono", 1, 288), ("Stereo", 2, 288), ("Quad", 4, 240), ("Surround_5_1", 6, 240))   # name, rendered channels, virtual sources per source -> 9.1.6
-# per-source cost model of the weighted sharding (measured): 6.3 ns per rendered source-channel-block + 0.027 ns per virtual source
-C4_COST = lambda ch, vs: 6.3 * ch + 0.027 * vs
+# per-source cost model of the weighted sharding, in SM-microseconds per source and block (measured on one B200): the render CTA's
+# duration / its sources (118 us / 128 mono, 121 / 64 stereo, 127 / 32 quad, 151 / 21 5.1 sources per CTA) + 0.9 for the panning kernel
+# (~the same 240-288 virtual sources for every layout)
+C4_COST = {"Mono": 0.92 + 0.9, "Stereo": 1.89 + 0.9, "Quad": 3.97 + 0.9, "Surround_5_1": 7.19 + 0.9}
 
 
 def run_config4(args):
@@ -976,12 +978,11 @@ def run_config4(args):
     per_layout = args.c4_per_layout * world
     total = 4 * per_layout
     weights = []
-    for _, ch, vs in C4_LAYOUTS:
-        weights += [C4_COST(ch, vs)] * per_layout
+    for name, _ch, _vs in C4_LAYOUTS:
+        weights += [C4_COST[name]] * per_layout
     begin, end = shard_range(total, world, rank, weights)
     ctx = J.Context(env.local)
     stream = ctx.torch_stream()
-    ctx_pan = J.Context(env.local, background=True)
     sampler = ClockSampler(env.local); sampler.start()
     units = []
     for li, (name, C, _vs) in enumerate(C4_LAYOUTS):
@@ -990,7 +991,7 @@ def run_config4(args):
             continue
         n = hi - lo
         uctx = J.Context(env.local)                     # one context (= one stream) per layout: the renderers' grids overlap instead of leaving tails
-        pan = J.VBAPanner(ctx_pan); assert pan.Initialize(M.Surround_9_1_6)
+        pan = J.VBAPanner(uctx); assert pan.Initialize(M.Surround_9_1_6)
         lay = pan.InitializeSourceLayout(getattr(M, name))
         seed = 0xC4 + 7919 * li + lo
         params = np.stack([util.pan_params(n, seed + 10 * b, edge=False) for b in range(2)])
@@ -1011,22 +1012,15 @@ def run_config4(args):
         final = torch.zeros((FRAMES, L), dtype=torch.float32, device=dev)
     exchange = make_peer_bus_exchange(ctx, FRAMES * L) if world > 1 else None
     seq = [0]
-    pan_stream = ctx_pan.torch_stream()
     ctx.synchronize()
     kcount = [0]
 
-    def issue_pan(k):
-        j = k & 1
-        # no jplg_renderer_wait_render_started here: with 800+ CTAs queued on 148 SMs the last layout's grid is only fully resident near the end of the
-        # block, which would push the panning kernels behind the renders they are meant to run beside (the low stream priority orders them instead)
-        for u in units:
-            u["rend"].UpdatePanned(u["pan"], u["lay"], u["params"][j], u["band"][j], u["delay"][j])
-
     def step():
+        # every layout on its own stream: panning kernel with the fused update, (push +) render, bus reduce; with 800+ render CTAs queued on 148 SMs
+        # the device is saturated by the renders alone, so the panning data is computed in stream order instead of one block ahead on a background
+        # context (measured: a low-priority panning stream starves behind the render grids and the next block then waits for it)
         k = kcount[0]; kcount[0] += 1
         j = k & 1
-        if k == 0:
-            issue_pan(0)
         with torch.cuda.stream(stream):
             start = torch.cuda.Event(); start.record(stream)
         for u in units:
@@ -1034,9 +1028,9 @@ def run_config4(args):
             st.wait_event(start)        # the previous block's sum has read this unit's bus
             with torch.cuda.stream(st):
                 u["bus"].zero_()
+            u["rend"].UpdatePanned(u["pan"], u["lay"], u["params"][j], u["band"][j], u["delay"][j])
             u["rend"].ProcessInterleaved(u["audio"][j], u["bus"], FRAMES)
             u["done"].record(st)
-        issue_pan(k + 1)                # the next block's panning data, on the background context beside the renders
         with torch.cuda.stream(stream):
             for u in units:
                 stream.wait_event(u["done"])
@@ -1049,7 +1043,6 @@ def run_config4(args):
 
     def barrier():
         with torch.cuda.stream(stream):
-            stream.wait_stream(pan_stream)
             if exchange is not None:
                 exchange.wait()
         if env.dist is not None:
@@ -1059,14 +1052,13 @@ def run_config4(args):
     for _ in range(args.warmup):
         step()
     barrier()
-    l0 = sum(u["ctx"].launch_count for u in units) + ctx.launch_count + ctx_pan.launch_count
+    l0 = sum(u["ctx"].launch_count for u in units) + ctx.launch_count
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with torch.cuda.stream(stream):
         e0.record(stream)
     for _ in range(args.steps):
         step()
     with torch.cuda.stream(stream):
-        stream.wait_stream(pan_stream)
         if exchange is not None:
             exchange.wait()
         e1.record(stream)
@@ -1074,7 +1066,20 @@ def run_config4(args):
     ms_rank = e0.elapsed_time(e1) / args.steps
     ms = env.max_over_ranks(ms_rank)
     per_rank = env.gather_floats(ms_rank)
-    launches = sum(u["ctx"].launch_count for u in units) + ctx.launch_count + ctx_pan.launch_count - l0
+    launches = sum(u["ctx"].launch_count for u in units) + ctx.launch_count - l0
+    breakdown = None
+    if not args.no_breakdown:
+        # separate short pass with every kernel bracketed by events (durations under overlap, not part of the timed region)
+        for c in [u["ctx"] for u in units]:
+            c.set_kernel_timing(True); c.reset_kernel_timing()
+        bsteps = 10
+        for _ in range(bsteps):
+            step()
+        barrier()
+        breakdown = {u["name"]: {k: round(u["ctx"].kernel_time(k)[0] / bsteps, 4) for k in ("mdap", "push", "render", "bus_reduce")} for u in units}
+        breakdown["note"] = "durations of concurrently running kernels (four streams share the SMs): they overlap and include time spent waiting for free SMs"
+        for c in [u["ctx"] for u in units]:
+            c.set_kernel_timing(False)
     # combined bus of the last block against the rank-ordered float sum of the ranks' buses
     bus_check, ok = "single GPU (no combine)", True
     if env.dist is not None:
@@ -1104,11 +1109,12 @@ def run_config4(args):
                             "MDAP gains + fused update + push + render + bus reduce per block, real-time schedule",
                             {"total_sources": total, "sources_this_rank": end - begin, "ring_size": units[0]["rend"].ring_size,
                              "real_time_multiple": BLOCK_S * 1e3 / ms,
-                             "sharding": "contiguous cost-weighted ranges (sharding.shard_range, cost = 6.3 ns x channels + 0.027 ns x virtual sources per source)",
+                             "sharding": "contiguous cost-weighted ranges (sharding.shard_range); cost per source in SM-us per block: " + json.dumps(C4_COST),
                              "shards_begin_end_sourcechannels": shards,
                              "parallelism": f"sources sharded over {world} GPU(s), peer-memory combine of the [512x16] bus" if world > 1 else "single GPU"},
                             launches, clocks)
         line["per_rank_ms_per_step"] = [round(x, 5) for x in per_rank]
+        line["kernel_ms_per_step_rank0"] = breakdown
         line["bus_check"] = bus_check
         _emit(line)
     for u in units:
@@ -1188,6 +1194,7 @@ def main():
     ap.add_argument("--capacity-sources", type=int, default=0, help="cap of the capacity pass's sources per GPU (0 = what fits in HBM)")
     ap.add_argument("--c4-per-layout", type=int, default=8192, help="config 4: sources per layout and GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-breakdown", action="store_true", help="config 4: skip the per-kernel timing pass")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-capacity", action="store_true", help="skip the capacity pass (value then falls back to the linear figure at --sources)")
     ap.add_argument("--no-offline", action="store_true", help="skip the comparison pass with the packed schedule")

@@ -311,6 +311,14 @@ JPLG_API jplg_status jplg_mix_add_and_apply_gain_ramp(jplg_context ctx, float* d
                                                       uint32_t dest_num_channels, uint32_t source_num_channels,
                                                       uint32_t frames, const float* gain_start, const float* gain_end, int32_t mem); /* :89-107 */
 JPLG_API jplg_status jplg_mix_apply_gain(jplg_context ctx, float* dest, uint32_t n, uint32_t frames, const float* gains, int32_t mem); /* :50-63 */
+/* Add (:32-48): dest[pair][f][dest_channel] += source[pair][f][source_channel]. The reference's mono-source overload (:41-48) is
+ * source_channel = 0, source_num_channels = 1. */
+JPLG_API jplg_status jplg_mix_add(jplg_context ctx, float* dest, const float* source, uint32_t n, uint32_t dest_channel, uint32_t source_channel,
+                                  uint32_t dest_num_channels, uint32_t source_num_channels, uint32_t frames, int32_t mem);
+/* DownmixToMono (:129-136): dest [n][frames] += source [n][frames][num_channels] summed in channel order; dest is not cleared and
+ * nothing is normalised, like the reference. (The reference's numSamples argument is frames * num_channels.) */
+JPLG_API jplg_status jplg_mix_downmix_to_mono(jplg_context ctx, float* dest, const float* source, uint32_t n, uint32_t num_channels,
+                                              uint32_t frames, int32_t mem);
 
 /* ---------------------------------------------------------------------------------------------- */
 /* ReverbBus x n  (replaces: inc/Auralization/LateReverb.h:34-117, src/Auralization/LateReverb.cpp:31-134;           */

@@ -19,7 +19,7 @@ from ._capi import (  # noqa: F401
     MEM_HOST, MEM_DEVICE, MEM_HOST_ASYNC, MODE_PARITY, MODE_THROUGHPUT,
     EChannel, ChannelMask, ChannelMap,
     Context, VBAPanner, SourceLayout, DirectSoundBatch, CrossoverBank, DelayBank, ReverbBusBatch, ERBusBatch,
-    add_and_apply_gain_ramp, apply_gain, normalize_weights, get_spread_from_source_size,
+    add_and_apply_gain_ramp, apply_gain, add, downmix_to_mono, normalize_weights, get_spread_from_source_size,
     STATE_FLOATS,
     BusExchange, DirectPathBatch, AirAbsorptionCache, default_band_centers, speed_of_sound_for_temperature, sanitize_fallback_dir,
     MODEL_NONE, MODEL_INVERSE, MODEL_LINEAR, MODEL_EXPONENTIAL,

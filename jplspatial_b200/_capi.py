@@ -101,6 +101,8 @@ _sig("jplg_delay_bank_read", _i32, [_vp, _fp, _u32, _i32, _fp, _i32])
 _sig("jplg_delay_bank_read_xfade", _i32, [_vp, _fp, _fp, _u32, _fp, _i32])
 _sig("jplg_mix_add_and_apply_gain_ramp", _i32, [_vp, _fp, _fp, _u32, _u32, _u32, _u32, _u32, _u32, _fp, _fp, _i32])
 _sig("jplg_mix_apply_gain", _i32, [_vp, _fp, _u32, _u32, _fp, _i32])
+_sig("jplg_mix_add", _i32, [_vp, _fp, _fp, _u32, _u32, _u32, _u32, _u32, _u32, _i32])
+_sig("jplg_mix_downmix_to_mono", _i32, [_vp, _fp, _fp, _u32, _u32, _u32, _i32])
 
 DECLARED_SYMBOLS = [n for n in dir(lib) if n.startswith("jplg_")]
 
@@ -737,6 +739,24 @@ def add_and_apply_gain_ramp(ctx, dest, source, dest_channel, source_channel, fra
     g1 = np.ascontiguousarray(gain_end, np.float32)
     ctx.check(lib.jplg_mix_add_and_apply_gain_ramp(ctx.h, d.ctypes.data, s.ctypes.data, d.shape[0], dest_channel, source_channel,
                                                    d.shape[2], s.shape[2], frames, g0.ctypes.data, g1.ctypes.data, MEM_HOST))
+    return d
+
+
+def add(ctx, dest, source, dest_channel, source_channel=0):
+    """Add (inc/Auralization/ChannelMixing.h:32-48) for n pairs: dest [n, frames, nDest] += source [n, frames, nSrc] (or [n, frames]: the mono overload)"""
+    d = np.array(dest, np.float32, copy=True, order="C")
+    s = np.ascontiguousarray(source, np.float32)
+    if s.ndim == 2:
+        s = s[:, :, None]
+    ctx.check(lib.jplg_mix_add(ctx.h, d.ctypes.data, s.ctypes.data, d.shape[0], dest_channel, source_channel, d.shape[2], s.shape[2], d.shape[1], MEM_HOST))
+    return d
+
+
+def downmix_to_mono(ctx, dest, source):
+    """DownmixToMono (ChannelMixing.h:129-136) for n pairs: dest [n, frames] += sum_ch source [n, frames, C]"""
+    d = np.array(dest, np.float32, copy=True, order="C")
+    s = np.ascontiguousarray(source, np.float32)
+    ctx.check(lib.jplg_mix_downmix_to_mono(ctx.h, d.ctypes.data, s.ctypes.data, d.shape[0], s.shape[2], d.shape[1], MEM_HOST))
     return d
 
 

@@ -1326,6 +1326,65 @@ jplg_status jplg_mix_add_and_apply_gain_ramp(jplg_context ctx, float* dest, cons
 	return JPLG_OK;
 }
 
+// Add (ChannelMixing.h:32-48). source_num_channels == 1 and source_channel == 0 is the reference's second overload (mono source).
+jplg_status jplg_mix_add(jplg_context ctx, float* dest, const float* source, uint32_t n, uint32_t dest_channel, uint32_t source_channel,
+						 uint32_t dest_num_channels, uint32_t source_num_channels, uint32_t frames, int32_t mem)
+{
+	if (mem != JPLG_MEM_HOST && mem != JPLG_MEM_DEVICE) return JPLG_ERR_INVALID_ARGUMENT;
+	if (!ctx || !dest || !source || dest_channel >= dest_num_channels || source_channel >= source_num_channels) return JPLG_ERR_INVALID_ARGUMENT;
+	JPLG_NEED_DEVICE(ctx);
+	if (n == 0 || frames == 0) return JPLG_OK;
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	const size_t nd = size_t(n) * frames * dest_num_channels, ns = size_t(n) * frames * source_num_channels;
+	float* dDest = dest; const float* dSrc = source;
+	if (mem == JPLG_MEM_HOST)
+	{
+		void *a, *s;
+		jplg_status st = Scratch(ctx, 0, nd * 4, &a); if (st) return st;
+		st = Scratch(ctx, 1, ns * 4, &s); if (st) return st;
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(a, dest, nd * 4, cudaMemcpyHostToDevice, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(s, source, ns * 4, cudaMemcpyHostToDevice, ctx->stream));
+		dDest = static_cast<float*>(a); dSrc = static_cast<float*>(s);
+	}
+	JPLG_CUDA_TRY(ctx, LaunchMixAdd(dDest, dSrc, n, dest_channel, source_channel, dest_num_channels, source_num_channels, frames, ctx->stream)); ctx->launches++;
+	if (mem == JPLG_MEM_HOST)
+	{
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(dest, dDest, nd * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	}
+	return JPLG_OK;
+}
+
+// DownmixToMono (ChannelMixing.h:129-136): dest [n][frames] += sum over channels of source [n][frames][num_channels]
+jplg_status jplg_mix_downmix_to_mono(jplg_context ctx, float* dest, const float* source, uint32_t n, uint32_t num_channels, uint32_t frames, int32_t mem)
+{
+	if (mem != JPLG_MEM_HOST && mem != JPLG_MEM_DEVICE) return JPLG_ERR_INVALID_ARGUMENT;
+	if (!ctx || !dest || !source) return JPLG_ERR_INVALID_ARGUMENT;
+	JPLG_NEED_DEVICE(ctx);
+	if (n == 0 || frames == 0 || num_channels == 0) return JPLG_OK;
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	const size_t nd = size_t(n) * frames, ns = nd * num_channels;
+	float* dDest = dest; const float* dSrc = source;
+	if (mem == JPLG_MEM_HOST)
+	{
+		void *a, *s;
+		jplg_status st = Scratch(ctx, 0, nd * 4, &a); if (st) return st;
+		st = Scratch(ctx, 1, ns * 4, &s); if (st) return st;
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(a, dest, nd * 4, cudaMemcpyHostToDevice, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(s, source, ns * 4, cudaMemcpyHostToDevice, ctx->stream));
+		dDest = static_cast<float*>(a); dSrc = static_cast<float*>(s);
+	}
+	JPLG_CUDA_TRY(ctx, LaunchDownmixToMono(dDest, dSrc, n, num_channels, frames, ctx->stream)); ctx->launches++;
+	if (mem == JPLG_MEM_HOST)
+	{
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(dest, dDest, nd * 4, cudaMemcpyDeviceToHost, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+	}
+	return JPLG_OK;
+}
+
 jplg_status jplg_mix_apply_gain(jplg_context ctx, float* dest, uint32_t n, uint32_t frames, const float* gains, int32_t mem)
 {
 	if (mem != JPLG_MEM_HOST && mem != JPLG_MEM_DEVICE) return JPLG_ERR_INVALID_ARGUMENT;   // JPLG_MEM_HOST_ASYNC: mdap / update / process_block only

@@ -117,6 +117,8 @@ namespace jplg
 	cudaError_t LaunchMixRamp(float* dest, const float* src, uint32_t n, uint32_t destCh, uint32_t srcCh, uint32_t nDest, uint32_t nSrc,
 							  uint32_t frames, const float* g0, const float* g1, cudaStream_t st);
 	cudaError_t LaunchApplyGain(float* dest, uint32_t n, uint32_t frames, const float* gains, cudaStream_t st);
+	cudaError_t LaunchMixAdd(float* dest, const float* src, uint32_t n, uint32_t destCh, uint32_t srcCh, uint32_t nDest, uint32_t nSrc, uint32_t frames, cudaStream_t st);
+	cudaError_t LaunchDownmixToMono(float* dest, const float* src, uint32_t n, uint32_t numChannels, uint32_t frames, cudaStream_t st);
 	//======================================================================
 	// ReverbBus bank (jplg_reverb_kernels.cu)
 	constexpr uint32_t kFdnRingSize = 8192;   // power of two above the longest FDN delay + 1 (4259); the reference sizes each line bit_ceil(delay + 1)

@@ -546,6 +546,17 @@ extern "C"
 		AddAndApplyGainRamp(dest, src, destCh, srcCh, nDest, nSrc, frames, g0, g1);
 	}
 
+	// ChannelMixing.h:32-48 Add (nSrc == 0 selects the mono-source overload) and :129-136 DownmixToMono
+	void ref_mix_add(float* dest, const float* src, uint32_t destCh, uint32_t srcCh, uint32_t nDest, uint32_t nSrc, uint32_t frames)
+	{
+		if (nSrc == 0) Add(dest, src, destCh, nDest, frames);
+		else Add(dest, src, destCh, srcCh, nDest, nSrc, frames);
+	}
+	void ref_downmix_to_mono(float* dest, const float* src, uint32_t numChannels, uint32_t numSamples)
+	{
+		DownmixToMono(dest, src, numChannels, numSamples);
+	}
+
 	//==========================================================================
 	// DirectSoundEffect (DirectSound.h:44-65)
 	void* ref_dse_create(float fs, uint32_t nSrc, uint32_t nOut, const float* bandGains, float delaySeconds, const float* mixMap)

@@ -42,6 +42,8 @@ class Ref:
         L.ref_slerp_simd.argtypes = [_vp, _vp, _f32, _u32]
         L.ref_smoother_run.argtypes = [_f32, _f32, _u32, _u32, _vp]
         L.ref_add_gain_ramp.argtypes = [_vp, _vp, _u32, _u32, _u32, _u32, _u32, _f32, _f32]
+        L.ref_mix_add.argtypes = [_vp, _vp, _u32, _u32, _u32, _u32, _u32]
+        L.ref_downmix_to_mono.argtypes = [_vp, _vp, _u32, _u32]
         for name in ("ref_reverb_create", "ref_erbus_create"):
             getattr(L, name).restype = _vp
         L.ref_reverb_create.argtypes = [_f32, _f32, _f32, _f32]
@@ -231,6 +233,15 @@ class Ref:
     def add_gain_ramp(self, dest, src, dest_ch, src_ch, n_dest, n_src, frames, g0, g1):
         d = self._f(dest).copy(); s = self._f(src)
         self.lib.ref_add_gain_ramp(d.ctypes.data, s.ctypes.data, dest_ch, src_ch, n_dest, n_src, frames, g0, g1); return d
+
+    def mix_add(self, dest, src, dest_ch, src_ch, n_dest, n_src, frames):
+        """Add (ChannelMixing.h:32-48); n_src == 0 calls the mono-source overload"""
+        d = self._f(dest).copy(); s = self._f(src)
+        self.lib.ref_mix_add(d.ctypes.data, s.ctypes.data, dest_ch, src_ch, n_dest, n_src, frames); return d
+
+    def downmix_to_mono(self, dest, src, num_channels):
+        d = self._f(dest).copy(); s = self._f(src)
+        self.lib.ref_downmix_to_mono(d.ctypes.data, s.ctypes.data, num_channels, s.size); return d
 
     def crossover(self, fs=48000.0):
         return RefCrossover(self, fs)

@@ -220,6 +220,14 @@ def test_channel_mixing_vs_reference(gpu_ctx, ref):
         assert util.bits_equal(out[i], r)
     flat = util.white_noise((n, frames), util.SEED + 65)
     assert util.bits_equal(J.apply_gain(gpu_ctx, flat, g0), (flat * g0[:, None]).astype(np.float32))
+    # Add, both overloads, and DownmixToMono (ChannelMixing.h:32-48, 129-136)
+    added = J.add(gpu_ctx, dest, src, 7, 1)
+    added_mono = J.add(gpu_ctx, dest, flat, 3)
+    down = J.downmix_to_mono(gpu_ctx, flat, dest)
+    for i in range(n):
+        assert util.bits_equal(added[i], ref.mix_add(dest[i], src[i], 7, 1, nd, ns, frames))
+        assert util.bits_equal(added_mono[i], ref.mix_add(dest[i], flat[i], 3, 0, nd, 0, frames))
+        assert util.bits_equal(down[i], ref.downmix_to_mono(flat[i], dest[i], nd))
 
 
 def test_empty_and_error_paths(gpu_ctx):
