@@ -958,10 +958,11 @@ def run_gains_config(args):
 
 
 C4_LAYOUTS = (("Mono", 1, 288), ("Stereo", 2, 288), ("Quad", 4, 240), ("Surround_5_1", 6, 240))   # name, rendered channels, virtual sources per source -> 9.1.6
-# per-source cost model of the weighted sharding, in SM-microseconds per source and block (measured on one B200): the render CTA's
-# duration / its sources (118 us / 128 mono, 121 / 64 stereo, 127 / 32 quad, 151 / 21 5.1 sources per CTA) + 0.9 for the panning kernel
-# (~the same 240-288 virtual sources for every layout)
-C4_COST = {"Mono": 0.92 + 0.9, "Stereo": 1.89 + 0.9, "Quad": 3.97 + 0.9, "Surround_5_1": 7.19 + 0.9}
+# per-source cost model of the weighted sharding, in nanoseconds of one whole B200 per source and block, from the pieces measured one at a time
+# (profiles/r02f_c4_serial.txt: 8,192 sources per layout): render = 45.5 us of the whole GPU per 8,192 source-channels (a 118 us CTA of 126-128
+# source-channels on 148 SMs), panning kernel 46 us per 8,192 sources whatever the layout (240-288 virtual sources each), ring push 14.7 us per 8,192
+# source-channels for multichannel sources (fused into the render for mono ones)
+C4_COST = {"Mono": 11.2, "Stereo": 20.5, "Quad": 33.4, "Surround_5_1": 50.4}
 
 
 def run_config4(args):
@@ -996,7 +997,12 @@ def run_config4(args):
         seed = 0xC4 + 7919 * li + lo
         params = np.stack([util.pan_params(n, seed + 10 * b, edge=False) for b in range(2)])
         band = (0.1 + 0.9 * util.uniform01(2 * n * 4, seed + 1)).reshape(2, n, 4).astype(np.float32)
-        delay = ((1.0 + 299.0 * util.uniform01(2 * n, seed + 2)) / 343.2).reshape(2, n).astype(np.float32)
+        # the same scene model as config 3 (make_inputs): linear trajectories, 1-300 m, +-30 m/s; the two parameter sets the steps alternate between
+        # are one block apart (independent random delays per block would be sources jumping by up to 300 m every 10.7 ms)
+        dist0 = 1.0 + 299.0 * util.uniform01(n, seed + 2)
+        speed = (util.uniform01(n, seed + 4) * 2.0 - 1.0) * 30.0
+        tt = (np.arange(2, dtype=np.float32) * np.float32(BLOCK_S))[:, None]
+        delay = (np.maximum(dist0[None] + speed[None] * tt, 0.5) / np.float32(343.2)).astype(np.float32)
         audio = util.white_noise((2, n, FRAMES, C), seed + 3)
         rend = J.DirectSoundBatch(uctx, FS, n, C, L, band[0], delay[0], np.zeros((n, C * L), np.float32), ring_size=args.ring, max_block_frames=FRAMES, mode=env.mode)
         ust = uctx.torch_stream()
@@ -1109,7 +1115,7 @@ def run_config4(args):
                             "MDAP gains + fused update + push + render + bus reduce per block, real-time schedule",
                             {"total_sources": total, "sources_this_rank": end - begin, "ring_size": units[0]["rend"].ring_size,
                              "real_time_multiple": BLOCK_S * 1e3 / ms,
-                             "sharding": "contiguous cost-weighted ranges (sharding.shard_range); cost per source in SM-us per block: " + json.dumps(C4_COST),
+                             "sharding": "contiguous cost-weighted ranges (sharding.shard_range); cost per source in ns of one whole GPU per block: " + json.dumps(C4_COST),
                              "shards_begin_end_sourcechannels": shards,
                              "parallelism": f"sources sharded over {world} GPU(s), peer-memory combine of the [512x16] bus" if world > 1 else "single GPU"},
                             launches, clocks)
