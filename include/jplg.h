@@ -258,6 +258,16 @@ JPLG_API jplg_status jplg_renderer_wait_block(jplg_renderer r);
 /* Same, but also writes every source's own contribution: per_source [N][frames][L] (overwritten). */
 JPLG_API jplg_status jplg_renderer_process_block_debug(jplg_renderer r, const float* in, float* bus, float* per_source,
                                                        uint32_t frames, int32_t mem);
+/* JPLG_MODE_THROUGHPUT renderers render small scenes TIME-PARALLEL: FourBandCrossover::ProcessBlock (inc/Auralization/CrossoverFilter.h:505-535)
+ * is a linear recurrence with coefficients shared by every source, so a block is cut into
+ * 16-frame tiles that are filtered from zero state in parallel, stitched by a scan over the tiles' 24-float filter states (s' = M s + e, M fixed
+ * per sample rate) and re-run from their true start states (jplg_scan_kernels.cu); the delay smoother and the Thiran all-pass stay sequential
+ * three-operation chains, bit for bit the reference's (their rounding is part of the result: integer-delay statics never forget a state error). It costs twice the filter arithmetic, so by default
+ * (policy -1) it is used only while the scene leaves the machine under-filled (<= 2,048 source-channels, whole 16-frame tiles); 0 = never, 1 = whenever a block qualifies. Same state arrays as the sequential kernel: the policy may change between blocks.
+ * Results agree with JPLG_MODE_PARITY to rounding (bar 1e-5 * max(|ref|, rms, 1e-3)); PARITY renderers ignore the policy. */
+JPLG_API jplg_status jplg_renderer_set_time_parallel(jplg_renderer r, int32_t policy);
+/* Blocks rendered through the time-parallel path so far (tests / benchmarks check which path ran). */
+JPLG_API uint64_t    jplg_renderer_time_parallel_blocks(jplg_renderer r);
 /* Device pointer of the renderer's partial bus for the LAST block ([frames][L], not accumulated into
  * anything): the buffer a multi-GPU caller reduces across ranks. */
 JPLG_API float*      jplg_renderer_device_bus(jplg_renderer r);

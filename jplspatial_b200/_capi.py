@@ -83,6 +83,8 @@ _sig("jplg_renderer_update_panned", _i32, [_vp, _vp, _vp, _vp, _vp, _vp, _i32])
 _sig("jplg_renderer_push_ahead", _i32, [_vp, _fp, _u32])
 _sig("jplg_renderer_wait_render_started", _i32, [_vp, _vp])
 _sig("jplg_renderer_device_bus", _vp, [_vp])
+_sig("jplg_renderer_set_time_parallel", _i32, [_vp, _i32])
+_sig("jplg_renderer_time_parallel_blocks", _u64, [_vp])
 _sig("jplg_renderer_ring_size", _u32, [_vp])
 _sig("jplg_renderer_state_export", _i32, [_vp, _fp, _fp, C.POINTER(_u64)])
 _sig("jplg_renderer_state_import", _i32, [_vp, _fp, _fp, _u64])
@@ -508,6 +510,14 @@ class DirectSoundBatch:
 
     def device_bus_ptr(self):
         return lib.jplg_renderer_device_bus(self.h)
+
+    def SetTimeParallel(self, policy):
+        """throughput mode's time-parallel path (jplg_renderer_set_time_parallel): -1 chosen by size, 0 never, 1 whenever a block qualifies"""
+        self.ctx.check(lib.jplg_renderer_set_time_parallel(self.h, int(policy)))
+
+    @property
+    def time_parallel_blocks(self):
+        return int(lib.jplg_renderer_time_parallel_blocks(self.h))
 
     def state_export(self, with_rings=False):
         st = np.zeros((self.N * self.C, STATE_FLOATS), np.float32)

@@ -577,6 +577,11 @@ struct jplg_renderer_t
 	int activeSet = 0;
 	bool pendingPanned = false, setFreeRecorded[2] = { false, false };
 	cudaEvent_t evUpdated = nullptr, evSetFree[2] = {};
+	// time-parallel throughput path (jplg_scan_kernels.cu): -1 = chosen by size, 0 = never, 1 = whenever the block qualifies
+	int32_t scanPolicy = -1;
+	float *scanM = nullptr, *scanScratch = nullptr;
+	uint32_t* scanCounters = nullptr;
+	uint64_t scanBlocks = 0;
 };
 
 // targets in the reference's layouts -> SoA per source-channel (UpdateParameters, src/Auralization/DirectSound.cpp:231-239)
@@ -638,7 +643,8 @@ static void FreeRenderer(jplg_renderer r)
 	if (r->evStarted) { cudaEventDestroy(r->evStarted); r->evStarted = nullptr; }
 	if (r->evUpdated) { cudaEventDestroy(r->evUpdated); r->evUpdated = nullptr; }
 	for (auto& e : r->evSetFree) if (e) { cudaEventDestroy(e); e = nullptr; }
-	for (float** q : { &r->tgt2Delay, &r->tgt2Band, &r->tgt2Mix }) if (*q) { cudaFree(*q); *q = nullptr; }
+	for (float** q : { &r->tgt2Delay, &r->tgt2Band, &r->tgt2Mix, &r->scanM, &r->scanScratch }) if (*q) { cudaFree(*q); *q = nullptr; }
+	if (r->scanCounters) { cudaFree(r->scanCounters); r->scanCounters = nullptr; }
 	if (r->evAhead) { if (r->ctx->auxReady) cudaStreamSynchronize(r->ctx->aux[1]); cudaEventDestroy(r->evAhead); r->evAhead = nullptr; }
 }
 
@@ -820,6 +826,40 @@ static jplg_status EnsureAux(jplg_context ctx)
 	return JPLG_OK;
 }
 
+// JPLG_MODE_THROUGHPUT renders small scenes time-parallel (jplg_scan_kernels.cu): the scan does the crossover arithmetic twice, so it pays only
+// while (source-channels x tiles) threads still find idle schedulers. Cross-over measured on a B200 (profiles/r02_scan_ab.txt); the policy can be
+// pinned with jplg_renderer_set_time_parallel.
+constexpr size_t kScanAutoMaxSC = 2048;
+static bool UseScanPath(jplg_renderer r, const RenderParams& rp)
+{
+	if (r->cfg.mode != JPLG_MODE_THROUGHPUT || r->scanPolicy == 0 || !RenderCanScan(rp)) return false;
+	if (r->scanPolicy > 0) return true;
+	return size_t(rp.numSC) <= kScanAutoMaxSC;
+}
+
+static jplg_status LaunchScan(jplg_renderer r, const RenderParams& rp)
+{
+	jplg_context ctx = r->ctx;
+	if (!r->scanM)
+	{
+		float M[24 * 24];
+		CrossoverTransition(r->coef, kScanTile, M);
+		if (cudaMalloc(reinterpret_cast<void**>(&r->scanM), sizeof(M)) != cudaSuccess
+			|| cudaMalloc(reinterpret_cast<void**>(&r->scanScratch), ScanScratchFloats(r->numSC, r->maxFrames) * sizeof(float)) != cudaSuccess
+			|| cudaMalloc(reinterpret_cast<void**>(&r->scanCounters), size_t(r->numCTAs) * sizeof(uint32_t)) != cudaSuccess)
+		{ cudaGetLastError(); return Fail(ctx, JPLG_ERR_OUT_OF_MEMORY, "process_block: time-parallel scratch allocation failed"); }
+		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(r->scanM, M, sizeof(M), cudaMemcpyHostToDevice, ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaMemsetAsync(r->scanCounters, 0, size_t(r->numCTAs) * sizeof(uint32_t), ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));   // M is a stack array
+	}
+	ScanParams sp{};
+	sp.rp = rp; sp.M = r->scanM; sp.scratch = r->scanScratch; sp.counters = r->scanCounters; sp.push = 1u;
+	JPLG_LAUNCH(ctx, JPLG_K_RENDER, LaunchRenderScan(sp, ctx->stream));
+	ctx->launches += 1;   // k_scan_front, k_scan_mix
+	r->scanBlocks++;
+	return JPLG_OK;
+}
+
 static jplg_status ProcessBlock(jplg_renderer r, const float* in, float* bus, float* perSource, uint32_t frames, int32_t mem)
 {
 	if (!r || (frames && (!in || !bus))) return JPLG_ERR_INVALID_ARGUMENT;
@@ -956,14 +996,20 @@ static jplg_status ProcessBlock(jplg_renderer r, const float* in, float* bus, fl
 	{
 		// real-time order: this block's input enters the rings now. Mono renderers let k_render's own push role do it (no separate kernel, the copy
 		// overlaps the start of the filters); everything else launches the push kernel first.
-		rp.fusedPush = RenderCanFusePush(rp) ? 1u : 0u;
+		const bool scan = UseScanPath(r, rp);
+		rp.fusedPush = (scan || RenderCanFusePush(rp)) ? 1u : 0u;    // the time-parallel path pushes inside its own first kernel
 		if (!rp.fusedPush)
 		{
 			JPLG_LAUNCH(ctx, JPLG_K_PUSH, LaunchPush(rp, 0, N, ctx->stream));
 			if (asyncSlot >= 0) JPLG_CUDA_TRY(ctx, cudaEventRecord(r->evPushedA[asyncSlot], ctx->stream));
 		}
 		if (!r->evStarted) JPLG_CUDA_TRY(ctx, cudaEventCreateWithFlags(&r->evStarted, cudaEventDisableTiming));
-		JPLG_LAUNCH(ctx, JPLG_K_RENDER, LaunchRender(rp, r->cfg.mode, 0, r->numCTAs, ctx->stream, r->evStarted));
+		if (scan)
+		{
+			jplg_status sst = LaunchScan(r, rp); if (sst != JPLG_OK) return sst;
+			JPLG_CUDA_TRY(ctx, cudaEventRecord(r->evStarted, ctx->stream));   // small grids: "resident" and "done" are the same thing here
+		}
+		else JPLG_LAUNCH(ctx, JPLG_K_RENDER, LaunchRender(rp, r->cfg.mode, 0, r->numCTAs, ctx->stream, r->evStarted));
 		r->startedRecorded = true;
 		if (rp.fusedPush && asyncSlot >= 0) JPLG_CUDA_TRY(ctx, cudaEventRecord(r->evPushedA[asyncSlot], ctx->stream));   // the staging slot was read by the render
 	}
@@ -1043,6 +1089,14 @@ jplg_status jplg_renderer_process_block_debug(jplg_renderer r, const float* in, 
 	if (!per_source) return JPLG_ERR_INVALID_ARGUMENT;
 	return ProcessBlock(r, in, bus, per_source, frames, mem);
 }
+jplg_status jplg_renderer_set_time_parallel(jplg_renderer r, int32_t policy)
+{
+	if (!r || policy < -1 || policy > 1) return JPLG_ERR_INVALID_ARGUMENT;
+	std::lock_guard<std::mutex> lk(r->ctx->mtx);
+	r->scanPolicy = policy;
+	return JPLG_OK;
+}
+uint64_t jplg_renderer_time_parallel_blocks(jplg_renderer r) { return r ? r->scanBlocks : 0; }
 float* jplg_renderer_device_bus(jplg_renderer r) { return r ? r->deviceBus : nullptr; }
 uint32_t jplg_renderer_ring_size(jplg_renderer r) { return r ? r->ringSize : 0; }
 

@@ -745,6 +745,45 @@ namespace jplg
 		const float rev[4] = { freq[3], freq[2], freq[1], freq[0] };
 		prep(rev, out + 15, out + 19, out + 23);
 	}
+	// State-transition matrix of the whole FourBandCrossover over T samples of zero input (the time-parallel throughput path, jplg_scan_kernels.cu):
+	// M[r][k] = state r after T zero-input samples started from the unit state k, state order as ST_FILTER (jplg_kernels.hpp). The network is
+	// linear and time-invariant (CrossoverFilter.h:64-76,294-310,371-401), so the state after a tile is M * (state before) + (zero-state response).
+	// Evaluated in double from the float coefficients, rounded once.
+	void CrossoverTransition(const float coef[27], uint32_t T, float M[24 * 24])
+	{
+		double cf[27];
+		for (int i = 0; i < 27; ++i) cf[i] = coef[i];
+		const double minusR = -1.41421356237309504880;
+		for (int k = 0; k < 24; ++k)
+		{
+			double st[24] = {};
+			st[k] = 1.0;
+			auto svf = [&](int c, int stride, double x, int i, double& yL, double& yB, double& yH)
+			{
+				const double g = cf[c], d = cf[c + stride], mrg = cf[c + 2 * stride];
+				yH = (mrg * st[i] + (x - st[i + 1])) * d;
+				yB = g * yH + st[i]; st[i] = g * yH + yB;
+				yL = g * yB + st[i + 1]; st[i + 1] = g * yB + yL;
+			};
+			for (uint32_t n = 0; n < T; ++n)
+			{
+				double yL, yB, yH, yL2, yB2, yH2;
+				svf(0, 1, 0.0, 0, yL, yB, yH);
+				svf(0, 1, yL, 2, yL2, yB2, yH2);
+				const double low = yL2, high = minusR * yB + (yL + yH - yL2);
+				double aL, aB, aH, bL, bB, bH, t0, t1, l0, l1, h2, h3;
+				svf(3, 4, low, 4, aL, aB, aH);
+				svf(4, 4, high, 6, bL, bB, bH);
+				svf(3, 4, aL, 8, l0, t0, t1);
+				svf(4, 4, bL, 10, l1, t0, t1);
+				svf(5, 4, aH, 12, t0, t1, h2);
+				svf(6, 4, bH, 14, t0, t1, h3);
+				const double o[4] = { l0, l1, h2, h3 };
+				for (int q = 0; q < 4; ++q) { double pL, pB, pH; svf(15 + q, 4, o[q], 16 + 2 * q, pL, pB, pH); }
+			}
+			for (int r = 0; r < 24; ++r) M[r * 24 + k] = static_cast<float>(st[r]);
+		}
+	}
 	//======================================================================
 	// Scene front-end builders
 	namespace

@@ -82,6 +82,7 @@ namespace jplg
 	// FourBandCrossover::Prepare (inc/Auralization/CrossoverFilter.h:425-431): 27 floats
 	// X2{g,d,-(R+g)}, X13{g[4],d[4],mrg[4]} (lanes f1,f3,f1,f3), allpass{g[4],d[4],mrg[4]} (lanes f3,f1,f3,f1)
 	void CrossoverCoefficients(float sampleRate, float f1, float f2, float f3, float out[27]);
+	void CrossoverTransition(const float coef[27], uint32_t T, float M[24 * 24]);   // zero-input state transition over T samples (time-parallel path)
 
 	// SmoothedValue<float>::GetExpAlpha (inc/Utilities/SmoothedValue.h:36-41)
 	float ExpAlpha(uint32_t ticks);

@@ -105,6 +105,24 @@ namespace jplg
 	cudaError_t LaunchFp32Probe(float* sink, uint32_t grid, uint32_t iters, cudaStream_t st);
 	cudaError_t LaunchStateTranspose(const float* in, float* out, uint32_t rows, uint32_t cols, cudaStream_t st);
 
+	// ---- time-parallel throughput path (jplg_scan_kernels.cu): the block as a scan over kScanTile-frame tiles
+	constexpr uint32_t kScanTile = 16;      // 480 = 30 tiles: a tile never straddles one of DirectSoundEffect's chunks
+	struct ScanParams
+	{
+		RenderParams rp;
+		const float* M;         // [24][24] zero-input state transition of the crossover over kScanTile frames (host: CrossoverTransition)
+		float* scratch;         // ScanScratchFloats(numSC, maxFrames) floats
+		uint32_t* counters;     // [numCTAs], zero between launches
+		uint32_t push;          // 1: k_scan_front also pushes the block's input into the rings (0: already pushed)
+		// carved out of `scratch` by LaunchRenderScan
+		float* xth;             // [frames][numSC] filtered, band-gained source signals
+		float* tileGain;        // [nTiles][numSC][L + 4] gain ramps at the tile starts
+		uint32_t nTiles;
+	};
+	size_t ScanScratchFloats(uint32_t numSC, uint32_t maxFrames);
+	bool RenderCanScan(const RenderParams& rp);   // plain N x DirectSoundEffect, whole tiles
+	cudaError_t LaunchRenderScan(const ScanParams& sp, cudaStream_t st);
+
 	// components
 	struct XoverParams { uint32_t n, frames; float coef[27]; float* state; /* [24][n] */ };
 	cudaError_t LaunchXoverRamp(const XoverParams& xp, const float* in, const float* g0, const float* g1, float* out, int mode, cudaStream_t st);

@@ -1,0 +1,474 @@
+// Time-parallel render path of JPLG_MODE_THROUGHPUT: stages K2 + K3 + K4 of N x DirectSoundEffect as a chunked linear-recurrence scan over
+// kScanTile-frame tiles (src/Auralization/DirectSound.cpp:95-229; BASELINE.json north_star stage 3).
+//
+// k_render (jplg_render_kernels.cu) walks a block sample by sample inside one thread per source-channel: 512 dependent steps of ~200 operations,
+// which leaves a small scene (a few thousand source-channels: fewer source-warps than the machine has schedulers) latency-bound on a handful of
+// SMs. Here only the two recurrences whose ROUNDING is part of the result stay sequential, as three-operation chains; everything else is spread
+// over (source-channel, tile) threads. k_scan_front: one CTA = 4 source-channels x 32 tile slots, phases separated by __syncthreads:
+//
+//   P0  all threads: DelayLine::Push of the block (with the reference's chunk quirk, DirectSound.cpp:107-128; see k_push)
+//   P1  one thread per sc, sequential: SmoothedValue::Tick for every frame (inc/Utilities/SmoothedValue.h:73-77). The smoothed delay decides the
+//       integer / fraction split of every tap (at 40,000 samples of delay one float ulp is 0.004 samples), so it is the reference's recurrence
+//       bit for bit, not a closed form.
+//   P2  per (sc, tile), parallel: DelayTap::SetDelay -> Thiran coefficient (1 - f) / (1 + f) -> GetReadWindow<2> (DelayLine.h:53-59,199-213;
+//       FractionalDelay.h:105-110): a[n], x[n], x[n-1]
+//   P3  one thread per sc, sequential: y[n] = a[n] (x[n] - y[n-1]) + x[n-1] (FractionalDelay.h:117-124), bit for bit: for a static source on an
+//       exactly-integer delay a = 1, the all-pass has its pole ON the unit circle and a differently-rounded state never decays —
+//       an affine scan of this stage (y_end = P y_start + Q per tile) drifted past the bar within 20 blocks (r02 measurement).
+//   P4  per (sc, tile), parallel: the FourBandCrossover (CrossoverFilter.h:505-535) on the tile's delayed samples from ZERO state: the zero-state
+//       end state e (24 floats)
+//   P5  one warp per sc: the 24-state scan over the tiles, s[t+1] = M s[t] + e[t], with M = the crossover's zero-input transition over
+//       kScanTile frames (fixed per sample rate, built on the host in double: CrossoverTransition); leaves every tile's true START state. Its
+//       lanes also run the reference's gain-ramp recurrences (`gain += delta` per frame, ChannelMixing.h:99-107, CrossoverFilter.h:518-531 — a
+//       constant increment rounds the same way step after step, the accumulated ramp drifts up to 480 x 0.5 ulp from start + n * delta, so the
+//       closed form is outside the bar) and leave the ramp values at the tile starts.
+//   P6  per (sc, tile), parallel: re-runs the tile's crossover from its start state with the ramped band gains -> Y [frame][sc]
+//
+// k_scan_mix: per (128 sc, tile) CTA, the gain-ramped mix of the CTA's source-channels into a partial bus (thread mapping of k_render's mix role);
+// the last tile-CTA of a source group to finish commits mCurrentGains = targets (DirectSound.cpp:221).
+//
+// The crossover is stable (its state errors decay), so the scan's re-association there stays at rounding level. Twice the filter arithmetic of
+// the sequential kernel (zero-state pass + final pass) plus the 24 x 24 scan: it only pays while the machine is under-filled; the launcher's
+// caller (jplg_api.cu) selects it by size. Bar: 1e-5 * max(|ref|, rms, 1e-3) per sample against oracle/_ref, tests/test_gpu_scan.py.
+#include "jplg_kernels.hpp"
+#include "jplg_render_common.cuh"
+
+namespace jplg
+{
+	namespace
+	{
+		constexpr uint32_t kT = kScanTile;
+		constexpr uint32_t kScanThreads = 128;
+		constexpr uint32_t kFrontSC = 4;                               // source-channels per k_scan_front CTA (one per warp in the sequential phases)
+		constexpr uint32_t kFrontSlots = kScanThreads / kFrontSC;      // tile slots per source-channel
+
+		struct ScanTile { uint32_t n0, chunkStart, chunkLen, t0; };
+		__device__ __forceinline__ ScanTile scan_tile(uint32_t t, uint32_t F)
+		{
+			ScanTile ti;
+			ti.n0 = t * kT;
+			const uint32_t k = ti.n0 / kChunkFrames;            // 480 = 30 * 16: a tile never straddles a chunk
+			ti.chunkStart = k * kChunkFrames;
+			ti.chunkLen = min(F - ti.chunkStart, kChunkFrames);
+			ti.t0 = ti.n0 - ti.chunkStart;
+			return ti;
+		}
+	}
+
+	// dynamic shared memory (floats): dly | a (P3 leaves the delayed samples here) | x | x1, each [4][nTiles * 17 + 8]; e [4][nTiles][25] + 32
+	__global__ void __launch_bounds__(kScanThreads)
+	k_scan_front(const ScanParams sp)
+	{
+		extern __shared__ __align__(16) float sF[];
+		const RenderParams& rp = sp.rp;
+		const uint32_t tid = threadIdx.x, F = rp.frames, nT = sp.nTiles, C = rp.srcChannels, L = rp.L, nG = L + 4;
+		const size_t nSC = rp.numSC;
+		const uint32_t scBase = blockIdx.x * kFrontSC;
+		// sample (q, frame n) lives at q * rowS + (n / 16) * 17 + n % 16: tiles 17 floats apart and rows 8 banks apart, so the 32 lanes of a warp
+		// (8 tile slots x 4 source-channels) hit 32 different banks in the parallel phases (exactly so for 32 tiles)
+		const uint32_t rowS = nT * (kT + 1) + 8u, arrS = kFrontSC * rowS;
+		float* sDly = sF;
+		float* sA = sDly + arrS;
+		float* sX = sA + arrS;
+		float* sX1 = sX + arrS;
+		float* sE = sX1 + arrS;      // state k of (q, tile t) at (q * nT + t) * 25 + k + 8 q
+		const uint32_t pos32 = static_cast<uint32_t>(rp.pos);
+
+		// ---- P0: ring pushes of the CTA's source-channels (chunk k pushes in[480k .. F) at push offset PushesThroughChunk(F, k))
+		if (sp.push)
+		{
+			// a thread keeps frames f = f0 + tid + 128 j of all four source-channels in registers (one memory latency for the whole push) and stores
+			// every frame once per chunk k <= f / 480 (the tail of the block enters the ring once per chunk boundary it lies behind)
+			const uint32_t numChunks = (F + kChunkFrames - 1) / kChunkFrames;
+			for (uint32_t f0 = 0; f0 < F; f0 += 4 * kScanThreads)
+			{
+				float v[kFrontSC][4];
+				#pragma unroll
+				for (uint32_t qq = 0; qq < kFrontSC; ++qq)
+				{
+					const uint32_t s0 = min(scBase + qq, rp.numSC - 1u), src = s0 / C, ch = s0 - src * C;
+					const float* in = rp.in + size_t(src) * F * C + ch;
+					#pragma unroll
+					for (uint32_t j = 0; j < 4; ++j) { const uint32_t f = f0 + tid + kScanThreads * j; v[qq][j] = f < F ? __ldcs(in + size_t(f) * C) : 0.0f; }
+				}
+				#pragma unroll
+				for (uint32_t qq = 0; qq < kFrontSC; ++qq)
+				{
+					if (scBase + qq >= rp.numSC) break;
+					float* ring = rp.rings + size_t(scBase + qq) * rp.ringSize;
+					#pragma unroll
+					for (uint32_t j = 0; j < 4; ++j)
+					{
+						const uint32_t f = f0 + tid + kScanThreads * j;
+						if (f >= F) continue;
+						for (uint32_t k = 0; k < numChunks && k * kChunkFrames <= f; ++k)
+							ring[(pos32 + PushesThroughChunk(F, k) + (f - k * kChunkFrames)) & rp.ringMask] = v[qq][j];
+					}
+				}
+			}
+		}
+		// ---- P1: the smoothed delay of every frame (thread 32 q = source-channel q: one per warp / scheduler)
+		if ((tid & 31u) == 0)
+		{
+			const uint32_t q = tid >> 5, sc = scBase + q;
+			if (sc < rp.numSC)
+			{
+				float cur = rp.state[ST_DELAY * nSC + sc];
+				const float tgt = rp.tgtDelay[sc], alpha = rp.alpha;
+				float* o = sDly + q * rowS;
+				for (uint32_t t = 0; t < nT; ++t)
+				{
+					#pragma unroll
+					for (uint32_t i = 0; i < kT; ++i)
+					{
+						cur = alpha * (tgt - cur) + cur;     // same expression as role D of k_render (the smoother does not restart at chunk boundaries)
+						o[t * (kT + 1) + i] = cur;
+					}
+				}
+				rp.state[ST_DELAY * nSC + sc] = cur;
+			}
+		}
+		__syncthreads();
+		// ---- P2: taps. thread = (tile slot, source-channel q = tid & 3): the four source-channels' rows interleave across lanes
+		const uint32_t q = tid & (kFrontSC - 1u), slot = tid / kFrontSC, sc = scBase + q;
+		const bool scValid = sc < rp.numSC;
+		if (scValid)
+		{
+			const float* ring = rp.rings + size_t(sc) * rp.ringSize;
+			for (uint32_t t = slot; t < nT; t += kFrontSlots)
+			{
+				const ScanTile ti = scan_tile(t, F);
+				const uint32_t pe = pos32 + PushesThroughChunk(F, ti.chunkStart / kChunkFrames + 1);   // ring push count after this chunk's pushes
+				float a[kT], x[kT], x1[kT];
+				#pragma unroll
+				for (uint32_t i = 0; i < kT; ++i)
+				{
+					const float d = static_cast<float>(ti.chunkLen - (ti.t0 + i)) + sDly[q * rowS + t * (kT + 1) + i];   // SetDelay(float(framesToProcess - s) + delay)
+					const uint32_t D = static_cast<uint32_t>(d);
+					const float fr = d - static_cast<float>(static_cast<int32_t>(D));
+					const uint32_t r = pe - 1u - D;
+					a[i] = thiran_coef(fr);
+					x[i] = ring[r & rp.ringMask];
+					x1[i] = ring[(r - 1u) & rp.ringMask];
+				}
+				#pragma unroll
+				for (uint32_t i = 0; i < kT; ++i) { const uint32_t o = q * rowS + t * (kT + 1) + i; sA[o] = a[i]; sX[o] = x[i]; sX1[o] = x1[i]; }
+			}
+		}
+		__syncthreads();
+		// ---- P3: the Thiran recurrence, in place over the coefficients
+		if ((tid & 31u) == 0)
+		{
+			const uint32_t qq = tid >> 5, s2 = scBase + qq;
+			if (s2 < rp.numSC)
+			{
+				float y1 = rp.state[ST_THIRAN_Y1 * nSC + s2];
+				float* a = sA + qq * rowS; const float* x = sX + qq * rowS; const float* x1 = sX1 + qq * rowS;
+				for (uint32_t t = 0; t < nT; ++t)
+				{
+					const uint32_t n0 = t * (kT + 1);
+					float va[kT], vx[kT], v1[kT];
+					#pragma unroll
+					for (uint32_t i = 0; i < kT; ++i) { va[i] = a[n0 + i]; vx[i] = x[n0 + i]; v1[i] = x1[n0 + i]; }
+					#pragma unroll
+					for (uint32_t i = 0; i < kT; ++i)
+					{
+						y1 = va[i] * (vx[i] - y1) + v1[i];     // Thiran1stInterpolator::Process: never fused in the reference
+						a[n0 + i] = y1;
+					}
+				}
+				rp.state[ST_THIRAN_Y1 * nSC + s2] = y1;
+			}
+		}
+		__syncthreads();
+		// ---- P4: zero-state response of every tile
+		if (scValid)
+		{
+			for (uint32_t t = slot; t < nT; t += kFrontSlots)
+			{
+				float st[24];
+				#pragma unroll
+				for (int k = 0; k < 24; ++k) st[k] = 0.0f;
+				const float* xi = sA + q * rowS + t * (kT + 1);
+				#pragma unroll
+				for (uint32_t i = 0; i < kT; ++i) { float bands[4]; xover_sample<1>(rp.coef, st, xi[i], bands); }
+				float* e = sE + (q * nT + t) * 25 + 8 * q;
+				#pragma unroll
+				for (int k = 0; k < 24; ++k) e[k] = st[k];
+			}
+		}
+		__syncthreads();
+		// ---- P5: warp w = source-channel w: the scan over the tiles; lane r < 24 owns row r of M and state r; every lane ramps up to two gains
+		{
+			const uint32_t w = tid >> 5, lane = tid & 31u, s5 = scBase + w;
+			if (s5 < rp.numSC)
+			{
+				const uint32_t r = min(lane, 23u);
+				float m[24];
+				#pragma unroll
+				for (int k = 0; k < 24; ++k) m[k] = sp.M[r * 24 + k];
+				float s = rp.state[(ST_FILTER + r) * nSC + s5];
+				const uint32_t chunk0 = min(F, kChunkFrames);
+				float g[2], dg[2];
+				#pragma unroll
+				for (uint32_t h = 0; h < 2; ++h)
+				{
+					const uint32_t j = lane + 32u * h;
+					float cur = 0.0f, tg = 0.0f;
+					if (j < L) { cur = rp.curMix[j * nSC + s5]; tg = rp.tgtMix[j * nSC + s5]; }
+					else if (j < nG) { cur = rp.state[(ST_BAND + j - L) * nSC + s5]; tg = rp.tgtBand[(j - L) * nSC + s5]; }
+					g[h] = cur; dg[h] = (tg - cur) / static_cast<float>(chunk0);
+				}
+				float* e = sE + w * nT * 25 + 8 * w + r;
+				for (uint32_t t = 0; t < nT; ++t)
+				{
+					const float et = e[t * 25];
+					__syncwarp();
+					if (lane < 24) e[t * 25] = s;                    // the tile's start state replaces its zero-state response in place
+					if (t * kT < chunk0)
+					{
+						float* gt = sp.tileGain + (size_t(t) * nSC + s5) * nG;    // [tile][sc][L + 4]
+						if (lane < nG) gt[lane] = g[0];
+						if (lane + 32u < nG) gt[lane + 32u] = g[1];
+						#pragma unroll
+						for (uint32_t i = 0; i < kT; ++i) { g[0] += dg[0]; g[1] += dg[1]; }
+					}
+					float a0 = et, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
+					#pragma unroll
+					for (int k = 0; k < 24; k += 4)
+					{
+						a0 = __fmaf_rn(m[k], __shfl_sync(0xffffffffu, s, k), a0);
+						a1 = __fmaf_rn(m[k + 1], __shfl_sync(0xffffffffu, s, k + 1), a1);
+						a2 = __fmaf_rn(m[k + 2], __shfl_sync(0xffffffffu, s, k + 2), a2);
+						a3 = __fmaf_rn(m[k + 3], __shfl_sync(0xffffffffu, s, k + 3), a3);
+					}
+					s = (a0 + a1) + (a2 + a3);
+				}
+				if (lane < 24) rp.state[(ST_FILTER + lane) * nSC + s5] = s;
+			}
+		}
+		__syncthreads();
+		// ---- P6: every tile again from its true start state, with the ramped band gains (CrossoverFilter.h:505-535) -> Y [frame][sc]
+		if (scValid)
+		{
+			float tgB[4], curB[4];
+			#pragma unroll
+			for (int b = 0; b < 4; ++b) { tgB[b] = rp.tgtBand[b * nSC + sc]; curB[b] = rp.state[(ST_BAND + b) * nSC + sc]; }
+			for (uint32_t t = slot; t < nT; t += kFrontSlots)
+			{
+				const ScanTile ti = scan_tile(t, F);
+				const bool ramping = ti.chunkStart == 0;      // later chunks sit at the target (mFilterGains = target after a chunk, DirectSound.cpp:225)
+				const float chunkF = static_cast<float>(ti.chunkLen);
+				float st[24], band[4], inc[4];
+				const float* e = sE + (q * nT + t) * 25 + 8 * q;
+				#pragma unroll
+				for (int k = 0; k < 24; ++k) st[k] = e[k];
+				const float* gt = sp.tileGain + (size_t(t) * nSC + sc) * nG;     // written by this CTA's P5 (same CTA: ordered by the barrier above)
+				#pragma unroll
+				for (int b = 0; b < 4; ++b)
+				{
+					const float b0 = ramping ? curB[b] : tgB[b];
+					inc[b] = (tgB[b] - b0) / chunkF;
+					band[b] = ramping ? gt[L + b] : tgB[b];
+				}
+				const float* xi = sA + q * rowS + t * (kT + 1);
+				float* yo = sp.xth + size_t(ti.n0) * nSC + sc;
+				#pragma unroll
+				for (uint32_t i = 0; i < kT; ++i)
+				{
+					float b[4];
+					xover_sample<1>(rp.coef, st, xi[i], b);
+					// (bands * gains).reduce() with the bands interleaved { b1, b3, b2, b4 } (CrossoverFilter.h:516-531, SIMD.h:938-945)
+					yo[size_t(i) * nSC] = (b[0] * band[0] + b[1] * band[2]) + (b[2] * band[1] + b[3] * band[3]);
+					#pragma unroll
+					for (int k = 0; k < 4; ++k) band[k] += inc[k];
+				}
+			}
+		}
+		__syncthreads();       // every tile has read the block-start band gains
+		if (tid < kFrontSC && scBase + tid < rp.numSC)
+		{
+			#pragma unroll
+			for (int b = 0; b < 4; ++b) rp.state[(ST_BAND + b) * nSC + scBase + tid] = rp.tgtBand[b * nSC + scBase + tid];
+		}
+	}
+
+	__device__ __forceinline__ void cp_async4(float* dstShared, const float* src)
+	{
+		asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(static_cast<uint32_t>(__cvta_generic_to_shared(dstShared))), "l"(src) : "memory");
+	}
+
+	// dynamic shared memory (floats): Y [kT][128] | P [J][nPairs][kT + 1] f2 | tg, cur, gt [128][Lp] (target gains, block-start gains, ramp values at
+	// the tile start: staged with 4-byte cp.async, so the ~50 scattered loads of a thread are all in flight at once).
+	// DEBUG: also writes every source's own contribution (jplg_renderer_process_block_debug), channel after channel like the reference's
+	// `dest += source * gain`.
+	template<bool DEBUG>
+	__global__ void __launch_bounds__(kScanThreads)
+	k_scan_mix(const ScanParams sp)
+	{
+		extern __shared__ __align__(16) float sScan[];
+		__shared__ uint32_t sLast;
+		const RenderParams& rp = sp.rp;
+		const uint32_t tid = threadIdx.x, cta = blockIdx.x, t = blockIdx.y;
+		const uint32_t C = rp.srcChannels, L = rp.L, nG = L + 4;
+		const uint32_t srcPerCTA = kScanThreads / C, scPerCTA = srcPerCTA * C, scBase = cta * scPerCTA;
+		const uint32_t numSCInCTA = min(scPerCTA, rp.numSC - scBase);
+		const size_t nSC = rp.numSC;
+		const uint32_t F = rp.frames;
+		const ScanTile ti = scan_tile(t, F);
+		const float chunkF = static_cast<float>(ti.chunkLen);
+		const bool ramping = ti.chunkStart == 0;      // later chunks sit at the target (mCurrentGains = target after a chunk, DirectSound.cpp:221)
+		const uint32_t nPairs = (L + 1) / 2, Lp = 2 * nPairs;
+		const uint32_t J = kScanThreads / nPairs, pStride = (kT + 1) * nPairs;
+		float* sY = sScan;
+		f2* sP = reinterpret_cast<f2*>(sScan + kT * kScanThreads);
+		float* sTg = reinterpret_cast<float*>(sP + J * pStride);
+		float* sCur = sTg + kScanThreads * Lp;
+		float* sGt = sCur + kScanThreads * Lp;
+
+		if (tid < numSCInCTA)
+		{
+			const uint32_t sc = scBase + tid;
+			const float* yi = sp.xth + size_t(ti.n0) * nSC + sc;
+			#pragma unroll
+			for (uint32_t i = 0; i < kT; ++i) cp_async4(sY + i * kScanThreads + tid, yi + size_t(i) * nSC);
+			const float* gt = sp.tileGain + (size_t(t) * nSC + sc) * nG;
+			for (uint32_t c = 0; c < L; ++c)
+			{
+				cp_async4(sTg + tid * Lp + c, rp.tgtMix + c * nSC + sc);
+				if (ramping) { cp_async4(sCur + tid * Lp + c, rp.curMix + c * nSC + sc); cp_async4(sGt + tid * Lp + c, gt + c); }
+			}
+			if (L < Lp) { sTg[tid * Lp + L] = 0.0f; sCur[tid * Lp + L] = 0.0f; sGt[tid * Lp + L] = 0.0f; }
+		}
+		asm volatile("cp.async.commit_group;" ::: "memory");
+		asm volatile("cp.async.wait_group 0;" ::: "memory");
+		__syncthreads();
+
+		// ---- K4: AddAndApplyGainRamp (ChannelMixing.h:89-107) for every (source-channel, output channel) of the tile, re-associated across sources:
+		// thread = (output channel pair, source subset), kT packed frame accumulators, fixed-order cross-subset reduce (the mix role of k_render)
+		const uint32_t mixP = tid % nPairs, mixJ = tid / nPairs;
+		const uint32_t c0 = 2 * mixP, c1 = c0 + 1;
+		const bool has1 = c1 < L, mixActive = mixJ < J;
+		const uint32_t srcPerSubset = (srcPerCTA + J - 1) / J;
+		const uint32_t subBegin = min(mixJ * srcPerSubset * C, numSCInCTA), subEnd = min((mixJ + 1) * srcPerSubset * C, numSCInCTA);
+		if (mixActive)
+		{
+			f2 acc[kT];
+			#pragma unroll
+			for (uint32_t i = 0; i < kT; ++i) acc[i] = 0ull;
+			const f2 one = pk(1.0f, 1.0f);
+			for (uint32_t s = subBegin; s < subEnd; ++s)
+			{
+				const float2 tg = *reinterpret_cast<const float2*>(sTg + s * Lp + c0);
+				f2 g = pk(tg.x, tg.y), dg = 0ull;
+				if (ramping)
+				{
+					const float2 a = *reinterpret_cast<const float2*>(sCur + s * Lp + c0), gs = *reinterpret_cast<const float2*>(sGt + s * Lp + c0);
+					dg = pk((tg.x - a.x) / chunkF, (tg.y - a.y) / chunkF);       // delta = (gainEnd - gainStart) / numFrames (ChannelMixing.h:99)
+					g = pk(gs.x, gs.y);                                            // the reference's accumulated ramp at the tile start (k_scan_front P5)
+				}
+				if (DEBUG)
+				{
+					const uint32_t gsc = scBase + s, src = gsc / C, k = gsc - src * C;
+					float* ps = rp.perSource + (size_t(src) * F + ti.n0) * L;
+					for (uint32_t i = 0; i < kT; ++i)
+					{
+						const float y = sY[i * kScanThreads + s];
+						const f2 v = mul2(pk(y, y), g);
+						float* o = ps + size_t(i) * L;
+						o[c0] = (k == 0 ? 0.0f : o[c0]) + lo(v);
+						if (has1) o[c1] = (k == 0 ? 0.0f : o[c1]) + hi(v);
+						acc[i] = fma2(v, one, acc[i]);
+						g = fma2(g, one, dg);
+					}
+				}
+				else
+				{
+					#pragma unroll
+					for (uint32_t i = 0; i < kT; ++i)
+					{
+						const float y = sY[i * kScanThreads + s];
+						acc[i] = fma2(mul2(pk(y, y), g), one, acc[i]);     // product rounded first, as in the per-source outputs (same bus either way)
+						g = fma2(g, one, dg);
+					}
+				}
+			}
+			f2* row = sP + mixJ * pStride + mixP * (kT + 1);
+			#pragma unroll
+			for (uint32_t i = 0; i < kT; ++i) row[i] = acc[i];
+		}
+		__syncthreads();
+		{
+			float* pb = rp.partial + (size_t(cta) * F + ti.n0) * L;
+			const float* sPf = reinterpret_cast<const float*>(sP);
+			for (uint32_t o = tid; o < kT * Lp; o += kScanThreads)
+			{
+				const uint32_t i = o / Lp, c = o - i * Lp;
+				const float* src = sPf + ((c >> 1) * (kT + 1) + i) * 2 + (c & 1u);
+				float sum = 0.0f;
+				for (uint32_t j = 0; j < J; ++j, src += 2 * pStride) sum += *src;
+				if (c < L) pb[i * L + c] = sum;
+			}
+		}
+		// ---- the last tile-CTA of this source group to get here commits current = target (every tile read the block-start values above)
+		__threadfence();
+		__syncthreads();
+		if (tid == 0) sLast = (atomicAdd(&sp.counters[cta], 1u) == sp.nTiles - 1u) ? 1u : 0u;
+		__syncthreads();
+		if (sLast)
+		{
+			__threadfence();
+			if (tid < numSCInCTA)
+			{
+				const uint32_t sc = scBase + tid;
+				for (uint32_t c = 0; c < L; ++c) rp.curMix[c * nSC + sc] = rp.tgtMix[c * nSC + sc];
+			}
+			if (tid == 0) sp.counters[cta] = 0u;
+		}
+	}
+
+	size_t ScanScratchFloats(uint32_t numSC, uint32_t maxFrames)
+	{
+		const size_t nT = (maxFrames + kScanTile - 1) / kScanTile;
+		// Y [maxFrames][numSC]; tileGain [nT][numSC][L + 4] (L <= 32)
+		return size_t(numSC) * (size_t(maxFrames) + nT * (kMaxChannelsDev + 4));
+	}
+
+	static size_t ScanFrontSmem(uint32_t frames)
+	{
+		const size_t nT = frames / kScanTile;
+		return (size_t(4) * kFrontSC * (nT * (kScanTile + 1) + 8) + size_t(kFrontSC) * nT * 25 + 32) * sizeof(float);
+	}
+
+	bool RenderCanScan(const RenderParams& rp)   // per-source debug output: a multichannel source's channels must sit in one subset (they do: subsets hold whole sources)
+	{
+		const bool er = rp.scPerRing > 1 || rp.plainPush || rp.groupsPerCTA > 1 || rp.flags;
+		return !er && rp.frames >= kScanTile && rp.frames % kScanTile == 0 && rp.numSC > 0 && ScanFrontSmem(rp.frames) <= 200 * 1024
+			   && TotalPushes(rp.frames) <= rp.ringSize;
+	}
+
+	cudaError_t LaunchRenderScan(const ScanParams& spIn, cudaStream_t st)
+	{
+		ScanParams sp = spIn;
+		const RenderParams& rp = sp.rp;
+		sp.nTiles = rp.frames / kScanTile;
+		const size_t nSC = rp.numSC;
+		sp.xth = sp.scratch;
+		sp.tileGain = sp.scratch + size_t(rp.frames) * nSC;
+		const uint32_t nPairs = (rp.L + 1) / 2, J = kScanThreads / nPairs;
+		const size_t dynFront = ScanFrontSmem(rp.frames);
+		const size_t dynMix = size_t(kT) * kScanThreads * sizeof(float) + size_t(J) * (kT + 1) * nPairs * sizeof(f2) + size_t(3) * kScanThreads * 2 * nPairs * sizeof(float);
+		static bool attr = false;
+		if (!attr)
+		{
+			cudaFuncSetAttribute(k_scan_front, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+			cudaFuncSetAttribute(k_scan_mix<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+			cudaFuncSetAttribute(k_scan_mix<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+			attr = true;
+		}
+		k_scan_front<<<(rp.numSC + kFrontSC - 1) / kFrontSC, kScanThreads, dynFront, st>>>(sp);
+		if (rp.perSource) k_scan_mix<true><<<dim3(rp.numCTAs, sp.nTiles), kScanThreads, dynMix, st>>>(sp);
+		else k_scan_mix<false><<<dim3(rp.numCTAs, sp.nTiles), kScanThreads, dynMix, st>>>(sp);
+		return cudaGetLastError();
+	}
+}
