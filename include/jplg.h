@@ -143,6 +143,21 @@ JPLG_API uint32_t jplg_channel_map_from_num_channels(uint32_t n);          /* Fr
  * (inc/Panning/VBAPanning2D.h:124-137), 3D panner (KB_983 LUT) otherwise (VBAPanning3D.h:157-166).
  * Builds the LUT on the host exactly as LUTBuilder2D / LUTBuilder do and uploads it. */
 JPLG_API jplg_status jplg_panner_create(jplg_context ctx, uint32_t target_mask, jplg_panner* out);
+/* The same with one of the reference's LUT storage variants (template parameter ELUTSize of VBAPanner3D, inc/Panning/VBAPLUT3D.h:93-104,186-204;
+ * 3D layouts only). The device always queries one repacked 16-byte cell table, so a variant changes what the table HOLDS: exactly what the
+ * reference's query of that variant returns.
+ *   JPLG_LUT_KB_983  float gains, direct speaker indices: the default, what jplg_panner_create builds
+ *   JPLG_LUT_KB_851  float gains, speakers through the per-triangle table (ExtractDynamicData :768-800). Layouts WITHOUT an LFE only: with one the
+ *                    reference shifts its triplet indices by the LFE's channel position (:618-620 -> :516-519) and reads past the table's end,
+ *                    so there is no defined output to match (JPLG_ERR_UNSUPPORTED)
+ *   JPLG_LUT_KB_786  gains packed to 24 bits and back (Gain24Bit, inc/Utilities/GainEncoding.h:30-62), direct speaker indices
+ *   JPLG_LUT_KB_655, JPLG_LUT_KB_65  JPLG_ERR_UNSUPPORTED: KB_655 inherits KB_851's indexing, KB_65 returns NaN rows upstream */
+#define JPLG_LUT_KB_983 0
+#define JPLG_LUT_KB_851 1
+#define JPLG_LUT_KB_786 2
+#define JPLG_LUT_KB_655 3
+#define JPLG_LUT_KB_65  4
+JPLG_API jplg_status jplg_panner_create_ex(jplg_context ctx, uint32_t target_mask, int32_t lut_variant, jplg_panner* out);
 JPLG_API void        jplg_panner_destroy(jplg_panner p);
 JPLG_API int32_t     jplg_panner_is_3d(jplg_panner p);
 JPLG_API uint32_t    jplg_panner_num_channels(jplg_panner p);              /* GetNumChannels :346 */

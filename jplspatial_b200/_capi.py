@@ -52,6 +52,7 @@ _sig("jplg_channel_map_has_top_channels", _i32, [_u32])
 _sig("jplg_channel_map_channel_index", _u32, [_u32, _u32])
 _sig("jplg_channel_map_from_num_channels", _u32, [_u32])
 _sig("jplg_panner_create", _i32, [_vp, _u32, C.POINTER(_vp)])
+_sig("jplg_panner_create_ex", _i32, [_vp, _u32, _i32, C.POINTER(_vp)])
 _sig("jplg_panner_destroy", None, [_vp])
 _sig("jplg_panner_is_3d", _i32, [_vp])
 _sig("jplg_panner_num_channels", _u32, [_vp])
@@ -301,6 +302,9 @@ class SourceLayout:
             pass
 
 
+LUT_KB_983, LUT_KB_851, LUT_KB_786, LUT_KB_655, LUT_KB_65 = 0, 1, 2, 3, 4   # ELUTSize (inc/Panning/VBAPLUT3D.h:93-104)
+
+
 class VBAPanner:
     """VBAPanner2D / VBAPanner3D (inc/Panning/PannerBase.h:315-389), batched."""
 
@@ -308,9 +312,10 @@ class VBAPanner:
         self.ctx = ctx
         self.h = None
 
-    def Initialize(self, channel_map):
+    def Initialize(self, channel_map, lut_variant=0):
+        """lut_variant: the reference's ELUTSize template parameter (LUT_KB_983 default, LUT_KB_851, LUT_KB_786; jplg_panner_create_ex)"""
         h = _vp()
-        st = lib.jplg_panner_create(self.ctx.h, _mask(channel_map), C.byref(h))
+        st = lib.jplg_panner_create_ex(self.ctx.h, _mask(channel_map), int(lut_variant), C.byref(h))
         if st != 0:
             self.last_error = lib.jplg_last_error(self.ctx.h).decode()
             return False  # like the reference: false + trace

@@ -311,16 +311,22 @@ static jplg_status UploadLUT(jplg_panner p)
 
 extern "C" {
 
-jplg_status jplg_panner_create(jplg_context ctx, uint32_t target_mask, jplg_panner* out)
+jplg_status jplg_panner_create_ex(jplg_context ctx, uint32_t target_mask, int32_t lut_variant, jplg_panner* out)
 {
 	if (!ctx || !out) return JPLG_ERR_INVALID_ARGUMENT;
 	*out = nullptr;
+	if (lut_variant == JPLG_LUT_KB_655 || lut_variant == JPLG_LUT_KB_65)
+		return Fail(ctx, JPLG_ERR_UNSUPPORTED, lut_variant == JPLG_LUT_KB_655
+			? "LUT variant KB_655 combines KB_851's triplet indirection (undefined with an LFE, VBAPLUT3D.h:618-620) with KB_786's gain packing: use one of those"
+			: "LUT variant KB_65 returns NaN rows in the reference (gains recomputed per query from a triangle table indexed like KB_851's): not built");
+	if (lut_variant < JPLG_LUT_KB_983 || lut_variant > JPLG_LUT_KB_65) return JPLG_ERR_INVALID_ARGUMENT;
 	auto* p = new jplg_panner_t();
 	p->ctx = ctx;
 	std::string err;
-	if (!BuildPanner(target_mask, p->host, err))
+	if (!BuildPanner(target_mask, p->host, err, lut_variant))
 	{
 		delete p;
+		if (err.find("LUT variant") != std::string::npos || err.find("LUT storage") != std::string::npos) return Fail(ctx, JPLG_ERR_UNSUPPORTED, "VBAPannerBase: " + err);
 		return Fail(ctx, err.find("triangulate") != std::string::npos ? JPLG_ERR_TRIANGULATION : JPLG_ERR_INVALID_CHANNEL_MAP, "VBAPannerBase: " + err);
 	}
 	const jplg_status st = UploadLUT(p);
@@ -328,6 +334,7 @@ jplg_status jplg_panner_create(jplg_context ctx, uint32_t target_mask, jplg_pann
 	*out = p;
 	return JPLG_OK;
 }
+jplg_status jplg_panner_create(jplg_context ctx, uint32_t target_mask, jplg_panner* out) { return jplg_panner_create_ex(ctx, target_mask, JPLG_LUT_KB_983, out); }
 void jplg_panner_destroy(jplg_panner p)
 {
 	if (!p) return;

@@ -465,12 +465,35 @@ namespace jplg
 		}
 		inline V3 Transform3(const Mat3& m, const V3& v) { return Add(Add(Scale(m.c0, v.x), Scale(m.c1, v.y)), Scale(m.c2, v.z)); }
 
-		bool Build3D(uint32_t targetMask, PannerData& out, std::string& error)
+		bool Build3D(uint32_t targetMask, PannerData& out, std::string& error, int lutVariant)
 		{
 			std::vector<V3> verts; uint32_t numDummies = 0, lfeIndex = 0;
 			SpeakerVertices(targetMask, verts, numDummies, lfeIndex);
 			const uint32_t numReal = static_cast<uint32_t>(verts.size()) - numDummies;
 			auto isDummy = [&](uint32_t idx) { return idx >= numReal; };
+			// ELUTSize storage variants (inc/Panning/VBAPLUT3D.h:93-104,186-204). The device serves every variant from the same repacked 16-byte cell
+			// table, so a variant is what the reference's own query of that variant RETURNS:
+			//   KB_786  gains go through Gain24Bit (inc/Utilities/GainEncoding.h:30-62) on their way into the table and back out of it
+			//   KB_851  speakers come from the per-triangle dynamic data (ExtractDynamicData :768-800) through a triplet index. The reference stores
+			//           that index as SanitizeSpeakerIndex(triI) (:618-620 -> :516-519), i.e. shifted by one for every triangle index >= the LFE's
+			//           CHANNEL index, and the last triangle then reads past the end of the table: with an LFE in the layout the variant has no
+			//           defined output, without one the index is untouched and the speakers are the triangle's (dummy replaced), unsanitised —
+			//           which is the same as sanitised when there is no LFE to skip.
+			if (lutVariant == 1 && (targetMask & uint32_t(CH_LFE)))
+			{
+				error = "LUT variant KB_851 is undefined for layouts with an LFE: the reference indexes its triangle table with a channel-sanitised triplet index (VBAPLUT3D.h:618-620,516-519) and reads past its end";
+				return false;
+			}
+			auto gain24 = [](float g)
+			{
+				// Gain24Bit(float): w24 = uint32(g * 2^24); w24 -= w24 >> 24; decode: w24 * (1 / (2^24 - 1)). The float -> uint32 conversion of the
+				// reference's x86-64 build is a 64-bit truncating convert whose low 32 bits are kept (negative gains wrap instead of clamping)
+				const float scaled = g * 16777216.0f;
+				uint32_t w = static_cast<uint32_t>(static_cast<int64_t>(scaled));
+				w -= (w >> 24);
+				const uint32_t stored = w & 0xffffffu;
+				return static_cast<float>(stored) * (1.0f / 16777215.0f);
+			};
 
 			out.tris.clear(); out.trisTabulated = false;
 			if (verts.size() == 3) out.tris = { 0, 1, 2 };
@@ -529,6 +552,8 @@ namespace jplg
 						g = Normalized(g);
 						float* gp = &out.lut3dGains[size_t(code) * 3];
 						gp[0] = g.x; gp[1] = g.y; gp[2] = g.z;
+						if (lutVariant == 2) { gp[0] = gain24(g.x); gp[1] = gain24(g.y); gp[2] = gain24(g.z); }
+						if (lutVariant == 1 && dummy >= 0) gp[dummy] = 0.0f;    // GainsFor: gains[dummyIndex] = 0 (:850-854); already zero before the normalisation
 						uint8_t* sp = &out.lut3dSpeakers[size_t(code) * 3];
 						sp[0] = sanitize(tri[0]); sp[1] = sanitize(tri[1]); sp[2] = sanitize(tri[2]);
 						found = true;
@@ -593,7 +618,7 @@ namespace jplg
 		return outTris.size() >= 12 && outTris.size() / 3 <= 64;
 	}
 
-	bool BuildPanner(uint32_t targetMask, PannerData& out, std::string& error)
+	bool BuildPanner(uint32_t targetMask, PannerData& out, std::string& error, int lutVariant)
 	{
 		out = PannerData{};
 		out.mask = targetMask;
@@ -604,8 +629,9 @@ namespace jplg
 		{
 			// Panning3D::IsValidTargetChannelMap (inc/Panning/VBAPanning3D.h:157-166)
 			if (out.numChannels < 3) { error = "Trying to initialize with < 3 channels, 3D panning is not possible for such layout."; return false; }
-			return Build3D(targetMask, out, error);
+			return Build3D(targetMask, out, error, lutVariant);
 		}
+		if (lutVariant != 0) { error = "LUT storage variants exist for 3D panners only (VBAPanning3D.h)."; return false; }
 		// Panning2D::IsValidTargetChannelMap (inc/Panning/VBAPanning2D.h:124-137)
 		if (out.numChannels == 1) { error = "Trying to initialize with single target channel, panning is not possible."; return false; }
 		return Build2D(targetMask, out, error);

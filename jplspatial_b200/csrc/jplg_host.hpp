@@ -54,7 +54,8 @@ namespace jplg
 	};
 
 	// VBAPannerBase::Initialize (PannerBase.h:455-482). Returns false + message like the reference returns false + JPL_ERROR_TAG.
-	bool BuildPanner(uint32_t targetMask, PannerData& out, std::string& error);
+	// lutVariant: 0 KB_983 (the reference's default), 1 KB_851, 2 KB_786 (ELUTSize, inc/Panning/VBAPLUT3D.h:93-104); 3D panners only
+	bool BuildPanner(uint32_t targetMask, PannerData& out, std::string& error, int lutVariant = 0);
 
 	// Generic speaker triangulation used for masks that are not in the reference-derived table.
 	bool TriangulateGeneric(const std::vector<V3>& verts, std::vector<uint8_t>& outTris);

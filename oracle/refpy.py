@@ -249,6 +249,21 @@ class Ref:
     def delay(self, min_size):
         return RefDelay(self, min_size)
 
+    def lut_variant(self, kind, target_mask, source_mask, params, dirs):
+        """VBAPanner3D<VBAPStandardTraits, ELUTSize kind> (kind 0 KB_983, 1 KB_851, 2 KB_786, 3 KB_655, 4 KB_65), one shot: ProcessVBAPData for
+        params [n][5] and GetSpeakerGains for dirs [m][3] -> (mix [n][stride], point [m][L]); None when the panner does not initialise"""
+        prm = self._f(params).reshape(-1, 5); d = self._f(dirs).reshape(-1, 3)
+        L = bin(int(target_mask)).count("1")
+        mix = np.zeros((prm.shape[0], 8 * L), np.float32); pt = np.zeros((d.shape[0], L), np.float32)
+        self.lib.ref_lut_variant.restype = C.c_int
+        self.lib.ref_lut_variant.argtypes = [C.c_int, _u32, _u32, _vp, _u32, _vp, _vp, _u32, _vp]
+        big = np.zeros((prm.shape[0] * 8 * L,), np.float32)
+        stride = int(self.lib.ref_lut_variant(int(kind), int(target_mask), int(source_mask), prm.ctypes.data, prm.shape[0], big.ctypes.data,
+                                              d.ctypes.data, d.shape[0], pt.ctypes.data))
+        if stride == 0:
+            return None
+        return big[: prm.shape[0] * stride].reshape(prm.shape[0], stride).copy(), pt
+
     def dse(self, fs, n_src, n_out, band_gains, delay_seconds, mix_map):
         return RefDSE(self, fs, n_src, n_out, band_gains, delay_seconds, mix_map)
 
