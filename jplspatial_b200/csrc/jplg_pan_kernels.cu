@@ -1,6 +1,6 @@
 // K1: batched VBAP / MDAP gain evaluation for sm_100a.
 //   k_point_gains_{2d,3d}  one thread per query         (GetSpeakerGains, inc/Panning/PannerBase.h:441-445)
-//   k_mdap_3d<G>           G = 16 or 32 lanes per source (ProcessVBAPData, PannerBase.h:486-728, 3D panner)
+//   k_mdap_3d<G>           G = 8 or 32 lanes per source (ProcessVBAPData, PannerBase.h:486-728, 3D panner)
 //   k_mdap_2d              one warp per source           (same, 2D panner)
 //   k_process_vs           one thread per virtual-source set (ProcessVirtualSources, PannerBase.h:731-804)
 // The direction -> LUT-index arithmetic is bit-exact with the reference's SSE2 build (jplg_device_math.cuh);
@@ -8,6 +8,7 @@
 // Compile with -fmad=false.
 #include "jplg_kernels.hpp"
 #include "jplg_device_math.cuh"
+#include <cstdlib>
 
 namespace jplg
 {
@@ -69,15 +70,21 @@ namespace jplg
 		return m;
 	}
 
-	// G lanes per source (G = 16 when the target has <= 16 channels: two sources share a warp, which halves the cost of the
-	// speaker-ordered accumulation and wastes fewer lanes on the 72 = 4.5 x 16 virtual sources of mono -> 7.1.4; else G = 32).
-	// Shared memory per group: ring sin/cos (2*24 floats) + one 16-B entry per virtual source + mixBuffer.
-	constexpr uint32_t kMdapRows = 32;   // virtual sources per accumulation batch (rows of the per-group gain matrix)
+	// G lanes per source. Targets with <= 16 channels take G = 8 (r02): four sources share a warp, so the per-source work every lane repeats (pan quaternion,
+	// per-channel basis, ring sines) is amortised over twice as many sources as with 16 lanes, the 72 = 9 x 8 virtual sources of mono -> 7.1.4 fill every lane slot
+	// (16 lanes: 4.5 -> 5 trips, 10 % idle), and each lane adds two columns of the gain matrix. Wider targets take one warp per source (G = 32).
+	// ROWS = virtual sources per accumulation batch (rows of the per-group gain matrix), STRIDE = floats between matrix rows: odd, so that the scatter of a
+	// batch (row = lane, column = speaker) and the column sums (row after row, column = lane) both spread over the banks (r01e: 1.5 conflicts per shared-memory
+	// instruction with the [32][16] matrix).
+	// Shared memory per group: ring sin/cos (2*24 floats) + gain matrix + mixBuffer.
+	template<int G> struct MdapShape { static constexpr uint32_t kRows = G == 8 ? 24u : 32u, kCols = G == 32 ? 32u : 16u, kStride = kCols + 1u, kGroupFloats = 48u + kRows * kStride + kMaxChannelsDev; };
 	template<int G>
 	__global__ void __launch_bounds__(JPLG_MDAP_WARPS * 32)
 	k_mdap_3d(const uint4* __restrict__ lut, const uint32_t* __restrict__ rsqTable, MdapLayoutParams lp,
 			  const float* __restrict__ params, uint32_t n, uint32_t L, float* __restrict__ out, const MdapFuse fz)
 	{
+		constexpr uint32_t kRows = MdapShape<G>::kRows, kStride = MdapShape<G>::kStride, kGroupFloats = MdapShape<G>::kGroupFloats;
+		constexpr uint32_t kColsPerLane = MdapShape<G>::kCols / G;      // columns a lane sums: 2 for G = 8, else 1
 		extern __shared__ __align__(16) unsigned char smemRaw[];
 		uint32_t* sRsq = reinterpret_cast<uint32_t*>(smemRaw);                       // 2048
 		float* sAzSin = reinterpret_cast<float*>(sRsq + 2048);                        // 32 (max 24 used: halfAndTail*4 <= 16)
@@ -85,21 +92,21 @@ namespace jplg
 		float* sGroupBase = sAzCos + 32;
 		constexpr uint32_t kGroups = JPLG_MDAP_WARPS * 32 / G;
 		const uint32_t grp = threadIdx.x / G, gl = threadIdx.x % G;
-		// per group: ring sin/cos [24+24] | gain matrix [kMdapRows][G] (row = virtual source of the current batch, column = speaker; all zero
+		// per group: ring sin/cos [24+24] | gain matrix [kRows][kStride] (row = virtual source of the current batch, column = speaker; all zero
 		// between batches) | mixBuffer [32]
-		float* sRingS = sGroupBase + grp * (48 + kMdapRows * G + kMaxChannelsDev);
+		float* sRingS = sGroupBase + grp * kGroupFloats;
 		float* sRingC = sRingS + 24;
 		float* sMat = sRingC + 24;
-		float* sMix = sMat + kMdapRows * G;                                           // [32] mixBuffer
+		float* sMix = sMat + kRows * kStride;                                         // [32] mixBuffer
 
-		for (uint32_t i = threadIdx.x; i < kGroups * kMdapRows * G; i += blockDim.x) sGroupBase[(i / (kMdapRows * G)) * (48 + kMdapRows * G + kMaxChannelsDev) + 48 + i % (kMdapRows * G)] = 0.0f;
+		for (uint32_t i = threadIdx.x; i < kGroups * kRows * kStride; i += blockDim.x) sGroupBase[(i / (kRows * kStride)) * kGroupFloats + 48 + i % (kRows * kStride)] = 0.0f;
 		for (uint32_t i = threadIdx.x; i < 2048; i += blockDim.x) sRsq[i] = rsqTable[i];
 		if (threadIdx.x < 32) { sAzSin[threadIdx.x] = lp.azSin[threadIdx.x]; sAzCos[threadIdx.x] = lp.azCos[threadIdx.x]; }
 		const uint32_t R = lp.numRings, H = lp.halfSamples;
 		const uint32_t packsHalf = R * H;
 		// virtual source -> (ring, azimuth slot, mirrored) of GenerateSpreadCap's pack order (VBAPanning3D.h:449-518): the same for every source,
 		// so the two integer divisions per virtual source are done once per CTA. Entry = ring | azimuth float index << 8 | mirror << 16.
-		uint32_t* sVsIdx = reinterpret_cast<uint32_t*>(sGroupBase + kGroups * (48 + kMdapRows * G + kMaxChannelsDev));
+		uint32_t* sVsIdx = reinterpret_cast<uint32_t*>(sGroupBase + kGroups * kGroupFloats);
 		for (uint32_t v = threadIdx.x; v < lp.numVS; v += blockDim.x)
 		{
 			const uint32_t pack = v >> 2, l4 = v & 3u;
@@ -133,7 +140,8 @@ namespace jplg
 				if (r < (R & ~3u)) sincos_simd(phi, s, c); else sincos_libm(phi, s, c);
 				sRingS[r] = s; sRingC[r] = c;
 			}
-			if (gl < L) sMix[gl] = 0.0f;
+			#pragma unroll
+			for (uint32_t k = 0; k < kColsPerLane; ++k) if (gl + k * G < L) sMix[gl + k * G] = 0.0f;
 			__syncwarp();
 
 			float* outSrc = out + size_t(src) * lp.numChannels * L;
@@ -143,18 +151,20 @@ namespace jplg
 				const Q4 qc{ lp.quats[ch][0], lp.quats[ch][1], lp.quats[ch][2], lp.quats[ch][3] };
 				const B3 basis = quat_to_basis(quat_mul(m.qPan, qc)); // PannerBase.h:593-601
 
-				// outGains[speakers[s]] += gains[s] in entry order (PannerBase.h:846-849), per speaker == lane. A batch of kMdapRows virtual sources
+				// outGains[speakers[s]] += gains[s] in entry order (PannerBase.h:846-849), per speaker == column. A batch of kRows virtual sources
 				// scatters its (vsWeight * g) * g values into the zeroed gain matrix (the three speakers of a cell are distinct: a triangle, the dummy
-				// replaced by an index not in it, VBAPLUT3D.h:803-815), then lane s adds column s row after row: the entries of other speakers
-				// contribute +0.0f, which leaves a non-negative running sum unchanged bit for bit, so the additions that matter happen in the
+				// replaced by an index not in it, VBAPLUT3D.h:803-815), then every column is added row after row by its lane: the entries of other
+				// speakers contribute +0.0f, which leaves a non-negative running sum unchanged bit for bit, so the additions that matter happen in the
 				// reference's order. 2 instructions per entry instead of a 14-instruction compare / select scan (ncu r01d: that scan was 33 % of
 				// the kernel's issued instructions).
-				float acc = 0.0f;
-				for (uint32_t vb = 0; vb < lp.numVS; vb += kMdapRows)
+				float acc[kColsPerLane];
+				#pragma unroll
+				for (uint32_t k = 0; k < kColsPerLane; ++k) acc[k] = 0.0f;
+				for (uint32_t vb = 0; vb < lp.numVS; vb += kRows)
 				{
-					uint32_t mine[kMdapRows / G];      // matrix offsets this lane wrote (to clear them afterwards), 3 x 10 bits each
+					uint32_t mine[kRows / G];      // speakers this lane wrote (to clear them afterwards), 3 x 8 bits each
 					#pragma unroll
-					for (uint32_t it = 0; it < kMdapRows / G; ++it)
+					for (uint32_t it = 0; it < kRows / G; ++it)
 					{
 						const uint32_t row = it * G + gl, v = vb + row;
 						mine[it] = 0xffffffffu;
@@ -174,66 +184,88 @@ namespace jplg
 							// (vsWeight * g) * g (PannerBase.h:836-839)
 							const float g0 = u2f(cell.x), g1 = u2f(cell.y), g2 = u2f(cell.z);
 							const uint32_t s0 = cell.w & 0xffu, s1 = (cell.w >> 8) & 0xffu, s2 = (cell.w >> 16) & 0xffu;
-							float* mrow = sMat + row * G;
-							if (s0 < G) mrow[s0] = (lp.vsWeight * g0) * g0;
-							if (s1 < G) mrow[s1] = (lp.vsWeight * g1) * g1;
-							if (s2 < G) mrow[s2] = (lp.vsWeight * g2) * g2;
+							float* mrow = sMat + row * kStride;
+							if (s0 < L) mrow[s0] = (lp.vsWeight * g0) * g0;
+							if (s1 < L) mrow[s1] = (lp.vsWeight * g1) * g1;
+							if (s2 < L) mrow[s2] = (lp.vsWeight * g2) * g2;
 							mine[it] = cell.w & 0xffffffu;
 						}
 					}
 					__syncwarp();
-					if (gl < L)
 					{
-						const uint32_t rows = min(kMdapRows, lp.numVS - vb);
-						const float* col = sMat + gl;
-						if (rows == kMdapRows)
+						const uint32_t rows = min(kRows, lp.numVS - vb);
+						#pragma unroll
+						for (uint32_t k = 0; k < kColsPerLane; ++k)
 						{
-							#pragma unroll
-							for (uint32_t e = 0; e < kMdapRows; ++e) acc += col[e * G];
+							if (gl + k * G >= L) continue;
+							const float* col = sMat + gl + k * G;
+							if (rows == kRows)
+							{
+								#pragma unroll
+								for (uint32_t e = 0; e < kRows; ++e) acc[k] += col[e * kStride];
+							}
+							else
+								for (uint32_t e = 0; e < rows; ++e) acc[k] += col[e * kStride];
 						}
-						else
-							for (uint32_t e = 0; e < rows; ++e) acc += col[e * G];
 					}
 					__syncwarp();
 					#pragma unroll
-					for (uint32_t it = 0; it < kMdapRows / G; ++it)
+					for (uint32_t it = 0; it < kRows / G; ++it)
 					{
 						if (mine[it] != 0xffffffffu)
 						{
-							float* mrow = sMat + (it * G + gl) * G;
+							float* mrow = sMat + (it * G + gl) * kStride;
 							const uint32_t s0 = mine[it] & 0xffu, s1 = (mine[it] >> 8) & 0xffu, s2 = (mine[it] >> 16) & 0xffu;
-							if (s0 < G) mrow[s0] = 0.0f;
-							if (s1 < G) mrow[s1] = 0.0f;
-							if (s2 < G) mrow[s2] = 0.0f;
+							if (s0 < L) mrow[s0] = 0.0f;
+							if (s1 < L) mrow[s1] = 0.0f;
+							if (s2 < L) mrow[s2] = 0.0f;
 						}
 					}
 					// the next batch's writes of a lane only touch rows it owns, which it has just cleared; readers of this batch are behind the barrier above
 				}
-				if (gl < L)
+				#pragma unroll
+				for (uint32_t k = 0; k < kColsPerLane; ++k)
 				{
-					if (valid) outSrc[ch * L + gl] = acc; // pre-normalisation value; rescaled below
-					sMix[gl] += acc;                       // mixBuffer[i] += gains[i] (:683-686)
+					const uint32_t c = gl + k * G;
+					if (c < L)
+					{
+						if (valid) outSrc[ch * L + c] = acc[k]; // pre-normalisation value; rescaled below
+						sMix[c] += acc[k];                       // mixBuffer[i] += gains[i] (:683-686)
+					}
 				}
 				__syncwarp();
 			}
 
 			// Normalise for the number of input channels (:694-713)
-			if (gl < L && valid)
+			#pragma unroll
+			for (uint32_t k = 0; k < kColsPerLane; ++k)
 			{
-				const float g = sMix[gl];
-				const float norm = g > 0.0f ? invsqrt_exact(g * nChF) : 0.0f;
-				for (uint32_t ch = 0; ch < lp.numChannels; ++ch)
+				const uint32_t c = gl + k * G;
+				if (c < L && valid)
 				{
-					const float v = outSrc[ch * L + gl] * norm;
-					outSrc[ch * L + gl] = v;
-					if (fz.tgtMix) fz.tgtMix[size_t(gl) * fz.numSC + size_t(src) * fz.rendC + fz.rows[ch]] = v;   // k_update_targets' transpose
+					const float g = sMix[c];
+					const float norm = g > 0.0f ? invsqrt_exact(g * nChF) : 0.0f;
+					for (uint32_t ch = 0; ch < lp.numChannels; ++ch)
+					{
+						const float v = outSrc[ch * L + c] * norm;
+						outSrc[ch * L + c] = v;
+						if (fz.tgtMix) fz.tgtMix[size_t(c) * fz.numSC + size_t(src) * fz.rendC + fz.rows[ch]] = v;   // k_update_targets' transpose
+					}
 				}
 			}
 			if (fz.tgtMix && valid)
 			{
-				if (fz.unpannedRows && gl < L)
-					for (uint32_t ch = 0; ch < fz.rendC; ++ch)
-						if ((fz.unpannedRows >> ch) & 1u) fz.tgtMix[size_t(gl) * fz.numSC + size_t(src) * fz.rendC + ch] = 0.0f;
+				if (fz.unpannedRows)
+				{
+					#pragma unroll
+					for (uint32_t k = 0; k < kColsPerLane; ++k)
+					{
+						const uint32_t c = gl + k * G;
+						if (c < L)
+							for (uint32_t ch = 0; ch < fz.rendC; ++ch)
+								if ((fz.unpannedRows >> ch) & 1u) fz.tgtMix[size_t(c) * fz.numSC + size_t(src) * fz.rendC + ch] = 0.0f;
+					}
+				}
 				// UpdateParameters (src/Auralization/DirectSound.cpp:231-239) for this source's channels: band gains, delay in samples
 				if (gl < 4)
 				{
@@ -371,12 +403,18 @@ namespace jplg
 		return cudaGetLastError();
 	}
 
-	static uint32_t MdapLanesPerSource(const PannerDev& p) { return (p.is3D && p.numChannels <= 16) ? 16u : 32u; }
+	// JPLG_MDAP_LANES=16 (experiment switch): the r01 mapping, 16 lanes per source for targets with <= 16 channels
+	static uint32_t MdapLanesPerSource(const PannerDev& p)
+	{
+		static const bool lanes16 = [] { const char* e = std::getenv("JPLG_MDAP_LANES"); return e && e[0] == '1' && e[1] == '6'; }();
+		return (p.is3D && p.numChannels <= 16) ? (lanes16 ? 16u : 8u) : 32u;
+	}
+	static uint32_t MdapGroupFloats(uint32_t G) { return G == 8 ? MdapShape<8>::kGroupFloats : G == 16 ? MdapShape<16>::kGroupFloats : MdapShape<32>::kGroupFloats; }
 
 	size_t MdapSmemBytes(const PannerDev& p, const MdapLayoutParams& lp)
 	{
 		const uint32_t groups = JPLG_MDAP_WARPS * 32 / MdapLanesPerSource(p);
-		if (p.is3D) return (2048 + 64) * 4 + size_t(groups) * (48 + kMdapRows * MdapLanesPerSource(p) + kMaxChannelsDev) * 4 + size_t(lp.numVS) * 4;
+		if (p.is3D) return (2048 + 64) * 4 + size_t(groups) * MdapGroupFloats(MdapLanesPerSource(p)) * 4 + size_t(lp.numVS) * 4;
 		return (2048 + JPLG_MDAP_WARPS * 32) * 4;
 	}
 
@@ -395,7 +433,7 @@ namespace jplg
 		if (grid > maxGrid) grid = maxGrid;
 		if (p.is3D)
 		{
-			auto kernel = groups == JPLG_MDAP_WARPS ? k_mdap_3d<32> : k_mdap_3d<16>;
+			auto kernel = groups == JPLG_MDAP_WARPS ? k_mdap_3d<32> : (groups == JPLG_MDAP_WARPS * 2 ? k_mdap_3d<16> : k_mdap_3d<8>);
 			cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
 			kernel<<<grid, JPLG_MDAP_WARPS * 32, smem, st>>>(p.lut3d, p.rsqTable, lp, params, n, p.numChannels, out, fz);
 		}
