@@ -77,14 +77,18 @@ namespace jplg
 	// batch (row = lane, column = speaker) and the column sums (row after row, column = lane) both spread over the banks (r01e: 1.5 conflicts per shared-memory
 	// instruction with the [32][16] matrix).
 	// Shared memory per group: ring sin/cos (2*24 floats) + gain matrix + mixBuffer.
-	template<int G> struct MdapShape { static constexpr uint32_t kRows = G == 8 ? 24u : 32u, kCols = G == 32 ? 32u : 16u, kStride = kCols + 1u, kGroupFloats = 48u + kRows * kStride + kMaxChannelsDev; };
-	template<int G>
+	// ROWS for G = 8 (same-box A/B, profiles/r02q_mdap_rows_ab.txt): 8-row batches need 22 KB of shared memory per CTA instead of 40 KB (9 instead of 5 resident
+	// CTAs per SM: the kernel waits on its LUT gathers, more warps hide them) and run a whole-machine launch 17 % faster (config 2: 91.4 -> 76.2 us); the fused
+	// update that runs BESIDE a render on the SMs it leaves free is 6 % slower that way (config 3 step 0.1275 -> 0.1344 ms), so it keeps 24-row batches.
+	template<int G, int ROWS8 = 24> struct MdapShape { static constexpr uint32_t kRows = G == 8 ? uint32_t(ROWS8) : 32u, kCols = G == 32 ? 32u : 16u, kStride = kCols + 1u, kGroupFloats = 48u + kRows * kStride + kMaxChannelsDev; };
+	template<int G, int ROWS8>
 	__global__ void __launch_bounds__(JPLG_MDAP_WARPS * 32)
 	k_mdap_3d(const uint4* __restrict__ lut, const uint32_t* __restrict__ rsqTable, MdapLayoutParams lp,
 			  const float* __restrict__ params, uint32_t n, uint32_t L, float* __restrict__ out, const MdapFuse fz)
 	{
-		constexpr uint32_t kRows = MdapShape<G>::kRows, kStride = MdapShape<G>::kStride, kGroupFloats = MdapShape<G>::kGroupFloats;
-		constexpr uint32_t kColsPerLane = MdapShape<G>::kCols / G;      // columns a lane sums: 2 for G = 8, else 1
+		using Shape = MdapShape<G, ROWS8>;
+		constexpr uint32_t kRows = Shape::kRows, kStride = Shape::kStride, kGroupFloats = Shape::kGroupFloats;
+		constexpr uint32_t kColsPerLane = Shape::kCols / G;      // columns a lane sums: 2 for G = 8, else 1
 		extern __shared__ __align__(16) unsigned char smemRaw[];
 		uint32_t* sRsq = reinterpret_cast<uint32_t*>(smemRaw);                       // 2048
 		float* sAzSin = reinterpret_cast<float*>(sRsq + 2048);                        // 32 (max 24 used: halfAndTail*4 <= 16)
@@ -409,12 +413,12 @@ namespace jplg
 		static const bool lanes16 = [] { const char* e = std::getenv("JPLG_MDAP_LANES"); return e && e[0] == '1' && e[1] == '6'; }();
 		return (p.is3D && p.numChannels <= 16) ? (lanes16 ? 16u : 8u) : 32u;
 	}
-	static uint32_t MdapGroupFloats(uint32_t G) { return G == 8 ? MdapShape<8>::kGroupFloats : G == 16 ? MdapShape<16>::kGroupFloats : MdapShape<32>::kGroupFloats; }
+	static uint32_t MdapGroupFloats(uint32_t G, bool rows8) { return G == 8 ? (rows8 ? MdapShape<8, 8>::kGroupFloats : MdapShape<8, 24>::kGroupFloats) : G == 16 ? MdapShape<16>::kGroupFloats : MdapShape<32>::kGroupFloats; }
 
-	size_t MdapSmemBytes(const PannerDev& p, const MdapLayoutParams& lp)
+	size_t MdapSmemBytes(const PannerDev& p, const MdapLayoutParams& lp, bool rows8)
 	{
 		const uint32_t groups = JPLG_MDAP_WARPS * 32 / MdapLanesPerSource(p);
-		if (p.is3D) return (2048 + 64) * 4 + size_t(groups) * MdapGroupFloats(MdapLanesPerSource(p)) * 4 + size_t(lp.numVS) * 4;
+		if (p.is3D) return (2048 + 64) * 4 + size_t(groups) * MdapGroupFloats(MdapLanesPerSource(p), rows8) * 4 + size_t(lp.numVS) * 4;
 		return (2048 + JPLG_MDAP_WARPS * 32) * 4;
 	}
 
@@ -426,14 +430,15 @@ namespace jplg
 		MdapLayoutParams lp = lpIn;
 		lp.paramStride = paramStride;
 		if (n == 0) return cudaSuccess;
-		const size_t smem = MdapSmemBytes(p, lp);
+		const bool rows8 = fz.tgtMix == nullptr;     // plain (foreground, whole machine) launches: 8-row batches; the fused background update: 24
+		const size_t smem = MdapSmemBytes(p, lp, rows8);
 		const uint32_t groups = JPLG_MDAP_WARPS * 32 / MdapLanesPerSource(p);
 		uint32_t grid = (n + groups - 1) / groups;
 		const uint32_t maxGrid = static_cast<uint32_t>(numSMs) * 8u; // persistent-ish: amortise the 8 KB rsqrt table load
 		if (grid > maxGrid) grid = maxGrid;
 		if (p.is3D)
 		{
-			auto kernel = groups == JPLG_MDAP_WARPS ? k_mdap_3d<32> : (groups == JPLG_MDAP_WARPS * 2 ? k_mdap_3d<16> : k_mdap_3d<8>);
+			auto kernel = groups == JPLG_MDAP_WARPS ? k_mdap_3d<32, 24> : (groups == JPLG_MDAP_WARPS * 2 ? k_mdap_3d<16, 24> : (rows8 ? k_mdap_3d<8, 8> : k_mdap_3d<8, 24>));
 			cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
 			kernel<<<grid, JPLG_MDAP_WARPS * 32, smem, st>>>(p.lut3d, p.rsqTable, lp, params, n, p.numChannels, out, fz);
 		}
