@@ -367,6 +367,7 @@ class Config3Pipeline:
         mix0 = self.pan.ProcessVBAPData(self.lay, h_params0).reshape(N, L_OUT)
         self.rend = J.DirectSoundBatch(self.ctx, FS, N, 1, L_OUT, band[0].cpu().numpy(), delay[0].cpu().numpy(), mix0, ring_size=ring,
                                        max_block_frames=FRAMES, mode=env.mode)
+        self.rend.SetMaxDelaySeconds(float(delay.max().item()))     # the delays live on the device from here on: jplg_renderer_push_ahead needs their bound
         with torch.cuda.stream(self.stream):
             self.d_mix = torch.empty((N, 1, L_OUT), dtype=torch.float32, device=dev)
             self.local_bus = torch.zeros((FRAMES, L_OUT), dtype=torch.float32, device=dev)

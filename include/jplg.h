@@ -256,13 +256,18 @@ JPLG_API jplg_status jplg_renderer_update_panned(jplg_renderer r, jplg_panner p,
 JPLG_API jplg_status jplg_renderer_process_block(jplg_renderer r, const float* in, float* bus, uint32_t frames, int32_t mem);
 /* Offline / throughput rendering: issues the ring pushes of the NEXT block (device pointer `in`, already resident) on a side stream, so that
  * they overlap the render of the block enqueued before this call: the copy is HBM-bound and runs on the SMs the render leaves free. The two
- * touch disjoint ring slots as long as the ring holds the longest delay in use plus four blocks, which the caller guarantees (true for the
- * reference ring size bit_ceil(2 fs) with delays up to 1.9 s). The next jplg_renderer_process_block must get the same `in` / `frames`
+ * touch disjoint ring slots as long as the ring holds the longest delay in use plus two blocks of pushes plus one chunk; the call checks that against
+ * the delay bound it knows (jplg_renderer_set_max_delay_seconds below) and fails otherwise (true for the reference ring size bit_ceil(2 fs) up to 1.7 s). The next jplg_renderer_process_block must get the same `in` / `frames`
  * (JPLG_MEM_DEVICE); it waits for these pushes instead of issuing its own (any other block simply overwrites them: the ring position only advances
  * in process_block). The side stream starts them once the render enqueued last is fully resident, and ranks above JPLG_CONTEXT_BACKGROUND
  * contexts, so they neither delay that render's placement nor trail behind background panning work. A real-time engine, whose next block does
  * not exist yet, does not need this call. */
 JPLG_API jplg_status jplg_renderer_push_ahead(jplg_renderer r, const float* in, uint32_t frames);
+/* Upper bound of the target delays (seconds) for renderers whose delays only exist on the device (jplg_renderer_update with JPLG_MEM_DEVICE,
+ * jplg_renderer_update_panned): host-side updates are tracked by the library itself. jplg_renderer_push_ahead refuses to run without a known bound, and
+ * when longest delay + two blocks of pushes + one 480-frame chunk does not fit the ring (the pushed-ahead block would overwrite samples the render of the
+ * current block still reads). Declaring a bound smaller than the delays actually in use is a caller error. */
+JPLG_API jplg_status jplg_renderer_set_max_delay_seconds(jplg_renderer r, float seconds);
 /* Makes `waiting`'s stream (a JPLG_CONTEXT_BACKGROUND context on the same device) wait until every CTA of the k_render launch enqueued last by
  * jplg_renderer_process_block is resident on the device. Work enqueued on `waiting` afterwards (the next block's jplg_panner_mdap, the scene
  * front-end) runs beside that render on the SMs it leaves free instead of occupying SMs its CTAs need. No-op before the first block. */
@@ -361,8 +366,9 @@ JPLG_API jplg_status jplg_reverb_bank_set_rt60(jplg_reverb_bank b, const float* 
 JPLG_API jplg_status jplg_reverb_bank_set_decay_slope(jplg_reverb_bank b, const float* slope_db_per_second, int32_t mem);
 /* AttenuationFilter::DecayGains of every FDN channel = dBToGain(slope * delaySeconds) (LateReverb.h:64-68): host out [n][16][4] */
 JPLG_API jplg_status jplg_reverb_bank_decay_gains(jplg_reverb_bank b, float* out);
-/* ProcessInterleaved(input, output, numFrames) for all n buses (:53-134). in [n][frames] (mono: in_channels must be 1);
- * out [n][frames][output_channels] interleaved, ACCUMULATED INTO like the reference's `output` span. */
+/* ProcessInterleaved(input, output, numFrames) for all n buses (:53-134). in [n][frames][in_channels] interleaved; multichannel input is down-mixed like
+ * the reference (DownmixToMono + ApplyGain(1 / in_channels), :80-92) for blocks of at most 480 frames — beyond one chunk the reference over-runs its scratch
+ * array (:83), so longer multichannel blocks are refused. out [n][frames][output_channels] interleaved, ACCUMULATED INTO like the reference's `output` span. */
 JPLG_API jplg_status jplg_reverb_bank_process(jplg_reverb_bank b, const float* in, uint32_t in_channels, float* out, uint32_t frames, int32_t mem);
 
 /* ---------------------------------------------------------------------------------------------- */

@@ -85,6 +85,7 @@ _sig("jplg_renderer_push_ahead", _i32, [_vp, _fp, _u32])
 _sig("jplg_renderer_wait_render_started", _i32, [_vp, _vp])
 _sig("jplg_renderer_device_bus", _vp, [_vp])
 _sig("jplg_renderer_set_time_parallel", _i32, [_vp, _i32])
+_sig("jplg_renderer_set_max_delay_seconds", _i32, [_vp, _f32])
 _sig("jplg_renderer_time_parallel_blocks", _u64, [_vp])
 _sig("jplg_renderer_ring_size", _u32, [_vp])
 _sig("jplg_renderer_state_export", _i32, [_vp, _fp, _fp, C.POINTER(_u64)])
@@ -515,6 +516,10 @@ class DirectSoundBatch:
 
     def device_bus_ptr(self):
         return lib.jplg_renderer_device_bus(self.h)
+
+    def SetMaxDelaySeconds(self, seconds):
+        """upper bound of device-resident target delays (jplg_renderer_set_max_delay_seconds): PushAhead needs it"""
+        self.ctx.check(lib.jplg_renderer_set_max_delay_seconds(self.h, float(seconds)))
 
     def SetTimeParallel(self, policy):
         """throughput mode's time-parallel path (jplg_renderer_set_time_parallel): -1 chosen by size, 0 never, 1 whenever a block qualifies"""

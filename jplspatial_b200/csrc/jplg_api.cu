@@ -584,6 +584,12 @@ struct jplg_renderer_t
 	int activeSet = 0;
 	bool pendingPanned = false, setFreeRecorded[2] = { false, false };
 	cudaEvent_t evUpdated = nullptr, evSetFree[2] = {};
+	// upper bound of the target delays in samples, as far as the HOST knows it: the maximum of host-side updates, or what the caller declared with
+	// jplg_renderer_set_max_delay_seconds for delays that only exist on the device (jplg_renderer_update(.., JPLG_MEM_DEVICE), update_panned).
+	// jplg_renderer_push_ahead needs it: the next block's pushes and the current render touch disjoint ring slots only while
+	// maxDelay + 2 * TotalPushes + 480 < ringSize.
+	float maxDelaySamples = 0.0f, declaredMaxDelaySamples = -1.0f;
+	bool delayBoundKnown = true;
 	// time-parallel throughput path (jplg_scan_kernels.cu): -1 = chosen by size, 0 = never, 1 = whenever the block qualifies
 	int32_t scanPolicy = -1;
 	float *scanM = nullptr, *scanScratch = nullptr;
@@ -655,6 +661,13 @@ static void FreeRenderer(jplg_renderer r)
 	if (r->evAhead) { if (r->ctx->auxReady) cudaStreamSynchronize(r->ctx->aux[1]); cudaEventDestroy(r->evAhead); r->evAhead = nullptr; }
 }
 
+// delays the host never sees (device-resident updates): known only through the caller's declared bound
+static void NoteDeviceDelays(jplg_renderer r)
+{
+	if (r->declaredMaxDelaySamples >= 0.0f) { r->maxDelaySamples = r->declaredMaxDelaySamples; r->delayBoundKnown = true; }
+	else r->delayBoundKnown = false;
+}
+
 static jplg_status RendererUpdateLocked(jplg_renderer r, const float* band, const float* delay, const float* mix, int32_t mem)
 {
 	jplg_context ctx = r->ctx;
@@ -668,6 +681,16 @@ static jplg_status RendererUpdateLocked(jplg_renderer r, const float* band, cons
 		if (band) { if (tryAlias && (al = MappedHostAlias(band))) dBand = al; else { JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(base, band, size_t(N) * 4 * 4, cudaMemcpyHostToDevice, ctx->stream)); dBand = base; } }
 		if (delay) { if (tryAlias && (al = MappedHostAlias(delay))) dDelay = al; else { JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(base + size_t(N) * 4, delay, size_t(N) * 4, cudaMemcpyHostToDevice, ctx->stream)); dDelay = base + size_t(N) * 4; } }
 		if (mix) { if (tryAlias && (al = MappedHostAlias(mix))) dMix = al; else { JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(base + size_t(N) * 5, mix, size_t(N) * C * L * 4, cudaMemcpyHostToDevice, ctx->stream)); dMix = base + size_t(N) * 5; } }
+	}
+	if (delay)
+	{
+		if (mem == JPLG_MEM_DEVICE) NoteDeviceDelays(r);
+		else
+		{
+			float mx = 0.0f;
+			for (uint32_t i = 0; i < N; ++i) mx = std::max(mx, delay[i] * r->cfg.sample_rate);
+			r->maxDelaySamples = mx; r->delayBoundKnown = true;      // a complete set of host-side delays replaces whatever was there
+		}
 	}
 	float *wBand = r->tgtBand, *wDelay = r->tgtDelay, *wMix = r->tgtMix;
 	if (r->pendingPanned)
@@ -813,6 +836,7 @@ jplg_status jplg_renderer_update_panned(jplg_renderer r, jplg_panner p, jplg_sou
 	JPLG_LAUNCH(ctx, JPLG_K_MDAP, LaunchMdap(p->dev, l->lp, pan_params, 5, N, static_cast<float*>(scratch), ctx->numSMs, ctx->stream, &fz));
 	JPLG_CUDA_TRY(ctx, cudaEventRecord(r->evUpdated, ctx->stream));
 	r->pendingPanned = true;
+	NoteDeviceDelays(r);
 	return JPLG_OK;
 }
 
@@ -1044,10 +1068,17 @@ jplg_status jplg_renderer_push_ahead(jplg_renderer r, const float* in, uint32_t 
 	jplg_context ctx = r->ctx;
 	JPLG_NEED_DEVICE(ctx);
 	if (frames > r->maxFrames) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "push_ahead: frames exceeds max_block_frames");
-	if (r->aheadIn) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "push_ahead: a block is already pushed ahead");
-	if (r->ringSize < 4u * TotalPushes(frames)) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "push_ahead: ring too small to hold a block ahead");
 	std::lock_guard<std::mutex> lk(ctx->mtx);
 	cudaSetDevice(ctx->device);
+	if (r->aheadIn) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "push_ahead: a block is already pushed ahead");
+	if (r->ringSize < 4u * TotalPushes(frames)) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "push_ahead: ring too small to hold a block ahead");
+	// the render of the current block reads samples up to (longest delay + this block's pushes + one chunk) old; the pushes issued here land
+	// TotalPushes further on: both fit the ring without meeting only below this bound
+	if (!r->delayBoundKnown)
+		return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "push_ahead: the target delays were set on the device (jplg_renderer_update with JPLG_MEM_DEVICE / jplg_renderer_update_panned); "
+			"declare their upper bound with jplg_renderer_set_max_delay_seconds first");
+	if (static_cast<double>(r->maxDelaySamples) + 2.0 * TotalPushes(frames) + kChunkFrames >= static_cast<double>(r->ringSize))
+		return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "push_ahead: longest delay + two blocks of pushes + one chunk does not fit the ring: the pushed-ahead block would overwrite samples the current render reads");
 	jplg_status ast = EnsureAux(ctx); if (ast != JPLG_OK) return ast;
 	if (!r->evAhead) JPLG_CUDA_TRY(ctx, cudaEventCreateWithFlags(&r->evAhead, cudaEventDisableTiming));
 	RenderParams rp{};
@@ -1080,10 +1111,18 @@ jplg_status jplg_renderer_wait_block(jplg_renderer r)
 	if (!r) return JPLG_ERR_INVALID_ARGUMENT;
 	jplg_context ctx = r->ctx;
 	JPLG_NEED_DEVICE(ctx);
-	if (r->asyncWaited >= r->asyncSubmitted) return JPLG_OK;   // nothing in flight
+	cudaEvent_t ev;
+	{
+		std::lock_guard<std::mutex> lk(ctx->mtx);
+		if (r->asyncWaited >= r->asyncSubmitted) return JPLG_OK;   // nothing in flight
+		ev = r->evDoneA[r->asyncWaited & 1];
+	}
 	cudaSetDevice(ctx->device);
-	JPLG_CUDA_TRY(ctx, cudaEventSynchronize(r->evDoneA[r->asyncWaited & 1]));
-	r->asyncWaited++;
+	JPLG_CUDA_TRY(ctx, cudaEventSynchronize(ev));      // not under the lock: another thread may enqueue the next block meanwhile
+	{
+		std::lock_guard<std::mutex> lk(ctx->mtx);
+		r->asyncWaited++;
+	}
 	return JPLG_OK;
 }
 
@@ -1095,6 +1134,14 @@ jplg_status jplg_renderer_process_block_debug(jplg_renderer r, const float* in, 
 {
 	if (!per_source) return JPLG_ERR_INVALID_ARGUMENT;
 	return ProcessBlock(r, in, bus, per_source, frames, mem);
+}
+jplg_status jplg_renderer_set_max_delay_seconds(jplg_renderer r, float seconds)
+{
+	if (!r || !(seconds >= 0.0f)) return JPLG_ERR_INVALID_ARGUMENT;
+	std::lock_guard<std::mutex> lk(r->ctx->mtx);
+	r->declaredMaxDelaySamples = seconds * r->cfg.sample_rate;
+	if (!r->delayBoundKnown || r->declaredMaxDelaySamples > r->maxDelaySamples) { r->maxDelaySamples = std::max(r->maxDelaySamples, r->declaredMaxDelaySamples); r->delayBoundKnown = true; }
+	return JPLG_OK;
 }
 jplg_status jplg_renderer_set_time_parallel(jplg_renderer r, int32_t policy)
 {
@@ -1588,8 +1635,12 @@ jplg_status jplg_reverb_bank_process(jplg_reverb_bank b, const float* in, uint32
 	jplg_context ctx = b->ctx;
 	JPLG_NEED_DEVICE(ctx);
 	if (frames == 0) return JPLG_OK;
-	if (in_channels != 1) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "jplg_reverb_bank_process: only mono input is supported (the reference's multichannel down-mix "
-		"path over-runs its 480-frame scratch array for blocks longer than one chunk, LateReverb.cpp:86)");
+	if (in_channels == 0) return JPLG_ERR_INVALID_ARGUMENT;
+	// Multichannel input: DownmixToMono + ApplyGain(1 / numIn) like the reference (LateReverb.cpp:80-92), for blocks of at most one 480-frame chunk. From
+	// its second chunk on the reference assigns `framesProcessed` (not `framesToProcess`) elements to a 480-element scratch array (:83) and over-runs
+	// it: there is no defined behaviour to match for longer multichannel blocks, so those are refused.
+	if (in_channels != 1 && frames > kChunkFrames) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "jplg_reverb_bank_process: multichannel input is supported for blocks of at most "
+		"480 frames (beyond that the reference's down-mix over-runs its scratch array, LateReverb.cpp:83)");
 	if (frames > b->maxFrames) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "jplg_reverb_bank_process: frames exceeds max_block_frames");
 	std::lock_guard<std::mutex> lk(ctx->mtx);
 	cudaSetDevice(ctx->device);
@@ -1597,9 +1648,23 @@ jplg_status jplg_reverb_bank_process(jplg_reverb_bank b, const float* in, uint32
 	const float* dIn = in; float* dOut = out;
 	if (mem == JPLG_MEM_HOST)
 	{
-		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(b->stageIn, in, nIn * 4, cudaMemcpyHostToDevice, ctx->stream));
+		if (in_channels == 1) { JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(b->stageIn, in, nIn * 4, cudaMemcpyHostToDevice, ctx->stream)); dIn = b->stageIn; }
+		else
+		{
+			void* raw = nullptr;
+			jplg_status sst = Scratch(ctx, 0, nIn * in_channels * 4, &raw); if (sst) return sst;
+			JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(raw, in, nIn * in_channels * 4, cudaMemcpyHostToDevice, ctx->stream));
+			dIn = static_cast<const float*>(raw);
+		}
 		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(b->stageOut, out, nOut * 4, cudaMemcpyHostToDevice, ctx->stream));
-		dIn = b->stageIn; dOut = b->stageOut;
+		dOut = b->stageOut;
+	}
+	if (in_channels != 1)
+	{
+		void* mono = nullptr;
+		jplg_status sst = Scratch(ctx, 1, nIn * 4, &mono); if (sst) return sst;
+		JPLG_LAUNCH(ctx, JPLG_K_OTHER, LaunchReverbDownmix(dIn, b->n, frames, in_channels, static_cast<float*>(mono), ctx->stream));
+		dIn = static_cast<const float*>(mono);
 	}
 	jplg_status st = ReverbRefreshDecay(b); if (st) return st;
 	FdnParams fp{}; fp.n = b->n; fp.L = b->L; fp.frames = frames; fp.pos = b->pos; std::memcpy(fp.coef, b->coef, sizeof(fp.coef));

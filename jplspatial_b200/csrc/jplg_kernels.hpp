@@ -159,6 +159,7 @@ namespace jplg
 	float FdnHadamardScale();
 	cudaError_t LaunchFdnDecay(const float* slope, uint32_t n, float invSampleRate, float* decay, int mode, cudaStream_t st);
 	cudaError_t LaunchFdn(const FdnParams& fp, int mode, cudaStream_t st);
+	cudaError_t LaunchReverbDownmix(const float* in, uint32_t n, uint32_t frames, uint32_t numIn, float* mono, cudaStream_t st);   // [n][frames][numIn] -> [n][frames]
 	//======================================================================
 	// Scene front-end (jplg_frontend_kernels.cu): the per-source body of SpatialManager::AdvanceSimulation
 	// (inc/SpatialManager.h:374-420) plus the parameter producers that sit between it and stages 1-3.

@@ -247,6 +247,25 @@ namespace jplg
 		return static_cast<float>(x * y);                  // SqrtConstevalFallback (:255), narrowed by `constexpr Sample`
 	}
 
+	// ReverbBus::ProcessInterleaved's multichannel input stage (src/Auralization/LateReverb.cpp:80-92): scratch = 0, DownmixToMono adds the channels in
+	// order (inc/Auralization/ChannelMixing.h:129-136), ApplyGain scales by 1 / numInChannels (:50-63). One thread per frame of one instance.
+	__global__ void k_reverb_downmix(const float* __restrict__ in, uint64_t total, uint32_t numIn, float norm, float* __restrict__ mono)
+	{
+		const uint64_t idx = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+		if (idx >= total) return;
+		const float* s = in + idx * numIn;
+		float d = 0.0f;
+		for (uint32_t ch = 0; ch < numIn; ++ch) d += s[ch];
+		mono[idx] = d * norm;
+	}
+	cudaError_t LaunchReverbDownmix(const float* in, uint32_t n, uint32_t frames, uint32_t numIn, float* mono, cudaStream_t st)
+	{
+		const uint64_t total = uint64_t(n) * frames;
+		if (total == 0) return cudaSuccess;
+		k_reverb_downmix<<<static_cast<uint32_t>((total + 255) / 256), 256, 0, st>>>(in, total, numIn, 1.0f / static_cast<float>(numIn), mono);
+		return cudaGetLastError();
+	}
+
 	cudaError_t LaunchFdnDecay(const float* slope, uint32_t n, float invSampleRate, float* decay, int mode, cudaStream_t st)
 	{
 		if (n == 0) return cudaSuccess;

@@ -383,6 +383,20 @@ def test_push_ahead_equals_plain_path():
     for b in range(blocks):
         assert np.abs(bus_a[b].cpu().numpy()).max() > 0
         assert util.bits_equal(bus_b[b].cpu().numpy(), bus_a[b].cpu().numpy()), f"block {b}: push-ahead path differs"
+    # the guard: delays that only exist on the device need a declared bound; a ring that cannot hold delay + two blocks of pushes + a chunk is refused
+    rc = make()
+    with torch.cuda.stream(stream):
+        d_delay = torch.from_numpy(sc["delay"][1]).to(dev)
+    rc.UpdateParameters(None, d_delay, None)
+    with pytest.raises(J.JplgError):
+        rc.PushAhead(d_audio[0], frames)
+    rc.SetMaxDelaySeconds(float(sc["delay"].max()))
+    rc.PushAhead(d_audio[0], frames)
+    rc.close()
+    rs = J.DirectSoundBatch(ctx, FS, N, C, L, sc["band"][0], sc["delay"][0], sc["mix"][0], ring_size=32768, max_block_frames=512)   # 0.87 s of delay = 42 k samples > the ring
+    with pytest.raises(J.JplgError):
+        rs.PushAhead(d_audio[0], frames)
+    rs.close()
     # a different block than the one pushed ahead: same result as without the stale pushes
     with torch.cuda.stream(stream):
         xa = torch.zeros((frames, L), dtype=torch.float32, device=dev); xb = torch.zeros((frames, L), dtype=torch.float32, device=dev)
@@ -447,6 +461,7 @@ def test_background_context_panning_one_block_ahead_equals_serial():
             pans[1][0].ProcessVBAPData(pans[1][1], d_params[b], out=d_mix2[b & 1])
             ev_mdap[b & 1].record(stream_bg)
 
+    rb.SetMaxDelaySeconds(float(sc["delay"].max()))      # device-side updates below: push_ahead needs the bound declared
     issue(0, False)
     for b in range(blocks):
         with torch.cuda.stream(stream):

@@ -108,6 +108,25 @@ def test_reverb_throughput_mode_tolerance(gpu_ctx, ref):
     assert np.all(np.abs(got.astype(np.float64) - want) <= tol), f"max excess {(np.abs(got - want) / tol).max()}"
 
 
+@pytest.mark.parametrize("n_in,frames", [(2, 480), (6, 256), (4, 100)])
+def test_reverb_multichannel_input_downmix_bit_exact(gpu_ctx, ref, n_in, frames):
+    """stereo / quad / 5.1 reverb sends at <= 480 frames: DownmixToMono + ApplyGain(1 / numIn) in front of the FDN (LateReverb.cpp:80-92), device and host buffers"""
+    n, L, blocks = 6, 12, (14 if frames >= 256 else 48)     # long enough for every feedback delay (1,609 .. 4,259 samples) to come round
+    x = (util.white_noise((blocks, n, frames, n_in), 777 + n_in) * np.float32(0.5)).astype(np.float32)
+    x[blocks // 2:, n // 2:] = 0.0
+    buses = [ref.reverb(FS) for _ in range(n)]
+    want = np.zeros((blocks, n, frames, L), np.float32)
+    for b in range(blocks):
+        for i in range(n):
+            buses[i].process(x[b, i], want[b, i], frames, n_in=n_in)
+    bank = J.ReverbBusBatch(gpu_ctx, n, FS, L)
+    got = np.zeros_like(want)
+    for b in range(blocks):
+        bank.ProcessInterleaved(x[b], got[b], frames, in_channels=n_in)
+    assert util.count_bit_mismatch(got, want) == 0, f"max abs {np.abs(got - want).max()}"
+    assert np.abs(want[-1]).max() > 1e-4
+
+
 def test_reverb_argument_errors(gpu_ctx):
     with pytest.raises(J.JplgError):
         J.ReverbBusBatch(gpu_ctx, 4, FS, 17)            # more outputs than FDN channels (asserted by the reference)
@@ -115,7 +134,7 @@ def test_reverb_argument_errors(gpu_ctx):
         J.ReverbBusBatch(gpu_ctx, 4, FS, 12, max_block_frames=2048)
     bank = J.ReverbBusBatch(gpu_ctx, 2, FS, 12)
     out = np.zeros((2, 512, 12), np.float32)
-    with pytest.raises(J.JplgError):
+    with pytest.raises(J.JplgError):     # multichannel input beyond one 480-frame chunk: the reference over-runs its scratch array (LateReverb.cpp:83)
         bank.ProcessInterleaved(np.zeros((2, 512, 2), np.float32), out, 512, in_channels=2)
     with pytest.raises(J.JplgError):
         bank.ProcessInterleaved(np.zeros((2, 600), np.float32), np.zeros((2, 600, 12), np.float32), 600)
