@@ -19,8 +19,8 @@ for k in range(4):
     rend.ProcessInterleaved(audio[k % 2], bus, F)
 ctx.synchronize()
 lib = ctypes.CDLL(J.lib_path)
-out = (ctypes.c_ulonglong * 10)()
+out = (ctypes.c_ulonglong * 15)()
 lib.jplg_debug_render_prof(out)
 for slot, name in enumerate(["D delay", "A front", "M mix", "Ba back lanes 0,1", "Bb back lanes 2,3"]):
-    tot, wait = out[2 * slot], out[2 * slot + 1]
-    print(f"{name}: lifetime {tot} cycles, in bar.sync {wait} ({100.0 * wait / max(tot, 1):.1f} %), busy {tot - wait}")
+    tot, wait, spin = out[3 * slot], out[3 * slot + 1], out[3 * slot + 2]
+    print(f"{name}: lifetime {tot} cycles, in bar.sync {wait} ({100.0 * wait / max(tot, 1):.1f} %), in mbarrier / counter spin waits {spin} ({100.0 * spin / max(tot, 1):.1f} %), busy {tot - wait - spin}")
