@@ -32,6 +32,7 @@
 // caller (jplg_api.cu) selects it by size. Bar: 1e-5 * max(|ref|, rms, 1e-3) per sample against oracle/_ref, tests/test_gpu_scan.py.
 #include "jplg_kernels.hpp"
 #include "jplg_render_common.cuh"
+#include <cstdlib>
 
 namespace jplg
 {
@@ -293,6 +294,320 @@ namespace jplg
 		}
 	}
 
+	//======================================================================
+	// k_scan_front_pipe: the same six phases as k_scan_front, but as STAGES of a pipeline over the tiles instead of barrier-separated phases. The
+	// two sequential recurrences (3 of the 32 us of k_scan_front each leave 124 of its 128 threads idle) get a warp of their own and trail each other by a
+	// quarter of the block; the parallel stages run behind them quarter by quarter:
+	//   warps 0-3  "tile" warps: thread = (tile slot, source-channel): P0 push, then for its tile P2 taps -> P4 zero-state pass -> P6 final pass
+	//   warp 4     P1 delay smoother, lanes 0-3 = the CTA's four source-channels in lock step
+	//   warp 5     P3 Thiran recurrence, lanes 0-3
+	//   warps 6-9  P5 state scan + gain ramps, one warp per source-channel
+	// Hand-offs are progress counters in shared memory (st.release / ld.acquire at CTA scope): tiles done by P1, P3, P5 (per source-channel), quarters
+	// (8 tiles) done by P2 and P4 per tile warp.
+	namespace
+	{
+		constexpr uint32_t kPipeThreads = 320;
+#ifdef JPLG_PROF
+		__device__ unsigned long long g_scanProf[16];
+		__device__ unsigned long long g_scanCta[3 * 1024];      // per CTA: globaltimer at start / end, SM id
+		__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+		__device__ __forceinline__ uint32_t smid() { uint32_t v; asm volatile("mov.u32 %0, %%smid;" : "=r"(v)); return v; }
+		#define SCAN_STAMP(i) do { if (blockIdx.x == 0 && lane == 0) g_scanProf[i] = clock64(); } while (0)
+#else
+		#define SCAN_STAMP(i)
+#endif
+		__device__ __forceinline__ uint32_t ld_acq(const uint32_t* p)
+		{
+			uint32_t v; asm volatile("ld.acquire.cta.shared::cta.u32 %0, [%1];" : "=r"(v) : "r"(static_cast<uint32_t>(__cvta_generic_to_shared(p))) : "memory"); return v;
+		}
+		__device__ __forceinline__ void st_rel(uint32_t* p, uint32_t v)
+		{
+			asm volatile("st.release.cta.shared::cta.u32 [%0], %1;" :: "r"(static_cast<uint32_t>(__cvta_generic_to_shared(p))), "r"(v) : "memory");
+		}
+		__device__ __forceinline__ void wait_ge(const uint32_t* p, uint32_t want) { while (ld_acq(p) < want) __nanosleep(100); }   // backing off: spinning tile warps otherwise take issue slots from the two recurrence warps they wait for
+	}
+
+	// dynamic shared memory: as k_scan_front, + flags: dlyDone, thDone, scanDone[4], tapDone[16], zsrDone[16] (uint32)
+	__global__ void __launch_bounds__(kPipeThreads)
+	k_scan_front_pipe(const ScanParams sp)
+	{
+		extern __shared__ __align__(16) float sF[];
+		const RenderParams& rp = sp.rp;
+		const uint32_t tid = threadIdx.x, warp = tid >> 5, lane = tid & 31u;
+		const uint32_t F = rp.frames, nT = sp.nTiles, C = rp.srcChannels, L = rp.L, nG = L + 4;
+		const size_t nSC = rp.numSC;
+		const uint32_t scBase = blockIdx.x * kFrontSC;
+		const uint32_t rowS = nT * (kT + 1) + 8u, arrS = kFrontSC * rowS;
+		float* sDly = sF;
+		float* sA = sDly + arrS;
+		float* sX = sA + arrS;
+		float* sX1 = sX + arrS;
+		float* sE = sX1 + arrS;
+		uint32_t* sFlag = reinterpret_cast<uint32_t*>(sE + kFrontSC * nT * 25 + 32);
+		uint32_t* dlyDone = sFlag;          // tiles whose smoothed delays are in sDly
+		uint32_t* thDone = sFlag + 1;       // tiles whose delayed samples are in sA
+		uint32_t* scanDone = sFlag + 2;     // [4] per source-channel: tiles whose start state (and gain ramps) are published
+		uint32_t* tapDone = sFlag + 8;      // [16] per (round, tile warp): the quarter's taps are in sA / sX / sX1
+		uint32_t* zsrDone = sFlag + 24;     // [16] per (round, tile warp): the quarter's zero-state end states are in sE
+#ifdef JPLG_PROF
+		if (tid == 0 && blockIdx.x < 1024) { g_scanCta[3 * blockIdx.x] = gtime(); g_scanCta[3 * blockIdx.x + 2] = smid(); if (blockIdx.x == 0) g_scanProf[12] = clock64(); }
+#endif
+		if (tid < 40) sFlag[tid] = 0u;
+		__syncthreads();
+		if (warp == 0) SCAN_STAMP(0);
+		const uint32_t pos32 = static_cast<uint32_t>(rp.pos);
+		const uint32_t rounds = (nT + kFrontSlots - 1) / kFrontSlots;
+
+		if (warp < 4)
+		{
+			//============================================================== tile warps
+			if (sp.push)
+			{
+				const uint32_t numChunks = (F + kChunkFrames - 1) / kChunkFrames;
+				for (uint32_t f0 = 0; f0 < F; f0 += 4 * kScanThreads)
+				{
+					float v[kFrontSC][4];
+					#pragma unroll
+					for (uint32_t qq = 0; qq < kFrontSC; ++qq)
+					{
+						const uint32_t s0 = min(scBase + qq, rp.numSC - 1u), src = s0 / C, ch = s0 - src * C;
+						const float* in = rp.in + size_t(src) * F * C + ch;
+						#pragma unroll
+						for (uint32_t j = 0; j < 4; ++j) { const uint32_t f = f0 + tid + kScanThreads * j; v[qq][j] = f < F ? __ldcs(in + size_t(f) * C) : 0.0f; }
+					}
+					#pragma unroll
+					for (uint32_t qq = 0; qq < kFrontSC; ++qq)
+					{
+						if (scBase + qq >= rp.numSC) break;
+						float* ring = rp.rings + size_t(scBase + qq) * rp.ringSize;
+						#pragma unroll
+						for (uint32_t j = 0; j < 4; ++j)
+						{
+							const uint32_t f = f0 + tid + kScanThreads * j;
+							if (f >= F) continue;
+							for (uint32_t k = 0; k < numChunks && k * kChunkFrames <= f; ++k)
+								ring[(pos32 + PushesThroughChunk(F, k) + (f - k * kChunkFrames)) & rp.ringMask] = v[qq][j];
+						}
+					}
+				}
+				__threadfence_block();
+				asm volatile("bar.sync 1, 128;" ::: "memory");      // the four tile warps: every push of the CTA's rings is visible before any tap reads them
+			}
+			if (warp == 0) SCAN_STAMP(1);
+			const uint32_t q = tid & (kFrontSC - 1u), slot = tid / kFrontSC, sc = scBase + q;
+			const bool scValid = sc < rp.numSC;
+			const float* ring = rp.rings + size_t(scValid ? sc : 0) * rp.ringSize;
+			float tgB[4] = { 0, 0, 0, 0 }, curB[4] = { 0, 0, 0, 0 };
+			if (scValid)
+			{
+				#pragma unroll
+				for (int b = 0; b < 4; ++b) { tgB[b] = rp.tgtBand[b * nSC + sc]; curB[b] = rp.state[(ST_BAND + b) * nSC + sc]; }
+			}
+			for (uint32_t r = 0; r < rounds; ++r)
+			{
+				const uint32_t t = slot + r * kFrontSlots;
+				const bool has = t < nT && scValid;
+				const uint32_t tLast = min(8u * warp + 7u + r * kFrontSlots, nT - 1u);      // the last tile of this warp's quarter
+				const ScanTile ti = scan_tile(min(t, nT - 1u), F);
+				// ---- P2: taps of the tile
+				wait_ge(dlyDone, tLast + 1u);
+				if (has)
+				{
+					const uint32_t pe = pos32 + PushesThroughChunk(F, ti.chunkStart / kChunkFrames + 1);
+					// (loops of this kernel are unrolled by 4, not 16: every tile thread runs its code once per tile, so fully unrolled bodies made the
+					// kernel wait on instruction fetch — 15 k cycles between CTA entry and the first barrier, `no_instruction` the top stall of P4 / P6)
+					#pragma unroll 4
+					for (uint32_t i = 0; i < kT; ++i)
+					{
+						const float d = static_cast<float>(ti.chunkLen - (ti.t0 + i)) + sDly[q * rowS + t * (kT + 1) + i];
+						const uint32_t D = static_cast<uint32_t>(d);
+						const float fr = d - static_cast<float>(static_cast<int32_t>(D));
+						const uint32_t rd = pe - 1u - D;
+						const uint32_t o = q * rowS + t * (kT + 1) + i;
+						sA[o] = thiran_coef(fr);
+						sX[o] = ring[rd & rp.ringMask];
+						sX1[o] = ring[(rd - 1u) & rp.ringMask];
+					}
+				}
+				__syncwarp();
+				if (lane == 0) st_rel(tapDone + 4 * r + warp, 1u);
+				if (warp == 0) SCAN_STAMP(2); if (warp == 3) SCAN_STAMP(3);
+				// ---- P4: zero-state pass of the tile
+				wait_ge(thDone, tLast + 1u);
+				if (has)
+				{
+					float st[24];
+					#pragma unroll
+					for (int k = 0; k < 24; ++k) st[k] = 0.0f;
+					const float* xi = sA + q * rowS + t * (kT + 1);
+					#pragma unroll 4
+					for (uint32_t i = 0; i < kT; ++i) { float bands[4]; xover_sample<1>(rp.coef, st, xi[i], bands); }
+					float* e = sE + (q * nT + t) * 25 + 8 * q;
+					#pragma unroll
+					for (int k = 0; k < 24; ++k) e[k] = st[k];
+				}
+				__syncwarp();
+				if (lane == 0) st_rel(zsrDone + 4 * r + warp, 1u);
+				if (warp == 0) SCAN_STAMP(4); if (warp == 3) SCAN_STAMP(5);
+				// ---- P6: final pass of the tile from its true start state
+				wait_ge(scanDone + q, min(t, nT - 1u) + 1u);
+				if (has)
+				{
+					const bool ramping = ti.chunkStart == 0;
+					const float chunkF = static_cast<float>(ti.chunkLen);
+					float st[24], band[4], inc[4];
+					const float* e = sE + (q * nT + t) * 25 + 8 * q;
+					#pragma unroll
+					for (int k = 0; k < 24; ++k) st[k] = e[k];
+					const float* gt = sp.tileGain + (size_t(t) * nSC + sc) * nG;
+					#pragma unroll
+					for (int b = 0; b < 4; ++b)
+					{
+						const float b0 = ramping ? curB[b] : tgB[b];
+						inc[b] = (tgB[b] - b0) / chunkF;
+						band[b] = ramping ? gt[L + b] : tgB[b];
+					}
+					const float* xi = sA + q * rowS + t * (kT + 1);
+					float* yo = sp.xth + size_t(ti.n0) * nSC + sc;
+					#pragma unroll 4
+					for (uint32_t i = 0; i < kT; ++i)
+					{
+						float b[4];
+						xover_sample<1>(rp.coef, st, xi[i], b);
+						yo[size_t(i) * nSC] = (b[0] * band[0] + b[1] * band[2]) + (b[2] * band[1] + b[3] * band[3]);
+						#pragma unroll
+						for (int k = 0; k < 4; ++k) band[k] += inc[k];
+					}
+				}
+			}
+		}
+		else if (warp == 4)
+		{
+			//============================================================== P1: delay smoother
+			const uint32_t q = lane, sc = scBase + q;
+			const bool on = q < kFrontSC && sc < rp.numSC;
+			float cur = on ? rp.state[ST_DELAY * nSC + sc] : 0.0f;
+			const float tgt = on ? rp.tgtDelay[sc] : 0.0f, alpha = rp.alpha;
+			float* o = sDly + min(q, kFrontSC - 1u) * rowS;
+			for (uint32_t t = 0; t < nT; ++t)
+			{
+				if (on)
+				{
+					#pragma unroll
+					for (uint32_t i = 0; i < kT; ++i)
+					{
+						cur = alpha * (tgt - cur) + cur;
+						o[t * (kT + 1) + i] = cur;
+					}
+				}
+				__syncwarp();
+				if (lane == 0) st_rel(dlyDone, t + 1u);
+			}
+			if (on) rp.state[ST_DELAY * nSC + sc] = cur;
+			SCAN_STAMP(6);
+		}
+		else if (warp == 5)
+		{
+			//============================================================== P3: Thiran recurrence
+			const uint32_t q = lane, sc = scBase + q;
+			const bool on = q < kFrontSC && sc < rp.numSC;
+			float y1 = on ? rp.state[ST_THIRAN_Y1 * nSC + sc] : 0.0f;
+			const uint32_t qq = min(q, kFrontSC - 1u);
+			float* a = sA + qq * rowS; const float* x = sX + qq * rowS; const float* x1 = sX1 + qq * rowS;
+			for (uint32_t t = 0; t < nT; ++t)
+			{
+				if ((t & 7u) == 0) wait_ge(tapDone + 4 * (t / kFrontSlots) + ((t % kFrontSlots) >> 3), 1u);
+				if (on)
+				{
+					const uint32_t n0 = t * (kT + 1);
+					float va[kT], vx[kT], v1[kT];
+					#pragma unroll
+					for (uint32_t i = 0; i < kT; ++i) { va[i] = a[n0 + i]; vx[i] = x[n0 + i]; v1[i] = x1[n0 + i]; }
+					#pragma unroll
+					for (uint32_t i = 0; i < kT; ++i)
+					{
+						y1 = va[i] * (vx[i] - y1) + v1[i];
+						a[n0 + i] = y1;
+					}
+				}
+				__syncwarp();
+				if (lane == 0) st_rel(thDone, t + 1u);
+			}
+			if (on) rp.state[ST_THIRAN_Y1 * nSC + sc] = y1;
+			SCAN_STAMP(7);
+		}
+		else
+		{
+			//============================================================== P5: state scan + gain ramps, warp per source-channel
+			const uint32_t w = warp - 6u, s5 = scBase + w;
+			if (s5 < rp.numSC)
+			{
+				const uint32_t r = min(lane, 23u);
+				float m[24];
+				#pragma unroll
+				for (int k = 0; k < 24; ++k) m[k] = sp.M[r * 24 + k];
+				float s = rp.state[(ST_FILTER + r) * nSC + s5];
+				const uint32_t chunk0 = min(F, kChunkFrames);
+				float g[2], dg[2];
+				#pragma unroll
+				for (uint32_t h = 0; h < 2; ++h)
+				{
+					const uint32_t j = lane + 32u * h;
+					float cur = 0.0f, tg = 0.0f;
+					if (j < L) { cur = rp.curMix[j * nSC + s5]; tg = rp.tgtMix[j * nSC + s5]; }
+					else if (j < nG) { cur = rp.state[(ST_BAND + j - L) * nSC + s5]; tg = rp.tgtBand[(j - L) * nSC + s5]; }
+					g[h] = cur; dg[h] = (tg - cur) / static_cast<float>(chunk0);
+				}
+				float* e = sE + w * nT * 25 + 8 * w + r;
+				for (uint32_t t = 0; t < nT; ++t)
+				{
+					if ((t & 7u) == 0) wait_ge(zsrDone + 4 * (t / kFrontSlots) + ((t % kFrontSlots) >> 3), 1u);
+					const float et = e[t * 25];
+					if (lane < 24) e[t * 25] = s;
+					if (t * kT < chunk0)
+					{
+						float* gt = sp.tileGain + (size_t(t) * nSC + s5) * nG;
+						if (lane < nG) gt[lane] = g[0];
+						if (lane + 32u < nG) gt[lane + 32u] = g[1];
+						#pragma unroll
+						for (uint32_t i = 0; i < kT; ++i) { g[0] += dg[0]; g[1] += dg[1]; }
+					}
+					__threadfence_block();
+					__syncwarp();
+					if (lane == 0) st_rel(scanDone + w, t + 1u);      // tile t's start state and ramp values are published
+					float a0 = et, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
+					#pragma unroll
+					for (int k = 0; k < 24; k += 4)
+					{
+						a0 = __fmaf_rn(m[k], __shfl_sync(0xffffffffu, s, k), a0);
+						a1 = __fmaf_rn(m[k + 1], __shfl_sync(0xffffffffu, s, k + 1), a1);
+						a2 = __fmaf_rn(m[k + 2], __shfl_sync(0xffffffffu, s, k + 2), a2);
+						a3 = __fmaf_rn(m[k + 3], __shfl_sync(0xffffffffu, s, k + 3), a3);
+					}
+					s = (a0 + a1) + (a2 + a3);
+				}
+				if (lane < 24) rp.state[(ST_FILTER + lane) * nSC + s5] = s;
+				if (w == 0) SCAN_STAMP(8);
+			}
+			else if (lane == 0) st_rel(scanDone + w, nT);     // no source-channel here: nobody must wait for it
+		}
+		if (warp == 0) SCAN_STAMP(9); if (warp == 3) SCAN_STAMP(10);
+		__syncthreads();       // every tile has read the block-start band gains
+		if (warp == 0) SCAN_STAMP(11);
+#ifdef JPLG_PROF
+		if (tid == 0 && blockIdx.x < 1024) { g_scanCta[3 * blockIdx.x + 1] = gtime(); if (blockIdx.x == 0) g_scanProf[13] = clock64(); }
+#endif
+		if (tid < kFrontSC && scBase + tid < rp.numSC)
+		{
+			#pragma unroll
+			for (int b = 0; b < 4; ++b) rp.state[(ST_BAND + b) * nSC + scBase + tid] = rp.tgtBand[b * nSC + scBase + tid];
+		}
+	}
+#ifdef JPLG_PROF
+	extern "C" __attribute__((visibility("default"))) void jplg_debug_scan_prof(unsigned long long* out) { cudaMemcpyFromSymbol(out, g_scanProf, sizeof(g_scanProf)); }
+	extern "C" __attribute__((visibility("default"))) void jplg_debug_scan_cta(unsigned long long* out) { cudaMemcpyFromSymbol(out, g_scanCta, sizeof(g_scanCta)); }
+#endif
+
 	__device__ __forceinline__ void cp_async4(float* dstShared, const float* src)
 	{
 		asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(static_cast<uint32_t>(__cvta_generic_to_shared(dstShared))), "l"(src) : "memory");
@@ -462,11 +777,17 @@ namespace jplg
 		if (!attr)
 		{
 			cudaFuncSetAttribute(k_scan_front, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+			cudaFuncSetAttribute(k_scan_front_pipe, cudaFuncAttributeMaxDynamicSharedMemorySize, 201 * 1024);
 			cudaFuncSetAttribute(k_scan_mix<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
 			cudaFuncSetAttribute(k_scan_mix<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
 			attr = true;
 		}
-		k_scan_front<<<(rp.numSC + kFrontSC - 1) / kFrontSC, kScanThreads, dynFront, st>>>(sp);
+		// JPLG_SCAN_PIPE=1 (experiment switch): the warp-pipelined k_scan_front_pipe instead of the barrier-separated phases. Same results; measured
+		// the same speed (r02v, 1,024 sources: 0.0567 vs 0.0561 ms per block): with ten warps per CTA the two recurrence warps advance 2.3 - 3.4 x
+		// slower than their 4.15-cycle dependent-issue latency allows (profiles/r02v_scan_pipe_timeline.txt), which eats what the overlap buys.
+		static const bool pipe = [] { const char* e = std::getenv("JPLG_SCAN_PIPE"); return e && e[0] == '1'; }();
+		if (!pipe) k_scan_front<<<(rp.numSC + kFrontSC - 1) / kFrontSC, kScanThreads, dynFront, st>>>(sp);
+		else k_scan_front_pipe<<<(rp.numSC + kFrontSC - 1) / kFrontSC, kPipeThreads, dynFront + 256, st>>>(sp);
 		if (rp.perSource) k_scan_mix<true><<<dim3(rp.numCTAs, sp.nTiles), kScanThreads, dynMix, st>>>(sp);
 		else k_scan_mix<false><<<dim3(rp.numCTAs, sp.nTiles), kScanThreads, dynMix, st>>>(sp);
 		return cudaGetLastError();
