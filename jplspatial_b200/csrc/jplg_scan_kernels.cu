@@ -57,6 +57,13 @@ namespace jplg
 	}
 
 	// dynamic shared memory (floats): dly | a (P3 leaves the delayed samples here) | x | x1, each [4][nTiles * 17 + 8]; e [4][nTiles][25] + 32
+#ifdef JPLG_PROF
+	__device__ unsigned long long g_frontProf[16];
+	#define FRONT_STAMP(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) g_frontProf[i] = clock64(); } while (0)
+	extern "C" __attribute__((visibility("default"))) void jplg_debug_front_prof(unsigned long long* out) { cudaMemcpyFromSymbol(out, g_frontProf, sizeof(g_frontProf)); }
+#else
+	#define FRONT_STAMP(i)
+#endif
 	__global__ void __launch_bounds__(kScanThreads)
 	k_scan_front(const ScanParams sp)
 	{
@@ -74,6 +81,7 @@ namespace jplg
 		float* sX1 = sX + arrS;
 		float* sE = sX1 + arrS;      // state k of (q, tile t) at (q * nT + t) * 25 + k + 8 q
 		const uint32_t pos32 = static_cast<uint32_t>(rp.pos);
+		FRONT_STAMP(0);
 
 		// ---- P0: ring pushes of the CTA's source-channels (chunk k pushes in[480k .. F) at push offset PushesThroughChunk(F, k))
 		if (sp.push)
@@ -130,6 +138,7 @@ namespace jplg
 			}
 		}
 		__syncthreads();
+		FRONT_STAMP(1);
 		// ---- P2: taps. thread = (tile slot, source-channel q = tid & 3): the four source-channels' rows interleave across lanes
 		const uint32_t q = tid & (kFrontSC - 1u), slot = tid / kFrontSC, sc = scBase + q;
 		const bool scValid = sc < rp.numSC;
@@ -157,6 +166,7 @@ namespace jplg
 			}
 		}
 		__syncthreads();
+		FRONT_STAMP(2);
 		// ---- P3: the Thiran recurrence, in place over the coefficients
 		if ((tid & 31u) == 0)
 		{
@@ -182,6 +192,7 @@ namespace jplg
 			}
 		}
 		__syncthreads();
+		FRONT_STAMP(3);
 		// ---- P4: zero-state response of every tile
 		if (scValid)
 		{
@@ -199,6 +210,7 @@ namespace jplg
 			}
 		}
 		__syncthreads();
+		FRONT_STAMP(4);
 		// ---- P5: warp w = source-channel w: the scan over the tiles; lane r < 24 owns row r of M and state r; every lane ramps up to two gains
 		{
 			const uint32_t w = tid >> 5, lane = tid & 31u, s5 = scBase + w;
@@ -221,11 +233,14 @@ namespace jplg
 					g[h] = cur; dg[h] = (tg - cur) / static_cast<float>(chunk0);
 				}
 				float* e = sE + w * nT * 25 + 8 * w + r;
+				// the state vector goes through a 16-byte aligned staging row: 6 broadcast LDS.128 per step instead of 24 shuffles (one warp-shuffle per
+				// cycle and SM is the ceiling of the shuffle form: 8 resident scan warps x 24 = 192 cycles per step)
+				float4* stage = reinterpret_cast<float4*>(sE + kFrontSC * nT * 25 + 32 + 32 * w);
 				for (uint32_t t = 0; t < nT; ++t)
 				{
 					const float et = e[t * 25];
+					if (lane < 24) { e[t * 25] = s; reinterpret_cast<float*>(stage)[lane] = s; }   // the tile's start state replaces its zero-state response in place
 					__syncwarp();
-					if (lane < 24) e[t * 25] = s;                    // the tile's start state replaces its zero-state response in place
 					if (t * kT < chunk0)
 					{
 						float* gt = sp.tileGain + (size_t(t) * nSC + s5) * nG;    // [tile][sc][L + 4]
@@ -236,19 +251,22 @@ namespace jplg
 					}
 					float a0 = et, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
 					#pragma unroll
-					for (int k = 0; k < 24; k += 4)
+					for (int k = 0; k < 6; ++k)
 					{
-						a0 = __fmaf_rn(m[k], __shfl_sync(0xffffffffu, s, k), a0);
-						a1 = __fmaf_rn(m[k + 1], __shfl_sync(0xffffffffu, s, k + 1), a1);
-						a2 = __fmaf_rn(m[k + 2], __shfl_sync(0xffffffffu, s, k + 2), a2);
-						a3 = __fmaf_rn(m[k + 3], __shfl_sync(0xffffffffu, s, k + 3), a3);
+						const float4 v = stage[k];
+						a0 = __fmaf_rn(m[4 * k], v.x, a0);
+						a1 = __fmaf_rn(m[4 * k + 1], v.y, a1);
+						a2 = __fmaf_rn(m[4 * k + 2], v.z, a2);
+						a3 = __fmaf_rn(m[4 * k + 3], v.w, a3);
 					}
 					s = (a0 + a1) + (a2 + a3);
+					__syncwarp();      // every lane has read the staging row before the next step overwrites it
 				}
 				if (lane < 24) rp.state[(ST_FILTER + lane) * nSC + s5] = s;
 			}
 		}
 		__syncthreads();
+		FRONT_STAMP(5);
 		// ---- P6: every tile again from its true start state, with the ramped band gains (CrossoverFilter.h:505-535) -> Y [frame][sc]
 		if (scValid)
 		{
@@ -286,12 +304,14 @@ namespace jplg
 				}
 			}
 		}
-		__syncthreads();       // every tile has read the block-start band gains
+		__syncthreads();
+		FRONT_STAMP(6);       // every tile has read the block-start band gains
 		if (tid < kFrontSC && scBase + tid < rp.numSC)
 		{
 			#pragma unroll
 			for (int b = 0; b < 4; ++b) rp.state[(ST_BAND + b) * nSC + scBase + tid] = rp.tgtBand[b * nSC + scBase + tid];
 		}
+			FRONT_STAMP(15);
 	}
 
 	//======================================================================
@@ -752,7 +772,7 @@ namespace jplg
 	static size_t ScanFrontSmem(uint32_t frames)
 	{
 		const size_t nT = frames / kScanTile;
-		return (size_t(4) * kFrontSC * (nT * (kScanTile + 1) + 8) + size_t(kFrontSC) * nT * 25 + 32) * sizeof(float);
+		return (size_t(4) * kFrontSC * (nT * (kScanTile + 1) + 8) + size_t(kFrontSC) * nT * 25 + 32 + 32 * kFrontSC) * sizeof(float);   // + 24-float staging row per scan warp
 	}
 
 	bool RenderCanScan(const RenderParams& rp)   // per-source debug output: a multichannel source's channels must sit in one subset (they do: subsets hold whole sources)
