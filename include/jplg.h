@@ -283,7 +283,7 @@ JPLG_API jplg_status jplg_renderer_process_block_debug(jplg_renderer r, const fl
  * 16-frame tiles that are filtered from zero state in parallel, stitched by a scan over the tiles' 24-float filter states (s' = M s + e, M fixed
  * per sample rate) and re-run from their true start states (jplg_scan_kernels.cu); the delay smoother and the Thiran all-pass stay sequential
  * three-operation chains, bit for bit the reference's (their rounding is part of the result: integer-delay statics never forget a state error). It costs twice the filter arithmetic, so by default
- * (policy -1) it is used only while the scene leaves the machine under-filled (<= 2,048 source-channels, whole 16-frame tiles); 0 = never, 1 = whenever a block qualifies. Same state arrays as the sequential kernel: the policy may change between blocks.
+ * (policy -1) it is used only while the scene leaves the machine under-filled (<= 3,072 source-channels, whole 16-frame tiles); 0 = never, 1 = whenever a block qualifies. Same state arrays as the sequential kernel: the policy may change between blocks.
  * Results agree with JPLG_MODE_PARITY to rounding (bar 1e-5 * max(|ref|, rms, 1e-3)); PARITY renderers ignore the policy. */
 JPLG_API jplg_status jplg_renderer_set_time_parallel(jplg_renderer r, int32_t policy);
 /* Blocks rendered through the time-parallel path so far (tests / benchmarks check which path ran). */

@@ -860,7 +860,7 @@ static jplg_status EnsureAux(jplg_context ctx)
 // JPLG_MODE_THROUGHPUT renders small scenes time-parallel (jplg_scan_kernels.cu): the scan does the crossover arithmetic twice, so it pays only
 // while (source-channels x tiles) threads still find idle schedulers. Cross-over measured on a B200 (profiles/r02_scan_ab.txt); the policy can be
 // pinned with jplg_renderer_set_time_parallel.
-constexpr size_t kScanAutoMaxSC = 2048;
+constexpr size_t kScanAutoMaxSC = 3072;
 static bool UseScanPath(jplg_renderer r, const RenderParams& rp)
 {
 	if (r->cfg.mode != JPLG_MODE_THROUGHPUT || r->scanPolicy == 0 || !RenderCanScan(rp)) return false;

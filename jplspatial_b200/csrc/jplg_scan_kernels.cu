@@ -33,6 +33,7 @@
 #include "jplg_kernels.hpp"
 #include "jplg_render_common.cuh"
 #include <cstdlib>
+#include <algorithm>
 
 namespace jplg
 {
@@ -72,69 +73,111 @@ namespace jplg
 		const uint32_t tid = threadIdx.x, F = rp.frames, nT = sp.nTiles, C = rp.srcChannels, L = rp.L, nG = L + 4;
 		const size_t nSC = rp.numSC;
 		const uint32_t scBase = blockIdx.x * kFrontSC;
-		// sample (q, frame n) lives at q * rowS + (n / 16) * 17 + n % 16: tiles 17 floats apart and rows 8 banks apart, so the 32 lanes of a warp
-		// (8 tile slots x 4 source-channels) hit 32 different banks in the parallel phases (exactly so for 32 tiles)
-		const uint32_t rowS = nT * (kT + 1) + 8u, arrS = kFrontSC * rowS;
-		float* sDly = sF;
-		float* sA = sDly + arrS;
-		float* sX = sA + arrS;
-		float* sX1 = sX + arrS;
-		float* sE = sX1 + arrS;      // state k of (q, tile t) at (q * nT + t) * 25 + k + 8 q
+		// One float4 per (source-channel q, frame n) at q * tapRow + (n / 16) * 17 + n % 16 (tiles 17 apart, rows + 2: a quarter-warp's STS.128 in P2 is
+		// conflict-free). Its life: P1 leaves the smoothed delay in .x; P2 replaces it with the taps { a, x[n], x[n-1], . }, so that P3 fetches a sample's
+		// operands with ONE LDS.128 (every memory instruction in a single-warp recurrence costs ~2 cycles of its chain); P3 leaves the delayed sample in .w.
+		const uint32_t tapRow = nT * (kT + 1) + 2u;
+		float4* sTap = reinterpret_cast<float4*>(sF);
+		float* sE = reinterpret_cast<float*>(sTap + kFrontSC * tapRow);      // state k of (q, tile t) at (q * nT + t) * 25 + k + 8 q
 		const uint32_t pos32 = static_cast<uint32_t>(rp.pos);
 		FRONT_STAMP(0);
 
-		// ---- P0: ring pushes of the CTA's source-channels (chunk k pushes in[480k .. F) at push offset PushesThroughChunk(F, k))
-		if (sp.push)
+		// ---- P0 (loads): ring pushes of the CTA's source-channels (chunk k pushes in[480k .. F) at push offset PushesThroughChunk(F, k)). A thread keeps
+		// frames f = tid + 128 j of all four source-channels in registers; the loads are in flight while P1 runs, the stores follow it.
+		const uint32_t numChunks = (F + kChunkFrames - 1) / kChunkFrames;
+		const bool pushInRegs = sp.push && F <= 4 * kScanThreads;
+		float pv[kFrontSC][4];
+		if (pushInRegs)
 		{
-			// a thread keeps frames f = f0 + tid + 128 j of all four source-channels in registers (one memory latency for the whole push) and stores
-			// every frame once per chunk k <= f / 480 (the tail of the block enters the ring once per chunk boundary it lies behind)
-			const uint32_t numChunks = (F + kChunkFrames - 1) / kChunkFrames;
-			for (uint32_t f0 = 0; f0 < F; f0 += 4 * kScanThreads)
+			#pragma unroll
+			for (uint32_t qq = 0; qq < kFrontSC; ++qq)
 			{
-				float v[kFrontSC][4];
+				const uint32_t s0 = min(scBase + qq, rp.numSC - 1u), src = s0 / C, ch = s0 - src * C;
+				const float* in = rp.in + size_t(src) * F * C + ch;
 				#pragma unroll
-				for (uint32_t qq = 0; qq < kFrontSC; ++qq)
+				for (uint32_t j = 0; j < 4; ++j) { const uint32_t f = tid + kScanThreads * j; pv[qq][j] = f < F ? __ldcs(in + size_t(f) * C) : 0.0f; }
+			}
+		}
+		else if (sp.push)
+		{
+			for (uint32_t qq = 0; qq < kFrontSC && scBase + qq < rp.numSC; ++qq)      // long blocks: plain element-wise push
+			{
+				const uint32_t s0 = scBase + qq, src = s0 / C, ch = s0 - src * C;
+				const float* in = rp.in + size_t(src) * F * C + ch;
+				float* ring = rp.rings + size_t(s0) * rp.ringSize;
+				for (uint32_t f = tid; f < F; f += kScanThreads)
 				{
-					const uint32_t s0 = min(scBase + qq, rp.numSC - 1u), src = s0 / C, ch = s0 - src * C;
-					const float* in = rp.in + size_t(src) * F * C + ch;
-					#pragma unroll
-					for (uint32_t j = 0; j < 4; ++j) { const uint32_t f = f0 + tid + kScanThreads * j; v[qq][j] = f < F ? __ldcs(in + size_t(f) * C) : 0.0f; }
-				}
-				#pragma unroll
-				for (uint32_t qq = 0; qq < kFrontSC; ++qq)
-				{
-					if (scBase + qq >= rp.numSC) break;
-					float* ring = rp.rings + size_t(scBase + qq) * rp.ringSize;
-					#pragma unroll
-					for (uint32_t j = 0; j < 4; ++j)
-					{
-						const uint32_t f = f0 + tid + kScanThreads * j;
-						if (f >= F) continue;
-						for (uint32_t k = 0; k < numChunks && k * kChunkFrames <= f; ++k)
-							ring[(pos32 + PushesThroughChunk(F, k) + (f - k * kChunkFrames)) & rp.ringMask] = v[qq][j];
-					}
+					const float v = in[size_t(f) * C];
+					for (uint32_t k = 0; k < numChunks && k * kChunkFrames <= f; ++k) ring[(pos32 + PushesThroughChunk(F, k) + (f - k * kChunkFrames)) & rp.ringMask] = v;
 				}
 			}
 		}
-		// ---- P1: the smoothed delay of every frame (thread 32 q = source-channel q: one per warp / scheduler)
-		if ((tid & 31u) == 0)
+		// ---- P1: warp 0, lanes 0-3 = the four source-channels in lock step: the smoothed delay of every frame (three dependent operations per frame).
+		// Warps 1-3 meanwhile run the reference's gain-ramp recurrences (`gain += delta` per frame, ChannelMixing.h:99-107, CrossoverFilter.h:518-531) for the
+		// L mix gains + 4 band gains of the four source-channels and leave them at every tile start of the first chunk — in warps of their own, because
+		// independent work interleaved INTO a recurrence's instruction stream slows it (measured: + 5 k cycles with the ramps in the delay warp).
+		if (tid < 32)
 		{
-			const uint32_t q = tid >> 5, sc = scBase + q;
-			if (sc < rp.numSC)
+			const uint32_t s1 = scBase + tid;
+			if (tid < kFrontSC && s1 < rp.numSC)
 			{
-				float cur = rp.state[ST_DELAY * nSC + sc];
-				const float tgt = rp.tgtDelay[sc], alpha = rp.alpha;
-				float* o = sDly + q * rowS;
+				float cur = rp.state[ST_DELAY * nSC + s1];
+				const float tgt = rp.tgtDelay[s1], alpha = rp.alpha;
+				float4* o = sTap + tid * tapRow;
 				for (uint32_t t = 0; t < nT; ++t)
 				{
 					#pragma unroll
 					for (uint32_t i = 0; i < kT; ++i)
 					{
 						cur = alpha * (tgt - cur) + cur;     // same expression as role D of k_render (the smoother does not restart at chunk boundaries)
-						o[t * (kT + 1) + i] = cur;
+						o[t * (kT + 1) + i].x = cur;
 					}
 				}
-				rp.state[ST_DELAY * nSC + sc] = cur;
+				rp.state[ST_DELAY * nSC + s1] = cur;
+			}
+		}
+		else
+		{
+			const uint32_t chunk0 = min(F, kChunkFrames), tilesRamped = (chunk0 + kT - 1) / kT;
+			float g[2], dg[2]; float* gp[2];
+			#pragma unroll
+			for (uint32_t h = 0; h < 2; ++h)
+			{
+				const uint32_t v = (tid - 32u) + 96u * h, qq = v / nG, j = v - qq * nG, s1 = scBase + qq;
+				float c0 = 0.0f, tg = 0.0f;
+				gp[h] = nullptr;
+				if (qq < kFrontSC && s1 < rp.numSC)
+				{
+					if (j < L) { c0 = rp.curMix[j * nSC + s1]; tg = rp.tgtMix[j * nSC + s1]; }
+					else { c0 = rp.state[(ST_BAND + j - L) * nSC + s1]; tg = rp.tgtBand[(j - L) * nSC + s1]; }
+					gp[h] = sp.tileGain + size_t(s1) * nG + j;        // + t * nSC * nG: [tile][sc][L + 4]
+				}
+				g[h] = c0; dg[h] = (tg - c0) / static_cast<float>(chunk0);
+			}
+			for (uint32_t t = 0; t < tilesRamped; ++t)
+			{
+				if (gp[0]) gp[0][size_t(t) * nSC * nG] = g[0];
+				if (gp[1]) gp[1][size_t(t) * nSC * nG] = g[1];
+				#pragma unroll
+				for (uint32_t i = 0; i < kT; ++i) { g[0] += dg[0]; g[1] += dg[1]; }
+			}
+		}
+		// ---- P0 (stores)
+		if (pushInRegs)
+		{
+			#pragma unroll
+			for (uint32_t qq = 0; qq < kFrontSC; ++qq)
+			{
+				if (scBase + qq >= rp.numSC) break;
+				float* ring = rp.rings + size_t(scBase + qq) * rp.ringSize;
+				#pragma unroll
+				for (uint32_t j = 0; j < 4; ++j)
+				{
+					const uint32_t f = tid + kScanThreads * j;
+					if (f >= F) continue;
+					for (uint32_t k = 0; k < numChunks && k * kChunkFrames <= f; ++k)
+						ring[(pos32 + PushesThroughChunk(F, k) + (f - k * kChunkFrames)) & rp.ringMask] = pv[qq][j];
+				}
 			}
 		}
 		__syncthreads();
@@ -149,47 +192,42 @@ namespace jplg
 			{
 				const ScanTile ti = scan_tile(t, F);
 				const uint32_t pe = pos32 + PushesThroughChunk(F, ti.chunkStart / kChunkFrames + 1);   // ring push count after this chunk's pushes
-				float a[kT], x[kT], x1[kT];
+				float4 tap[kT];
 				#pragma unroll
 				for (uint32_t i = 0; i < kT; ++i)
 				{
-					const float d = static_cast<float>(ti.chunkLen - (ti.t0 + i)) + sDly[q * rowS + t * (kT + 1) + i];   // SetDelay(float(framesToProcess - s) + delay)
+					const float d = static_cast<float>(ti.chunkLen - (ti.t0 + i)) + sTap[q * tapRow + t * (kT + 1) + i].x;   // SetDelay(float(framesToProcess - s) + delay)
 					const uint32_t D = static_cast<uint32_t>(d);
 					const float fr = d - static_cast<float>(static_cast<int32_t>(D));
 					const uint32_t r = pe - 1u - D;
-					a[i] = thiran_coef(fr);
-					x[i] = ring[r & rp.ringMask];
-					x1[i] = ring[(r - 1u) & rp.ringMask];
+					tap[i] = make_float4(thiran_coef(fr), ring[r & rp.ringMask], ring[(r - 1u) & rp.ringMask], 0.0f);
 				}
 				#pragma unroll
-				for (uint32_t i = 0; i < kT; ++i) { const uint32_t o = q * rowS + t * (kT + 1) + i; sA[o] = a[i]; sX[o] = x[i]; sX1[o] = x1[i]; }
+				for (uint32_t i = 0; i < kT; ++i) sTap[q * tapRow + t * (kT + 1) + i] = tap[i];
 			}
 		}
 		__syncthreads();
 		FRONT_STAMP(2);
-		// ---- P3: the Thiran recurrence, in place over the coefficients
-		if ((tid & 31u) == 0)
+		// ---- P3: the Thiran recurrence, lanes 0-3 of warp 0 = the four source-channels in lock step
+		if (tid < kFrontSC && scBase + tid < rp.numSC)
 		{
-			const uint32_t qq = tid >> 5, s2 = scBase + qq;
-			if (s2 < rp.numSC)
+			const uint32_t s2 = scBase + tid;
+			float y1 = rp.state[ST_THIRAN_Y1 * nSC + s2];
+			float4* tp = sTap + tid * tapRow;
+			for (uint32_t t = 0; t < nT; ++t)
 			{
-				float y1 = rp.state[ST_THIRAN_Y1 * nSC + s2];
-				float* a = sA + qq * rowS; const float* x = sX + qq * rowS; const float* x1 = sX1 + qq * rowS;
-				for (uint32_t t = 0; t < nT; ++t)
+				const uint32_t n0 = t * (kT + 1);
+				float4 v[kT];
+				#pragma unroll
+				for (uint32_t i = 0; i < kT; ++i) v[i] = tp[n0 + i];
+				#pragma unroll
+				for (uint32_t i = 0; i < kT; ++i)
 				{
-					const uint32_t n0 = t * (kT + 1);
-					float va[kT], vx[kT], v1[kT];
-					#pragma unroll
-					for (uint32_t i = 0; i < kT; ++i) { va[i] = a[n0 + i]; vx[i] = x[n0 + i]; v1[i] = x1[n0 + i]; }
-					#pragma unroll
-					for (uint32_t i = 0; i < kT; ++i)
-					{
-						y1 = va[i] * (vx[i] - y1) + v1[i];     // Thiran1stInterpolator::Process: never fused in the reference
-						a[n0 + i] = y1;
-					}
+					y1 = v[i].x * (v[i].y - y1) + v[i].z;     // Thiran1stInterpolator::Process: never fused in the reference
+					tp[n0 + i].w = y1;
 				}
-				rp.state[ST_THIRAN_Y1 * nSC + s2] = y1;
 			}
+			rp.state[ST_THIRAN_Y1 * nSC + s2] = y1;
 		}
 		__syncthreads();
 		FRONT_STAMP(3);
@@ -201,9 +239,9 @@ namespace jplg
 				float st[24];
 				#pragma unroll
 				for (int k = 0; k < 24; ++k) st[k] = 0.0f;
-				const float* xi = sA + q * rowS + t * (kT + 1);
+				const float4* xi = sTap + q * tapRow + t * (kT + 1);
 				#pragma unroll
-				for (uint32_t i = 0; i < kT; ++i) { float bands[4]; xover_sample<1>(rp.coef, st, xi[i], bands); }
+				for (uint32_t i = 0; i < kT; ++i) { float bands[4]; xover_sample<1>(rp.coef, st, xi[i].w, bands); }
 				float* e = sE + (q * nT + t) * 25 + 8 * q;
 				#pragma unroll
 				for (int k = 0; k < 24; ++k) e[k] = st[k];
@@ -211,7 +249,7 @@ namespace jplg
 		}
 		__syncthreads();
 		FRONT_STAMP(4);
-		// ---- P5: warp w = source-channel w: the scan over the tiles; lane r < 24 owns row r of M and state r; every lane ramps up to two gains
+		// ---- P5: warp w = source-channel w: the scan over the tiles; lane r < 24 owns row r of M and state r
 		{
 			const uint32_t w = tid >> 5, lane = tid & 31u, s5 = scBase + w;
 			if (s5 < rp.numSC)
@@ -221,17 +259,6 @@ namespace jplg
 				#pragma unroll
 				for (int k = 0; k < 24; ++k) m[k] = sp.M[r * 24 + k];
 				float s = rp.state[(ST_FILTER + r) * nSC + s5];
-				const uint32_t chunk0 = min(F, kChunkFrames);
-				float g[2], dg[2];
-				#pragma unroll
-				for (uint32_t h = 0; h < 2; ++h)
-				{
-					const uint32_t j = lane + 32u * h;
-					float cur = 0.0f, tg = 0.0f;
-					if (j < L) { cur = rp.curMix[j * nSC + s5]; tg = rp.tgtMix[j * nSC + s5]; }
-					else if (j < nG) { cur = rp.state[(ST_BAND + j - L) * nSC + s5]; tg = rp.tgtBand[(j - L) * nSC + s5]; }
-					g[h] = cur; dg[h] = (tg - cur) / static_cast<float>(chunk0);
-				}
 				float* e = sE + w * nT * 25 + 8 * w + r;
 				// the state vector goes through a 16-byte aligned staging row: 6 broadcast LDS.128 per step instead of 24 shuffles (one warp-shuffle per
 				// cycle and SM is the ceiling of the shuffle form: 8 resident scan warps x 24 = 192 cycles per step)
@@ -241,14 +268,6 @@ namespace jplg
 					const float et = e[t * 25];
 					if (lane < 24) { e[t * 25] = s; reinterpret_cast<float*>(stage)[lane] = s; }   // the tile's start state replaces its zero-state response in place
 					__syncwarp();
-					if (t * kT < chunk0)
-					{
-						float* gt = sp.tileGain + (size_t(t) * nSC + s5) * nG;    // [tile][sc][L + 4]
-						if (lane < nG) gt[lane] = g[0];
-						if (lane + 32u < nG) gt[lane + 32u] = g[1];
-						#pragma unroll
-						for (uint32_t i = 0; i < kT; ++i) { g[0] += dg[0]; g[1] += dg[1]; }
-					}
 					float a0 = et, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
 					#pragma unroll
 					for (int k = 0; k < 6; ++k)
@@ -290,13 +309,13 @@ namespace jplg
 					inc[b] = (tgB[b] - b0) / chunkF;
 					band[b] = ramping ? gt[L + b] : tgB[b];
 				}
-				const float* xi = sA + q * rowS + t * (kT + 1);
+				const float4* xi = sTap + q * tapRow + t * (kT + 1);
 				float* yo = sp.xth + size_t(ti.n0) * nSC + sc;
 				#pragma unroll
 				for (uint32_t i = 0; i < kT; ++i)
 				{
 					float b[4];
-					xover_sample<1>(rp.coef, st, xi[i], b);
+					xover_sample<1>(rp.coef, st, xi[i].w, b);
 					// (bands * gains).reduce() with the bands interleaved { b1, b3, b2, b4 } (CrossoverFilter.h:516-531, SIMD.h:938-945)
 					yo[size_t(i) * nSC] = (b[0] * band[0] + b[1] * band[2]) + (b[2] * band[1] + b[3] * band[3]);
 					#pragma unroll
@@ -637,6 +656,13 @@ namespace jplg
 	// the tile start: staged with 4-byte cp.async, so the ~50 scattered loads of a thread are all in flight at once).
 	// DEBUG: also writes every source's own contribution (jplg_renderer_process_block_debug), channel after channel like the reference's
 	// `dest += source * gain`.
+#ifdef JPLG_PROF
+	__device__ unsigned long long g_mixProf[16];
+	#define MIX_STAMP(i) do { if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) g_mixProf[i] = clock64(); } while (0)
+	extern "C" __attribute__((visibility("default"))) void jplg_debug_mix_prof(unsigned long long* out) { cudaMemcpyFromSymbol(out, g_mixProf, sizeof(g_mixProf)); }
+#else
+	#define MIX_STAMP(i)
+#endif
 	template<bool DEBUG>
 	__global__ void __launch_bounds__(kScanThreads)
 	k_scan_mix(const ScanParams sp)
@@ -644,6 +670,7 @@ namespace jplg
 		extern __shared__ __align__(16) float sScan[];
 		__shared__ uint32_t sLast;
 		const RenderParams& rp = sp.rp;
+		MIX_STAMP(0);
 		const uint32_t tid = threadIdx.x, cta = blockIdx.x, t = blockIdx.y;
 		const uint32_t C = rp.srcChannels, L = rp.L, nG = L + 4;
 		const uint32_t srcPerCTA = kScanThreads / C, scPerCTA = srcPerCTA * C, scBase = cta * scPerCTA;
@@ -678,6 +705,7 @@ namespace jplg
 		asm volatile("cp.async.commit_group;" ::: "memory");
 		asm volatile("cp.async.wait_group 0;" ::: "memory");
 		__syncthreads();
+		MIX_STAMP(1);
 
 		// ---- K4: AddAndApplyGainRamp (ChannelMixing.h:89-107) for every (source-channel, output channel) of the tile, re-associated across sources:
 		// thread = (output channel pair, source subset), kT packed frame accumulators, fixed-order cross-subset reduce (the mix role of k_render)
@@ -733,6 +761,7 @@ namespace jplg
 			for (uint32_t i = 0; i < kT; ++i) row[i] = acc[i];
 		}
 		__syncthreads();
+		MIX_STAMP(2);
 		{
 			float* pb = rp.partial + (size_t(cta) * F + ti.n0) * L;
 			const float* sPf = reinterpret_cast<const float*>(sP);
@@ -748,8 +777,10 @@ namespace jplg
 		// ---- the last tile-CTA of this source group to get here commits current = target (every tile read the block-start values above)
 		__threadfence();
 		__syncthreads();
+		MIX_STAMP(3);
 		if (tid == 0) sLast = (atomicAdd(&sp.counters[cta], 1u) == sp.nTiles - 1u) ? 1u : 0u;
 		__syncthreads();
+		MIX_STAMP(4);
 		if (sLast)
 		{
 			__threadfence();
@@ -760,6 +791,7 @@ namespace jplg
 			}
 			if (tid == 0) sp.counters[cta] = 0u;
 		}
+		MIX_STAMP(15);
 	}
 
 	size_t ScanScratchFloats(uint32_t numSC, uint32_t maxFrames)
@@ -772,7 +804,10 @@ namespace jplg
 	static size_t ScanFrontSmem(uint32_t frames)
 	{
 		const size_t nT = frames / kScanTile;
-		return (size_t(4) * kFrontSC * (nT * (kScanTile + 1) + 8) + size_t(kFrontSC) * nT * 25 + 32 + 32 * kFrontSC) * sizeof(float);   // + 24-float staging row per scan warp
+		// k_scan_front: float4 tap rows, zero-state / start states, a 24-float staging row per scan warp; k_scan_front_pipe: four float rows (+ 8) instead of the
+		// float4 rows (its flags follow, + 256 bytes at the launch): the larger of the two
+		const size_t phases = size_t(4) * kFrontSC * (nT * (kScanTile + 1) + 2), pipe = size_t(4) * kFrontSC * (nT * (kScanTile + 1) + 8);
+		return (std::max(phases, pipe) + size_t(kFrontSC) * nT * 25 + 32 + 32 * kFrontSC) * sizeof(float);
 	}
 
 	bool RenderCanScan(const RenderParams& rp)   // per-source debug output: a multichannel source's channels must sit in one subset (they do: subsets hold whole sources)

@@ -19,3 +19,6 @@ names = {0: "entry", 1: "P0 push + P1 delay", 2: "P2 taps", 3: "P3 Thiran", 4: "
 prev = out[0]
 for i in (1, 2, 3, 4, 5, 6, 15):
     print(f"{names[i]:22s} {out[i] - prev:7d} cycles  (cumulative {out[i] - out[0]:7d} = {(out[i] - out[0]) / 1.96e3:6.2f} us)"); prev = out[i]
+
+mx = (ctypes.c_ulonglong * 16)(); ctypes.CDLL(J.lib_path).jplg_debug_mix_prof(mx)
+print("k_scan_mix CTA (0,0):", [int(mx[i] - mx[0]) for i in (1, 2, 3, 4, 5, 15) if mx[i]], "cycles after entry at its barriers / end")
