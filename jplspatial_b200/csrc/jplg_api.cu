@@ -868,7 +868,7 @@ static bool UseScanPath(jplg_renderer r, const RenderParams& rp)
 	return size_t(rp.numSC) <= kScanAutoMaxSC;
 }
 
-static jplg_status LaunchScan(jplg_renderer r, const RenderParams& rp)
+static jplg_status LaunchScan(jplg_renderer r, const RenderParams& rp, float* busAcc)
 {
 	jplg_context ctx = r->ctx;
 	if (!r->scanM)
@@ -877,14 +877,15 @@ static jplg_status LaunchScan(jplg_renderer r, const RenderParams& rp)
 		CrossoverTransition(r->coef, kScanTile, M);
 		if (cudaMalloc(reinterpret_cast<void**>(&r->scanM), sizeof(M)) != cudaSuccess
 			|| cudaMalloc(reinterpret_cast<void**>(&r->scanScratch), ScanScratchFloats(r->numSC, r->maxFrames) * sizeof(float)) != cudaSuccess
-			|| cudaMalloc(reinterpret_cast<void**>(&r->scanCounters), size_t(r->numCTAs) * sizeof(uint32_t)) != cudaSuccess)
+			|| cudaMalloc(reinterpret_cast<void**>(&r->scanCounters), (size_t(r->numCTAs) + r->maxFrames / kScanTile + 1) * sizeof(uint32_t)) != cudaSuccess)
 		{ cudaGetLastError(); return Fail(ctx, JPLG_ERR_OUT_OF_MEMORY, "process_block: time-parallel scratch allocation failed"); }
 		JPLG_CUDA_TRY(ctx, cudaMemcpyAsync(r->scanM, M, sizeof(M), cudaMemcpyHostToDevice, ctx->stream));
-		JPLG_CUDA_TRY(ctx, cudaMemsetAsync(r->scanCounters, 0, size_t(r->numCTAs) * sizeof(uint32_t), ctx->stream));
+		JPLG_CUDA_TRY(ctx, cudaMemsetAsync(r->scanCounters, 0, (size_t(r->numCTAs) + r->maxFrames / kScanTile + 1) * sizeof(uint32_t), ctx->stream));
 		JPLG_CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));   // M is a stack array
 	}
 	ScanParams sp{};
 	sp.rp = rp; sp.M = r->scanM; sp.scratch = r->scanScratch; sp.counters = r->scanCounters; sp.push = 1u;
+	sp.deviceBus = r->deviceBus; sp.busAcc = busAcc;
 	JPLG_LAUNCH(ctx, JPLG_K_RENDER, LaunchRenderScan(sp, ctx->stream));
 	ctx->launches += 1;   // k_scan_front, k_scan_mix
 	r->scanBlocks++;
@@ -970,6 +971,7 @@ static jplg_status ProcessBlock(jplg_renderer r, const float* in, float* bus, fl
 		r->activeSet ^= 1;
 		r->pendingPanned = false;
 	}
+	bool scanReduced = false;
 	RenderParams rp{};
 	rp.numSC = r->numSC; rp.srcChannels = C; rp.L = L; rp.ringSize = r->ringSize; rp.ringMask = r->ringSize - 1; rp.pos = r->pos; rp.frames = frames;
 	rp.alpha = r->alpha; std::memcpy(rp.coef, r->coef, sizeof(rp.coef));
@@ -1037,7 +1039,8 @@ static jplg_status ProcessBlock(jplg_renderer r, const float* in, float* bus, fl
 		if (!r->evStarted) JPLG_CUDA_TRY(ctx, cudaEventCreateWithFlags(&r->evStarted, cudaEventDisableTiming));
 		if (scan)
 		{
-			jplg_status sst = LaunchScan(r, rp); if (sst != JPLG_OK) return sst;
+			jplg_status sst = LaunchScan(r, rp, dBus); if (sst != JPLG_OK) return sst;
+			scanReduced = true;
 			JPLG_CUDA_TRY(ctx, cudaEventRecord(r->evStarted, ctx->stream));   // small grids: "resident" and "done" are the same thing here
 		}
 		else JPLG_LAUNCH(ctx, JPLG_K_RENDER, LaunchRender(rp, r->cfg.mode, 0, r->numCTAs, ctx->stream, r->evStarted));
@@ -1045,7 +1048,7 @@ static jplg_status ProcessBlock(jplg_renderer r, const float* in, float* bus, fl
 		if (rp.fusedPush && asyncSlot >= 0) JPLG_CUDA_TRY(ctx, cudaEventRecord(r->evPushedA[asyncSlot], ctx->stream));   // the staging slot was read by the render
 	}
 	if (r->evSetFree[r->activeSet]) { JPLG_CUDA_TRY(ctx, cudaEventRecord(r->evSetFree[r->activeSet], ctx->stream)); r->setFreeRecorded[r->activeSet] = true; }
-	JPLG_LAUNCH(ctx, JPLG_K_BUS_REDUCE, LaunchBusReduce(rp, r->deviceBus, dBus, ctx->stream));
+	if (!scanReduced) JPLG_LAUNCH(ctx, JPLG_K_BUS_REDUCE, LaunchBusReduce(rp, r->deviceBus, dBus, ctx->stream));   // the time-parallel path reduces inside k_scan_mix
 	r->pos += TotalPushes(frames);
 	if (mem == JPLG_MEM_HOST)
 	{

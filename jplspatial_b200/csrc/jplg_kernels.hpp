@@ -112,7 +112,9 @@ namespace jplg
 		RenderParams rp;
 		const float* M;         // [24][24] zero-input state transition of the crossover over kScanTile frames (host: CrossoverTransition)
 		float* scratch;         // ScanScratchFloats(numSC, maxFrames) floats
-		uint32_t* counters;     // [numCTAs], zero between launches
+		uint32_t* counters;     // [numCTAs + maxFrames / kScanTile], zero between launches: tiles done per source group, source groups done per tile
+		float* deviceBus;       // [frames][L] the block's bus (k_scan_mix reduces the partial buses itself: no LaunchBusReduce on this path)
+		float* busAcc;          // caller's bus, accumulated into (may be null)
 		uint32_t push;          // 1: k_scan_front also pushes the block's input into the rings (0: already pushed)
 		// carved out of `scratch` by LaunchRenderScan
 		float* xth;             // [frames][numSC] filtered, band-gained source signals

@@ -81,6 +81,7 @@ namespace jplg
 		float* sE = reinterpret_cast<float*>(sTap + kFrontSC * tapRow);      // state k of (q, tile t) at (q * nT + t) * 25 + k + 8 q
 		const uint32_t pos32 = static_cast<uint32_t>(rp.pos);
 		FRONT_STAMP(0);
+		asm volatile("griddepcontrol.launch_dependents;" ::: "memory");     // k_scan_mix may be scheduled now: its CTAs wait (griddepcontrol.wait) for this grid to finish
 
 		// ---- P0 (loads): ring pushes of the CTA's source-channels (chunk k pushes in[480k .. F) at push offset PushesThroughChunk(F, k)). A thread keeps
 		// frames f = tid + 128 j of all four source-channels in registers; the loads are in flight while P1 runs, the stores follow it.
@@ -652,10 +653,16 @@ namespace jplg
 		asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(static_cast<uint32_t>(__cvta_generic_to_shared(dstShared))), "l"(src) : "memory");
 	}
 
-	// dynamic shared memory (floats): Y [kT][128] | P [J][nPairs][kT + 1] f2 | tg, cur, gt [128][Lp] (target gains, block-start gains, ramp values at
-	// the tile start: staged with 4-byte cp.async, so the ~50 scattered loads of a thread are all in flight at once).
+	// k_scan_mix: CTA = (128 source-channels, one tile), kMixThreads threads. With one or two warps per scheduler every instruction costs its full latency
+	// (r02y: 1,934 instructions per warp in 14.9 k cycles with 128 threads), so the work is spread thin: staging by (source-channel, quarter), the mix by
+	// (output channel pair, subset of TWO sources), the cross-subset reduce by output element. The last CTA of a tile to finish also sums the tile's
+	// partial buses over the source groups in a fixed order into the device bus and the caller's bus (no k_bus_reduce launch on this path); the last tile-CTA
+	// of a source group commits mCurrentGains = targets (DirectSound.cpp:221).
+	// dynamic shared memory (floats): Y [kT][128] | P [Jused][nPairs][kT + 1] f2 | tg, cur, gt [128][Lp] (target gains, block-start gains, ramp values at
+	// the tile start: staged with 4-byte cp.async, so the scattered loads of a thread are all in flight at once).
 	// DEBUG: also writes every source's own contribution (jplg_renderer_process_block_debug), channel after channel like the reference's
 	// `dest += source * gain`.
+	namespace { constexpr uint32_t kMixThreads = 256, kMixSC = 128; }
 #ifdef JPLG_PROF
 	__device__ unsigned long long g_mixProf[16];
 	#define MIX_STAMP(i) do { if (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) g_mixProf[i] = clock64(); } while (0)
@@ -664,16 +671,16 @@ namespace jplg
 	#define MIX_STAMP(i)
 #endif
 	template<bool DEBUG>
-	__global__ void __launch_bounds__(kScanThreads)
+	__global__ void __launch_bounds__(kMixThreads)
 	k_scan_mix(const ScanParams sp)
 	{
 		extern __shared__ __align__(16) float sScan[];
-		__shared__ uint32_t sLast;
+		__shared__ uint32_t sLast, sLastOfTile;
 		const RenderParams& rp = sp.rp;
 		MIX_STAMP(0);
 		const uint32_t tid = threadIdx.x, cta = blockIdx.x, t = blockIdx.y;
 		const uint32_t C = rp.srcChannels, L = rp.L, nG = L + 4;
-		const uint32_t srcPerCTA = kScanThreads / C, scPerCTA = srcPerCTA * C, scBase = cta * scPerCTA;
+		const uint32_t srcPerCTA = kMixSC / C, scPerCTA = srcPerCTA * C, scBase = cta * scPerCTA;
 		const uint32_t numSCInCTA = min(scPerCTA, rp.numSC - scBase);
 		const size_t nSC = rp.numSC;
 		const uint32_t F = rp.frames;
@@ -681,26 +688,33 @@ namespace jplg
 		const float chunkF = static_cast<float>(ti.chunkLen);
 		const bool ramping = ti.chunkStart == 0;      // later chunks sit at the target (mCurrentGains = target after a chunk, DirectSound.cpp:221)
 		const uint32_t nPairs = (L + 1) / 2, Lp = 2 * nPairs;
-		const uint32_t J = kScanThreads / nPairs, pStride = (kT + 1) * nPairs;
+		const uint32_t J = kMixThreads / nPairs, pStride = (kT + 1) * nPairs;
+		const uint32_t srcPerSubset = (srcPerCTA + J - 1) / J, Jused = (srcPerCTA + srcPerSubset - 1) / srcPerSubset;
 		float* sY = sScan;
-		f2* sP = reinterpret_cast<f2*>(sScan + kT * kScanThreads);
-		float* sTg = reinterpret_cast<float*>(sP + J * pStride);
-		float* sCur = sTg + kScanThreads * Lp;
-		float* sGt = sCur + kScanThreads * Lp;
+		f2* sP = reinterpret_cast<f2*>(sScan + kT * kMixSC);
+		float* sTg = reinterpret_cast<float*>(sP + Jused * pStride);
+		float* sCur = sTg + kMixSC * Lp;
+		float* sGt = sCur + kMixSC * Lp;
 
-		if (tid < numSCInCTA)
+		// launched with programmatic stream serialisation: the CTAs may be resident before k_scan_front has finished; nothing it wrote is read before this
+		asm volatile("griddepcontrol.wait;" ::: "memory");
 		{
-			const uint32_t sc = scBase + tid;
-			const float* yi = sp.xth + size_t(ti.n0) * nSC + sc;
-			#pragma unroll
-			for (uint32_t i = 0; i < kT; ++i) cp_async4(sY + i * kScanThreads + tid, yi + size_t(i) * nSC);
-			const float* gt = sp.tileGain + (size_t(t) * nSC + sc) * nG;
-			for (uint32_t c = 0; c < L; ++c)
+			// staging: thread = (source-channel, quarter): four of the tile's frames and every fourth output channel
+			const uint32_t col = tid & (kMixSC - 1u), part = tid / kMixSC;
+			if (col < numSCInCTA)
 			{
-				cp_async4(sTg + tid * Lp + c, rp.tgtMix + c * nSC + sc);
-				if (ramping) { cp_async4(sCur + tid * Lp + c, rp.curMix + c * nSC + sc); cp_async4(sGt + tid * Lp + c, gt + c); }
+				const uint32_t sc = scBase + col;
+				const float* yi = sp.xth + size_t(ti.n0) * nSC + sc;
+				#pragma unroll
+				for (uint32_t i = part; i < kT; i += kMixThreads / kMixSC) cp_async4(sY + i * kMixSC + col, yi + size_t(i) * nSC);
+				const float* gt = sp.tileGain + (size_t(t) * nSC + sc) * nG;
+				for (uint32_t c = part; c < L; c += kMixThreads / kMixSC)
+				{
+					cp_async4(sTg + col * Lp + c, rp.tgtMix + c * nSC + sc);
+					if (ramping) { cp_async4(sCur + col * Lp + c, rp.curMix + c * nSC + sc); cp_async4(sGt + col * Lp + c, gt + c); }
+				}
+				if (part == 0 && L < Lp) { sTg[col * Lp + L] = 0.0f; sCur[col * Lp + L] = 0.0f; sGt[col * Lp + L] = 0.0f; }
 			}
-			if (L < Lp) { sTg[tid * Lp + L] = 0.0f; sCur[tid * Lp + L] = 0.0f; sGt[tid * Lp + L] = 0.0f; }
 		}
 		asm volatile("cp.async.commit_group;" ::: "memory");
 		asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -711,8 +725,7 @@ namespace jplg
 		// thread = (output channel pair, source subset), kT packed frame accumulators, fixed-order cross-subset reduce (the mix role of k_render)
 		const uint32_t mixP = tid % nPairs, mixJ = tid / nPairs;
 		const uint32_t c0 = 2 * mixP, c1 = c0 + 1;
-		const bool has1 = c1 < L, mixActive = mixJ < J;
-		const uint32_t srcPerSubset = (srcPerCTA + J - 1) / J;
+		const bool has1 = c1 < L, mixActive = mixJ < Jused;
 		const uint32_t subBegin = min(mixJ * srcPerSubset * C, numSCInCTA), subEnd = min((mixJ + 1) * srcPerSubset * C, numSCInCTA);
 		if (mixActive)
 		{
@@ -728,7 +741,7 @@ namespace jplg
 				{
 					const float2 a = *reinterpret_cast<const float2*>(sCur + s * Lp + c0), gs = *reinterpret_cast<const float2*>(sGt + s * Lp + c0);
 					dg = pk((tg.x - a.x) / chunkF, (tg.y - a.y) / chunkF);       // delta = (gainEnd - gainStart) / numFrames (ChannelMixing.h:99)
-					g = pk(gs.x, gs.y);                                            // the reference's accumulated ramp at the tile start (k_scan_front P5)
+					g = pk(gs.x, gs.y);                                            // the reference's accumulated ramp at the tile start (k_scan_front P1)
 				}
 				if (DEBUG)
 				{
@@ -736,7 +749,7 @@ namespace jplg
 					float* ps = rp.perSource + (size_t(src) * F + ti.n0) * L;
 					for (uint32_t i = 0; i < kT; ++i)
 					{
-						const float y = sY[i * kScanThreads + s];
+						const float y = sY[i * kMixSC + s];
 						const f2 v = mul2(pk(y, y), g);
 						float* o = ps + size_t(i) * L;
 						o[c0] = (k == 0 ? 0.0f : o[c0]) + lo(v);
@@ -750,7 +763,7 @@ namespace jplg
 					#pragma unroll
 					for (uint32_t i = 0; i < kT; ++i)
 					{
-						const float y = sY[i * kScanThreads + s];
+						const float y = sY[i * kMixSC + s];
 						acc[i] = fma2(mul2(pk(y, y), g), one, acc[i]);     // product rounded first, as in the per-source outputs (same bus either way)
 						g = fma2(g, one, dg);
 					}
@@ -762,25 +775,49 @@ namespace jplg
 		}
 		__syncthreads();
 		MIX_STAMP(2);
+		float* pb = rp.partial + (size_t(cta) * F + ti.n0) * L;
+		if (tid < kT * Lp)
 		{
-			float* pb = rp.partial + (size_t(cta) * F + ti.n0) * L;
 			const float* sPf = reinterpret_cast<const float*>(sP);
-			for (uint32_t o = tid; o < kT * Lp; o += kScanThreads)
-			{
-				const uint32_t i = o / Lp, c = o - i * Lp;
-				const float* src = sPf + ((c >> 1) * (kT + 1) + i) * 2 + (c & 1u);
-				float sum = 0.0f;
-				for (uint32_t j = 0; j < J; ++j, src += 2 * pStride) sum += *src;
-				if (c < L) pb[i * L + c] = sum;
-			}
+			const uint32_t i = tid / Lp, c = tid - i * Lp;
+			const float* src = sPf + ((c >> 1) * (kT + 1) + i) * 2 + (c & 1u);
+			float s0 = 0.0f, s1 = 0.0f;      // two interleaved chains, combined at the end: fixed order
+			uint32_t j = 0;
+			for (; j + 1 < Jused; j += 2, src += 4 * pStride) { s0 += src[0]; s1 += src[2 * pStride]; }
+			if (j < Jused) s0 += src[0];
+			if (c < L) pb[i * L + c] = s0 + s1;
 		}
-		// ---- the last tile-CTA of this source group to get here commits current = target (every tile read the block-start values above)
+		// ---- last arrivers: of this tile (over the source groups) -> bus reduction; of this source group (over the tiles) -> current = target
 		__threadfence();
 		__syncthreads();
 		MIX_STAMP(3);
-		if (tid == 0) sLast = (atomicAdd(&sp.counters[cta], 1u) == sp.nTiles - 1u) ? 1u : 0u;
+		if (tid == 0)
+		{
+			sLast = (atomicAdd(&sp.counters[cta], 1u) == sp.nTiles - 1u) ? 1u : 0u;
+			sLastOfTile = (atomicAdd(&sp.counters[rp.numCTAs + t], 1u) == rp.numCTAs - 1u) ? 1u : 0u;
+		}
 		__syncthreads();
-		MIX_STAMP(4);
+		if (sLastOfTile)
+		{
+			__threadfence();
+			if (tid < kT * L)
+			{
+				// out[o] = sum over the source groups in ascending order (deterministic); also accumulated into the caller's bus like k_bus_reduce does
+				const size_t o = size_t(ti.n0) * L + tid;
+				float sum = 0.0f;
+				for (uint32_t x0 = 0; x0 < rp.numCTAs; x0 += 8)      // eight loads in flight, added in ascending order
+				{
+					float v[8];
+					#pragma unroll
+					for (uint32_t k = 0; k < 8; ++k) v[k] = x0 + k < rp.numCTAs ? __ldcg(rp.partial + size_t(x0 + k) * F * L + o) : 0.0f;
+					#pragma unroll
+					for (uint32_t k = 0; k < 8; ++k) if (x0 + k < rp.numCTAs) sum += v[k];
+				}
+				sp.deviceBus[o] = sum;
+				if (sp.busAcc) sp.busAcc[o] += sum;
+			}
+			if (tid == 0) sp.counters[rp.numCTAs + t] = 0u;
+		}
 		if (sLast)
 		{
 			__threadfence();
@@ -825,16 +862,17 @@ namespace jplg
 		const size_t nSC = rp.numSC;
 		sp.xth = sp.scratch;
 		sp.tileGain = sp.scratch + size_t(rp.frames) * nSC;
-		const uint32_t nPairs = (rp.L + 1) / 2, J = kScanThreads / nPairs;
+		const uint32_t nPairs = (rp.L + 1) / 2, J = kMixThreads / nPairs, srcPerCTA = kMixSC / rp.srcChannels;
+		const uint32_t srcPerSubset = (srcPerCTA + J - 1) / J, Jused = (srcPerCTA + srcPerSubset - 1) / srcPerSubset;
 		const size_t dynFront = ScanFrontSmem(rp.frames);
-		const size_t dynMix = size_t(kT) * kScanThreads * sizeof(float) + size_t(J) * (kT + 1) * nPairs * sizeof(f2) + size_t(3) * kScanThreads * 2 * nPairs * sizeof(float);
+		const size_t dynMix = size_t(kT) * kMixSC * sizeof(float) + size_t(Jused) * (kT + 1) * nPairs * sizeof(f2) + size_t(3) * kMixSC * 2 * nPairs * sizeof(float);
 		static bool attr = false;
 		if (!attr)
 		{
 			cudaFuncSetAttribute(k_scan_front, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
 			cudaFuncSetAttribute(k_scan_front_pipe, cudaFuncAttributeMaxDynamicSharedMemorySize, 201 * 1024);
-			cudaFuncSetAttribute(k_scan_mix<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
-			cudaFuncSetAttribute(k_scan_mix<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024);
+			cudaFuncSetAttribute(k_scan_mix<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
+			cudaFuncSetAttribute(k_scan_mix<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024);
 			attr = true;
 		}
 		// JPLG_SCAN_PIPE=1 (experiment switch): the warp-pipelined k_scan_front_pipe instead of the barrier-separated phases. Same results; measured
@@ -843,8 +881,17 @@ namespace jplg
 		static const bool pipe = [] { const char* e = std::getenv("JPLG_SCAN_PIPE"); return e && e[0] == '1'; }();
 		if (!pipe) k_scan_front<<<(rp.numSC + kFrontSC - 1) / kFrontSC, kScanThreads, dynFront, st>>>(sp);
 		else k_scan_front_pipe<<<(rp.numSC + kFrontSC - 1) / kFrontSC, kPipeThreads, dynFront + 256, st>>>(sp);
-		if (rp.perSource) k_scan_mix<true><<<dim3(rp.numCTAs, sp.nTiles), kScanThreads, dynMix, st>>>(sp);
-		else k_scan_mix<false><<<dim3(rp.numCTAs, sp.nTiles), kScanThreads, dynMix, st>>>(sp);
+		{
+			// programmatic dependent launch: the mix grid's launch latency overlaps the front kernel's run (both are a few microseconds on this path)
+			cudaLaunchConfig_t cfg = {};
+			cfg.gridDim = dim3(rp.numCTAs, sp.nTiles); cfg.blockDim = dim3(kMixThreads); cfg.dynamicSmemBytes = dynMix; cfg.stream = st;
+			cudaLaunchAttribute at[1];
+			at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+			at[0].val.programmaticStreamSerializationAllowed = pipe ? 0 : 1;     // (k_scan_front_pipe does not signal)
+			cfg.attrs = at; cfg.numAttrs = 1;
+			if (rp.perSource) cudaLaunchKernelEx(&cfg, k_scan_mix<true>, sp);
+			else cudaLaunchKernelEx(&cfg, k_scan_mix<false>, sp);
+		}
 		return cudaGetLastError();
 	}
 }
