@@ -430,11 +430,15 @@ namespace jplg
 		MdapLayoutParams lp = lpIn;
 		lp.paramStride = paramStride;
 		if (n == 0) return cudaSuccess;
-		const bool rows8 = fz.tgtMix == nullptr;     // plain (foreground, whole machine) launches: 8-row batches; the fused background update: 24
+		static const int rowsEnv = [] { const char* e = std::getenv("JPLG_MDAP_ROWS8"); return e ? std::atoi(e) : -1; }();
+		bool rows8 = fz.tgtMix == nullptr;     // plain (foreground, whole machine) launches: 8-row batches; the fused background update: 24
+		if (rowsEnv >= 0) rows8 = rowsEnv != 0;
 		const size_t smem = MdapSmemBytes(p, lp, rows8);
 		const uint32_t groups = JPLG_MDAP_WARPS * 32 / MdapLanesPerSource(p);
 		uint32_t grid = (n + groups - 1) / groups;
-		const uint32_t maxGrid = static_cast<uint32_t>(numSMs) * 8u; // persistent-ish: amortise the 8 KB rsqrt table load
+		// JPLG_MDAP_CTAS_PER_SM=n, JPLG_MDAP_ROWS8=0/1 (experiment switches): grid cap, batch rows of the 8-lane kernel whatever the launch kind
+		static const uint32_t capPerSM = [] { const char* e = std::getenv("JPLG_MDAP_CTAS_PER_SM"); const int v = e ? std::atoi(e) : 0; return v > 0 ? uint32_t(v) : 8u; }();
+		const uint32_t maxGrid = static_cast<uint32_t>(numSMs) * capPerSM; // persistent-ish: amortise the 8 KB rsqrt table load
 		if (grid > maxGrid) grid = maxGrid;
 		if (p.is3D)
 		{
