@@ -6,27 +6,29 @@
 // SMs. Here only the two recurrences whose ROUNDING is part of the result stay sequential, as three-operation chains; everything else is spread
 // over (source-channel, tile) threads. k_scan_front: one CTA = 4 source-channels x 32 tile slots, phases separated by __syncthreads:
 //
-//   P0  all threads: DelayLine::Push of the block (with the reference's chunk quirk, DirectSound.cpp:107-128; see k_push)
-//   P1  one thread per sc, sequential: SmoothedValue::Tick for every frame (inc/Utilities/SmoothedValue.h:73-77). The smoothed delay decides the
-//       integer / fraction split of every tap (at 40,000 samples of delay one float ulp is 0.004 samples), so it is the reference's recurrence
-//       bit for bit, not a closed form.
+//   P0  all threads: DelayLine::Push of the block (with the reference's chunk quirk, DirectSound.cpp:107-128; see k_push): loads before P1, stores after it
+//   P1  warp 0, lanes 0-3 = the four source-channels in lock step, sequential: SmoothedValue::Tick for every frame (inc/Utilities/SmoothedValue.h:73-77).
+//       The smoothed delay decides the integer / fraction split of every tap (at 40,000 samples of delay one float ulp is 0.004 samples), so it is the
+//       reference's recurrence bit for bit, not a closed form. Warps 1-3 meanwhile run the reference's gain-ramp recurrences (`gain += delta` per frame,
+//       ChannelMixing.h:99-107, CrossoverFilter.h:518-531 — a constant increment rounds the same way step after step, the accumulated ramp drifts up to
+//       480 x 0.5 ulp from start + n * delta, so the closed form is outside the bar) and leave the ramp values at the tile starts.
 //   P2  per (sc, tile), parallel: DelayTap::SetDelay -> Thiran coefficient (1 - f) / (1 + f) -> GetReadWindow<2> (DelayLine.h:53-59,199-213;
-//       FractionalDelay.h:105-110): a[n], x[n], x[n-1]
-//   P3  one thread per sc, sequential: y[n] = a[n] (x[n] - y[n-1]) + x[n-1] (FractionalDelay.h:117-124), bit for bit: for a static source on an
+//       FractionalDelay.h:105-110): { a[n], x[n], x[n-1] } as one float4 per sample
+//   P3  lanes 0-3 of warp 0, sequential: y[n] = a[n] (x[n] - y[n-1]) + x[n-1] (FractionalDelay.h:117-124), bit for bit: for a static source on an
 //       exactly-integer delay a = 1, the all-pass has its pole ON the unit circle and a differently-rounded state never decays —
 //       an affine scan of this stage (y_end = P y_start + Q per tile) drifted past the bar within 20 blocks (r02 measurement).
 //   P4  per (sc, tile), parallel: the FourBandCrossover (CrossoverFilter.h:505-535) on the tile's delayed samples from ZERO state: the zero-state
 //       end state e (24 floats)
 //   P5  one warp per sc: the 24-state scan over the tiles, s[t+1] = M s[t] + e[t], with M = the crossover's zero-input transition over
-//       kScanTile frames (fixed per sample rate, built on the host in double: CrossoverTransition); leaves every tile's true START state. Its
-//       lanes also run the reference's gain-ramp recurrences (`gain += delta` per frame, ChannelMixing.h:99-107, CrossoverFilter.h:518-531 — a
-//       constant increment rounds the same way step after step, the accumulated ramp drifts up to 480 x 0.5 ulp from start + n * delta, so the
-//       closed form is outside the bar) and leave the ramp values at the tile starts.
+//       kScanTile frames (fixed per sample rate, built on the host in double: CrossoverTransition); leaves every tile's true START state
 //   P6  per (sc, tile), parallel: re-runs the tile's crossover from its start state with the ramped band gains -> Y [frame][sc]
 //
-// k_scan_mix: per (128 sc, tile) CTA, the gain-ramped mix of the CTA's source-channels into a partial bus (thread mapping of k_render's mix role);
-// the last tile-CTA of a source group to finish commits mCurrentGains = targets (DirectSound.cpp:221).
+// k_scan_mix: per (128 sc, tile) CTA, the gain-ramped mix of the CTA's source-channels into a partial bus (thread mapping of k_render's mix role); the
+// last CTA of a tile to finish reduces the tile's partial buses over the source groups in a fixed order (no k_bus_reduce launch on this path), the last
+// tile-CTA of a source group commits mCurrentGains = targets (DirectSound.cpp:221). Launched as a programmatic dependent of k_scan_front.
 //
+// With one or two warps per scheduler every instruction costs its full latency, so these kernels are as long as their longest per-thread instruction
+// sequence: the design rule behind the float4 taps, the lock-step recurrence lanes and the ramps in warps of their own (profiles/r02v_scan_pipe_timeline.txt).
 // The crossover is stable (its state errors decay), so the scan's re-association there stays at rounding level. Twice the filter arithmetic of
 // the sequential kernel (zero-state pass + final pass) plus the 24 x 24 scan: it only pays while the machine is under-filled; the launcher's
 // caller (jplg_api.cu) selects it by size. Bar: 1e-5 * max(|ref|, rms, 1e-3) per sample against oracle/_ref, tests/test_gpu_scan.py.
@@ -57,7 +59,7 @@ namespace jplg
 		}
 	}
 
-	// dynamic shared memory (floats): dly | a (P3 leaves the delayed samples here) | x | x1, each [4][nTiles * 17 + 8]; e [4][nTiles][25] + 32
+	// dynamic shared memory: float4 taps [4][nTiles * 17 + 2] | e [4][nTiles][25] + 32 floats | a 32-float staging row per scan warp
 #ifdef JPLG_PROF
 	__device__ unsigned long long g_frontProf[16];
 	#define FRONT_STAMP(i) do { if (blockIdx.x == 0 && threadIdx.x == 0) g_frontProf[i] = clock64(); } while (0)
