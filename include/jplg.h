@@ -370,6 +370,16 @@ JPLG_API jplg_status jplg_reverb_bank_decay_gains(jplg_reverb_bank b, float* out
  * the reference (DownmixToMono + ApplyGain(1 / in_channels), :80-92) for blocks of at most 480 frames — beyond one chunk the reference over-runs its scratch
  * array (:83), so longer multichannel blocks are refused. out [n][frames][output_channels] interleaved, ACCUMULATED INTO like the reference's `output` span. */
 JPLG_API jplg_status jplg_reverb_bank_process(jplg_reverb_bank b, const float* in, uint32_t in_channels, float* out, uint32_t frames, int32_t mem);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it). jplg_reverb_bank_process with DEVICE pointers only (`in`, `out` as above, JPLG_MEM_DEVICE implied) that
+ * allocates nothing: the mono down-mix of a multichannel input goes to a file-scope device array of JPLG_REVERB_NO_ALLOC_MAX_FLOATS floats (960 KiB, held
+ * by every GPU that loads the library until the process exits) instead of the context's growable scratch. instances * frames beyond that size is refused
+ * with JPLG_ERR_INVALID_ARGUMENT (jplg_last_error says so); mono input does not use the scratch and has no such limit. Same kernels and results as
+ * jplg_reverb_bank_process. The array is shared by every bank and context on a device and keeps the last call's contents (nothing in it needs clearing:
+ * the down-mix overwrites every element the FDN kernel reads); calls that overlap on the GPU (different contexts' streams) race on it. The first call on
+ * a device looks the array's address up (cudaGetSymbolAddress): make it once outside a graph capture. */
+#define JPLG_REVERB_NO_ALLOC_MAX_FLOATS 245760u
+JPLG_API jplg_status jplg_reverb_bank_process_no_alloc(jplg_reverb_bank b, const float* in, uint32_t in_channels, float* out, uint32_t frames);
 
 /* ---------------------------------------------------------------------------------------------- */
 /* ERBus x B  (replaces: inc/Auralization/EarlyReflectionsBus.h:45-249,                              */

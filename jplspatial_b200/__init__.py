@@ -20,7 +20,7 @@ from ._capi import (  # noqa: F401
     EChannel, ChannelMask, ChannelMap,
     Context, VBAPanner, SourceLayout, DirectSoundBatch, CrossoverBank, DelayBank, ReverbBusBatch, ERBusBatch,
     add_and_apply_gain_ramp, apply_gain, add, downmix_to_mono, normalize_weights, get_spread_from_source_size,
-    STATE_FLOATS,
+    STATE_FLOATS, REVERB_NO_ALLOC_MAX_FLOATS,
     BusExchange, DirectPathBatch, AirAbsorptionCache, default_band_centers, speed_of_sound_for_temperature, sanitize_fallback_dir,
     MODEL_NONE, MODEL_INVERSE, MODEL_LINEAR, MODEL_EXPONENTIAL,
     CURVE_CONSTANT, CURVE_LINEAR, CURVE_SINE_FADE_IN, CURVE_SINE_FADE_OUT, CURVE_SCURVE, CURVE_LOG_1_41, CURVE_LOG_3, CURVE_EXP_1_41, CURVE_EXP_3,

@@ -559,6 +559,8 @@ _sig("jplg_reverb_bank_set_rt60", _i32, [_vp, _fp, _i32])
 _sig("jplg_reverb_bank_set_decay_slope", _i32, [_vp, _fp, _i32])
 _sig("jplg_reverb_bank_decay_gains", _i32, [_vp, _fp])
 _sig("jplg_reverb_bank_process", _i32, [_vp, _fp, _u32, _fp, _u32, _i32])
+_sig("jplg_reverb_bank_process_no_alloc", _i32, [_vp, _fp, _u32, _fp, _u32])
+REVERB_NO_ALLOC_MAX_FLOATS = 245760   # JPLG_REVERB_NO_ALLOC_MAX_FLOATS (include/jplg.h)
 
 
 class ReverbBusBatch:
@@ -594,6 +596,11 @@ class ReverbBusBatch:
             o, mem_o = out.ctypes.data, MEM_HOST
         assert mem_a == mem_o, "input and output must live in the same memory space"
         self.ctx.check(lib.jplg_reverb_bank_process(self.h, a, int(in_channels), o, int(frames), mem_a))
+
+    def ProcessInterleavedNoAlloc(self, inp, out, frames, in_channels=1):
+        """jplg_reverb_bank_process_no_alloc: device tensors only, no allocation on the call (the down-mix scratch is a static device array)"""
+        assert _is_torch(inp) and _is_torch(out) and inp.is_cuda and out.is_cuda and inp.is_contiguous() and out.is_contiguous()
+        self.ctx.check(lib.jplg_reverb_bank_process_no_alloc(self.h, inp.data_ptr(), int(in_channels), out.data_ptr(), int(frames)))
 
     def __del__(self):
         try:

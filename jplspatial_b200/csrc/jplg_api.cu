@@ -1683,6 +1683,42 @@ jplg_status jplg_reverb_bank_process(jplg_reverb_bank b, const float* in, uint32
 	return JPLG_OK;
 }
 
+// jplg_reverb_bank_process for callers that must not allocate (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc): DEVICE pointers
+// only, and the mono down-mix of a multichannel input goes to a file-scope device array (jplg_reverb_kernels.cu) instead of the context's growable
+// scratch. No cudaMalloc / cudaFree / allocating routine on this path; n * frames beyond the array's size is refused. Same kernels, same order, same results.
+jplg_status jplg_reverb_bank_process_no_alloc(jplg_reverb_bank b, const float* in, uint32_t in_channels, float* out, uint32_t frames)
+{
+	if (!b || (frames && (!in || !out))) return JPLG_ERR_INVALID_ARGUMENT;
+	jplg_context ctx = b->ctx;
+	JPLG_NEED_DEVICE(ctx);
+	if (frames == 0) return JPLG_OK;
+	if (in_channels == 0) return JPLG_ERR_INVALID_ARGUMENT;
+	if (in_channels != 1 && frames > kChunkFrames) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "jplg_reverb_bank_process_no_alloc: multichannel input is supported for blocks of at most "
+		"480 frames (beyond that the reference's down-mix over-runs its scratch array, LateReverb.cpp:83)");
+	if (frames > b->maxFrames) return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "jplg_reverb_bank_process_no_alloc: frames exceeds max_block_frames");
+	const size_t nIn = size_t(b->n) * frames;
+	if (in_channels != 1 && nIn > kReverbNoAllocMaxFloats)
+		return Fail(ctx, JPLG_ERR_INVALID_ARGUMENT, "jplg_reverb_bank_process_no_alloc: instances * frames = " + std::to_string(nIn) + " exceeds the static scratch of "
+			+ std::to_string(kReverbNoAllocMaxFloats) + " floats (JPLG_REVERB_NO_ALLOC_MAX_FLOATS); use jplg_reverb_bank_process or a smaller bank / block");
+	std::lock_guard<std::mutex> lk(ctx->mtx);
+	cudaSetDevice(ctx->device);
+	const float* dIn = in;
+	if (in_channels != 1)
+	{
+		float* mono = nullptr;
+		JPLG_CUDA_TRY(ctx, ReverbNoAllocScratch(ctx->device, &mono));
+		JPLG_LAUNCH(ctx, JPLG_K_OTHER, LaunchReverbDownmix(in, b->n, frames, in_channels, mono, ctx->stream));
+		dIn = mono;
+	}
+	jplg_status st = ReverbRefreshDecay(b); if (st) return st;
+	FdnParams fp{}; fp.n = b->n; fp.L = b->L; fp.frames = frames; fp.pos = b->pos; std::memcpy(fp.coef, b->coef, sizeof(fp.coef));
+	fp.hadamardScale = FdnHadamardScale();
+	fp.state = b->state; fp.decay = b->decay; fp.rings = b->rings; fp.in = dIn; fp.out = out;
+	JPLG_LAUNCH(ctx, JPLG_K_FDN, LaunchFdn(fp, b->mode, ctx->stream));
+	b->pos += frames;
+	return JPLG_OK;
+}
+
 //==================================================================================================
 // ERBus bank (EarlyReflectionsBus.h:45-249, EarlyReflectionsBus.cpp:83-417): B buses x up to T taps, every tap = smoothed fractional
 // delay + four-band filter + gain-ramped pan reading the bus' ONE mono ring. The taps run through k_render (scPerRing = T,

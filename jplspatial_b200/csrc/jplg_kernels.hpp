@@ -162,6 +162,10 @@ namespace jplg
 	cudaError_t LaunchFdnDecay(const float* slope, uint32_t n, float invSampleRate, float* decay, int mode, cudaStream_t st);
 	cudaError_t LaunchFdn(const FdnParams& fp, int mode, cudaStream_t st);
 	cudaError_t LaunchReverbDownmix(const float* in, uint32_t n, uint32_t frames, uint32_t numIn, float* mono, cudaStream_t st);   // [n][frames][numIn] -> [n][frames]
+	// jplg_reverb_bank_process_no_alloc: device address of the file-scope mono down-mix scratch (jplg_reverb_kernels.cu), resolved once per device
+	// with cudaGetSymbolAddress; `device` must be current. kReverbNoAllocMaxFloats = JPLG_REVERB_NO_ALLOC_MAX_FLOATS (include/jplg.h).
+	constexpr size_t kReverbNoAllocMaxFloats = 245760;
+	cudaError_t ReverbNoAllocScratch(int device, float** out);
 	//======================================================================
 	// Scene front-end (jplg_frontend_kernels.cu): the per-source body of SpatialManager::AdvanceSimulation
 	// (inc/SpatialManager.h:374-420) plus the parameter producers that sit between it and stages 1-3.

@@ -14,6 +14,7 @@
 #include "jplg_kernels.hpp"
 #include "jplg_render_common.cuh"   // mad, svf, packed FP32x2 helpers
 #include <cstring>
+#include <mutex>
 
 namespace jplg
 {
@@ -310,6 +311,35 @@ namespace jplg
 		if (total == 0) return cudaSuccess;
 		k_reverb_downmix<<<static_cast<uint32_t>((total + 255) / 256), 256, 0, st>>>(in, total, numIn, 1.0f / static_cast<float>(numIn), mono);
 		return cudaGetLastError();
+	}
+
+	//======================================================================
+	// Scratch of jplg_reverb_bank_process_no_alloc (include/jplg.h): the mono down-mix of a multichannel reverb input, [n][frames], in a file-scope device
+	// array instead of the context's cudaMalloc'ed scratch. 245,760 floats = 960 KiB, held by every GPU that loads the library until the process exits.
+	// k_reverb_downmix overwrites every element k_fdn later reads, so nothing in it has to start at zero; all calls share it (calls that overlap on
+	// the GPU race). In HOST code the array's name is a host-side stand-in, not a device address: the device address comes from cudaGetSymbolAddress,
+	// looked up once per device with that device current.
+	static __device__ __align__(256) float g_reverbNoAllocMono[kReverbNoAllocMaxFloats];
+
+	cudaError_t ReverbNoAllocScratch(int device, float** out)
+	{
+		constexpr int kMaxDevices = 64;
+		static std::mutex mtx;
+		static float* addr[kMaxDevices] = {};
+		*out = nullptr;
+		if (device < 0 || device >= kMaxDevices) return cudaErrorInvalidDevice;
+		std::lock_guard<std::mutex> lk(mtx);
+		if (!addr[device])
+		{
+			int current = -1;
+			cudaError_t e = cudaGetDevice(&current); if (e != cudaSuccess) return e;
+			if (current != device) return cudaErrorInvalidDevice;      // the caller makes the context's device current first
+			void* p = nullptr;
+			e = cudaGetSymbolAddress(&p, g_reverbNoAllocMono); if (e != cudaSuccess) return e;
+			addr[device] = static_cast<float*>(p);
+		}
+		*out = addr[device];
+		return cudaSuccess;
 	}
 
 	cudaError_t LaunchFdnDecay(const float* slope, uint32_t n, float invSampleRate, float* decay, int mode, cudaStream_t st)
