@@ -252,7 +252,10 @@ namespace jplg
 		}
 		__syncthreads();
 		FRONT_STAMP(4);
-		// ---- P5: warp w = source-channel w: the scan over the tiles; lane r < 24 owns row r of M and state r
+		// ---- P5: warp w = source-channel w: the scan over the tiles, s[t+1] = M s[t] + e[t]; lane r < 24 owns row r of M and state r (lanes 24-31 shadow
+		// row 23: same addresses, same values, no divergence). The state vector goes through a 16-byte aligned staging row: 6 broadcast LDS.128 per step
+		// instead of 24 shuffles. (Tried: the scan blocked in groups of four tiles with M^4 — 3 + nT/4 + 3 dependent steps instead of nT, but three times
+		// the products in the same single warp: 1,024 sources 0.0421 -> 0.0468 ms per block, profiles/r02zz_scan_width_ab.txt.)
 		{
 			const uint32_t w = tid >> 5, lane = tid & 31u, s5 = scBase + w;
 			if (s5 < rp.numSC)
@@ -263,26 +266,31 @@ namespace jplg
 				for (int k = 0; k < 24; ++k) m[k] = sp.M[r * 24 + k];
 				float s = rp.state[(ST_FILTER + r) * nSC + s5];
 				float* e = sE + w * nT * 25 + 8 * w + r;
-				// the state vector goes through a 16-byte aligned staging row: 6 broadcast LDS.128 per step instead of 24 shuffles (one warp-shuffle per
-				// cycle and SM is the ceiling of the shuffle form: 8 resident scan warps x 24 = 192 cycles per step)
-				float4* stage = reinterpret_cast<float4*>(sE + kFrontSC * nT * 25 + 32 + 32 * w);
-				for (uint32_t t = 0; t < nT; ++t)
+				float* stage = sE + kFrontSC * nT * 25 + 32 + 32 * w;
+				auto matvec = [](const float (&mm)[24], const float* row, float add)
 				{
-					const float et = e[t * 25];
-					if (lane < 24) { e[t * 25] = s; reinterpret_cast<float*>(stage)[lane] = s; }   // the tile's start state replaces its zero-state response in place
-					__syncwarp();
-					float a0 = et, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
+					const float4* v4 = reinterpret_cast<const float4*>(row);
+					float a0 = add, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
 					#pragma unroll
 					for (int k = 0; k < 6; ++k)
 					{
-						const float4 v = stage[k];
-						a0 = __fmaf_rn(m[4 * k], v.x, a0);
-						a1 = __fmaf_rn(m[4 * k + 1], v.y, a1);
-						a2 = __fmaf_rn(m[4 * k + 2], v.z, a2);
-						a3 = __fmaf_rn(m[4 * k + 3], v.w, a3);
+						const float4 v = v4[k];
+						a0 = __fmaf_rn(mm[4 * k], v.x, a0);
+						a1 = __fmaf_rn(mm[4 * k + 1], v.y, a1);
+						a2 = __fmaf_rn(mm[4 * k + 2], v.z, a2);
+						a3 = __fmaf_rn(mm[4 * k + 3], v.w, a3);
 					}
-					s = (a0 + a1) + (a2 + a3);
-					__syncwarp();      // every lane has read the staging row before the next step overwrites it
+					return (a0 + a1) + (a2 + a3);
+				};
+				{
+					for (uint32_t t = 0; t < nT; ++t)
+					{
+						const float et = e[t * 25];
+						e[t * 25] = s; stage[lane] = s;           // the tile's start state replaces its zero-state response in place
+						__syncwarp();
+						s = matvec(m, stage, et);
+						__syncwarp();      // every lane has read the staging row before the next step overwrites it
+					}
 				}
 				if (lane < 24) rp.state[(ST_FILTER + lane) * nSC + s5] = s;
 			}
@@ -290,11 +298,20 @@ namespace jplg
 		__syncthreads();
 		FRONT_STAMP(5);
 		// ---- P6: every tile again from its true start state, with the ramped band gains (CrossoverFilter.h:505-535) -> Y [frame][sc]
+		float tgB[4] = { 0.0f, 0.0f, 0.0f, 0.0f }, curB[4] = { 0.0f, 0.0f, 0.0f, 0.0f };
 		if (scValid)
 		{
-			float tgB[4], curB[4];
 			#pragma unroll
 			for (int b = 0; b < 4; ++b) { tgB[b] = rp.tgtBand[b * nSC + sc]; curB[b] = rp.state[(ST_BAND + b) * nSC + sc]; }
+		}
+		__syncthreads();      // every thread has read the block-start band gains: slot 0 commits mFilterGains = target now (DirectSound.cpp:225), under the pass
+		if (scValid)
+		{
+			if (slot == 0)
+			{
+				#pragma unroll
+				for (int b = 0; b < 4; ++b) rp.state[(ST_BAND + b) * nSC + sc] = tgB[b];
+			}
 			for (uint32_t t = slot; t < nT; t += kFrontSlots)
 			{
 				const ScanTile ti = scan_tile(t, F);
@@ -326,13 +343,7 @@ namespace jplg
 				}
 			}
 		}
-		__syncthreads();
-		FRONT_STAMP(6);       // every tile has read the block-start band gains
-		if (tid < kFrontSC && scBase + tid < rp.numSC)
-		{
-			#pragma unroll
-			for (int b = 0; b < 4; ++b) rp.state[(ST_BAND + b) * nSC + scBase + tid] = rp.tgtBand[b * nSC + scBase + tid];
-		}
+		FRONT_STAMP(6);
 			FRONT_STAMP(15);
 	}
 
@@ -650,6 +661,10 @@ namespace jplg
 	extern "C" __attribute__((visibility("default"))) void jplg_debug_scan_cta(unsigned long long* out) { cudaMemcpyFromSymbol(out, g_scanCta, sizeof(g_scanCta)); }
 #endif
 
+	__device__ __forceinline__ void cp_async16(float* dstShared, const float* src)
+	{
+		asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(static_cast<uint32_t>(__cvta_generic_to_shared(dstShared))), "l"(src) : "memory");
+	}
 	__device__ __forceinline__ void cp_async4(float* dstShared, const float* src)
 	{
 		asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(static_cast<uint32_t>(__cvta_generic_to_shared(dstShared))), "l"(src) : "memory");
@@ -698,25 +713,40 @@ namespace jplg
 		float* sCur = sTg + kMixSC * Lp;
 		float* sGt = sCur + kMixSC * Lp;
 
-		// launched with programmatic stream serialisation: the CTAs may be resident before k_scan_front has finished; nothing it wrote is read before this
-		asm volatile("griddepcontrol.wait;" ::: "memory");
+		// Launched with programmatic stream serialisation: the CTAs are resident while k_scan_front still runs. What that kernel does not write (the
+		// target and block-start gains) is staged before griddepcontrol.wait, under its run time; its outputs (Y, the ramp values at the tile start) after.
+		const uint32_t col = tid & (kMixSC - 1u), part = tid / kMixSC;     // staging: thread = (source-channel, half): every second output channel
+		if (col < numSCInCTA)
 		{
-			// staging: thread = (source-channel, quarter): four of the tile's frames and every fourth output channel
-			const uint32_t col = tid & (kMixSC - 1u), part = tid / kMixSC;
-			if (col < numSCInCTA)
+			const uint32_t sc = scBase + col;
+			for (uint32_t c = part; c < L; c += kMixThreads / kMixSC)
 			{
-				const uint32_t sc = scBase + col;
-				const float* yi = sp.xth + size_t(ti.n0) * nSC + sc;
-				#pragma unroll
-				for (uint32_t i = part; i < kT; i += kMixThreads / kMixSC) cp_async4(sY + i * kMixSC + col, yi + size_t(i) * nSC);
-				const float* gt = sp.tileGain + (size_t(t) * nSC + sc) * nG;
-				for (uint32_t c = part; c < L; c += kMixThreads / kMixSC)
-				{
-					cp_async4(sTg + col * Lp + c, rp.tgtMix + c * nSC + sc);
-					if (ramping) { cp_async4(sCur + col * Lp + c, rp.curMix + c * nSC + sc); cp_async4(sGt + col * Lp + c, gt + c); }
-				}
-				if (part == 0 && L < Lp) { sTg[col * Lp + L] = 0.0f; sCur[col * Lp + L] = 0.0f; sGt[col * Lp + L] = 0.0f; }
+				cp_async4(sTg + col * Lp + c, rp.tgtMix + c * nSC + sc);
+				if (ramping) cp_async4(sCur + col * Lp + c, rp.curMix + c * nSC + sc);
 			}
+			if (part == 0 && L < Lp) { sTg[col * Lp + L] = 0.0f; sCur[col * Lp + L] = 0.0f; sGt[col * Lp + L] = 0.0f; }
+		}
+		asm volatile("cp.async.commit_group;" ::: "memory");
+		asm volatile("griddepcontrol.wait;" ::: "memory");
+		if (((nSC | scBase) & 3u) == 0)
+		{
+			// Y tile: rows of up to 128 consecutive source-channels, 16 bytes per copy (a last quad may reach past a ragged group: still inside Y, columns unused)
+			for (uint32_t e = tid; e < kT * (kMixSC / 4); e += kMixThreads)
+			{
+				const uint32_t i = e / (kMixSC / 4), c4 = (e - i * (kMixSC / 4)) * 4;
+				if (c4 < numSCInCTA) cp_async16(sY + i * kMixSC + c4, sp.xth + size_t(ti.n0 + i) * nSC + scBase + c4);
+			}
+		}
+		else if (col < numSCInCTA)
+		{
+			const float* yi = sp.xth + size_t(ti.n0) * nSC + scBase + col;
+			#pragma unroll
+			for (uint32_t i = part; i < kT; i += kMixThreads / kMixSC) cp_async4(sY + i * kMixSC + col, yi + size_t(i) * nSC);
+		}
+		if (ramping && col < numSCInCTA)
+		{
+			const float* gt = sp.tileGain + (size_t(t) * nSC + scBase + col) * nG;
+			for (uint32_t c = part; c < L; c += kMixThreads / kMixSC) cp_async4(sGt + col * Lp + c, gt + c);
 		}
 		asm volatile("cp.async.commit_group;" ::: "memory");
 		asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -826,7 +856,14 @@ namespace jplg
 			if (tid < numSCInCTA)
 			{
 				const uint32_t sc = scBase + tid;
-				for (uint32_t c = 0; c < L; ++c) rp.curMix[c * nSC + sc] = rp.tgtMix[c * nSC + sc];
+				for (uint32_t cb = 0; cb < L; cb += 8)          // eight loads in flight before the first store (the two arrays may alias as far as the compiler knows)
+				{
+					float v[8];
+					#pragma unroll
+					for (uint32_t k = 0; k < 8; ++k) v[k] = cb + k < L ? __ldcg(rp.tgtMix + (cb + k) * nSC + sc) : 0.0f;
+					#pragma unroll
+					for (uint32_t k = 0; k < 8; ++k) if (cb + k < L) rp.curMix[(cb + k) * nSC + sc] = v[k];
+				}
 			}
 			if (tid == 0) sp.counters[cta] = 0u;
 		}
