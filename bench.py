@@ -1141,7 +1141,12 @@ def run_config5(args):
     sampler = ClockSampler(env.local); sampler.start()
     x = util.white_noise((4, N, FRAMES), 5 + env.rank) * np.float32(0.5)
     rt = (0.3 + 2.7 * util.uniform01(N * 4, 6)).reshape(N, 4).astype(np.float32)
-    rev = J.ReverbBusBatch(ctx, N, FS, L, mode=env.mode); rev.SetRT60(rt)
+    # The reverb bank and the ER bank are independent components (ReverbBus / ERBus objects of the reference's bus graph): each gets a context (stream) of
+    # its own, so the FDN kernel fills the SMs the ER render's last, partly filled wave leaves idle (--c5-serial: both on one stream, the earlier order).
+    overlap = not args.c5_serial
+    ctx2 = J.Context(env.local) if overlap else ctx
+    stream2 = ctx2.torch_stream()
+    rev = J.ReverbBusBatch(ctx2, N, FS, L, mode=env.mode); rev.SetRT60(rt)
     er = J.ERBusBatch(ctx, N, TAPS, FS, L, mode=env.mode)
     u = util.uniform01(N * TAPS * (6 + L), 7).reshape(N, TAPS, 6 + L)
     for i in range(N):
@@ -1159,26 +1164,33 @@ def run_config5(args):
         er.ProcessInterleaved(d_x[k % 4].reshape(N, FRAMES, 1), d_er, FRAMES)
     for _ in range(args.warmup):
         step()
-    ctx.synchronize()
+    ctx.synchronize(); ctx2.synchronize()
     if env.dist is not None:
         env.dist.barrier()
-    l0 = ctx.launch_count
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with torch.cuda.stream(stream):
-        e0.record(stream)
+    l0 = ctx.launch_count + (ctx2.launch_count if overlap else 0)
+    e0, e1, ej = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True), torch.cuda.Event()
+    e0.record(stream)
+    if overlap:
+        stream2.wait_event(e0)          # the reverb stream starts inside the timed region ...
     for _ in range(args.steps):
         step()
-    with torch.cuda.stream(stream):
-        e1.record(stream)
+    if overlap:
+        ej.record(stream2); stream.wait_event(ej)      # ... and is joined before the stop event
+    e1.record(stream)
     torch.cuda.synchronize()
     ms = env.max_over_ranks(e0.elapsed_time(e1)) / args.steps
-    launches = ctx.launch_count - l0
+    launches = ctx.launch_count + (ctx2.launch_count if overlap else 0) - l0
     clocks = sampler.stop()
     if env.rank == 0:
         line = _simple_line(args, env, "real-time reverb instances @48kHz/512-frame->7.1.4 (FDN16 + 16-tap ER bus)", "instances", N * env.world * BLOCK_S / (ms * 1e-3), ms,
                             "BASELINE config 5: 4,096 x (16th-order FDN late reverb + early-reflection bus with 16 taps) per GPU, mono in -> 7.1.4, 48 kHz / 512 frames",
-                            {"instances_per_gpu": N, "parallelism": "independent instances, no exchange" if env.world > 1 else "single GPU"}, launches, clocks)
+                            {"instances_per_gpu": N, "parallelism": "independent instances, no exchange" if env.world > 1 else "single GPU",
+                             "streams": "reverb bank and ER bank on one context each, overlapped (every step runs both once; the reverb stream is joined before the stop event)"
+                             if overlap else "one stream"}, launches, clocks)
         _emit(line)
+    del rev
+    if overlap:
+        ctx2.close()
     ctx.close()
     env.finish()
 
@@ -1206,6 +1218,7 @@ def main():
     ap.add_argument("--no-capacity", action="store_true", help="skip the capacity pass (value then falls back to the linear figure at --sources)")
     ap.add_argument("--no-offline", action="store_true", help="skip the comparison pass with the packed schedule")
     ap.add_argument("--no-push-ahead", action="store_true", help="packed schedule without jplg_renderer_push_ahead (diagnostic)")
+    ap.add_argument("--c5-serial", action="store_true", help="config 5: reverb bank and ER bank on one stream (default: one context each, overlapped)")
     ap.add_argument("--no-pan-overlap", action="store_true",
                     help="compute the panning data on the rendering context's stream instead of a background context (jplg_context_create_ex) "
                          "that works one block ahead on the SMs the render leaves free")
