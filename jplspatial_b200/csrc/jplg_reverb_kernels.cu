@@ -8,6 +8,8 @@
 //                 Every FDN delay (1609..4259 samples) is longer than a block, so inside a block the only time recurrences are the 16
 //                 per-channel crossover filters; delayed samples are staged from the rings, and the new ring samples / output frames are
 //                 staged back, through shared memory with coalesced global accesses.
+//                 The stage-in is double-buffered (cp.async: tile k+1 arrives while tile k runs); the crossover runs its ten SVFs after X2 as five
+//                 packed FP32x2 filters (xover_process_sample2).
 //
 // Arithmetic modes as in jplg_render_kernels.cu: PARITY = every reference FMA as mul + add (the SSE2 baseline semantic), THROUGHPUT = fused.
 // Compile with -fmad=false.
@@ -138,6 +140,10 @@ namespace jplg
 		}
 	}
 
+	__device__ __forceinline__ void cp_async4_fdn(float* dstShared, const float* src)
+	{
+		asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" :: "r"(static_cast<uint32_t>(__cvta_generic_to_shared(dstShared))), "l"(src) : "memory");
+	}
 	constexpr uint32_t kFdnTile = 32;        // frames per shared-memory tile
 	constexpr uint32_t kFdnInstPerCTA = 8;   // 8 instances x 16 channels = 128 threads
 	constexpr uint32_t kFdnRow = kFdnTile + 1;
@@ -148,9 +154,18 @@ namespace jplg
 	__global__ void __launch_bounds__(kFdnInstPerCTA * 16)
 	k_fdn(const FdnParams fp, const PackedConsts K)
 	{
-		__shared__ float sDel[kFdnInstPerCTA * 16][kFdnRow];   // one row per (instance, channel): the tile's delayed samples, overwritten in place by the samples to push
-		__shared__ float sIn[kFdnInstPerCTA][kFdnTile];
+#ifdef JPLG_FDN_NO_PREFETCH
+		__shared__ float sDelA[1][kFdnInstPerCTA * 16][kFdnRow];
+		__shared__ float sInA[1][kFdnInstPerCTA][kFdnTile];
 		__shared__ float sOut[kFdnInstPerCTA][kFdnTile][16];   // FDN output mix per frame (first L used)
+#else
+		// two stage-in buffers: tile k+1's delayed samples and inputs are fetched (cp.async) while tile k is computed and staged out. Every FDN delay (>= 1,609
+		// samples) exceeds the longest block (1,024 frames), so a block never reads a sample it pushes itself: the prefetch cannot overtake a push.
+		extern __shared__ __align__(16) float sFdn[];
+		float (*sDelA)[kFdnInstPerCTA * 16][kFdnRow] = reinterpret_cast<float (*)[kFdnInstPerCTA * 16][kFdnRow]>(sFdn);
+		float (*sInA)[kFdnInstPerCTA][kFdnTile] = reinterpret_cast<float (*)[kFdnInstPerCTA][kFdnTile]>(sFdn + 2 * kFdnInstPerCTA * 16 * kFdnRow);
+		float (*sOut)[kFdnTile][16] = reinterpret_cast<float (*)[kFdnTile][16]>(sFdn + 2 * kFdnInstPerCTA * 16 * kFdnRow + 2 * kFdnInstPerCTA * kFdnTile);
+#endif
 
 		const uint32_t tid = threadIdx.x, lane = tid & 31u, warp = tid >> 5;
 		const uint32_t c = tid & 15u;                          // FDN channel
@@ -173,9 +188,37 @@ namespace jplg
 		const f2 gA = pk(g[0], g[2]), gB = pk(g[1], g[3]);
 #endif
 		const uint32_t oFrame0 = tid / L, oChan0 = tid - oFrame0 * L, oStepFrame = (kFdnInstPerCTA * 16) / L, oStepChan = (kFdnInstPerCTA * 16) - oStepFrame * L;
-		for (uint32_t t0 = 0; t0 < fp.frames; t0 += kFdnTile)
+#ifndef JPLG_FDN_NO_PREFETCH
+		// ---- stage in (asynchronous): warp w fetches rows [32w, 32w+32): delayed[c][n] = pushed[n - 1 - D_c] (GetReadWindow<1>(D) before this frame's push),
+		// 32 + 2 copies of 4 bytes per thread in flight; rows / frames outside the bank or the block are zero-filled with plain stores
+		auto prefetch = [&](uint32_t t0n, uint32_t buf)
+		{
+			const uint32_t lenN = min(kFdnTile, fp.frames - t0n);
+			#pragma unroll 8
+			for (uint32_t r = 0; r < 32; ++r)
+			{
+				const uint32_t row = warp * 32 + r, rInst = instBase + (row >> 4), rc = row & 15u;
+				float* d = &sDelA[buf][row][lane];
+				if (rInst < fp.n && lane < lenN)
+					cp_async4_fdn(d, fp.rings + (size_t(rInst) * 16u + rc) * kFdnRingSize + ((pos32 + t0n + lane - 1u - cFdnDelays[rc]) & ringMask));
+				else *d = 0.0f;
+			}
+			for (uint32_t e = tid; e < kFdnInstPerCTA * kFdnTile; e += blockDim.x)
+			{
+				const uint32_t i = e / kFdnTile, f = e - i * kFdnTile;
+				if (instBase + i < fp.n && f < lenN) cp_async4_fdn(&sInA[buf][i][f], fp.in + size_t(instBase + i) * fp.frames + t0n + f);
+			}
+			asm volatile("cp.async.commit_group;" ::: "memory");
+		};
+		if (fp.frames) prefetch(0, 0);
+#endif
+		uint32_t tileIdx = 0;
+		for (uint32_t t0 = 0; t0 < fp.frames; t0 += kFdnTile, ++tileIdx)
 		{
 			const uint32_t len = min(kFdnTile, fp.frames - t0);
+#ifdef JPLG_FDN_NO_PREFETCH
+			float (*sDel)[kFdnRow] = sDelA[0];
+			float (*sIn)[kFdnTile] = sInA[0];
 			// ---- stage in: warp w loads rows [32w, 32w+32): delayed[c][n] = pushed[n - 1 - D_c] (GetReadWindow<1>(D) before this frame's push).
 			// Eight independent loads are issued before the first dependent shared-memory store (DRAM latency is paid once per batch).
 			for (uint32_t r0 = 0; r0 < 32; r0 += 8)
@@ -198,6 +241,13 @@ namespace jplg
 				if (instBase + i < fp.n && f < len) sIn[i][f] = fp.in[size_t(instBase + i) * fp.frames + t0 + f];
 			}
 			__syncthreads();
+#else
+			float (*sDel)[kFdnRow] = sDelA[tileIdx & 1u];
+			float (*sIn)[kFdnTile] = sInA[tileIdx & 1u];
+			asm volatile("cp.async.wait_group 0;" ::: "memory");
+			__syncthreads();            // this tile has landed; the other buffer and sOut are free (the stage-out of the tile before is done)
+			if (t0 + kFdnTile < fp.frames) prefetch(t0 + kFdnTile, (tileIdx + 1u) & 1u);
+#endif
 
 			// ---- compute, pass 1 (no time recurrence): the feedback mix and the output mix only need the delayed samples, so every
 			//      frame of the tile is independent here. x[f] overwrites the delayed sample in place.
@@ -270,7 +320,9 @@ namespace jplg
 				ff += oStepFrame; oc += oStepChan;
 				if (oc >= L) { oc -= L; ++ff; }
 			}
+#ifdef JPLG_FDN_NO_PREFETCH
 			__syncthreads();
+#endif
 		}
 
 #ifndef JPLG_FDN_SCALAR
@@ -355,7 +407,20 @@ namespace jplg
 		if (fp.n == 0 || fp.frames == 0) return cudaSuccess;
 		const uint32_t grid = (fp.n + kFdnInstPerCTA - 1) / kFdnInstPerCTA;
 		const PackedConsts K = MakePackedConsts(fp.coef);
-		if (mode == 0) k_fdn<0><<<grid, kFdnInstPerCTA * 16, 0, st>>>(fp, K); else k_fdn<1><<<grid, kFdnInstPerCTA * 16, 0, st>>>(fp, K);
+#ifdef JPLG_FDN_NO_PREFETCH
+		const size_t dyn = 0;
+#else
+		const size_t dyn = (size_t(2) * kFdnInstPerCTA * 16 * kFdnRow + size_t(2) * kFdnInstPerCTA * kFdnTile + size_t(kFdnInstPerCTA) * kFdnTile * 16) * sizeof(float);   // 52 KB
+		static bool attr[64] = {};                        // function attributes are per device
+		int dev = 0; cudaGetDevice(&dev);
+		if (dev >= 0 && dev < 64 && !attr[dev])
+		{
+			cudaFuncSetAttribute(k_fdn<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(dyn));
+			cudaFuncSetAttribute(k_fdn<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(dyn));
+			attr[dev] = true;
+		}
+#endif
+		if (mode == 0) k_fdn<0><<<grid, kFdnInstPerCTA * 16, dyn, st>>>(fp, K); else k_fdn<1><<<grid, kFdnInstPerCTA * 16, dyn, st>>>(fp, K);
 		return cudaGetLastError();
 	}
 }
